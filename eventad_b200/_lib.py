@@ -1,0 +1,93 @@
+"""ctypes loader of libeventad_b200.so (the C ABI in include/eventad_b200.h).
+
+There is no CPU fallback: if the library is missing or a call fails, a RuntimeError is raised (the reference raises
+RuntimeError through AT_ASSERTM for non-CUDA / non-contiguous inputs, /root/reference/src/dagr/graph/ev_graph.cu:9-12).
+"""
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libeventad_b200.so")
+_lib = None
+
+ERRORS = {-1: "EVAD_ERR_ARG (bad argument)", -2: "EVAD_ERR_WORKSPACE (workspace too small)",
+          -3: "EVAD_ERR_LAUNCH (CUDA launch failed)", -4: "EVAD_ERR_UNSUPPORTED"}
+STATUS_BITS = {1: "event outside the sensor / batch range", 2: "LUT offset outside its table",
+               4: "voxel id outside the cluster table", 8: "coarse edge buffer overflow"}
+
+c_p = ctypes.c_void_p
+c_i = ctypes.c_int
+c_i64 = ctypes.c_int64
+c_sz = ctypes.c_size_t
+c_f = ctypes.c_float
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} is missing: run `python -m eventad_b200.build` (there is no CPU fallback)")
+        L = ctypes.CDLL(LIB_PATH)
+        _declare(L)
+        _lib = L
+    return _lib
+
+
+def _sig(L, name, restype, argtypes):
+    f = getattr(L, name)
+    f.restype = restype
+    f.argtypes = argtypes
+
+
+def _declare(L):
+    _sig(L, "evad_version", c_i, [])
+    _sig(L, "evad_compiled_arch", c_i, [])
+    _sig(L, "evad_scan_ws_bytes", c_sz, [c_i64])
+    _sig(L, "evad_exclusive_scan", c_i, [c_p, c_p, c_i64, c_p, c_p, c_sz, c_p])
+    _sig(L, "evad_sort_ws_bytes", c_sz, [c_i64])
+    _sig(L, "evad_sort_pairs", c_i, [c_p, c_p, c_p, c_p, c_i64, c_i, c_p, c_sz, c_p])
+    _sig(L, "evad_graph_ws_bytes", c_sz, [c_i64, c_i, c_i, c_i, c_i])
+    _sig(L, "evad_graph_build", c_i, [c_p, c_p, c_i64, c_i, c_i, c_i, c_i, c_i, c_i, c_i,
+                                      c_p, c_p, c_p, c_p, c_i64, c_p, c_p, c_p, c_p, c_sz, c_p])
+
+
+def check(rc: int, what: str = ""):
+    if rc != 0:
+        raise RuntimeError(f"eventad_b200: {what} failed: {ERRORS.get(rc, rc)}")
+
+
+def ptr(t):
+    """device pointer of a tensor (None -> NULL); the tensor must be a contiguous CUDA tensor."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("eventad_b200: tensor must be a CUDA tensor (no CPU fallback)")
+    if not t.is_contiguous():
+        raise RuntimeError("eventad_b200: tensor must be contiguous")
+    return t.data_ptr()
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def check_status(status: torch.Tensor, what: str = ""):
+    """Reads the device status word (synchronises) and raises on any set bit."""
+    s = int(status.item())
+    if s:
+        msgs = [m for b, m in STATUS_BITS.items() if s & b]
+        raise RuntimeError(f"eventad_b200: {what}: " + "; ".join(msgs))
+
+
+class Workspace:
+    """Grow-only scratch buffer per device (torch-owned memory; the library never allocates)."""
+
+    def __init__(self):
+        self.buf = None
+
+    def get(self, nbytes: int, device) -> torch.Tensor:
+        if self.buf is None or self.buf.numel() < nbytes or self.buf.device != torch.device(device):
+            self.buf = torch.empty(int(nbytes * 1.25) + 1024, dtype=torch.uint8, device=device)
+        return self.buf

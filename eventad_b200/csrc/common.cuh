@@ -1,0 +1,58 @@
+// eventad_b200/csrc/common.cuh -- shared helpers for the sm_100a kernels (no torch headers anywhere in csrc/).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+#include "../../include/eventad_b200.h"
+
+#define EVAD_CHECK_LAUNCH()                                   \
+    do {                                                      \
+        cudaError_t e__ = cudaGetLastError();                 \
+        if (e__ != cudaSuccess) return EVAD_ERR_LAUNCH;       \
+    } while (0)
+
+#define EVAD_TRY(expr)                                        \
+    do {                                                      \
+        int r__ = (expr);                                     \
+        if (r__ != EVAD_OK) return r__;                       \
+    } while (0)
+
+static inline int evad_cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+static inline size_t evad_align(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+// bump allocator over a caller-provided workspace; never allocates device memory itself
+struct EvadArena {
+    char* base;
+    size_t cap;
+    size_t off;
+    bool ok;
+    EvadArena(void* p, size_t bytes) : base((char*)p), cap(bytes), off(0), ok(true) {}
+    template <typename T>
+    T* take(size_t n) {
+        size_t bytes = evad_align(n * sizeof(T));
+        if (base != nullptr && off + bytes > cap) ok = false;
+        T* r = base ? (T*)(base + off) : nullptr;
+        off += bytes;
+        return r;
+    }
+};
+
+// ---- primitives implemented in primitives.cu ----
+// exclusive scan of n uint32 (in may alias out); if total != nullptr the grand total is written to *total.
+// tmp must hold evad_scan_tmp_elems(n) uint32.
+size_t evad_scan_tmp_elems(long long n);
+int evad_exclusive_scan_u32(const uint32_t* in, uint32_t* out, long long n, uint32_t* total, uint32_t* tmp,
+                            cudaStream_t st);
+// stable LSD radix sort of (key,val) uint32 pairs on the low key_bits bits, ping-ponging between the buffer
+// pairs (k0,v0) and (k1,v1); the input is in k0 (and v0 unless iota_vals, which means val = position).
+// The buffer pair that holds the result is returned through res_k/res_v (host pointers, known at enqueue time).
+size_t evad_sort_tmp_elems(long long n);
+int evad_sort_pairs_u32(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int iota_vals, long long n,
+                        int key_bits, uint32_t* tmp, uint32_t** res_k, uint32_t** res_v, cudaStream_t st);
+
+__device__ __forceinline__ unsigned evad_lanemask_lt() {
+    unsigned m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}

@@ -1,0 +1,153 @@
+"""AsyncGraph / SlidingWindowGraph with the reference's constructor, attributes and call signatures
+(/root/reference/src/dagr/graph/ev_graph.py:18-166), running on the sm_100a kernels of libeventad_b200.so.
+
+The reference keeps a `[B, Q, H, W]` int32 FIFO tensor (39 MB per 320x240 sample) that it clears and re-fills per
+call; here a call after `reset()` is served by `evad_graph_build` (pixel-bucket sort + neighbour scan, graph.cu) and
+produces the identical `edge_index`.  Besides the reference's return value the dst-major CSR of the last call is
+kept in `self.csr = (rowptr[N+1] int32, src int32, num_edges int32[1])` for the fused layers.
+"""
+import torch
+
+from .. import _lib
+
+
+class AsyncGraph:
+    def __init__(self, width=640, height=480, batch_size=1, max_num_neighbors=16, max_queue_size=512, radius=7,
+                 delta_t_us=600000):
+        self.radius = radius
+        self.delta_t_us = delta_t_us
+        self.max_index = 0
+        self.min_index = 0
+        self.max_queue_size = max_queue_size
+        self.max_num_neighbors = max_num_neighbors
+        self.width = width
+        self.height = height
+        self.batch_size = batch_size
+        self.device = None
+        self.edges = torch.zeros((2, 0), dtype=torch.long)
+        self.all_timestamps = torch.zeros((0,), dtype=torch.int32)
+        self.csr = None
+        self._ws = _lib.Workspace()
+        self._status = None
+        self._stream_state = None
+
+    def initialize(self, n_ev, device):
+        self.edges = torch.zeros((2, 0), dtype=torch.long, device=device)
+        self.all_timestamps = torch.zeros((0,), dtype=torch.int32, device=device)
+        self._status = torch.zeros(1, dtype=torch.int32, device=device)
+
+    def reset(self):
+        self.edges = torch.zeros((2, 0), dtype=torch.long, device=self.device)
+        self.all_timestamps = torch.zeros((0,), dtype=torch.int32, device=self.device)
+        self.max_index = 0
+        self.min_index = 0
+        self.csr = None
+        self._stream_state = None
+
+    # ------------------------------------------------------------------ device-resident build (no host sync)
+    def build_csr(self, batch, pos, want_edge_index=False, want_cells=False):
+        """Enqueues evad_graph_build for a fresh graph.  Returns dict(rowptr, src, num_edges, edge_index, cell_perm,
+        cell_start); all sizes are upper bounds, `num_edges` lives on the device."""
+        if not (batch.is_cuda and pos.is_cuda):
+            raise RuntimeError("batch must be a CUDA tensor")            # CHECK_CUDA, ev_graph.cu:9
+        if batch.device != pos.device:
+            raise RuntimeError("batch and pos must be in same CUDA device")
+        assert batch.dtype == torch.int32, [type(batch), batch.dtype]   # ev_graph.py:73
+        batch = batch.contiguous()
+        pos = pos.contiguous()
+        if pos.dtype != torch.int32:
+            pos = pos.int()
+        dev = batch.device
+        n = batch.shape[0]
+        if self.device is None:
+            self.device = dev
+            self.initialize(n, dev)
+        K = int(self.max_num_neighbors)
+        L = _lib.lib()
+        rowptr = torch.empty(n + 1, dtype=torch.int32, device=dev)
+        src = torch.empty(max(n * K, 1), dtype=torch.int32, device=dev)
+        num_edges = torch.empty(1, dtype=torch.int32, device=dev)
+        edge_index = torch.empty((2, max(n * K, 1)), dtype=torch.int64, device=dev) if want_edge_index else None
+        ncells = self.batch_size * self.height * self.width
+        cell_perm = torch.empty(max(n, 1), dtype=torch.int32, device=dev) if want_cells else None
+        cell_start = torch.empty(ncells + 2, dtype=torch.int32, device=dev) if want_cells else None
+        nbytes = L.evad_graph_ws_bytes(n, self.batch_size, self.height, self.width, K)
+        ws = self._ws.get(nbytes, dev)
+        rc = L.evad_graph_build(_lib.ptr(batch), _lib.ptr(pos), n, int(self.batch_size), int(self.height),
+                                int(self.width), int(self.radius), int(self.delta_t_us), int(self.max_queue_size), K,
+                                _lib.ptr(rowptr), _lib.ptr(src), _lib.ptr(num_edges), _lib.ptr(edge_index),
+                                max(n * K, 1), _lib.ptr(cell_perm), _lib.ptr(cell_start), _lib.ptr(self._status),
+                                _lib.ptr(ws), ws.numel(), _lib.stream())
+        _lib.check(rc, "evad_graph_build")
+        return dict(rowptr=rowptr, src=src, num_edges=num_edges, edge_index=edge_index, cell_perm=cell_perm,
+                    cell_start=cell_start)
+
+    def forward(self, batch, pos, collect_edges=True):
+        n_ev = len(batch)
+        if self.device is None:
+            if not batch.is_cuda:
+                raise RuntimeError("batch must be a CUDA tensor")
+            self.device = batch.device
+            self.initialize(n_ev, self.device)
+        if n_ev == 0:
+            return torch.zeros((2, 0), device=self.device, dtype=torch.int32)   # ev_graph.py:71
+        assert type(batch) is torch.Tensor and batch.dtype == torch.int32, [type(batch), batch.dtype]
+        pos = pos.int() if pos.dtype != torch.int32 else pos
+
+        if self.max_index == 0 and self.min_index == 0 and self._stream_state is None:
+            out = self.build_csr(batch, pos, want_edge_index=True)
+            self.all_timestamps = torch.cat([self.all_timestamps, pos[:, 2]])
+            self.max_index += n_ev
+            e = int(out["num_edges"].item())                    # the reference syncs here too (mask compaction)
+            _lib.check_status(self._status, "graph build")
+            self.csr = (out["rowptr"], out["src"][:e], out["num_edges"])
+            edge_indices = out["edge_index"][:, :e]
+        else:
+            from .stream import append_events
+            edge_indices = append_events(self, batch, pos)
+        if collect_edges:
+            self.edges = torch.cat([self.edges, edge_indices], dim=-1)
+        return edge_indices
+
+
+class SlidingWindowGraph(AsyncGraph):
+    def __init__(self, width=640, height=480, batch_size=1, max_num_neighbors=16, max_queue_size=1024, radius=7,
+                 delta_t_us=600000):
+        AsyncGraph.__init__(self, width, height, batch_size, max_num_neighbors, max_queue_size, radius, delta_t_us)
+
+    @property
+    def init(self):
+        return len(self.all_timestamps) > 0
+
+    def delete_nodes(self, n_delete, delete_edges=True, return_edges=True):
+        self.all_timestamps = self.all_timestamps[n_delete:]
+        self.min_index += n_delete
+        if self._stream_state is not None:
+            self._stream_state.delete(n_delete)
+        deleted_edges = None
+        if delete_edges:
+            mask = (self.edges[0] < n_delete) | (self.edges[1] < n_delete)
+            deleted_edges = self.edges[:, mask].clone()
+            self.edges = self.edges[:, ~mask]
+        self.edges.add_(-n_delete)
+        if delete_edges and return_edges:
+            return deleted_edges
+
+    def forward(self, batch, pos, return_node_counts=False, return_total_edges=False, delete_nodes=True,
+                collect_edges=True):
+        n_delete = len(batch) if self.init else 0
+        edges = AsyncGraph.forward(self, batch, pos, collect_edges=collect_edges)
+        if return_total_edges:
+            total_edges = self.edges.clone()
+        if return_node_counts:
+            tot_nodes = len(self.all_timestamps)
+        ret = [edges]
+        if delete_nodes:
+            ret.append(self.delete_nodes(n_delete))
+        if return_total_edges:
+            ret.append(total_edges)
+        if return_node_counts:
+            ret.append([n_delete, len(batch), tot_nodes])
+        if len(ret) == 1:
+            ret = ret[0]
+        return ret

@@ -1,0 +1,78 @@
+"""Synthetic ROL-shaped event windows (SURVEY.md section 8d / BASELINE.md 3.3).
+
+W x H = 320 x 240, T = 1_000_000 us, a window = the last 50 ms (t in [950000, 1000000], sorted, t[-1] = T,
+mirroring /root/reference/src/dagr/data/dsec_data.py:124-130), polarity +-1, two spatial distributions:
+  "U"  uniform pixels;
+  "C"  ROL-like clustered: 70 % of the events from 24 drifting Gaussian blobs (sigma 6 px), 30 % uniform.
+Raw layout follows the reference's Data before `format_data` (src/dagr/utils/buffers.py:33-44):
+pos int16 [N,2] (x,y), t int32 [N], x int8 [N,1] (polarity), batch int64 [N], sample-major.
+"""
+from types import SimpleNamespace
+
+import numpy as np
+
+W_DEFAULT, H_DEFAULT, T_DEFAULT = 320, 240, 1_000_000
+
+
+def make_window(n_events: int, seed: int = 0, dist: str = "U", width: int = W_DEFAULT, height: int = H_DEFAULT,
+                time_window: int = T_DEFAULT, t_span: int = 50_000):
+    rng = np.random.default_rng(seed)
+    n = int(n_events)
+    t = np.sort(rng.integers(time_window - t_span, time_window + 1, n)).astype(np.int32)
+    if n > 0:
+        t[-1] = time_window
+    if dist == "U":
+        x = rng.integers(0, width, n)
+        y = rng.integers(0, height, n)
+    elif dist == "C":
+        n_blob = int(0.7 * n)
+        k = 24
+        cx = rng.uniform(0, width, k)
+        cy = rng.uniform(0, height, k)
+        vx = rng.uniform(-8, 8, k)
+        vy = rng.uniform(-8, 8, k)
+        which = rng.integers(0, k, n_blob)
+        frac = (t[:n_blob].astype(np.float64) - (time_window - t_span)) / max(t_span, 1)
+        bx = cx[which] + vx[which] * frac + rng.normal(0, 6.0, n_blob)
+        by = cy[which] + vy[which] * frac + rng.normal(0, 6.0, n_blob)
+        ux = rng.integers(0, width, n - n_blob)
+        uy = rng.integers(0, height, n - n_blob)
+        x = np.concatenate([np.clip(np.rint(bx), 0, width - 1).astype(np.int64), ux])
+        y = np.concatenate([np.clip(np.rint(by), 0, height - 1).astype(np.int64), uy])
+        perm = rng.permutation(n)                      # blob / uniform events interleaved in time
+        x, y = x[perm], y[perm]
+    else:
+        raise ValueError(dist)
+    p = (rng.integers(0, 2, n) * 2 - 1).astype(np.int8)
+    return SimpleNamespace(x=x.astype(np.int16), y=y.astype(np.int16), t=t, p=p)
+
+
+def make_batch(n_events_per_window, batch_size: int = 1, seed: int = 0, dist: str = "U",
+               width: int = W_DEFAULT, height: int = H_DEFAULT, time_window: int = T_DEFAULT):
+    """Raw (un-normalised) batch: dict of numpy arrays, windows concatenated sample-major."""
+    if np.isscalar(n_events_per_window):
+        n_events_per_window = [int(n_events_per_window)] * batch_size
+    xs, ys, ts, ps, bs = [], [], [], [], []
+    for b, n in enumerate(n_events_per_window):
+        w = make_window(n, seed * 1000 + b, dist, width, height, time_window)
+        xs.append(w.x); ys.append(w.y); ts.append(w.t); ps.append(w.p)
+        bs.append(np.full(len(w.x), b, np.int64))
+    return dict(pos=np.stack([np.concatenate(xs), np.concatenate(ys)], 1).astype(np.int16),
+                t=np.concatenate(ts).astype(np.int32),
+                x=np.concatenate(ps).astype(np.int8).reshape(-1, 1),
+                batch=np.concatenate(bs),
+                num_graphs=len(n_events_per_window), width=width, height=height, time_window=time_window)
+
+
+def make_image_features(batch_size: int, channels=(16, 64, 64, 64, 64), width: int = W_DEFAULT,
+                        height: int = H_DEFAULT, seed: int = 0):
+    """Stand-in for HookModule's five 1x1-projected ResNet maps (net_img.py:122-135, shapes SURVEY A.6):
+    strides 2,4,8,16,32 of the (H,W) image, float32, seeded."""
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    feats = []
+    for i, c in enumerate(channels):
+        s = 2 ** (i + 1)
+        h, w = -(-height // s), -(-width // s)
+        feats.append(torch.randn((batch_size, c, h, w), generator=g, dtype=torch.float32))
+    return feats

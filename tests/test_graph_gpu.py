@@ -1,0 +1,83 @@
+"""Bit-exact parity of the sm_100a event-graph builder with the C oracle (oracle/evg_oracle.c), through the
+reference-shaped SlidingWindowGraph API (reference: src/dagr/graph/ev_graph.py, ev_graph.cu)."""
+import numpy as np
+import pytest
+import torch
+
+from eventad_b200 import synthetic
+
+pytestmark = pytest.mark.gpu
+
+
+def _pos_int(raw):
+    return np.concatenate([raw["pos"].astype(np.int32), raw["t"].reshape(-1, 1)], 1).astype(np.int32)
+
+
+def _run_both(batch, pos, W, H, B, K=16, Q=128, r=4, dt=10000):
+    from eventad_b200.graph.ev_graph import SlidingWindowGraph
+    from oracle.evg import OracleSlidingWindowGraph
+    g = SlidingWindowGraph(width=W, height=H, batch_size=B, max_num_neighbors=K, max_queue_size=Q, radius=r,
+                           delta_t_us=dt)
+    e = g.forward(torch.from_numpy(batch).int().cuda(), torch.from_numpy(pos).int().cuda(), delete_nodes=False)
+    o = OracleSlidingWindowGraph(width=W, height=H, batch_size=B, max_num_neighbors=K, max_queue_size=Q, radius=r,
+                                 delta_t_us=dt)
+    eo = o.forward(batch, pos, delete_nodes=False)
+    return e, eo, g
+
+
+@pytest.mark.parametrize("n,dist,B", [(1, "U", 1), (2, "U", 1), (500, "U", 1), (5000, "C", 1), (50_000, "U", 1),
+                                      (50_000, "C", 1), (100_000, "U", 1), (30_000, "C", 3), (200_000, "C", 2)])
+def test_edge_index_bit_exact(n, dist, B):
+    raw = synthetic.make_batch(n, B, seed=n % 7, dist=dist)
+    pos = _pos_int(raw)
+    batch = raw["batch"].astype(np.int32)
+    e, eo, g = _run_both(batch, pos, raw["width"], raw["height"], B)
+    assert e.dtype == torch.int64 and e.shape[0] == 2
+    assert e.shape[1] == eo.shape[1]
+    assert np.array_equal(e.cpu().numpy(), eo)
+    rowptr, src, ne = g.csr
+    assert int(ne.item()) == eo.shape[1]
+    assert np.array_equal(src.cpu().numpy().astype(np.int64), eo[0])
+    deg = np.diff(rowptr.cpu().numpy())
+    assert np.array_equal(np.repeat(np.arange(len(batch)), deg), eo[1])
+
+
+def test_queue_cap_and_ties():
+    """> Q events on one pixel (FIFO cap hides the oldest), equal timestamps, border pixels, tiny sensor."""
+    rng = np.random.default_rng(3)
+    W, H, n = 12, 9, 4000
+    x = rng.integers(0, W, n); y = rng.integers(0, H, n)
+    x[:1500] = 5; y[:1500] = 4                         # 1500 events on one pixel, Q = 16
+    x[1500:1600] = 0; y[1500:1600] = 0
+    t = np.sort(rng.integers(0, 3000, n)) // 7 * 7       # ties
+    perm = rng.permutation(n)
+    pos = np.stack([x[perm], y[perm], t], 1).astype(np.int32)
+    batch = np.zeros(n, np.int32)
+    for K, Q, r, dt in [(16, 16, 4, 500), (8, 4, 2, 100), (32, 128, 1, 10_000), (5, 3, 3, 0)]:
+        e, eo, _ = _run_both(batch, pos, W, H, 1, K=K, Q=Q, r=r, dt=dt)
+        assert np.array_equal(e.cpu().numpy(), eo), (K, Q, r, dt)
+
+
+def test_unsorted_timestamps_and_negative_dt():
+    rng = np.random.default_rng(5)
+    W, H, n = 40, 30, 20_000
+    pos = np.stack([rng.integers(0, W, n), rng.integers(0, H, n), rng.integers(0, 50_000, n)], 1).astype(np.int32)
+    batch = np.sort(rng.integers(0, 2, n)).astype(np.int32)
+    e, eo, _ = _run_both(batch, pos, W, H, 2, dt=7000)
+    assert np.array_equal(e.cpu().numpy(), eo)
+
+
+def test_empty_and_errors():
+    from eventad_b200.graph.ev_graph import SlidingWindowGraph
+    g = SlidingWindowGraph(width=32, height=32, batch_size=1, max_queue_size=8, radius=2, delta_t_us=100)
+    e = g.forward(torch.zeros(0, dtype=torch.int32, device="cuda"), torch.zeros((0, 3), dtype=torch.int32, device="cuda"),
+                  delete_nodes=False)
+    assert e.shape == (2, 0)
+    with pytest.raises(RuntimeError):
+        g.forward(torch.zeros(4, dtype=torch.int32), torch.zeros((4, 3), dtype=torch.int32), delete_nodes=False)
+    with pytest.raises(AssertionError):
+        g.forward(torch.zeros(4, dtype=torch.int64, device="cuda"), torch.zeros((4, 3), dtype=torch.int32, device="cuda"),
+                  delete_nodes=False)
+    bad = torch.tensor([[40, 1, 5], [1, 1, 6]], dtype=torch.int32, device="cuda")      # x outside the sensor
+    with pytest.raises(RuntimeError):
+        g.forward(torch.zeros(2, dtype=torch.int32, device="cuda"), bad, delete_nodes=False)
