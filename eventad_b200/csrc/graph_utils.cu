@@ -1,0 +1,206 @@
+// eventad_b200/csrc/graph_utils.cu -- format glue around the kernels: COO <-> CSR, Cartesian edge attributes,
+// image-feature sampling + concat.
+//
+// Reference pieces replaced (paths relative to /root/reference/src/dagr/model):
+//   layers/components.py:25-35 + networks/net.py:120-121  Cartesian edge attributes (+ clamp on the first layer)
+//   networks/net.py:15-17,122-123,200-228                 sampling_skip (grid_sample + cat) and cat(x, pos[:, :2])
+//   layers/pooling.py:64                                  `unique(dim=-1)` ordering (src-major) of coarse edges
+#include "common.cuh"
+
+// ------------------------------------------------------------------------------------------------ COO -> CSR
+__global__ void __launch_bounds__(256) coo_keys_kernel(const int64_t* __restrict__ dst, int64_t e, int64_t n,
+                                                       uint32_t* __restrict__ keys, uint32_t* __restrict__ status) {
+    int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= e) return;
+    int64_t d = dst[t];
+    if (d < 0 || d >= n) { atomicOr(status, EVAD_STATUS_EVENT_OOB); d = 0; }
+    keys[t] = (uint32_t)d;
+}
+
+__global__ void __launch_bounds__(256) coo_finish_kernel(const uint32_t* __restrict__ skey,
+                                                         const uint32_t* __restrict__ seid,
+                                                         const int64_t* __restrict__ src64, int64_t e, int64_t n,
+                                                         int32_t* __restrict__ rowptr, int32_t* __restrict__ src,
+                                                         int32_t* __restrict__ eid) {
+    int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t <= n) {                                            // rowptr[t] = lower_bound(skey, t)
+        int64_t lo = 0, hi = e;
+        while (lo < hi) {
+            int64_t mid = (lo + hi) >> 1;
+            if ((int64_t)skey[mid] < t) lo = mid + 1; else hi = mid;
+        }
+        rowptr[t] = (int32_t)lo;
+    }
+    if (t < e) {
+        const uint32_t id = seid[t];
+        src[t] = (int32_t)src64[id];
+        eid[t] = (int32_t)id;
+    }
+}
+
+extern "C" size_t evad_coo_to_csr_ws_bytes(int64_t e) {
+    const int64_t m = e > 0 ? e : 1;
+    return 4 * evad_align((size_t)m * 4) + evad_sort_tmp_elems(m) * 4 + 512;
+}
+
+extern "C" int evad_coo_to_csr(const int64_t* edge_index, int64_t stride, int64_t e, int64_t n, int32_t* rowptr,
+                               int32_t* src, int32_t* eid, uint32_t* status, void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!rowptr || !src || !eid || !status || e < 0 || n < 0 || n >= (1ll << 31) || e >= (1ll << 31)) return EVAD_ERR_ARG;
+    if (e > 0 && (!edge_index || !ws)) return EVAD_ERR_ARG;
+    if (ws_bytes < evad_coo_to_csr_ws_bytes(e)) return EVAD_ERR_WORKSPACE;
+    EvadArena a(ws, ws_bytes);
+    const int64_t m = e > 0 ? e : 1;
+    uint32_t* k0 = a.take<uint32_t>(m); uint32_t* v0 = a.take<uint32_t>(m);
+    uint32_t* k1 = a.take<uint32_t>(m); uint32_t* v1 = a.take<uint32_t>(m);
+    uint32_t* tmp = a.take<uint32_t>(evad_sort_tmp_elems(m));
+    uint32_t *sk = k0, *sv = v0;
+    if (e > 0) {
+        coo_keys_kernel<<<evad_cdiv(e, 256), 256, 0, st>>>(edge_index + stride, e, n, k0, status);
+        EVAD_CHECK_LAUNCH();
+        int bits = 1;
+        while ((1ll << bits) < n) bits++;
+        EVAD_TRY(evad_sort_pairs_u32(k0, v0, k1, v1, 1, e, bits, tmp, &sk, &sv, st));
+    }
+    const int64_t work = (n + 1 > e) ? n + 1 : e;
+    coo_finish_kernel<<<evad_cdiv(work, 256), 256, 0, st>>>(sk, sv, edge_index, e, n, rowptr, src, eid);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ CSR -> COO
+__global__ void __launch_bounds__(256) csr_expand_kernel(const int32_t* __restrict__ rowptr,
+                                                         const int32_t* __restrict__ src, int64_t n_cap,
+                                                         const int32_t* __restrict__ n_dev, int64_t e_cap,
+                                                         int64_t* __restrict__ out_src, int64_t* __restrict__ out_dst,
+                                                         uint32_t* __restrict__ keys, uint32_t* __restrict__ dsts) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t n = n_dev ? min((int64_t)*n_dev, n_cap) : n_cap;
+    if (i >= n) return;
+    for (int e = rowptr[i]; e < rowptr[i + 1] && e < e_cap; e++) {
+        if (out_src) { out_src[e] = src[e]; out_dst[e] = i; }
+        if (keys) { keys[e] = (uint32_t)src[e]; dsts[e] = (uint32_t)i; }
+    }
+}
+
+__global__ void __launch_bounds__(256) csr_pad_keys_kernel(const int32_t* __restrict__ num_edges, int64_t e_cap,
+                                                           uint32_t pad, uint32_t* __restrict__ keys) {
+    int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < e_cap && e >= *num_edges) keys[e] = pad;
+}
+
+__global__ void __launch_bounds__(256) csr_srcmajor_kernel(const uint32_t* __restrict__ skey,
+                                                           const uint32_t* __restrict__ sslot,
+                                                           const uint32_t* __restrict__ dsts,
+                                                           const int32_t* __restrict__ num_edges, int64_t e_cap,
+                                                           int64_t* __restrict__ out_src, int64_t* __restrict__ out_dst,
+                                                           int32_t* __restrict__ slot_of) {
+    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= e_cap || q >= *num_edges) return;
+    out_src[q] = skey[q];
+    out_dst[q] = dsts[sslot[q]];
+    if (slot_of) slot_of[q] = (int32_t)sslot[q];
+}
+
+extern "C" size_t evad_csr_to_coo_ws_bytes(int64_t e_cap) {
+    const int64_t m = e_cap > 0 ? e_cap : 1;
+    return 5 * evad_align((size_t)m * 4) + evad_sort_tmp_elems(m) * 4 + 512;
+}
+
+extern "C" int evad_csr_to_coo(const int32_t* rowptr, const int32_t* src, int64_t n_cap, const int32_t* n_dev,
+                               int64_t e_cap, const int32_t* num_edges, int src_major, int64_t* edge_index,
+                               int64_t stride, int32_t* slot_of, void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!rowptr || !src || !num_edges || !edge_index || n_cap < 0 || e_cap < 0) return EVAD_ERR_ARG;
+    if (n_cap == 0 || e_cap == 0) return EVAD_OK;
+    if (!src_major) {
+        csr_expand_kernel<<<evad_cdiv(n_cap, 256), 256, 0, st>>>(rowptr, src, n_cap, n_dev, e_cap, edge_index,
+                                                               edge_index + stride, nullptr, nullptr);
+        EVAD_CHECK_LAUNCH();
+        return EVAD_OK;
+    }
+    if (!ws || ws_bytes < evad_csr_to_coo_ws_bytes(e_cap)) return EVAD_ERR_WORKSPACE;
+    EvadArena a(ws, ws_bytes);
+    uint32_t* k0 = a.take<uint32_t>(e_cap); uint32_t* v0 = a.take<uint32_t>(e_cap);
+    uint32_t* k1 = a.take<uint32_t>(e_cap); uint32_t* v1 = a.take<uint32_t>(e_cap);
+    uint32_t* dsts = a.take<uint32_t>(e_cap);
+    uint32_t* tmp = a.take<uint32_t>(evad_sort_tmp_elems(e_cap));
+    csr_expand_kernel<<<evad_cdiv(n_cap, 256), 256, 0, st>>>(rowptr, src, n_cap, n_dev, e_cap, nullptr, nullptr, k0, dsts);
+    EVAD_CHECK_LAUNCH();
+    csr_pad_keys_kernel<<<evad_cdiv(e_cap, 256), 256, 0, st>>>(num_edges, e_cap, (uint32_t)n_cap, k0);
+    EVAD_CHECK_LAUNCH();
+    int bits = 1;
+    while ((1ll << bits) <= n_cap) bits++;
+    uint32_t *sk, *sv;
+    EVAD_TRY(evad_sort_pairs_u32(k0, v0, k1, v1, 1, e_cap, bits, tmp, &sk, &sv, st));
+    csr_srcmajor_kernel<<<evad_cdiv(e_cap, 256), 256, 0, st>>>(sk, sv, dsts, num_edges, e_cap, edge_index,
+                                                             edge_index + stride, slot_of);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ Cartesian
+__global__ void __launch_bounds__(256) cartesian_kernel(const float* __restrict__ pos, int ld_pos, int dims,
+                                                        const int64_t* __restrict__ row, const int64_t* __restrict__ col,
+                                                        int64_t e_cap, const int32_t* __restrict__ num_edges,
+                                                        float two_m, int clamp01, float* __restrict__ out) {
+    int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t ne = num_edges ? min((int64_t)*num_edges, e_cap) : e_cap;
+    if (e >= ne) return;
+    const int64_t j = row[e], i = col[e];
+    for (int d = 0; d < dims; d++) {
+        float a = __fadd_rn(__fdiv_rn(__fsub_rn(pos[j * ld_pos + d], pos[i * ld_pos + d]), two_m), 0.5f);
+        if (clamp01) a = fminf(fmaxf(a, 0.f), 1.f);
+        out[e * dims + d] = a;
+    }
+}
+
+extern "C" int evad_cartesian(const float* pos, int ld_pos, int dims, const int64_t* edge_index, int64_t stride,
+                              int64_t e_cap, const int32_t* num_edges, float two_m, int clamp01, float* out,
+                              void* stream) {
+    if (!pos || !edge_index || !out || dims < 1 || ld_pos < dims || e_cap < 0) return EVAD_ERR_ARG;
+    if (e_cap == 0) return EVAD_OK;
+    cartesian_kernel<<<evad_cdiv(e_cap, 256), 256, 0, (cudaStream_t)stream>>>(pos, ld_pos, dims, edge_index,
+                                                                            edge_index + stride, e_cap, num_edges,
+                                                                            two_m, clamp01, out);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ sampling + concat
+#include "sample.cuh"
+
+// out[i, :] = [ x[i, 0:cx] | sample(feat)(C) | pos_x, pos_y (append_pos) | 0 ... ]  up to ldo columns
+__global__ void __launch_bounds__(256) sample_concat_kernel(const float* __restrict__ x, int ldx, int cx,
+                                                            const float* __restrict__ pos, int ld_pos,
+                                                            const int32_t* __restrict__ batch, int64_t n_cap,
+                                                            const int32_t* __restrict__ n_dev, PoolSample S,
+                                                            int append_pos, float* __restrict__ out, int ldo) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t n = n_dev ? min((int64_t)*n_dev, n_cap) : n_cap;
+    const int64_t i = t / ldo;
+    const int c = (int)(t - i * ldo);
+    if (i >= n) return;
+    const int cs = S.feat ? S.C : 0;
+    float v = 0.f;
+    if (c < cx) v = x[i * ldx + c];
+    else if (c < cx + cs) v = sample_feat(S, pos[i * ld_pos], pos[i * ld_pos + 1], (float)batch[i], c - cx);
+    else if (append_pos && c < cx + cs + 2) v = pos[i * ld_pos + (c - cx - cs)];
+    out[t] = v;
+}
+
+extern "C" int evad_sample_concat(const float* x, int ldx, int cx, const float* pos, int ld_pos, const int32_t* batch,
+                                  int64_t n_cap, const int32_t* n_dev, const float* feat, int feat_b, int feat_h,
+                                  int feat_w, int feat_c, float width, float height, int append_pos, float* out,
+                                  int ldo, void* stream) {
+    if (!pos || !out || n_cap < 0 || cx < 0 || (cx > 0 && !x) || (feat && !batch)) return EVAD_ERR_ARG;
+    const int cs = feat ? feat_c : 0;
+    if (ldo < cx + cs + (append_pos ? 2 : 0)) return EVAD_ERR_ARG;
+    if (n_cap == 0) return EVAD_OK;
+    PoolSample S{feat, feat_b, feat_h, feat_w, feat_c, width, height};
+    sample_concat_kernel<<<evad_cdiv(n_cap * ldo, 256), 256, 0, (cudaStream_t)stream>>>(x, ldx, cx, pos, ld_pos, batch,
+                                                                                      n_cap, n_dev, S, append_pos, out,
+                                                                                      ldo);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}

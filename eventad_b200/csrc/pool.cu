@@ -1,0 +1,318 @@
+// eventad_b200/csrc/pool.cu -- voxel-grid pooling for sm_100a.
+//
+// Reference path replaced per call of Pooling.forward (paths relative to /root/reference/src/dagr/model):
+//   layers/pooling.py:55-57   torch_cluster.grid_cluster over [x,y,t,batch] + consecutive_cluster (torch.unique)
+//   layers/pooling.py:58-64   edge_index = cluster[edge_index]; drop self loops; unique(dim=-1)
+//   layers/pooling.py:66-77   batch[perm], pool_pos (scatter mean), scatter_max / _avg_pool_x
+//   layers/pooling.py:47-49,86 round_to_pixel
+//   networks/net.py:15-17,200-228 sampling_skip: grid_sample of the CNN map at the nodes + concat, done right
+//                              before every pooling call -- fused here so the [n, C+64] concat never exists.
+// Design: nodes are grouped per voxel by one stable radix sort of (voxel id, node id); one CTA owns one voxel:
+// thread 0 sums the positions serially in ascending node order (bit-identical to the CPU scatter_add the oracle
+// models), the threads reduce the channels, and the coarse in-edges are collected in a shared-memory bitmap, which
+// yields them de-duplicated and sorted with no global sort and no atomics on global memory.
+#include "common.cuh"
+#include "sample.cuh"
+
+#define PL_THREADS 128
+#define PL_BITS 4096                                        // bitmap chunk: one 32-bit word per thread
+
+struct PoolGeom {
+    float sx, sy, st;        // voxel size (x, y, t); the batch dimension has size 1
+    int nvx, nvy, nvt;       // voxels per dimension = ((end-start)/size).long() + 1  (computed by the host like torch_cluster)
+    uint32_t key_bound;      // nvx*nvy*nvt*(B+1): valid keys are < key_bound
+};
+
+// torch_cluster grid_cluster, D = 4, start = 0: c_d = (int64)(p_d / size_d) in fp32
+__global__ void __launch_bounds__(256) pool_keys_kernel(const float* __restrict__ pos, int ld_pos,
+                                                        const int32_t* __restrict__ batch, int64_t n_cap,
+                                                        const int32_t* __restrict__ n_dev, PoolGeom G,
+                                                        uint32_t* __restrict__ keys, uint32_t* __restrict__ status) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_cap) return;
+    const int64_t n = n_dev ? min((int64_t)*n_dev, n_cap) : n_cap;
+    if (i >= n) { keys[i] = G.key_bound; return; }          // padding sorts to the end
+    const long long cx = (long long)__fdiv_rn(pos[i * ld_pos], G.sx);
+    const long long cy = (long long)__fdiv_rn(pos[i * ld_pos + 1], G.sy);
+    const long long ct = (long long)__fdiv_rn(pos[i * ld_pos + 2], G.st);
+    const long long cb = (long long)__fdiv_rn((float)batch[i], 1.0f);
+    long long key = cx + (long long)G.nvx * (cy + (long long)G.nvy * (ct + (long long)G.nvt * cb));
+    if (cx < 0 || cy < 0 || ct < 0 || cb < 0 || key >= (long long)G.key_bound) {
+        atomicOr(status, EVAD_STATUS_CLUSTER_OOB);
+        key = min(max(key, 0ll), (long long)G.key_bound - 1);
+    }
+    keys[i] = (uint32_t)key;
+}
+
+__global__ void __launch_bounds__(256) pool_flag_kernel(const uint32_t* __restrict__ skey, int64_t n_cap,
+                                                        uint32_t key_bound, uint32_t* __restrict__ flag) {
+    int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_cap) return;
+    const uint32_t k = skey[p];
+    flag[p] = (p > 0 && k < key_bound && k != skey[p - 1]) ? 1u : 0u;
+}
+
+// dense ids (consecutive_cluster), segment starts, cluster[] in node order
+__global__ void __launch_bounds__(256) pool_relabel_kernel(const uint32_t* __restrict__ skey,
+                                                           const uint32_t* __restrict__ sidx,
+                                                           const uint32_t* __restrict__ flag,
+                                                           const uint32_t* __restrict__ excl, int64_t n_cap,
+                                                           uint32_t key_bound, int32_t* __restrict__ cluster,
+                                                           int32_t* __restrict__ seg_start,
+                                                           int32_t* __restrict__ n_out) {
+    int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p == 0 && (n_cap == 0 || skey[0] >= key_bound)) { *n_out = 0; seg_start[0] = 0; }
+    if (p >= n_cap) return;
+    if (skey[p] >= key_bound) return;
+    const uint32_t d = excl[p] + flag[p];
+    cluster[sidx[p]] = (int32_t)d;
+    if (p == 0 || flag[p]) seg_start[d] = (int32_t)p;
+    if (p == n_cap - 1 || skey[p + 1] >= key_bound) { seg_start[d + 1] = (int32_t)(p + 1); *n_out = (int32_t)(d + 1); }
+}
+
+// c10::div_floor_floating (torch.div(..., rounding_mode='floor') on floats), used by round_to_pixel (pooling.py:47-49)
+__device__ __forceinline__ float div_floor_f(float a, float b) {
+    if (b == 0.f) return __fdiv_rn(a, b);
+    const float mod = fmodf(a, b);
+    float div = __fdiv_rn(__fsub_rn(a, mod), b);
+    if (mod != 0.f && ((b < 0.f) != (mod < 0.f))) div = __fsub_rn(div, 1.f);
+    float fl;
+    if (div != 0.f) {
+        fl = floorf(div);
+        if (__fsub_rn(div, fl) > 0.5f) fl = __fadd_rn(fl, 1.f);
+    } else {
+        fl = copysignf(0.f, __fdiv_rn(a, b));
+    }
+    return fl;
+}
+
+// ------------------------------------------------------------------------------------------------ per-voxel reduce
+// One CTA per output cluster.  x_out row = [reduced x (cx) | reduced sampled map (S.C) | pos_x, pos_y (if append_pos)].
+__global__ void __launch_bounds__(PL_THREADS) pool_reduce_kernel(
+    const uint32_t* __restrict__ sidx, const int32_t* __restrict__ seg_start, const int32_t* __restrict__ n_out,
+    const float* __restrict__ pos, int ld_pos, const int32_t* __restrict__ batch, const float* __restrict__ x, int ldx,
+    int cx, PoolSample S, int aggr_mean, float inv_w, float inv_h, int append_pos, float* __restrict__ x_out, int ldo,
+    float* __restrict__ pos_out, int32_t* __restrict__ batch_out) {
+    const int c = blockIdx.x;
+    if (c >= *n_out) return;
+    const int s0 = seg_start[c], s1 = seg_start[c + 1];
+    __shared__ float s_pos[2];
+    if (threadIdx.x == 0) {
+        // pool_pos = scatter mean: fp32 sums in ascending node order, then / count.clamp(min=1)
+        float sx = 0.f, sy = 0.f, st = 0.f;
+        for (int p = s0; p < s1; p++) {
+            const int64_t i = sidx[p];
+            sx = __fadd_rn(sx, pos[i * ld_pos]);
+            sy = __fadd_rn(sy, pos[i * ld_pos + 1]);
+            st = __fadd_rn(st, pos[i * ld_pos + 2]);
+        }
+        const float cnt = fmaxf((float)(s1 - s0), 1.f);
+        float mx = __fdiv_rn(sx, cnt), my = __fdiv_rn(sy, cnt);
+        const float mt = __fdiv_rn(st, cnt);
+        // round_to_pixel: floor_divide(p + 1e-5, wh_inv) * wh_inv
+        mx = __fmul_rn(div_floor_f(__fadd_rn(mx, 1e-5f), inv_w), inv_w);
+        my = __fmul_rn(div_floor_f(__fadd_rn(my, 1e-5f), inv_h), inv_h);
+        pos_out[(int64_t)c * 3] = mx;
+        pos_out[(int64_t)c * 3 + 1] = my;
+        pos_out[(int64_t)c * 3 + 2] = mt;
+        batch_out[c] = batch[sidx[s1 - 1]];                 // perm: last writer wins = largest node id (pooling.py:15,66)
+        s_pos[0] = mx;
+        s_pos[1] = my;
+    }
+    const int ctot = cx + (S.feat ? S.C : 0);
+    const float cntf = fmaxf((float)(s1 - s0), 1.f);
+    for (int ch = threadIdx.x; ch < ctot; ch += PL_THREADS) {
+        float acc = 0.f;
+        for (int p = s0; p < s1; p++) {
+            const int64_t i = sidx[p];
+            float v;
+            if (ch < cx) v = x[i * ldx + ch];
+            else v = sample_feat(S, pos[i * ld_pos], pos[i * ld_pos + 1], (float)batch[i], ch - cx);
+            if (aggr_mean) acc = __fadd_rn(acc, v);
+            else acc = (p == s0) ? v : fmaxf(acc, v);
+        }
+        if (aggr_mean) acc = __fdiv_rn(acc, cntf);
+        x_out[(int64_t)c * ldo + ch] = acc;
+    }
+    if (append_pos) {
+        __syncthreads();
+        if (threadIdx.x < 2) x_out[(int64_t)c * ldo + ctot + threadIdx.x] = s_pos[threadIdx.x];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ coarse edges
+// One CTA per destination cluster: mark cluster[src] of every in-edge of every member (self loops dropped) in a
+// shared-memory bitmap over [lo, hi]; FILL=false counts the distinct sources, FILL=true writes them (ascending).
+template <bool FILL>
+__global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
+    const uint32_t* __restrict__ sidx, const int32_t* __restrict__ seg_start, const int32_t* __restrict__ n_out,
+    const int32_t* __restrict__ rowptr_in, const int32_t* __restrict__ src_in, const int32_t* __restrict__ cluster,
+    uint32_t* __restrict__ deg, const uint32_t* __restrict__ rowptr_out, int32_t* __restrict__ src_out, int64_t e_cap,
+    uint32_t* __restrict__ status) {
+    const int c = blockIdx.x;
+    const int nc = *n_out;
+    if (c >= nc) {
+        if (!FILL && c == nc) deg[c] = 0;
+        return;
+    }
+    __shared__ uint32_t bits[PL_BITS / 32];
+    __shared__ int s_lo, s_hi;
+    __shared__ uint32_t s_warp[PL_THREADS / 32 + 1];
+    const int s0 = seg_start[c], s1 = seg_start[c + 1];
+    if (threadIdx.x == 0) { s_lo = 0x7fffffff; s_hi = -1; }
+    __syncthreads();
+    int lo = 0x7fffffff, hi = -1;
+    for (int p = s0 + threadIdx.x; p < s1; p += PL_THREADS) {
+        const int i = (int)sidx[p];
+        for (int e = rowptr_in[i]; e < rowptr_in[i + 1]; e++) {
+            const int sc = cluster[src_in[e]];
+            if (sc != c) { lo = min(lo, sc); hi = max(hi, sc); }
+        }
+    }
+    atomicMin(&s_lo, lo);
+    atomicMax(&s_hi, hi);
+    __syncthreads();
+    lo = s_lo; hi = s_hi;
+    uint32_t total = 0;
+    const uint32_t base_out = FILL ? rowptr_out[c] : 0u;
+    for (int w0 = lo; w0 <= hi; w0 += PL_BITS) {
+        bits[threadIdx.x] = 0u;
+        __syncthreads();
+        for (int p = s0 + threadIdx.x; p < s1; p += PL_THREADS) {
+            const int i = (int)sidx[p];
+            for (int e = rowptr_in[i]; e < rowptr_in[i + 1]; e++) {
+                const int sc = cluster[src_in[e]];
+                const int r = sc - w0;
+                if (sc != c && r >= 0 && r < PL_BITS) atomicOr(&bits[r >> 5], 1u << (r & 31));
+            }
+        }
+        __syncthreads();
+        uint32_t word = bits[threadIdx.x];
+        const uint32_t pc = __popc(word);
+        // block exclusive scan of pc (4 warps)
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        uint32_t inc = pc;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += t;
+        }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        uint32_t woff = 0, chunk_total = 0;
+#pragma unroll
+        for (int w = 0; w < PL_THREADS / 32; w++) {
+            if (w < warp) woff += s_warp[w];
+            chunk_total += s_warp[w];
+        }
+        if (FILL) {
+            uint32_t o = base_out + total + woff + inc - pc;
+            while (word) {
+                const int b = __ffs(word) - 1;
+                word &= word - 1;
+                if ((int64_t)o < e_cap) src_out[o] = w0 + threadIdx.x * 32 + b;
+                else atomicOr(status, EVAD_STATUS_EDGE_OVERFLOW);
+                o++;
+            }
+        }
+        total += chunk_total;
+        __syncthreads();
+    }
+    if (!FILL && threadIdx.x == 0) deg[c] = total;
+}
+
+__global__ void pool_finish_edges_kernel(const uint32_t* __restrict__ rowptr_u, const int32_t* __restrict__ n_out,
+                                         int64_t c_cap, int32_t* __restrict__ rowptr_out,
+                                         int32_t* __restrict__ num_edges) {
+    int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int nc = *n_out;
+    if (c <= nc && c <= c_cap) rowptr_out[c] = (int32_t)rowptr_u[c];
+    if (c == nc) *num_edges = (int32_t)rowptr_u[c];
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+struct PoolWs {
+    uint32_t *k0, *v0, *k1, *v1, *flag, *excl, *deg, *rowptr_u, *sort_tmp, *scan_tmp;
+    int32_t* seg_start;
+};
+
+static size_t pool_ws_layout(EvadArena& a, int64_t n_cap, int64_t c_cap, PoolWs* w) {
+    const int64_t n = n_cap > 0 ? n_cap : 1;
+    w->k0 = a.take<uint32_t>(n); w->v0 = a.take<uint32_t>(n);
+    w->k1 = a.take<uint32_t>(n); w->v1 = a.take<uint32_t>(n);
+    w->flag = a.take<uint32_t>(n);
+    w->excl = a.take<uint32_t>(n);
+    w->seg_start = a.take<int32_t>(c_cap + 2);
+    w->deg = a.take<uint32_t>(c_cap + 2);
+    w->rowptr_u = a.take<uint32_t>(c_cap + 2);
+    w->sort_tmp = a.take<uint32_t>(evad_sort_tmp_elems(n));
+    const int64_t m = n > c_cap + 2 ? n : c_cap + 2;
+    w->scan_tmp = a.take<uint32_t>(evad_scan_tmp_elems(m));
+    return a.off;
+}
+
+extern "C" size_t evad_voxel_pool_ws_bytes(int64_t n_cap, int64_t c_cap) {
+    EvadArena a(nullptr, 0);
+    PoolWs w;
+    return pool_ws_layout(a, n_cap, c_cap, &w) + 256;
+}
+
+extern "C" int evad_voxel_pool(const evad_pool_params_t* p, int64_t n_cap, const int32_t* n_dev, const float* pos,
+                               int ld_pos, const int32_t* batch, const float* x, int ldx, int cx,
+                               const int32_t* rowptr_in, const int32_t* src_in, int64_t c_cap, int64_t e_cap,
+                               int32_t* cluster, int32_t* n_out, float* x_out, int ldo, float* pos_out,
+                               int32_t* batch_out, int32_t* rowptr_out, int32_t* src_out, int32_t* num_edges_out,
+                               uint32_t* status, void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!p || !pos || !batch || !x || !cluster || !n_out || !x_out || !pos_out || !batch_out || !status || !ws)
+        return EVAD_ERR_ARG;
+    if (n_cap < 0 || c_cap < 1 || ld_pos < 3 || cx < 0 || p->batch_size < 1) return EVAD_ERR_ARG;
+    const bool want_edges = rowptr_in && src_in && rowptr_out && src_out && num_edges_out;
+    const int ctot = cx + (p->feat ? p->feat_c : 0);
+    if (ldo < ctot + (p->append_pos ? 2 : 0)) return EVAD_ERR_ARG;
+    const long long kb = (long long)p->nvx * p->nvy * p->nvt * ((long long)p->batch_size + 1);
+    if (kb >= (1ll << 31)) return EVAD_ERR_UNSUPPORTED;
+    EvadArena a(ws, ws_bytes);
+    PoolWs w;
+    pool_ws_layout(a, n_cap, c_cap, &w);
+    if (!a.ok) return EVAD_ERR_WORKSPACE;
+    PoolGeom G{p->size_x, p->size_y, p->size_t, p->nvx, p->nvy, p->nvt, (uint32_t)kb};
+    PoolSample S{p->feat, p->feat_b, p->feat_h, p->feat_w, p->feat_c, p->width, p->height};
+    const int64_t n = n_cap > 0 ? n_cap : 1;
+    if (n_cap == 0) {
+        cudaMemsetAsync(n_out, 0, sizeof(int32_t), st);
+        if (want_edges) { cudaMemsetAsync(num_edges_out, 0, sizeof(int32_t), st); cudaMemsetAsync(rowptr_out, 0, sizeof(int32_t), st); }
+        return EVAD_OK;
+    }
+    pool_keys_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(pos, ld_pos, batch, n_cap, n_dev, G, w.k0, status);
+    EVAD_CHECK_LAUNCH();
+    int key_bits = 1;
+    while ((1ll << key_bits) <= kb) key_bits++;             // keys take values 0..kb (kb = padding)
+    uint32_t *skey, *sidx;
+    EVAD_TRY(evad_sort_pairs_u32(w.k0, w.v0, w.k1, w.v1, 1, n_cap, key_bits, w.sort_tmp, &skey, &sidx, st));
+    pool_flag_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(skey, n_cap, G.key_bound, w.flag);
+    EVAD_CHECK_LAUNCH();
+    EVAD_TRY(evad_exclusive_scan_u32(w.flag, w.excl, n_cap, nullptr, w.scan_tmp, st));
+    pool_relabel_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(skey, sidx, w.flag, w.excl, n_cap, G.key_bound, cluster,
+                                                         w.seg_start, n_out);
+    EVAD_CHECK_LAUNCH();
+    pool_reduce_kernel<<<(unsigned)c_cap, PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, pos, ld_pos, batch, x, ldx, cx, S,
+                                                              p->aggr_mean, p->inv_w, p->inv_h, p->append_pos, x_out,
+                                                              ldo, pos_out, batch_out);
+    EVAD_CHECK_LAUNCH();
+    if (want_edges) {
+        pool_edges_kernel<false><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, src_in,
+                                                                             cluster, w.deg, nullptr, nullptr, e_cap,
+                                                                             status);
+        EVAD_CHECK_LAUNCH();
+        EVAD_TRY(evad_exclusive_scan_u32(w.deg, w.rowptr_u, c_cap + 1, nullptr, w.scan_tmp, st));
+        pool_edges_kernel<true><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, src_in,
+                                                                            cluster, w.deg, w.rowptr_u, src_out, e_cap,
+                                                                            status);
+        EVAD_CHECK_LAUNCH();
+        pool_finish_edges_kernel<<<evad_cdiv(c_cap + 1, 256), 256, 0, st>>>(w.rowptr_u, n_out, c_cap, rowptr_out,
+                                                                          num_edges_out);
+        EVAD_CHECK_LAUNCH();
+    }
+    return EVAD_OK;
+}

@@ -1,0 +1,203 @@
+// eventad_b200/csrc/spline_small.cu -- fused LUT SplineConv for the full-resolution layer (cin <= 32, cout == 16).
+//
+// Reference path replaced per call (paths relative to /root/reference/src/dagr/model):
+//   layers/spline_conv.py:39-47  message_lut: gather x_j, gather lut[ix,iy] ([E,cin,cout] materialised), einsum
+//   PyG propagate sum aggregation (atomics on the GPU), layers/spline_conv.py:72-76 root weight
+//   layers/conv.py:23-28,47-56   eval BatchNorm, activation, skip Linear + BatchNorm
+// Here: the (2r+1)^2 LUT (+ root and skip matrices) sits in shared memory (103 KB at cin 19->20), one warp owns one
+// destination node (CSR row), the two half-warps take alternate edges, lane&15 is the output channel; no atomics,
+// no [E,cin,cout] tensor, BN/ReLU/skip fused into the epilogue.
+#include "spline_common.cuh"
+
+#define SS_COUT 16
+#define SS_THREADS 256
+#define SS_WARPS (SS_THREADS / 32)
+
+__global__ void lut_build_kernel(const float* __restrict__ weight, const float* __restrict__ root_w,
+                                 const float* __restrict__ skip_w, int cin, int cin_pad, int cout, EvadSplineMode M,
+                                 float* __restrict__ lut) {
+    const int nlut = M.nx * M.ny;
+    const int64_t total = (int64_t)(nlut + 2) * cin_pad * cout;
+    int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= total) return;
+    const int o = (int)(t % cout);
+    const int i = (int)((t / cout) % cin_pad);
+    const int l = (int)(t / ((int64_t)cout * cin_pad));
+    float v = 0.f;
+    if (i < cin) {
+        if (l < nlut) {
+            const int ix = l / M.ny, iy = l - ix * M.ny;
+            // (bil_w[..., None, None] * weight[indices]).sum(1)   (spline_conv.py:33)
+#pragma unroll
+            for (int s = 0; s < 4; s++) {
+                const int mx = s & 1, my = s >> 1;
+                int kk = M.tab_k[2 * ix + mx] + M.ks * M.tab_k[2 * (M.nx + iy) + my];
+                if (kk < 0) kk += M.ks * M.ks;
+                const float b = __fmul_rn(M.tab_w[2 * ix + mx], M.tab_w[2 * (M.nx + iy) + my]);
+                v = __fadd_rn(v, __fmul_rn(b, weight[((int64_t)kk * cin + i) * cout + o]));
+            }
+        } else if (l == nlut) {
+            v = root_w ? root_w[(int64_t)o * cin + i] : 0.f;
+        } else {
+            v = skip_w ? skip_w[(int64_t)o * cin + i] : 0.f;
+        }
+    }
+    lut[t] = v;
+}
+
+extern "C" int evad_spline_lut_build(const float* weight, const float* root_w, const float* skip_w, int cin,
+                                     int cin_pad, int cout, const evad_spline_mode_t* mode_h, float* lut,
+                                     void* stream) {
+    if (!weight || !mode_h || !lut || cin < 1 || cin_pad < cin || cout < 1) return EVAD_ERR_ARG;
+    if (!mode_h->tab_k || !mode_h->tab_w) return EVAD_ERR_ARG;
+    const int64_t total = (int64_t)(mode_h->nx * mode_h->ny + 2) * cin_pad * cout;
+    lut_build_kernel<<<evad_cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(weight, root_w, skip_w, cin, cin_pad,
+                                                                             cout, *mode_h, lut);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
+__device__ __forceinline__ float epi_apply(const evad_epilogue_t& E, float acc, int64_t row, int o) {
+    float v = acc;
+    if (E.scale) v = __fmul_rn(v, E.scale[o]);
+    if (E.shift) v = __fadd_rn(v, E.shift[o]);
+    if (E.addend) v = __fadd_rn(v, E.addend[row * E.ld_add + o]);
+    if (E.relu) v = fmaxf(v, 0.f);
+    return v;
+}
+
+template <int CIN_PAD>
+__global__ void __launch_bounds__(SS_THREADS) spline_small_kernel(
+    const int32_t* __restrict__ rowptr, const int32_t* __restrict__ src, int64_t n, const float* __restrict__ x,
+    int ldx, EvadPseudo P, EvadSplineMode M, const float* __restrict__ lut, evad_epilogue_t E, float* __restrict__ out,
+    int ldo, int has_skip, evad_epilogue_t ES, float* __restrict__ skip_out, int ld_skip, uint32_t* __restrict__ status) {
+    extern __shared__ __align__(16) float lut_s[];
+    const int nlut = M.nx * M.ny;
+    {   // stage the LUT (+root, +skip) in shared memory, 128-bit copies
+        const int total4 = (nlut + 2) * CIN_PAD * SS_COUT / 4;
+        const float4* g = reinterpret_cast<const float4*>(lut);
+        float4* s = reinterpret_cast<float4*>(lut_s);
+        for (int t = threadIdx.x; t < total4; t += SS_THREADS) s[t] = g[t];
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int half = lane >> 4, o = lane & 15;
+    const int64_t stride = (int64_t)gridDim.x * SS_WARPS;
+    for (int64_t i = (int64_t)blockIdx.x * SS_WARPS + warp; i < n; i += stride) {
+        const int r0 = rowptr[i], r1 = rowptr[i + 1];
+        float acc = 0.f;
+        for (int c0 = r0; c0 < r1; c0 += 32) {
+            const int cnt = min(32, r1 - c0);
+            int j = 0, cls = 0;
+            if (lane < cnt) {
+                j = src[c0 + lane];
+                float ax, ay;
+                evad_pseudo(P, c0 + lane, j, (int)i, &ax, &ay);
+                int ix, iy;
+                evad_lut_index(M, ax, ay, &ix, &iy, status);
+                cls = ix * M.ny + iy;
+            }
+            for (int t = 0; t < cnt; t += 2) {
+                const int ee = t + half;
+                const int jj = __shfl_sync(0xffffffffu, j, ee & 31);
+                const int cc = __shfl_sync(0xffffffffu, cls, ee & 31);
+                if (ee < cnt) {
+                    float xr[CIN_PAD];
+                    const float4* xp = reinterpret_cast<const float4*>(x + (int64_t)jj * ldx);
+#pragma unroll
+                    for (int q = 0; q < CIN_PAD / 4; q++) {
+                        const float4 v = __ldg(xp + q);
+                        xr[4 * q] = v.x; xr[4 * q + 1] = v.y; xr[4 * q + 2] = v.z; xr[4 * q + 3] = v.w;
+                    }
+                    const float* w = lut_s + (cc * CIN_PAD) * SS_COUT + o;
+                    // the odd half-warp walks channel pairs swapped (c ^ 1): its 16 lanes then hit the other 16 banks
+#pragma unroll
+                    for (int c = 0; c < CIN_PAD; c += 2) {
+                        const float xa = half ? xr[c + 1] : xr[c];      // selects keep xr[] in registers
+                        const float xb = half ? xr[c] : xr[c + 1];
+                        acc = fmaf(w[(c + half) * SS_COUT], xa, acc);
+                        acc = fmaf(w[(c + 1 - half) * SS_COUT], xb, acc);
+                    }
+                }
+            }
+        }
+        // root weight (and skip Linear) on x_i: half h takes channels c with (c & 1) == h
+        float acc2 = 0.f;
+        {
+            float xr[CIN_PAD];
+            const float4* xp = reinterpret_cast<const float4*>(x + i * ldx);
+#pragma unroll
+            for (int q = 0; q < CIN_PAD / 4; q++) {
+                const float4 v = __ldg(xp + q);
+                xr[4 * q] = v.x; xr[4 * q + 1] = v.y; xr[4 * q + 2] = v.z; xr[4 * q + 3] = v.w;
+            }
+            const float* wr = lut_s + (nlut * CIN_PAD) * SS_COUT + o;
+            const float* wk = wr + CIN_PAD * SS_COUT;
+#pragma unroll
+            for (int c = 0; c < CIN_PAD; c += 2) {
+                const int ci = c + half;
+                const float xv = half ? xr[c + 1] : xr[c];
+                acc = fmaf(wr[ci * SS_COUT], xv, acc);
+                if (has_skip) acc2 = fmaf(wk[ci * SS_COUT], xv, acc2);
+            }
+        }
+        acc += __shfl_xor_sync(0xffffffffu, acc, 16);
+        acc2 += __shfl_xor_sync(0xffffffffu, acc2, 16);
+        if (half == 0) {
+            out[i * ldo + o] = epi_apply(E, acc, i, o);
+        } else if (has_skip) {
+            skip_out[i * ld_skip + o] = epi_apply(ES, acc2, i, o);
+        }
+    }
+}
+
+template <int CIN_PAD>
+static int launch_small(const int32_t* rowptr, const int32_t* src, int64_t n, const float* x, int ldx,
+                        const evad_pseudo_t& P, const evad_spline_mode_t& M, const float* lut, const evad_epilogue_t& E,
+                        float* out, int ldo, int has_skip, const evad_epilogue_t& ES, float* skip_out, int ld_skip,
+                        uint32_t* status, cudaStream_t st) {
+    const size_t smem = (size_t)(M.nx * M.ny + 2) * CIN_PAD * SS_COUT * sizeof(float);
+    if (smem > 227 * 1024) return EVAD_ERR_UNSUPPORTED;
+    static bool attr_done = false;                          // per instantiation
+    if (!attr_done) {
+        if (cudaFuncSetAttribute(spline_small_kernel<CIN_PAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
+            cudaSuccess)
+            return EVAD_ERR_LAUNCH;
+        attr_done = true;
+    }
+    const int ctas_per_sm = smem > 110 * 1024 ? 1 : 2;
+    int64_t want = (n + SS_WARPS - 1) / SS_WARPS;
+    int grid = (int)(want < (int64_t)148 * ctas_per_sm ? want : (int64_t)148 * ctas_per_sm);
+    if (grid < 1) grid = 1;
+    spline_small_kernel<CIN_PAD><<<grid, SS_THREADS, smem, st>>>(rowptr, src, n, x, ldx, P, M, lut, E, out, ldo, has_skip,
+                                                               ES, skip_out, ld_skip, status);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
+extern "C" int evad_spline_conv_small(const int32_t* rowptr, const int32_t* src, int64_t n, const float* x, int ldx,
+                                      int cin, int cin_pad, int cout, const evad_pseudo_t* pseudo_h,
+                                      const evad_spline_mode_t* mode_h, const float* lut, const evad_epilogue_t* epi_h,
+                                      float* out, int ldo, const evad_epilogue_t* skip_epi_h, float* skip_out,
+                                      int ld_skip, uint32_t* status, void* stream) {
+    if (!rowptr || !src || !x || !pseudo_h || !mode_h || !lut || !epi_h || !out || !status) return EVAD_ERR_ARG;
+    if (cout != SS_COUT || cin_pad < cin || cin_pad % 4 != 0 || cin_pad > 32 || ldx % 4 != 0 || ldx < cin_pad)
+        return EVAD_ERR_UNSUPPORTED;
+    if (((uintptr_t)x & 15) || ((uintptr_t)lut & 15)) return EVAD_ERR_ARG;
+    if (!mode_h->use_lut) return EVAD_ERR_UNSUPPORTED;
+    if (n <= 0) return EVAD_OK;
+    const int has_skip = skip_epi_h != nullptr && skip_out != nullptr;
+    evad_epilogue_t es = has_skip ? *skip_epi_h : *epi_h;
+    cudaStream_t st = (cudaStream_t)stream;
+#define EVAD_SS_CASE(C)                                                                                              \
+    case C:                                                                                                          \
+        return launch_small<C>(rowptr, src, n, x, ldx, *pseudo_h, *mode_h, lut, *epi_h, out, ldo, has_skip, es,     \
+                               skip_out, ld_skip, status, st);
+    switch (cin_pad) {
+        EVAD_SS_CASE(4) EVAD_SS_CASE(8) EVAD_SS_CASE(12) EVAD_SS_CASE(16) EVAD_SS_CASE(20) EVAD_SS_CASE(24)
+        EVAD_SS_CASE(28) EVAD_SS_CASE(32)
+    default:
+        return EVAD_ERR_UNSUPPORTED;
+    }
+#undef EVAD_SS_CASE
+}

@@ -78,6 +78,129 @@ int evad_graph_build(const int32_t* batch, const int32_t* pos, int64_t n_events,
                      int64_t edge_index_stride, int32_t* cell_perm, int32_t* cell_start, uint32_t* status,
                      void* ws, size_t ws_bytes, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * SplineConv message passing.
+ * Replaces MySplineConv.forward/_forward/message_lut/init_lut (src/dagr/model/layers/spline_conv.py:16-78), PyG
+ * MessagePassing.propagate (gather x_j, sum aggregation), torch_spline_conv.spline_basis/spline_weighting, and the
+ * eval-mode BatchNormData + activation (+ skip branch) that ConvBlock / ConvBlockWithSkip apply right after
+ * (src/dagr/model/layers/conv.py:23-28,47-56).
+ *
+ * Graphs are passed as dst-major CSR: rowptr[n+1], src[E]; slot order inside a row = the reference's edge order
+ * for that destination, so sums are accumulated in the reference's (CPU scatter_add) order.
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef struct {
+    const float* edge_attr; /* [E, ld_attr] pseudo-coordinates in ORIGINAL edge order, or NULL -> computed from pos */
+    const int32_t* eid;     /* original edge id of CSR slot e (NULL = identity); only used with edge_attr */
+    int ld_attr;
+    const float* pos;       /* [n, ld_pos] node positions (x, y, ...) */
+    int ld_pos;
+    float two_m;            /* fp32(2 * max_value) of T.Cartesian (components.py:25-35) */
+    int clamp01;            /* clamp attr to [0,1] (net.py:121, first layer only) */
+} evad_pseudo_t;
+
+typedef struct {
+    int use_lut;            /* 1: message_lut semantics (snap to the integer LUT lattice); 0: spline_basis on attr */
+    float r00, r02, r11, r12; /* attr_remapping_matrix (spline_conv.py:21-24) */
+    int nx, ny;             /* LUT extent 2*rx+1, 2*ry+1 */
+    const int32_t* tab_k;   /* [nx+ny][2] kernel tap index per lattice coordinate (x table, then y table) */
+    const float* tab_w;     /* [nx+ny][2] tap weights */
+    int ks;                 /* kernel size per dimension */
+} evad_spline_mode_t;
+
+/* per-output-channel affine (eval BatchNorm folded: scale = gamma/sqrt(var+eps), shift = beta - mean*scale; or the
+ * conv bias), optional residual addend [n, ld_add] and ReLU:  y = act(acc*scale + shift + addend) */
+typedef struct {
+    const float* scale;     /* [cout] or NULL (=1) */
+    const float* shift;     /* [cout] or NULL (=0) */
+    const float* addend;    /* [n, ld_add] or NULL */
+    int ld_add;
+    int relu;
+} evad_epilogue_t;
+
+/* Dense LUT of init_lut: lut[(ix*ny+iy)][cin_pad][cout] = sum_s basis_s * weight[idx_s]; rows cin..cin_pad-1 zero.
+ * Two extra matrices are appended: [nx*ny] = root weight lin.weight^T, [nx*ny+1] = skip weight^T (or zeros). */
+int evad_spline_lut_build(const float* weight /*[ks*ks,cin,cout]*/, const float* root_w /*[cout,cin]*/,
+                          const float* skip_w /*[cout,cin] or NULL*/, int cin, int cin_pad, int cout,
+                          const evad_spline_mode_t* mode_h, float* lut, void* stream);
+
+/* Fused small-channel SplineConv (cin_pad <= 32, cout == 16), LUT resident in shared memory, one warp per
+ * destination node:  out = epi(sum_e lut[ix_e,iy_e]^T x[src_e] + root^T x[i]);
+ * optionally also skip_out = skip_epi(skip^T x[i])  (the Linear+BN skip branch of ConvBlockWithSkip). */
+int evad_spline_conv_small(const int32_t* rowptr, const int32_t* src, int64_t n, const float* x, int ldx, int cin,
+                           int cin_pad, int cout, const evad_pseudo_t* pseudo_h, const evad_spline_mode_t* mode_h,
+                           const float* lut, const evad_epilogue_t* epi_h, float* out, int ldo,
+                           const evad_epilogue_t* skip_epi_h, float* skip_out, int ld_skip, uint32_t* status,
+                           void* stream);
+
+/* General SplineConv, step 1: per destination node aggregate the sources per kernel tap:
+ *   A[i, k*cin + c] = sum_{e: tap k} basis_e,k * x[src_e, c]   (k < ks*ks),   A[i, ks*ks*cin + c] = x[i, c]
+ * n_dev (device int32, may be NULL) = actual node count when only an upper bound n is known on the host. */
+int evad_spline_aggregate(const int32_t* rowptr, const int32_t* src, int64_t n, const int32_t* n_dev, const float* x,
+                          int ldx, int cin, const evad_pseudo_t* pseudo_h, const evad_spline_mode_t* mode_h, float* A,
+                          int64_t lda, uint32_t* status, void* stream);
+
+/* General SplineConv, step 2 (also Linear): out[m, :] = epi(A[m, :K] @ W[K, N]) in fp32 on the CUDA cores. */
+int evad_gemm_epilogue(const float* A, int64_t lda, const float* W /*[K,N] row-major*/, int64_t m,
+                       const int32_t* m_dev, int k, int n, const evad_epilogue_t* epi_h, float* out, int ldo,
+                       void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Voxel-grid pooling.
+ * Replaces Pooling.forward (src/dagr/model/layers/pooling.py:51-97): torch_cluster.grid_cluster on [x,y,t,batch],
+ * consecutive_cluster, cluster[edge_index] + self-loop drop + unique(dim=-1), pool_pos, scatter_max / _avg_pool_x,
+ * round_to_pixel; and the sampling_skip that precedes every pooling call (src/dagr/model/networks/net.py:15-17,200-228)
+ * when `feat` is given (the [n, C+64] concat is never materialised).
+ * The input graph is dst-major CSR; the coarse graph comes out as dst-major CSR with ascending sources per row
+ * (the transposed order of the reference's lexicographic unique; see evad_csr_to_coo).
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef struct {
+    float size_x, size_y, size_t; /* voxel_size[0..2] (pooling.py:24) */
+    int nvx, nvy, nvt;            /* ((end - start) / size).long() + 1 per dim, as torch_cluster computes it */
+    int batch_size;               /* run-time number of samples; ids of the (t == 1.0) quirk use slot batch_size */
+    float inv_w, inv_h;           /* wh_inv = 1 / [W, H] in fp32 (pooling.py:32) */
+    int aggr_mean;                /* 0: max (scatter_max), 1: mean (_avg_pool_x) */
+    int append_pos;               /* also write the coarse (x, y) after the pooled channels (net.py:135) */
+    const float* feat;            /* optional CHANNEL-LAST CNN map [feat_b, feat_h, feat_w, feat_c], or NULL */
+    int feat_b, feat_h, feat_w, feat_c;
+    float width, height;          /* data.width[0], data.height[0] */
+} evad_pool_params_t;
+
+size_t evad_voxel_pool_ws_bytes(int64_t n_cap, int64_t c_cap);
+/* n_cap nodes at most (n_dev: device int32 actual count or NULL), c_cap >= number of output clusters (host bound),
+ * e_cap = capacity of src_out.  Outputs: cluster[n_cap] dense ids in node order, n_out[1], x_out[c_cap, ldo],
+ * pos_out[c_cap,3], batch_out[c_cap], rowptr_out[c_cap+1], src_out[e_cap], num_edges_out[1] (edge outputs optional:
+ * pass rowptr_in = NULL to skip). */
+int evad_voxel_pool(const evad_pool_params_t* params_h, int64_t n_cap, const int32_t* n_dev, const float* pos,
+                    int ld_pos, const int32_t* batch, const float* x, int ldx, int cx, const int32_t* rowptr_in,
+                    const int32_t* src_in, int64_t c_cap, int64_t e_cap, int32_t* cluster, int32_t* n_out,
+                    float* x_out, int ldo, float* pos_out, int32_t* batch_out, int32_t* rowptr_out, int32_t* src_out,
+                    int32_t* num_edges_out, uint32_t* status, void* ws, size_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Format glue.
+ * ---------------------------------------------------------------------------------------------------------- */
+/* edge_index int64 [2][stride] in any order -> dst-major CSR (stable: slots of a row keep the original edge order,
+ * i.e. the order in which PyG's scatter-add visits them); eid[slot] = original edge id. */
+size_t evad_coo_to_csr_ws_bytes(int64_t num_edges);
+int evad_coo_to_csr(const int64_t* edge_index, int64_t stride, int64_t num_edges, int64_t n_nodes, int32_t* rowptr,
+                    int32_t* src, int32_t* eid, uint32_t* status, void* ws, size_t ws_bytes, void* stream);
+/* dst-major CSR -> edge_index int64 [2][stride]; src_major = 0 keeps CSR order (the graph builder's reference order),
+ * src_major = 1 gives the (src, dst)-lexicographic order of `edge_index.unique(dim=-1)` (pooling.py:64).
+ * slot_of (optional) [e_cap]: CSR slot of each output column. */
+size_t evad_csr_to_coo_ws_bytes(int64_t e_cap);
+int evad_csr_to_coo(const int32_t* rowptr, const int32_t* src, int64_t n_cap, const int32_t* n_dev, int64_t e_cap,
+                    const int32_t* num_edges, int src_major, int64_t* edge_index, int64_t stride, int32_t* slot_of,
+                    void* ws, size_t ws_bytes, void* stream);
+/* PyG T.Cartesian(norm=True, cat=False, max_value=m) (+ optional clamp to [0,1], net.py:121):
+ * out[e, d] = (pos[row[e], d] - pos[col[e], d]) / two_m + 0.5 for d < dims. */
+int evad_cartesian(const float* pos, int ld_pos, int dims, const int64_t* edge_index, int64_t stride, int64_t e_cap,
+                   const int32_t* num_edges, float two_m, int clamp01, float* out, void* stream);
+/* sampling_skip + cat(x, pos[:, :2]) (net.py:15-17,116,122-123): out[i] = [x[i,:cx] | grid_sample(feat)(feat_c) |
+ * pos_x, pos_y | zero padding]; feat is CHANNEL-LAST [feat_b, feat_h, feat_w, feat_c] or NULL. */
+int evad_sample_concat(const float* x, int ldx, int cx, const float* pos, int ld_pos, const int32_t* batch,
+                       int64_t n_cap, const int32_t* n_dev, const float* feat, int feat_b, int feat_h, int feat_w,
+                       int feat_c, float width, float height, int append_pos, float* out, int ldo, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
