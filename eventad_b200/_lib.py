@@ -24,6 +24,27 @@ c_sz = ctypes.c_size_t
 c_f = ctypes.c_float
 
 
+class PseudoT(ctypes.Structure):
+    _fields_ = [("edge_attr", c_p), ("eid", c_p), ("ld_attr", c_i), ("pos", c_p), ("ld_pos", c_i),
+                ("two_m", c_f), ("clamp01", c_i)]
+
+
+class SplineModeT(ctypes.Structure):
+    _fields_ = [("use_lut", c_i), ("r00", c_f), ("r02", c_f), ("r11", c_f), ("r12", c_f), ("nx", c_i), ("ny", c_i),
+                ("tab_k", c_p), ("tab_w", c_p), ("ks", c_i)]
+
+
+class EpilogueT(ctypes.Structure):
+    _fields_ = [("scale", c_p), ("shift", c_p), ("addend", c_p), ("ld_add", c_i), ("relu", c_i)]
+
+
+class PoolParamsT(ctypes.Structure):
+    _fields_ = [("size_x", c_f), ("size_y", c_f), ("size_t", c_f), ("nvx", c_i), ("nvy", c_i), ("nvt", c_i),
+                ("batch_size", c_i), ("inv_w", c_f), ("inv_h", c_f), ("aggr_mean", c_i), ("append_pos", c_i),
+                ("feat", c_p), ("feat_b", c_i), ("feat_h", c_i), ("feat_w", c_i), ("feat_c", c_i),
+                ("width", c_f), ("height", c_f)]
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -51,6 +72,23 @@ def _declare(L):
     _sig(L, "evad_graph_ws_bytes", c_sz, [c_i64, c_i, c_i, c_i, c_i])
     _sig(L, "evad_graph_build", c_i, [c_p, c_p, c_i64, c_i, c_i, c_i, c_i, c_i, c_i, c_i,
                                       c_p, c_p, c_p, c_p, c_i64, c_p, c_p, c_p, c_p, c_sz, c_p])
+    P = ctypes.POINTER
+    _sig(L, "evad_spline_lut_build", c_i, [c_p, c_p, c_p, c_i, c_i, c_i, P(SplineModeT), c_p, c_p])
+    _sig(L, "evad_spline_conv_small", c_i, [c_p, c_p, c_i64, c_p, c_i, c_i, c_i, c_i, P(PseudoT), P(SplineModeT), c_p,
+                                            P(EpilogueT), c_p, c_i, P(EpilogueT), c_p, c_i, c_p, c_p])
+    _sig(L, "evad_spline_aggregate", c_i, [c_p, c_p, c_i64, c_p, c_p, c_i, c_i, P(PseudoT), P(SplineModeT), c_p, c_i64,
+                                           c_p, c_p])
+    _sig(L, "evad_gemm_epilogue", c_i, [c_p, c_i64, c_p, c_i64, c_p, c_i, c_i, P(EpilogueT), c_p, c_i, c_p])
+    _sig(L, "evad_voxel_pool_ws_bytes", c_sz, [c_i64, c_i64])
+    _sig(L, "evad_voxel_pool", c_i, [P(PoolParamsT), c_i64, c_p, c_p, c_i, c_p, c_p, c_i, c_i, c_p, c_p, c_i64, c_i64,
+                                     c_p, c_p, c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_p])
+    _sig(L, "evad_coo_to_csr_ws_bytes", c_sz, [c_i64])
+    _sig(L, "evad_coo_to_csr", c_i, [c_p, c_i64, c_i64, c_i64, c_p, c_p, c_p, c_p, c_p, c_sz, c_p])
+    _sig(L, "evad_csr_to_coo_ws_bytes", c_sz, [c_i64])
+    _sig(L, "evad_csr_to_coo", c_i, [c_p, c_p, c_i64, c_p, c_i64, c_p, c_i, c_p, c_i64, c_p, c_p, c_sz, c_p])
+    _sig(L, "evad_cartesian", c_i, [c_p, c_i, c_i, c_p, c_i64, c_i64, c_p, c_f, c_i, c_p, c_p])
+    _sig(L, "evad_sample_concat", c_i, [c_p, c_i, c_i, c_p, c_i, c_p, c_i64, c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_f,
+                                        c_i, c_p, c_i, c_p])
 
 
 def check(rc: int, what: str = ""):
@@ -66,6 +104,17 @@ def ptr(t):
         raise RuntimeError("eventad_b200: tensor must be a CUDA tensor (no CPU fallback)")
     if not t.is_contiguous():
         raise RuntimeError("eventad_b200: tensor must be contiguous")
+    return t.data_ptr()
+
+
+def ptr_rows(t):
+    """device pointer of a 2-D tensor whose rows are contiguous (stride(1) == 1); the row stride is passed separately."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("eventad_b200: tensor must be a CUDA tensor (no CPU fallback)")
+    if t.dim() != 2 or (t.shape[1] > 1 and t.stride(1) != 1):
+        raise RuntimeError("eventad_b200: tensor rows must be contiguous")
     return t.data_ptr()
 
 

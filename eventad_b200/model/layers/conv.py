@@ -1,0 +1,94 @@
+"""ConvBlock, ConvBlockWithSkip, Layer with the reference's constructors and state-dict keys
+(/root/reference/src/dagr/model/layers/conv.py:10-72).  In eval mode `Layer.forward` runs the fused kernels:
+conv + folded BatchNorm + ReLU, and conv + BatchNorm + (Linear + BatchNorm skip) + ReLU, each one or two launches."""
+import torch
+
+from ... import ops
+from ..utils import shallow_copy
+from .components import BatchNormData, Linear
+from .spline_conv import MySplineConv, get_csr
+
+
+def _fold(bn_data, conv_bias=None):
+    scale, shift = ops.fold_bn(bn_data.module)
+    if conv_bias is not None:
+        shift = shift + conv_bias.detach().float() * scale
+    return scale, shift
+
+
+class ConvBlock(torch.nn.Module):
+    def __init__(self, in_channels: int, out_channels: int, args, degree=1) -> None:
+        super(ConvBlock, self).__init__()
+        self.dim = args.edge_attr_dim
+        self.activation = getattr(torch.nn.functional, args.activation, torch.nn.functional.elu)
+        self.conv = MySplineConv(in_channels=in_channels, out_channels=out_channels, args=args, bias=False, degree=degree)
+        self.norm = BatchNormData(in_channels=out_channels)
+
+    def forward(self, data):
+        data = self.conv(data)
+        data = self.norm(data)
+        data.x = self.activation(data.x)
+        return data
+
+
+class ConvBlockWithSkip(torch.nn.Module):
+    def __init__(self, in_channel: int, out_channel: int, skip_in_channel: int, args) -> None:
+        super(ConvBlockWithSkip, self).__init__()
+        self.dim = args.edge_attr_dim
+        self.conv = MySplineConv(in_channels=in_channel, out_channels=out_channel, args=args, bias=False)
+        self.activation = getattr(torch.nn.functional, args.activation, torch.nn.functional.elu)
+        self.norm = BatchNormData(in_channels=out_channel)
+        self.lin = Linear(skip_in_channel, out_channel, bias=False)
+        self.norm_skip = BatchNormData(in_channels=out_channel)
+
+    def forward(self, data, data_skip):
+        data = self.conv(data)
+        data_skip = self.lin(data_skip)
+        data_skip = self.norm_skip(data_skip)
+        data = self.norm(data)
+        data.x = self.activation(data.x + data_skip.x)
+        return data
+
+
+class Layer(torch.nn.Module):
+    def __init__(self, in_channels: int, out_channels: int, args) -> None:
+        super(Layer, self).__init__()
+        self.in_channel = in_channels
+        self.out_channel = out_channels
+        self.conv_block1 = ConvBlock(in_channels, out_channels, args)
+        self.conv_block2 = ConvBlockWithSkip(out_channels, out_channels, in_channels, args=args)
+
+    # fused eval path on raw tensors (used by Layer.forward and by the fused Net.forward)
+    def run_fused(self, x, rowptr, src, n_cap, n_dev, pseudo, status):
+        b1, b2 = self.conv_block1, self.conv_block2
+        relu = b1.activation is torch.nn.functional.relu
+        s1, h1 = _fold(b1.norm, b1.conv.bias)
+        s2, h2 = _fold(b2.norm, b2.conv.bias)
+        ss, hs = _fold(b2.norm_skip, b2.lin.mlp.bias)
+        y, skip = b1.conv.run(x, rowptr, src, n_cap, n_dev, pseudo, dict(scale=s1, shift=h1, relu=relu), status,
+                              skip_weight=b2.lin.mlp.weight, skip_epi=dict(scale=ss, shift=hs))
+        if not relu:
+            y = b1.activation(y)
+        out, _ = b2.conv.run(y, rowptr, src, n_cap, n_dev, pseudo, dict(scale=s2, shift=h2, addend=skip, relu=relu), status)
+        if not relu:
+            out = b2.activation(out)
+        return out
+
+    def forward(self, data):
+        if self.training:
+            data_skip = shallow_copy(data)
+            data = self.conv_block1(data)
+            return self.conv_block2(data, data_skip)
+        x = data.x.float()
+        n = x.shape[0]
+        status = ops.new_status(x.device)
+        if data.edge_index.numel() > 0:
+            csr = get_csr(data)
+            rowptr, src = csr["rowptr"], csr["src"]
+            pseudo = dict(edge_attr=data.edge_attr[:, :self.conv_block1.dim].float().contiguous(), eid=csr["eid"])
+        else:
+            rowptr = torch.zeros(n + 1, dtype=torch.int32, device=x.device)
+            src = torch.zeros(1, dtype=torch.int32, device=x.device)
+            pseudo = dict(edge_attr=torch.zeros((1, 2), device=x.device), eid=None)
+        data.x = self.run_fused(x, rowptr, src, n, None, pseudo, status)[:n]
+        return data

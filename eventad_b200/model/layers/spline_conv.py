@@ -1,0 +1,206 @@
+"""MySplineConv / SplineConvToDense with the reference's constructor, attributes and state-dict keys
+(/root/reference/src/dagr/model/layers/spline_conv.py:9-118; base class PyG SplineConv 2.6.1: `weight [K,Cin,Cout]`,
+`lin.weight [Cout,Cin]`, optional `bias`, persistent buffers `kernel_size`, `is_open_spline`), running on the
+sm_100a kernels (csrc/spline_small.cu, csrc/spline_general.cu).  There is no PyTorch fallback for the message passing.
+"""
+import math
+
+import torch
+
+from ... import ops
+
+
+class _PyGLinear(torch.nn.Module):
+    """torch_geometric.nn.dense.linear.Linear(in, out, bias=False): key `weight` [out, in]."""
+
+    def __init__(self, in_channels, out_channels):
+        super().__init__()
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.weight = torch.nn.Parameter(torch.empty(out_channels, in_channels))
+        self.register_parameter("bias", None)
+
+    def forward(self, x):
+        return torch.nn.functional.linear(x, self.weight)
+
+
+def get_csr(data):
+    """dst-major CSR of data.edge_index, cached on the Data object (built by evad_coo_to_csr when missing)."""
+    c = getattr(data, "_csr", None)
+    ei = data.edge_index
+    if c is not None and c.get("edge_index_ptr") == (ei.data_ptr(), tuple(ei.shape)):
+        return c
+    n = data.x.shape[0]
+    rowptr, src, eid = ops.coo_to_csr(ei, n)
+    c = dict(rowptr=rowptr, src=src, eid=eid, edge_index_ptr=(ei.data_ptr(), tuple(ei.shape)))
+    data._csr = c
+    return c
+
+
+class MySplineConv(torch.nn.Module):
+    def __init__(self, in_channels, out_channels, args, bias=False, degree=1, **kwargs):
+        super().__init__()
+        self.reproducible = False
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.dim = args.edge_attr_dim
+        self.degree = degree
+        self.aggr = args.aggr
+        self.root_weight = True
+        if self.dim != 2 or degree != 1:
+            raise NotImplementedError("the EventAD path uses dim=2, degree=1 (spline_conv.py:10-14)")
+        if self.aggr not in ("sum", "add"):
+            raise NotImplementedError("only sum aggregation is implemented (reference default, SURVEY A.1)")
+        ks = int(args.kernel_size)
+        self.register_buffer("kernel_size", torch.tensor([ks] * self.dim, dtype=torch.long))
+        self.register_buffer("is_open_spline", torch.ones(self.dim, dtype=torch.uint8))
+        self.K = ks ** self.dim
+        self.weight = torch.nn.Parameter(torch.empty(self.K, in_channels, out_channels))
+        self.lin = _PyGLinear(in_channels, out_channels)
+        if bias:
+            self.bias = torch.nn.Parameter(torch.empty(out_channels))
+        else:
+            self.register_parameter("bias", None)
+        self.reset_parameters()
+        self._mode = None           # LUT parameters after init_lut
+        self._cache = {}
+        self.message = self.message_basis
+
+    def reset_parameters(self):
+        bound = 1.0 / math.sqrt(self.in_channels * self.K)
+        torch.nn.init.uniform_(self.weight, -bound, bound)
+        torch.nn.init.uniform_(self.lin.weight, -bound, bound)
+        if self.bias is not None:
+            torch.nn.init.zeros_(self.bias)
+
+    # ---- reference API -------------------------------------------------------------------------------------
+    def init_lut(self, height, width, rx=None, Mx=None, ry=None, My=None):
+        """Switches to message_lut semantics (spline_conv.py:16-37).  The dense [2rx+1, 2ry+1, Cin, Cout] table is
+        only materialised for the shared-memory kernel of the small first layer; the general kernel snaps edges to
+        the same integer lattice and evaluates the same basis values from two 1-D tables."""
+        self._mode = ops.spline_mode_lut(height, width, rx, Mx, ry, My, int(self.kernel_size[0]), self.weight.device)
+        self.attr_remapping_matrix = self._mode["R"]
+        self._cache = {}
+        self.message = self.message_lut
+
+    def message_lut(self, x_j, edge_attr):
+        raise RuntimeError("message passing runs inside the fused CUDA kernels; call forward()")
+
+    message_basis = message_lut
+
+    def mode(self):
+        m = self._mode
+        if m is None:
+            m = self._cache.get("basis_mode")
+            if m is None:
+                m = self._cache["basis_mode"] = ops.spline_mode_basis(int(self.kernel_size[0]))
+        elif m["tab_k"].device != self.weight.device:
+            m["tab_k"] = m["tab_k"].to(self.weight.device)
+            m["tab_w"] = m["tab_w"].to(self.weight.device)
+        return m
+
+    # ---- cached weight layouts -----------------------------------------------------------------------------
+    def _versions(self, extra=None):
+        v = [self.weight._version, self.lin.weight._version, self.weight.device]
+        if extra is not None:
+            v.append(extra._version)
+        return tuple(v)
+
+    def wcat(self):
+        """[K*Cin + Cin, Cout]: the K tap matrices stacked, then lin.weight^T (root weight)."""
+        key = self._versions()
+        c = self._cache.get("wcat")
+        if c is None or c[0] != key:
+            w = torch.cat([self.weight.detach().reshape(self.K * self.in_channels, self.out_channels),
+                           self.lin.weight.detach().t()], 0).contiguous().float()
+            c = self._cache["wcat"] = (key, w)
+        return c[1]
+
+    def small_lut(self, skip_weight=None):
+        cin_pad = (self.in_channels + 3) // 4 * 4
+        key = self._versions(skip_weight)
+        c = self._cache.get("lut")
+        if c is None or c[0] != key:
+            lut = ops.build_lut(self.weight.float(), self.lin.weight.float(),
+                                skip_weight.float() if skip_weight is not None else None, cin_pad, self.mode())
+            c = self._cache["lut"] = (key, lut)
+        return c[1]
+
+    def small_ok(self):
+        m = self.mode()
+        return (m["use_lut"] == 1 and self.out_channels == 16 and self.in_channels <= 32 and
+                (m["nx"] * m["ny"] + 2) * ((self.in_channels + 3) // 4 * 4) * 16 * 4 <= 227 * 1024)
+
+    # ---- kernels ---------------------------------------------------------------------------------------------
+    def run(self, x, rowptr, src, n_cap, n_dev, pseudo, epi, status, skip_weight=None, skip_epi=None):
+        """x [n_cap, >=Cin] float32 -> epi(conv(x)) [n_cap, Cout] (+ skip_epi(x @ skip_weight^T) when requested)."""
+        cin = self.in_channels
+        if self.small_ok() and n_dev is None:
+            cin_pad = (cin + 3) // 4 * 4
+            # rows must be 16-byte aligned and zero beyond Cin; a [n, cin_pad] input is trusted to be zero padded
+            if not (x.stride(1) == 1 and x.stride(0) % 4 == 0 and x.data_ptr() % 16 == 0 and x.shape[1] == cin_pad):
+                xp = torch.zeros((x.shape[0], cin_pad), dtype=torch.float32, device=x.device)
+                xp[:, :cin] = x[:, :cin]
+                x = xp
+            return ops.spline_conv_small(rowptr, src, n_cap, x, cin, self.small_lut(skip_weight), self.mode(), pseudo, epi,
+                                         status, skip_epi)
+        x = x.contiguous()
+        A = ops.spline_aggregate(rowptr, src, n_cap, n_dev, x, cin, self.mode(), pseudo, status)
+        out = ops.gemm_epilogue(A, self.wcat(), n_cap, n_dev, epi)
+        skip = None
+        if skip_epi is not None:
+            skip = ops.gemm_epilogue(x, skip_weight.detach().t().contiguous().float(), n_cap, n_dev, skip_epi, k=cin)
+        return out, skip
+
+    def forward(self, data):
+        x = data.x.float()
+        n = x.shape[0]
+        status = ops.new_status(x.device)
+        if data.edge_index.numel() > 0:
+            csr = get_csr(data)
+            rowptr, src, eid = csr["rowptr"], csr["src"], csr["eid"]
+            attr = data.edge_attr[:, :self.dim].float().contiguous()
+            pseudo = dict(edge_attr=attr, eid=eid)
+        else:
+            rowptr = torch.zeros(n + 1, dtype=torch.int32, device=x.device)
+            src = torch.zeros(1, dtype=torch.int32, device=x.device)
+            pseudo = dict(edge_attr=torch.zeros((1, 2), device=x.device), eid=None)
+        epi = dict(shift=self.bias.detach().float() if self.bias is not None else None)
+        out, _ = self.run(x, rowptr, src, n, None, pseudo, epi, status)
+        data.x = out[:n]
+        return data
+
+
+def to_dense(self, x, pos, pooling, batch=None, batch_size=None):
+    """spline_conv.py:80-106 (head only; not on the EventAD path, kept for API completeness)."""
+    if hasattr(self, "batch_size"):
+        B = self.batch_size
+    elif batch_size is not None:
+        self.batch_size = batch_size
+        B = batch_size
+    elif batch is None:
+        batch = torch.zeros(size=(len(x),), dtype=torch.long, device=x.device)
+        B = 1
+        self.batch_size = B
+    else:
+        B = batch.max().item() + 1
+        self.batch_size = B
+    if not hasattr(self, "dense"):
+        W, H = (1 / pooling[:2] + 1e-3).long()
+        C = x.shape[-1]
+        self.dense = torch.zeros(size=(B, C, H, W), dtype=x.dtype, device=x.device)
+    est_x, est_y = (pos[:, :2] / pooling[:2]).t().long()
+    self.dense = self.dense.detach()
+    self.dense.zero_()
+    dense = self.dense[:B] if B < self.dense.shape[0] else self.dense
+    dense[batch.long(), :, est_y, est_x] = x
+    return dense
+
+
+class SplineConvToDense(MySplineConv):
+    def forward(self, data, batch_size=None):
+        data = super().forward(data)
+        if data.batch is None:
+            data.batch = torch.zeros(len(data.x), dtype=torch.long, device=data.x.device)
+        return self.to_dense(data.x, data.pos, data.pooling, data.batch, batch_size=batch_size)
+
+    def to_dense(self, x, pos, pooling, batch=None, batch_size=None):
+        return to_dense(self, x, pos, pooling, batch, batch_size=batch_size)

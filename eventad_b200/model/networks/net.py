@@ -1,0 +1,273 @@
+"""DAGR backbone `Net` with the reference's constructor, module tree and state-dict keys
+(/root/reference/src/dagr/model/networks/net.py:15-228).
+
+`forward` has two implementations with identical results:
+  * the module-by-module composition of the reference (EV_TGN -> Cartesian -> Layer -> Pooling ...), every module
+    calling the sm_100a kernels through the C ABI (used in training mode or with `fused=False`);
+  * the fused eval path (`forward_fused`): one device-resident pipeline without host synchronisation until the
+    outputs are read: graph CSR -> x0 assembly -> layer 1 (2 launches) -> pool (sampling fused) -> layer ... ;
+    it is CUDA-graph capturable.
+"""
+import torch
+
+from ... import _lib, ops
+from ...data import Batch, Data
+from ..layers.components import Cartesian, CartesianTransform, two_m_of
+from ..layers.conv import Layer
+from ..layers.ev_tgn import EV_TGN, denormalize_pos
+from ..layers.pooling import Pooling
+from ..utils import shallow_copy
+from .net_img import HookModule
+
+
+def sampling_skip(data, image_feat):
+    """net.py:15-17 through evad_sample_concat."""
+    if data.batch is None or len(data.batch) != len(data.pos):
+        data.batch = torch.zeros(len(data.pos), dtype=torch.long, device=data.x.device)
+    return ops.sample_concat(data.x.float(), data.pos.float(), data.batch.int(), ops.to_channel_last(image_feat.float()),
+                             float(data.width[0]), float(data.height[0]))
+
+
+def sample_features(data, image_feat, image_sample_mode="bilinear"):
+    """net.py:200-209."""
+    if data.batch is None or len(data.batch) != len(data.pos):
+        data.batch = torch.zeros(len(data.pos), dtype=torch.long, device=data.x.device)
+    return ops.sample_concat(None, data.pos.float(), data.batch.int(), ops.to_channel_last(image_feat.float()),
+                             float(data.width[0]), float(data.height[0]))
+
+
+def compute_pooling_at_each_layer(pooling_dim_at_output, num_layers):
+    py, px = map(int, pooling_dim_at_output.split("x"))
+    pooling_base = torch.tensor([1.0 / px, 1.0 / py, 1.0 / 1])
+    poolings = []
+    for i in range(num_layers):
+        pooling = pooling_base / 2 ** (3 - i)
+        pooling[-1] = 1
+        poolings.append(pooling)
+    return torch.stack(poolings)
+
+
+class GraphOut(Data):
+    """Output of the fused path: `edge_index` (reference order of `unique(dim=-1)`) and `edge_attr` are materialised
+    on first access from the dst-major CSR the kernels keep."""
+
+    def __init__(self, **kw):
+        self._lazy = None
+        super().__init__(**kw)
+
+    @property
+    def edge_index(self):
+        if self.__dict__.get("_edge_index") is None and self._lazy is not None:
+            self._materialise()
+        return self.__dict__.get("_edge_index")
+
+    @edge_index.setter
+    def edge_index(self, v):
+        self.__dict__["_edge_index"] = v
+
+    @property
+    def edge_attr(self):
+        if self.__dict__.get("_edge_attr") is None and self._lazy is not None:
+            self._materialise()
+        return self.__dict__.get("_edge_attr")
+
+    @edge_attr.setter
+    def edge_attr(self, v):
+        self.__dict__["_edge_attr"] = v
+
+    def keys(self):
+        return [k for k in ("x", "edge_index", "edge_attr", "pos", "batch") if getattr(self, k) is not None]
+
+    def _materialise(self):
+        z = self._lazy
+        n, e = self.x.shape[0], z["e"]
+        if e > 0:
+            ei = ops.csr_to_coo(z["rowptr"], z["src"], n, None, e, z["num_edges"], True)[:, :e]
+            attr = ops.cartesian(self.pos, ei, z["two_m"], False)
+        else:
+            ei = torch.zeros((2, 0), dtype=torch.long, device=self.x.device)
+            attr = torch.zeros((0, 3), dtype=torch.float32, device=self.x.device)
+        self.__dict__["_edge_index"], self.__dict__["_edge_attr"] = ei, attr
+        self._csr = dict(rowptr=z["rowptr"], src=z["src"], eid=None, edge_index_ptr=None)
+
+
+class Net(torch.nn.Module):
+    def __init__(self, args, height, width):
+        super().__init__()
+        channels = [1, int(args.base_width * 32), int(args.after_pool_width * 64), int(args.net_stem_width * 128),
+                    int(args.net_stem_width * 128), int(args.net_stem_width * 128)]
+        self.out_channels_cnn = []
+        if args.use_image:
+            import torchvision.models as tvm
+            ctor = getattr(tvm, args.img_net)
+            # the reference builds `img_net(pretrained=True)` (net.py:43), which downloads ImageNet weights; the
+            # weights that matter come from the DAGR checkpoint (`backbone.net.module.*`), so default to no download
+            module = ctor(weights="DEFAULT") if getattr(args, "img_net_pretrained", False) else ctor(weights=None)
+            self.out_channels_cnn = [256, 256]
+            self.net = HookModule(module, input_channels=3, height=height, width=width,
+                                  feature_layers=["conv1", "layer1", "layer2", "layer3", "layer4"],
+                                  output_layers=["layer3", "layer4"], feature_channels=channels[1:],
+                                  output_channels=self.out_channels_cnn)
+        self.use_image = args.use_image
+        self.num_scales = args.num_scales
+        self.num_classes = dict(dsec=2).get(args.dataset, 2)
+        self.events_to_graph = EV_TGN(args)
+
+        output_channels = channels[1:]
+        self.out_channels = output_channels[-2:]
+        input_channels = channels[:-1]
+        if self.use_image:
+            input_channels = [input_channels[i] + self.net.feature_channels[i] for i in range(len(input_channels))]
+
+        poolings = compute_pooling_at_each_layer(args.pooling_dim_at_output, num_layers=4)
+        max_vals_for_cartesian = 2 * poolings[:, :2].max(-1).values
+        self.strides = torch.ceil(poolings[-2:, 1] * height).numpy().astype("int32").tolist()
+
+        effective_radius = 2 * float(int(args.radius * width + 2) / width)
+        self.edge_attrs = Cartesian(norm=True, cat=False, max_value=effective_radius)
+        self.conv_block1 = Layer(2 + input_channels[0], output_channels[0], args=args)
+
+        kw = dict(width=width, height=height, batch_size=args.batch_size,
+                  keep_temporal_ordering=args.keep_temporal_ordering)
+        cart1 = CartesianTransform(norm=True, cat=False, max_value=2 * effective_radius)
+        self.pool1 = Pooling(poolings[0], transform=cart1, aggr=args.pooling_aggr, **kw)
+        self.layer2 = Layer(input_channels[1] + 2, output_channels[1], args=args)
+        cart2 = CartesianTransform(norm=True, cat=False, max_value=max_vals_for_cartesian[1])
+        self.pool2 = Pooling(poolings[1], transform=cart2, aggr=args.pooling_aggr, **kw)
+        self.layer3 = Layer(input_channels[2] + 2, output_channels[2], args=args)
+        cart3 = CartesianTransform(norm=True, cat=False, max_value=max_vals_for_cartesian[2])
+        self.pool3 = Pooling(poolings[2], transform=cart3, aggr=args.pooling_aggr, **kw)
+        self.layer4 = Layer(input_channels[3] + 2, output_channels[3], args=args)
+        cart4 = CartesianTransform(norm=True, cat=False, max_value=max_vals_for_cartesian[3])
+        self.pool4 = Pooling(poolings[3], transform=cart4, aggr='mean', **kw)
+        self.layer5 = Layer(input_channels[4] + 2, output_channels[4], args=args)
+        self.cache = []
+        self.fused = True
+        self.height, self.width = height, width
+
+    def get_output_sizes(self):
+        poolings = [self.pool3.voxel_size[:2], self.pool4.voxel_size[:2]]
+        return [(1 / p + 1e-3).cpu().int().numpy().tolist()[::-1] for p in poolings]
+
+    # ------------------------------------------------------------------------------------------------ reference
+    def forward(self, data, reset=True, image_feat=None):
+        image_outputs = None
+        if self.use_image and image_feat is None:
+            image_feat, image_outputs = self.net(data.image)
+        if hasattr(data, 'reset'):
+            reset = data.reset
+        if self.fused and not self.training and reset:
+            output = self.forward_fused(data, image_feat)
+        else:
+            output = self.forward_modules(data, image_feat, reset)
+        if self.use_image:
+            return output[-self.num_scales:], (image_outputs[-self.num_scales:] if image_outputs is not None else None)
+        return output[-self.num_scales:]
+
+    def forward_modules(self, data, image_feat, reset=True):
+        """Module-by-module composition, line by line net.py:113-197."""
+        data = self.events_to_graph(data, reset=reset)
+        if self.use_image:
+            data.x = sampling_skip(data, image_feat[0].detach())
+            data.skipped = True
+            data.num_image_channels = image_feat[0].shape[1]
+        data = self.edge_attrs(data)
+        data.edge_attr = torch.clamp(data.edge_attr, min=0, max=1)
+        data.x = torch.cat((data.x, data.pos[:, :2]), dim=1)
+        data = self.conv_block1(data)
+        pools = [self.pool1, self.pool2, self.pool3, self.pool4]
+        layers = [self.layer2, self.layer3, self.layer4, self.layer5]
+        out3 = None
+        for k in range(4):
+            if self.use_image:
+                data.x = sampling_skip(data, image_feat[k + 1].detach())
+            data = pools[k](data)
+            if self.use_image:
+                data.skipped = True
+                data.num_image_channels = image_feat[k + 1].shape[1]
+            data.x = torch.cat((data.x, data.pos[:, :2]), dim=1)
+            data = layers[k](data)
+            if k == 2:
+                out3 = shallow_copy(data)
+                out3.pooling = self.pool3.voxel_size[:3]
+        out4 = data
+        out4.pooling = self.pool4.voxel_size[:3]
+        return [out3, out4]
+
+    # ------------------------------------------------------------------------------------------------ fused
+    def enqueue_fused(self, x, pos, batch_i32, num_graphs, feats_nhwc, width, height, time_window):
+        """Enqueues the whole event branch; returns device tensors sized by host-known upper bounds plus `counts`
+        (int32[12]: n1,E1,n2,E2,n3,E3,n4,E4) and `status`.  No host synchronisation; capturable in a CUDA graph."""
+        dev = pos.device
+        n = pos.shape[0]
+        g = self.events_to_graph
+        if g.graph_creators is None:
+            g.init_graph_creator(Data(pos=pos, width=[width], height=[height], time_window=[time_window],
+                                      _num_graphs=num_graphs))
+        gc = g.graph_creators
+        gc.batch_size = max(gc.batch_size, num_graphs)
+        gc.reset()
+        denorm = torch.tensor([int(width), int(height), int(time_window)], device=dev)
+        pos_int = (denorm.view(1, -1) * pos + 1e-3).int()
+        graph = gc.build_csr(batch_i32, pos_int)
+        status = gc._status
+        rowptr, src = graph["rowptr"], graph["src"]
+        f = feats_nhwc if self.use_image else [None] * 5
+        cin1 = self.conv_block1.in_channel
+        x0 = ops.sample_concat(x, pos, batch_i32, f[0], width, height, append_pos=True, ldo=(cin1 + 3) // 4 * 4)
+        pseudo = dict(pos=pos, two_m=two_m_of(self.edge_attrs.max), clamp01=True)
+        xk = self.conv_block1.run_fused(x0, rowptr, src, n, None, pseudo, status)
+        counts = torch.zeros(12, dtype=torch.int32, device=dev)
+        pools = [self.pool1, self.pool2, self.pool3, self.pool4]
+        layers = [self.layer2, self.layer3, self.layer4, self.layer5]
+        cur = dict(x=xk, pos=pos, batch=batch_i32, rowptr=rowptr, src=src, n_cap=n, n_dev=None, e_cap=src.shape[0])
+        outs = []
+        for k in range(4):
+            p = pools[k]
+            key_bound = p._nv[0] * p._nv[1] * p._nv[2] * (num_graphs + 1)
+            c_cap = max(1, min(cur["n_cap"], key_bound))
+            e_cap = max(1, min(cur["e_cap"], c_cap * 64))
+            r = ops.voxel_pool(cur["x"], cur["pos"], cur["batch"], cur["rowptr"], cur["src"], cur["n_cap"], cur["n_dev"],
+                               p._vs, p._nv, num_graphs, p._inv_wh, p.aggr, width, height, f[k + 1], append_pos=True,
+                               c_cap=c_cap, e_cap=e_cap, status=status)
+            counts[2 * k:2 * k + 1].copy_(r["n_out"])
+            counts[2 * k + 1:2 * k + 2].copy_(r["num_edges"])
+            pseudo = dict(pos=r["pos"], two_m=two_m_of(p.transform.max), clamp01=False)
+            xo = layers[k].run_fused(r["x"], r["rowptr"], r["src"], c_cap, r["n_out"], pseudo, status)
+            cur = dict(x=xo, pos=r["pos"], batch=r["batch"], rowptr=r["rowptr"], src=r["src"], n_cap=c_cap,
+                       n_dev=r["n_out"], e_cap=e_cap)
+            if k >= 2:
+                outs.append(dict(x=xo, pos=r["pos"], batch=r["batch"], rowptr=r["rowptr"], src=r["src"],
+                                 num_edges=r["num_edges"], two_m=two_m_of(p.transform.max), k=k))
+        return dict(outs=outs, counts=counts, status=status)
+
+    def finalize_fused(self, res):
+        """One device->host read (counts + status), then tight views."""
+        c = torch.cat([res["counts"], res["status"].view(-1)]).cpu().tolist()
+        if c[12]:
+            _lib.check_status(res["status"], "fused DAGR forward")
+        datas = []
+        pool_sizes = [self.pool3.voxel_size[:3], self.pool4.voxel_size[:3]]
+        for o, ps in zip(res["outs"], pool_sizes):
+            k = o["k"]
+            nk, ek = c[2 * k], c[2 * k + 1]
+            d = GraphOut(x=o["x"][:nk], pos=o["pos"][:nk], batch=o["batch"][:nk].long())
+            d._lazy = dict(rowptr=o["rowptr"][:nk + 1], src=o["src"], num_edges=o["num_edges"], e=ek, two_m=o["two_m"])
+            d.pooling = ps
+            d.skipped = True
+            datas.append(d)
+        return datas
+
+    def forward_fused(self, data, image_feat):
+        n = data.pos.shape[0]
+        dev = data.pos.device
+        if data.batch is None:
+            data.batch = torch.zeros(n, dtype=torch.long, device=dev)
+        num_graphs = data.num_graphs
+        feats = [ops.to_channel_last(fm.detach().float()) for fm in image_feat] if self.use_image else None
+        res = self.enqueue_fused(data.x.float().contiguous(), data.pos.float().contiguous(), data.batch.int(), num_graphs,
+                                 feats, int(data.width[0]), int(data.height[0]), int(data.time_window[0]))
+        outs = self.finalize_fused(res)
+        for o in outs:
+            o.width, o.height = data.width, data.height
+        return outs

@@ -1,0 +1,258 @@
+"""Tensor-level wrappers of the C ABI (include/eventad_b200.h).  Every function only enqueues kernels on the current
+torch CUDA stream; sizes that depend on the data stay on the device (int32 cells) unless a caller asks for a tight
+tensor.  No function here has a CPU or PyTorch fallback."""
+import ctypes
+import math
+
+import torch
+
+from . import _lib
+from ._lib import EpilogueT, PoolParamsT, PseudoT, SplineModeT, check, ptr, ptr_rows, stream
+
+_WS = {}
+
+
+def _ws(nbytes, device):
+    key = (torch.device(device).index, torch.cuda.current_stream().cuda_stream)
+    w = _WS.get(key)
+    if w is None:
+        w = _WS[key] = _lib.Workspace()
+    return w.get(nbytes, device)
+
+
+def new_status(device):
+    return torch.zeros(1, dtype=torch.int32, device=device)
+
+
+# --------------------------------------------------------------------------------------------------- graph formats
+def coo_to_csr(edge_index: torch.Tensor, n_nodes: int, status=None):
+    """edge_index int64 [2,E] (any order) -> (rowptr int32[n+1], src int32[E], eid int32[E]) dst-major, stable."""
+    L = _lib.lib()
+    dev = edge_index.device
+    e = edge_index.shape[1]
+    ei = edge_index.contiguous()
+    if ei.dtype != torch.int64:
+        ei = ei.long()
+    rowptr = torch.empty(n_nodes + 1, dtype=torch.int32, device=dev)
+    src = torch.empty(max(e, 1), dtype=torch.int32, device=dev)
+    eid = torch.empty(max(e, 1), dtype=torch.int32, device=dev)
+    status = status if status is not None else new_status(dev)
+    ws = _ws(L.evad_coo_to_csr_ws_bytes(e), dev)
+    check(L.evad_coo_to_csr(ptr(ei) if e > 0 else None, ei.stride(0) if e > 0 else 0, e, n_nodes, ptr(rowptr), ptr(src),
+                            ptr(eid), ptr(status), ptr(ws), ws.numel(), stream()), "evad_coo_to_csr")
+    return rowptr, src[:e], eid[:e]
+
+
+def csr_to_coo(rowptr, src, n_cap, n_dev, e_cap, num_edges, src_major: bool, want_slots=False):
+    """-> edge_index int64 [2, e_cap] (first num_edges columns valid) and optionally slot_of int32[e_cap]."""
+    L = _lib.lib()
+    dev = rowptr.device
+    ei = torch.empty((2, max(e_cap, 1)), dtype=torch.int64, device=dev)
+    slot_of = torch.empty(max(e_cap, 1), dtype=torch.int32, device=dev) if want_slots else None
+    ws = _ws(L.evad_csr_to_coo_ws_bytes(e_cap), dev)
+    check(L.evad_csr_to_coo(ptr(rowptr), ptr(src), n_cap, ptr(n_dev), e_cap, ptr(num_edges), int(src_major), ptr(ei),
+                            ei.stride(0), ptr(slot_of), ptr(ws), ws.numel(), stream()), "evad_csr_to_coo")
+    return (ei, slot_of) if want_slots else ei
+
+
+def cartesian(pos, edge_index, two_m: float, clamp01: bool, num_edges=None, dims=None):
+    """PyG T.Cartesian(norm=True, cat=False, max_value=two_m/2) (+clamp): [E, dims] float32."""
+    L = _lib.lib()
+    e_cap = edge_index.shape[1]
+    dims = dims or pos.shape[1]
+    out = torch.empty((e_cap, dims), dtype=torch.float32, device=pos.device)
+    if e_cap == 0:
+        return out
+    pos = pos.contiguous()
+    check(L.evad_cartesian(ptr(pos), pos.stride(0), dims, ptr_rows(edge_index), edge_index.stride(0), e_cap, ptr(num_edges),
+                           float(two_m), int(clamp01), ptr(out), stream()), "evad_cartesian")
+    return out
+
+
+def to_channel_last(feat: torch.Tensor) -> torch.Tensor:
+    """[B,C,h,w] -> contiguous [B,h,w,C] (the layout the sampling kernels read)."""
+    return feat.permute(0, 2, 3, 1).contiguous()
+
+
+def sample_concat(x, pos, batch_i32, feat_nhwc, width, height, append_pos=False, ldo=None, n_dev=None):
+    """[x | grid_sample(feat) | pos_xy | 0-pad] -> [n, ldo] (net.py sampling_skip + cat(x, pos[:, :2]))."""
+    L = _lib.lib()
+    n = pos.shape[0]
+    cx = 0 if x is None else x.shape[1]
+    cs = 0 if feat_nhwc is None else feat_nhwc.shape[3]
+    width_total = cx + cs + (2 if append_pos else 0)
+    ldo = ldo or width_total
+    out = torch.empty((n, ldo), dtype=torch.float32, device=pos.device)
+    if n == 0:
+        return out
+    if x is not None:
+        x = x.contiguous()
+    pos = pos.contiguous()
+    fb, fh, fw, fc = (feat_nhwc.shape if feat_nhwc is not None else (0, 0, 0, 0))
+    check(L.evad_sample_concat(ptr(x), x.stride(0) if x is not None else 0, cx, ptr(pos), pos.stride(0), ptr(batch_i32), n,
+                               ptr(n_dev), ptr(feat_nhwc), fb, fh, fw, fc, float(width), float(height), int(append_pos),
+                               ptr(out), ldo, stream()), "evad_sample_concat")
+    return out
+
+
+# --------------------------------------------------------------------------------------------------- spline tables
+def spline_mode_basis(kernel_size: int):
+    return dict(use_lut=0, ks=int(kernel_size), nx=0, ny=0, r=(0.0, 0.0, 0.0, 0.0), tab_k=None, tab_w=None)
+
+
+def _table_1d(r, M, extent, ks):
+    """Per-lattice-coordinate taps of init_lut (/root/reference/src/dagr/model/layers/spline_conv.py:26-33) for one
+    dimension: a = d / (2*M*extent) + 0.5 on d = -r..r, then the degree-1 open-spline basis of torch_spline_conv."""
+    d = torch.arange(-r, r + 1).float()
+    a = d / (2 * M * extent) + 0.5
+    v = a * float(ks - 1)
+    vi = v.to(torch.long)
+    k0 = torch.fmod(vi + 0, ks)
+    k1 = torch.fmod(vi + 1, ks)
+    f = v - torch.floor(v)
+    w0 = 1 - f - 0 + 2 * f * 0
+    w1 = 1 - f - 1 + 2 * f * 1
+    return torch.stack([k0, k1], 1).int(), torch.stack([w0, w1], 1).float()
+
+
+def spline_mode_lut(height, width, rx, Mx, ry=None, My=None, kernel_size=5, device="cuda"):
+    """message_lut parameters: attr_remapping_matrix (spline_conv.py:21-24) + per-dimension tap tables."""
+    ry = ry or rx
+    My = My or Mx
+    R = torch.Tensor([[2 * Mx * width, 0, -Mx * width + rx], [0, 2 * My * height, -My * height + ry]])
+    kx, wx = _table_1d(rx, Mx, width, kernel_size)
+    ky, wy = _table_1d(ry, My, height, kernel_size)
+    return dict(use_lut=1, ks=int(kernel_size), nx=2 * rx + 1, ny=2 * ry + 1,
+                r=(float(R[0, 0]), float(R[0, 2]), float(R[1, 1]), float(R[1, 2])),
+                tab_k=torch.cat([kx, ky], 0).contiguous().to(device), tab_w=torch.cat([wx, wy], 0).contiguous().to(device),
+                R=R)
+
+
+def _mode_struct(mode):
+    return SplineModeT(use_lut=mode["use_lut"], r00=mode["r"][0], r02=mode["r"][1], r11=mode["r"][2], r12=mode["r"][3],
+                       nx=mode["nx"], ny=mode["ny"], tab_k=ptr(mode["tab_k"]), tab_w=ptr(mode["tab_w"]), ks=mode["ks"])
+
+
+def _pseudo_struct(edge_attr=None, eid=None, pos=None, two_m=1.0, clamp01=False):
+    return PseudoT(edge_attr=ptr(edge_attr), eid=ptr(eid), ld_attr=edge_attr.stride(0) if edge_attr is not None else 0,
+                   pos=ptr(pos), ld_pos=pos.stride(0) if pos is not None else 0, two_m=float(two_m), clamp01=int(clamp01))
+
+
+def _epi_struct(scale=None, shift=None, addend=None, relu=False):
+    return EpilogueT(scale=ptr(scale), shift=ptr(shift), addend=ptr(addend),
+                     ld_add=addend.stride(0) if addend is not None else 0, relu=int(relu))
+
+
+def fold_bn(bn: torch.nn.BatchNorm1d):
+    """eval BatchNorm as y = x*scale + shift."""
+    scale = bn.weight / torch.sqrt(bn.running_var + bn.eps)
+    shift = bn.bias - bn.running_mean * scale
+    return scale.detach().float().contiguous(), shift.detach().float().contiguous()
+
+
+# --------------------------------------------------------------------------------------------------- SplineConv
+def build_lut(weight, root_w, skip_w, cin_pad, mode):
+    L = _lib.lib()
+    k, cin, cout = weight.shape
+    n = mode["nx"] * mode["ny"] + 2
+    lut = torch.empty((n, cin_pad, cout), dtype=torch.float32, device=weight.device)
+    m = _mode_struct(mode)
+    check(L.evad_spline_lut_build(ptr(weight.detach().contiguous()), ptr(root_w.detach().contiguous()),
+                                  ptr(skip_w.detach().contiguous()) if skip_w is not None else None, cin, cin_pad, cout,
+                                  ctypes.byref(m), ptr(lut), stream()), "evad_spline_lut_build")
+    return lut
+
+
+def spline_conv_small(rowptr, src, n, x, cin, lut, mode, pseudo, epi, status, skip_epi=None, out=None, skip_out=None):
+    """Fused LUT conv, cout = 16.  x: [n, ldx] with ldx % 4 == 0, zero padded beyond cin.  Returns (out, skip_out)."""
+    L = _lib.lib()
+    cin_pad = lut.shape[1]
+    cout = lut.shape[2]
+    if out is None:
+        out = torch.empty((n, cout), dtype=torch.float32, device=x.device)
+    if skip_epi is not None and skip_out is None:
+        skip_out = torch.empty((n, cout), dtype=torch.float32, device=x.device)
+    m = _mode_struct(mode)
+    p = _pseudo_struct(**pseudo)
+    e = _epi_struct(**epi)
+    se = _epi_struct(**skip_epi) if skip_epi is not None else None
+    check(L.evad_spline_conv_small(ptr(rowptr), ptr(src), n, ptr(x), x.stride(0), cin, cin_pad, cout, ctypes.byref(p),
+                                   ctypes.byref(m), ptr(lut), ctypes.byref(e), ptr(out), out.stride(0),
+                                   ctypes.byref(se) if se is not None else None, ptr(skip_out),
+                                   skip_out.stride(0) if skip_out is not None else 0, ptr(status), stream()),
+          "evad_spline_conv_small")
+    return out, skip_out
+
+
+def spline_aggregate(rowptr, src, n_cap, n_dev, x, cin, mode, pseudo, status):
+    """A[i] = [per-tap aggregated sources (ks*ks*cin) | x_i (cin)]."""
+    L = _lib.lib()
+    lda = (mode["ks"] ** 2 + 1) * cin
+    A = torch.empty((max(n_cap, 1), lda), dtype=torch.float32, device=x.device)
+    m = _mode_struct(mode)
+    p = _pseudo_struct(**pseudo)
+    check(L.evad_spline_aggregate(ptr(rowptr), ptr(src), n_cap, ptr(n_dev), ptr(x), x.stride(0), cin, ctypes.byref(p),
+                                  ctypes.byref(m), ptr(A), lda, ptr(status), stream()), "evad_spline_aggregate")
+    return A
+
+
+def gemm_epilogue(A, W, m_cap, m_dev, epi, out=None, k=None):
+    """out = epi(A[:, :k] @ W) ; W [k, n] row-major."""
+    L = _lib.lib()
+    k = k or W.shape[0]
+    n = W.shape[1]
+    if out is None:
+        out = torch.empty((max(m_cap, 1), n), dtype=torch.float32, device=A.device)
+    e = _epi_struct(**epi)
+    check(L.evad_gemm_epilogue(ptr(A), A.stride(0), ptr(W), m_cap, ptr(m_dev), k, n, ctypes.byref(e), ptr(out),
+                               out.stride(0), stream()), "evad_gemm_epilogue")
+    return out
+
+
+# --------------------------------------------------------------------------------------------------- pooling
+def pool_geometry(voxel_size4: torch.Tensor, end4: torch.Tensor):
+    """num_voxels per dimension exactly as torch_cluster computes them: ((end - start) / size).long() + 1, start = 0."""
+    nv = ((end4.cpu() - 0) / voxel_size4.cpu()).to(torch.long) + 1
+    return [int(v) for v in nv[:3]]
+
+
+def voxel_pool(x, pos, batch_i32, rowptr, src, n_cap, n_dev, voxel_size, nv, batch_size, inv_wh, aggr, width, height,
+               feat_nhwc=None, append_pos=False, ldo=None, c_cap=None, e_cap=None, status=None):
+    """Returns dict(cluster, n_out, x, pos, batch, rowptr, src, num_edges); all arrays sized by c_cap / e_cap."""
+    L = _lib.lib()
+    dev = pos.device
+    cx = x.shape[1]
+    cs = 0 if feat_nhwc is None else feat_nhwc.shape[3]
+    ctot = cx + cs + (2 if append_pos else 0)
+    ldo = ldo or ctot
+    key_bound = nv[0] * nv[1] * nv[2] * (batch_size + 1)
+    c_cap = int(c_cap if c_cap is not None else max(1, min(n_cap, key_bound)))
+    want_edges = rowptr is not None
+    if e_cap is None:
+        e_cap = int(src.shape[0]) if want_edges else 0
+    e_cap = max(int(e_cap), 1)
+    status = status if status is not None else new_status(dev)
+    cluster = torch.empty(max(n_cap, 1), dtype=torch.int32, device=dev)
+    n_out = torch.zeros(1, dtype=torch.int32, device=dev)
+    x_out = torch.empty((c_cap, ldo), dtype=torch.float32, device=dev)
+    if ldo > ctot:
+        x_out[:, ctot:].zero_()
+    pos_out = torch.empty((c_cap, 3), dtype=torch.float32, device=dev)
+    batch_out = torch.empty(c_cap, dtype=torch.int32, device=dev)
+    rowptr_out = torch.zeros(c_cap + 1, dtype=torch.int32, device=dev) if want_edges else None
+    src_out = torch.empty(e_cap, dtype=torch.int32, device=dev) if want_edges else None
+    num_edges = torch.zeros(1, dtype=torch.int32, device=dev) if want_edges else None
+    fb, fh, fw, fc = (feat_nhwc.shape if feat_nhwc is not None else (0, 0, 0, 0))
+    P = PoolParamsT(size_x=float(voxel_size[0]), size_y=float(voxel_size[1]), size_t=float(voxel_size[2]), nvx=nv[0],
+                    nvy=nv[1], nvt=nv[2], batch_size=int(batch_size), inv_w=float(inv_wh[0]), inv_h=float(inv_wh[1]),
+                    aggr_mean=int(aggr == "mean"), append_pos=int(append_pos), feat=ptr(feat_nhwc), feat_b=fb, feat_h=fh,
+                    feat_w=fw, feat_c=fc, width=float(width), height=float(height))
+    ws = _ws(L.evad_voxel_pool_ws_bytes(n_cap, c_cap), dev)
+    x = x.contiguous()
+    pos = pos.contiguous()
+    check(L.evad_voxel_pool(ctypes.byref(P), n_cap, ptr(n_dev), ptr(pos), pos.stride(0), ptr(batch_i32), ptr(x),
+                            x.stride(0), cx, ptr(rowptr), ptr(src), c_cap, e_cap, ptr(cluster), ptr(n_out), ptr(x_out), ldo,
+                            ptr(pos_out), ptr(batch_out), ptr(rowptr_out), ptr(src_out), ptr(num_edges), ptr(status),
+                            ptr(ws), ws.numel(), stream()), "evad_voxel_pool")
+    return dict(cluster=cluster, n_out=n_out, x=x_out, pos=pos_out, batch=batch_out, rowptr=rowptr_out, src=src_out,
+                num_edges=num_edges, c_cap=c_cap, e_cap=e_cap, status=status)

@@ -1,0 +1,154 @@
+"""Layer-level parity of the sm_100a kernels with the torch-CPU oracle (oracle/dagr_layers.py, oracle/dagr_ops.py),
+through the reference-shaped modules.  Integer results (cluster ids, coarse edges, batch) are compared bit-exactly;
+fp32 features within rtol 1e-4 / atol 1e-5 (BASELINE.json north_star)."""
+import numpy as np
+import pytest
+import torch
+
+from tests.util import assert_close, make_backbone, make_data, net_state_dict
+
+pytestmark = pytest.mark.gpu
+
+
+def _graph(data_cpu, args, width=320, height=240):
+    from oracle.dagr_net import events_to_graph
+    return events_to_graph(data_cpu.pos, data_cpu.batch, data_cpu.num_graphs, args.radius, args.max_neighbors, width,
+                           height, 1000000)
+
+
+def test_cartesian_bit_exact():
+    from eventad_b200 import ops
+    from oracle import dagr_ops
+    model, args = make_backbone(use_image=False)
+    d = make_data(20_000, 2, seed=1)
+    ei = _graph(d, args)
+    for m, clamp in ((0.03125, True), (0.0625, False), (torch.tensor(0.1) * 2, False)):
+        ref = dagr_ops.cartesian(d.pos, ei, m)
+        if clamp:
+            ref = torch.clamp(ref, 0, 1)
+        from eventad_b200.model.layers.components import two_m_of
+        got = ops.cartesian(d.pos.cuda(), ei.cuda(), two_m_of(m), clamp)
+        assert torch.equal(got.cpu(), ref)
+
+
+@pytest.mark.parametrize("B", [1, 3])
+def test_sample_features(B):
+    from eventad_b200 import ops, synthetic
+    from oracle import dagr_layers
+    d = make_data(5000, B, seed=2)
+    feats = synthetic.make_image_features(B, seed=3)
+    for f in (feats[0], feats[1], feats[4]):
+        ref = dagr_layers.sample_features(d.pos, d.batch, f, 320, 240)
+        got = ops.sample_concat(None, d.pos.cuda(), d.batch.int().cuda(), ops.to_channel_last(f.cuda()), 320, 240)
+        assert_close(got, ref, rtol=1e-5, atol=1e-6, what="sample_features")
+
+
+def _conv_case(cin, cout, mode, n=3000, seed=0):
+    """One MySplineConv on a real event graph; mode in {'lut', 'basis'}."""
+    from types import SimpleNamespace
+    from eventad_b200.data import Data
+    from eventad_b200.model.layers.spline_conv import MySplineConv
+    from oracle import dagr_layers, dagr_ops
+    model, args = make_backbone(use_image=False)
+    d = make_data(n, 1, seed=seed, dist="C")
+    ei = _graph(d, args)
+    torch.manual_seed(seed)
+    conv = MySplineConv(cin, cout, args, bias=(seed % 2 == 1))
+    if conv.bias is not None:
+        conv.bias.data.uniform_(-0.5, 0.5)
+    x = torch.randn(n, cin)
+    attr = torch.clamp(dagr_ops.cartesian(d.pos, ei, 0.03125), 0, 1)
+    lut = dagr_layers.lut_params_layer1(args.radius, 320) if mode == "lut" else None
+    sd = {"c." + k: v.detach() for k, v in conv.state_dict().items()}
+    ref = dagr_layers.spline_conv(x, ei, attr, sd, "c.", lut, 240, 320)
+    conv = conv.cuda()
+    if mode == "lut":
+        conv.init_lut(height=240, width=320, **{k: lut[k] for k in ("rx", "Mx")})
+    data = Data(x=x.cuda(), edge_index=ei.cuda(), edge_attr=attr.cuda(), pos=d.pos.cuda())
+    out = conv(data).x
+    assert_close(out, ref, what=f"MySplineConv {cin}->{cout} {mode}")
+
+
+@pytest.mark.parametrize("cin,cout,mode", [(19, 16, "lut"), (16, 16, "lut"), (19, 16, "basis"), (82, 64, "lut"),
+                                           (64, 64, "basis"), (130, 64, "lut"), (5, 16, "lut"), (7, 3, "basis")])
+def test_spline_conv(cin, cout, mode):
+    _conv_case(cin, cout, mode, seed=cin % 2)
+
+
+def test_spline_conv_shuffled_edges_and_empty():
+    """edge_index in arbitrary order (the CSR builder must keep per-destination order) and a graph without edges."""
+    from eventad_b200.data import Data
+    from eventad_b200.model.layers.spline_conv import MySplineConv
+    from oracle import dagr_layers, dagr_ops
+    model, args = make_backbone(use_image=False)
+    d = make_data(2000, 1, seed=4)
+    ei = _graph(d, args)
+    perm = torch.randperm(ei.shape[1], generator=torch.Generator().manual_seed(0))
+    ei = ei[:, perm]
+    attr = dagr_ops.cartesian(d.pos, ei, 0.03125)
+    torch.manual_seed(0)
+    conv = MySplineConv(12, 64, args)
+    x = torch.randn(2000, 12)
+    sd = {"c." + k: v.detach() for k, v in conv.state_dict().items()}
+    ref = dagr_layers.spline_conv(x, ei, attr, sd, "c.", None)
+    out = conv.cuda()(Data(x=x.cuda(), edge_index=ei.cuda(), edge_attr=attr.cuda())).x
+    assert_close(out, ref, what="shuffled edges")
+    empty = torch.zeros((2, 0), dtype=torch.long)
+    ref0 = dagr_layers.spline_conv(x, empty, torch.zeros((0, 3)), sd, "c.", None)
+    out0 = conv(Data(x=x.cuda(), edge_index=empty.cuda(), edge_attr=torch.zeros((0, 3)).cuda())).x
+    assert_close(out0, ref0, what="no edges")
+
+
+@pytest.mark.parametrize("which", ["conv_block1", "layer2"])
+def test_layer_fused(which):
+    from eventad_b200.data import Data
+    from oracle import dagr_layers, dagr_ops
+    model, args = make_backbone(use_image=False, seed=1)
+    model.cache_luts(320, 240, args.radius)
+    sd = net_state_dict(model)
+    d = make_data(4000, 1, seed=5, dist="C")
+    ei = _graph(d, args)
+    layer = getattr(model.backbone, which)
+    cin = layer.in_channel
+    x = torch.randn(4000, cin, generator=torch.Generator().manual_seed(1))
+    if which == "conv_block1":
+        attr = torch.clamp(dagr_ops.cartesian(d.pos, ei, 0.03125), 0, 1)
+        lut = dagr_layers.lut_params_layer1(args.radius, 320)
+    else:   # layer-2 LUT geometry on the fine graph: offsets stay inside the 25x25 table
+        attr = dagr_ops.cartesian(d.pos, ei, 0.0625)
+        p = model.backbone.pool1
+        lut = dagr_layers.lut_params_from_pool(p.voxel_size.cpu(), p.transform.max, 240, 320)
+    ref = dagr_layers.layer(x, ei, attr, sd, which + ".", lut, 240, 320)
+    layer = layer.cuda()
+    out = layer(Data(x=x.cuda(), edge_index=ei.cuda(), edge_attr=attr.cuda(), pos=d.pos.cuda())).x
+    assert_close(out, ref, what=which)
+
+
+@pytest.mark.parametrize("B,n,level,aggr", [(1, 20_000, 0, "max"), (3, 9_000, 0, "max"), (1, 50_000, 1, "max"),
+                                            (2, 6_000, 3, "mean"), (1, 300, 2, "max")])
+def test_pooling(B, n, level, aggr):
+    """Pooling.forward vs the oracle: cluster ids, coarse edge_index, batch bit-exact; pos bit-exact; x max exact."""
+    from eventad_b200.data import Batch
+    from oracle import dagr_layers
+    from oracle.dagr_net import compute_pooling_at_each_layer
+    model, args = make_backbone(use_image=False)
+    d = make_data(n, B, seed=6, dist="C")          # the last event of every sample has t == 1.0 (cluster quirk)
+    ei = _graph(d, args)
+    pool = [model.backbone.pool1, model.backbone.pool2, model.backbone.pool3, model.backbone.pool4][level]
+    assert pool.aggr == aggr
+    n = d.pos.shape[0]                              # make_data takes events PER window
+    x = torch.randn(n, 24, generator=torch.Generator().manual_seed(2))
+    voxel3 = compute_pooling_at_each_layer(args.pooling_dim_at_output, 4)[level]
+    ref = dagr_layers.pooling(x, d.pos, d.batch, ei, voxel3, 320, 240, args.batch_size, pool.transform.max, aggr)
+    data = Batch(x=x.cuda(), pos=d.pos.cuda(), batch=d.batch.cuda(), edge_index=ei.cuda())
+    data.width, data.height = d.width, d.height
+    out = pool.cuda()(data)
+    assert torch.equal(out.cluster.cpu(), ref.cluster)
+    assert torch.equal(out.edge_index.cpu(), ref.edge_index)
+    assert torch.equal(out.batch.cpu(), ref.batch)
+    assert torch.equal(out.pos.cpu(), ref.pos)
+    if aggr == "max":
+        assert torch.equal(out.x.cpu(), ref.x)
+    else:
+        assert_close(out.x, ref.x, what="mean pool")
+    assert torch.equal(out.edge_attr.cpu(), ref.edge_attr)

@@ -1,0 +1,69 @@
+"""End-to-end parity of the event branch (`Net.forward`, fused and module-by-module) with the torch-CPU oracle
+(oracle/dagr_net.py) on seeded synthetic ROL-shaped windows.  Graph structure bit-exact, features within
+rtol 1e-4 / atol 1e-5."""
+import pytest
+import torch
+
+from eventad_b200 import synthetic
+from tests.util import assert_close, make_backbone, make_data, net_state_dict
+
+pytestmark = pytest.mark.gpu
+
+
+def _compare(outs, ref, what):
+    assert len(outs) == len(ref) == 2
+    for o, r, name in zip(outs, ref, ("out3", "out4")):
+        assert o.x.shape == r.x.shape, (what, name, o.x.shape, r.x.shape)
+        assert torch.equal(o.batch.cpu(), r.batch), (what, name)
+        assert torch.equal(o.edge_index.cpu(), r.edge_index), (what, name)
+        assert torch.equal(o.pos[:, :2].cpu(), r.pos[:, :2]), (what, name)
+        assert_close(o.pos, r.pos, rtol=1e-6, atol=1e-7, what=f"{what} {name} pos")
+        assert_close(o.edge_attr, r.edge_attr, rtol=1e-6, atol=1e-6, what=f"{what} {name} edge_attr")
+        assert_close(o.x, r.x, what=f"{what} {name} x")
+
+
+@pytest.mark.parametrize("n,B,dist,use_image", [(20_000, 1, "U", True), (30_000, 1, "C", True), (12_000, 3, "C", True),
+                                                (20_000, 2, "U", False), (50_000, 1, "C", True)])
+def test_net_forward_matches_oracle(n, B, dist, use_image):
+    from oracle.dagr_net import net_forward
+    model, args = make_backbone(seed=n % 5, use_image=use_image)
+    model.cache_luts(320, 240, args.radius)
+    sd = net_state_dict(model)
+    d = make_data(n, B, seed=7, dist=dist)
+    feats = synthetic.make_image_features(B, seed=1) if use_image else None
+    ref = net_forward(sd, args, d.x, d.pos, d.batch, B, feats, 320, 240)
+    model = model.cuda()
+    net = model.backbone
+    for fused in (True, False):
+        net.fused = fused
+        dg = make_data(n, B, seed=7, dist=dist, device="cuda")
+        with torch.no_grad():
+            res = net(dg, image_feat=[f.cuda() for f in feats] if use_image else None)
+        outs = res[0] if use_image else res
+        _compare(outs, ref, f"fused={fused}")
+
+
+def test_basis_mode_matches_oracle():
+    """Without cache_luts the PyG basis message is used (DAGR training configuration)."""
+    from oracle.dagr_net import net_forward
+    model, args = make_backbone(seed=3, use_image=False)
+    sd = net_state_dict(model)
+    d = make_data(15_000, 1, seed=8, dist="C")
+    ref = net_forward(sd, args, d.x, d.pos, d.batch, 1, None, 320, 240, use_lut=False)
+    net = model.cuda().backbone
+    with torch.no_grad():
+        outs = net(make_data(15_000, 1, seed=8, dist="C", device="cuda"))
+    _compare(outs, ref, "basis")
+
+
+def test_extract_features_api():
+    model, args = make_backbone(seed=0, use_image=True)
+    model.cache_luts(320, 240, args.radius)
+    model = model.cuda()
+    d = make_data(10_000, 2, seed=9, device="cuda")
+    d.image = torch.rand((2, 3, 240, 320), device="cuda")
+    feats = model.extract_features(d)
+    out3, out4 = feats
+    assert out4.x.shape[1] == 64 and out3.x.shape[1] == 64
+    assert out4.x.shape[0] <= 36 * 2 and out4.pos.shape == (out4.x.shape[0], 3)
+    assert torch.isfinite(out4.x).all()
