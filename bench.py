@@ -1,0 +1,294 @@
+#!/usr/bin/env python
+"""bench.py -- GNN-branch throughput of EventAD's DAGR event branch on B200 (contract: see the task statement).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            our sm_100a path
+  python bench.py --impl reference [--steps K] [--warmup W]      the CPU restatement of the reference path (oracle/)
+
+A "step" is one pass of the hot path (event-graph build -> 5 SplineConv layers -> 4 voxel poolings, CNN-feature
+sampling fused) over one batch of `--windows` synthetic ROL-shaped 50 ms windows of `--events` events each
+(320x240, T = 1e6 us).  Metric: GNN-branch Mevents/s, whole job (all ranks).  One JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "GNN-branch Mevents/s"
+UNIT = "Mevents/s"
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=20)
+    p.add_argument("--warmup", type=int, default=5)
+    p.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    p.add_argument("--events", type=int, default=100_000, help="events per 50 ms window")
+    p.add_argument("--windows", type=int, default=8, help="windows per step (batch)")
+    p.add_argument("--dist", default="U", choices=["U", "C"])
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--latency-iters", type=int, default=100)
+    return p.parse_args()
+
+
+def workload_config(a):
+    return {"workload": f"dagr-s GNN branch forward (EV_TGN graph r=4px dt=10ms K=16 Q=128 -> Layer(19,16) -> 4x "
+                        f"[sample CNN map + voxel pool + Layer(.,64)]), 320x240, {a.events} events/window, "
+                        f"{a.windows} windows/step, dist {a.dist}, use_image=True (CNN maps resident), LUT mode",
+            "events_per_window": a.events, "windows_per_step": a.windows, "distribution": a.dist,
+            "l2": "8 rotating input sets (>126 MB with intermediates; per-step traffic ~3 KB/event >> L2)",
+            "parallelism": "independent windows per rank, no data-path collective"}
+
+
+# ------------------------------------------------------------------------------------------------ clocks sampler
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower() == "active" for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU reference arm
+def cpu_reference_run(a, steps, warmup):
+    """Times the CPU restatement of the reference path (oracle/: C graph builder with OpenMP + torch-CPU layers with
+    all host threads) on one window of `a.events` events per step.  Returns (Mevents/s, ms/step, cores, sample)."""
+    from eventad_b200 import synthetic
+    from oracle.dagr_net import net_forward
+    from tests.util import make_backbone, make_data, net_state_dict
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    model, args = make_backbone(seed=0, use_image=True)
+    sd = net_state_dict(model)
+    feats = synthetic.make_image_features(1, seed=1)
+    times = []
+    for s in range(warmup + steps):
+        d = make_data(a.events, 1, seed=100 + s, dist=a.dist)
+        t0 = time.perf_counter()
+        net_forward(sd, args, d.x, d.pos, d.batch, 1, feats, 320, 240)
+        if s >= warmup:
+            times.append(time.perf_counter() - t0)
+    ms = 1e3 * float(np.mean(times))
+    sample = f"{steps} x 1 window of {a.events} events (dist {a.dist}), B=1, oracle/ C graph builder (OpenMP) + torch-CPU layers"
+    return a.events / (ms * 1e-3) / 1e6, ms, cores, sample
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps, warmup = max(1, min(a.steps, 5)), max(1, min(a.warmup, 1))
+    v, ms, cores, sample = cpu_reference_run(a, steps, warmup)
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": steps,
+            "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": workload_config(a),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "the reference has no CPU path for the graph builder and its PyG stack is not installable here; "
+                    "this is the CPU restatement in oracle/ (kind=port), timed with all host threads"}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def build_runner(dev):
+    from eventad_b200.engine import EventBranchRunner
+    from tests.util import make_backbone
+    model, args = make_backbone(seed=0, use_image=True)
+    model.cache_luts(320, 240, args.radius)
+    return EventBranchRunner(model, dev), args
+
+
+def run_b200(a):
+    import torch.distributed as dist
+    from eventad_b200 import _lib, ops, synthetic
+    from eventad_b200.engine import pin_raw, raw_bytes
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L = _lib.lib()
+    runner, args = build_runner(dev)
+    B, N = a.windows, a.events
+    n_sets = 8
+    raws = [pin_raw(synthetic.make_batch(N, B, seed=1000 * rank + s, dist=a.dist)) for s in range(n_sets)]
+    feats = [f.to(dev) for f in synthetic.make_image_features(B, seed=rank)]
+    datas = [runner.to_device(r) for r in raws]                      # inputs resident in HBM for `value`
+    torch.cuda.synchronize()
+    events_per_step = N * B
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device(i):
+        return runner.forward_device(datas[i % n_sets], feats)
+
+    for i in range(a.warmup):
+        step_device(i)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    timer = ops.KernelTimer()
+    ops.TIMER = timer
+    launches0 = L.evad_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(a.steps):
+        step_device(a.warmup + i)
+    e1.record()
+    barrier()
+    launches = L.evad_launch_count() - launches0
+    ops.TIMER = None
+    ms_total = e0.elapsed_time(e1)
+    stage = timer.summary()
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- end to end through the public call: pinned host events -> H2D -> format_data -> forward -> D2H results
+    for i in range(min(a.warmup, 3)):
+        runner.infer(raws[i % n_sets], feats)
+    barrier()
+    d2h = 0
+    e0.record()
+    for i in range(a.steps):
+        _, d2h = runner.infer(raws[(a.warmup + i) % n_sets], feats)
+    e1.record()
+    barrier()
+    ms_e2e = e0.elapsed_time(e1)
+
+    t = torch.tensor([ms_total, ms_e2e], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, ms_e2e = float(t[0]), float(t[1])
+    value = world * events_per_step * a.steps / (ms_total * 1e-3) / 1e6
+    e2e_value = world * events_per_step * a.steps / (ms_e2e * 1e-3) / 1e6
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (CUDA events around every C-ABI call inside the timed region)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_kind = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    gc = runner.net.events_to_graph.graph_creators
+    e_sets, n1_sets = [], []
+    for d in datas:
+        denorm = torch.tensor([320, 240, 1_000_000], device=dev)
+        pos_int = (denorm.view(1, -1) * d.pos + 1e-3).int()
+        gc.reset()
+        e_sets.append(int(gc.build_csr(d.batch.int(), pos_int)["num_edges"].item()))
+    E = float(np.mean(e_sets))
+    Ntot = float(events_per_step)
+    stage_ms = {k: v[1] / a.steps for k, v in stage.items()}
+    dom = "spline_conv_small_c19"
+    dom_ms = stage_ms.get(dom, None)
+    # algorithmic bytes of one conv1a launch: x0 rows 80 B + pos 12 B + rowptr 4 B read per
+    # node, src 4 B per edge, conv output 64 B + skip output 64 B written per node; gathers counted once
+    dom_bytes = Ntot * (80 + 12 + 4 + 64 + 64) + 4 * E
+    roofline = None
+    if dom_ms:
+        ach = dom_bytes / (dom_ms * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "kernel": "spline_small_kernel<20> (conv_block1.conv_block1: 19->16 LUT conv + BN + ReLU + skip Linear/BN)",
+                    "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                    "peak_source": peak_kind, "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": dom_ms,
+                    "share_of_step": dom_ms / (ms_total / a.steps)}
+    n1 = 2240.0 * B                                              # pool-1 nodes (upper bound without the t==T extras)
+    path_bytes = 1200 * Ntot + 108 * E + 1100 * n1                # SURVEY.md 8(d) module-boundary model
+    path_ach = path_bytes / (ms_total / a.steps * 1e-3) / 1e9
+    path_roofline = {"bound": "hbm", "model": "SURVEY 8(d): 1200*N + 108*E + 1100*N1 bytes per step", "achieved": path_ach,
+                     "peak": peak, "unit": "GB/s", "frac": path_ach / peak, "edges_per_step": E}
+
+    # ---- p50 latency of one 100k-event window (B = 1), device-resident, CUDA events, single stream
+    lat = None
+    if a.latency_iters > 0:
+        raw1 = [pin_raw(synthetic.make_batch(N, 1, seed=77 + s, dist=a.dist)) for s in range(4)]
+        d1 = [runner.to_device(r) for r in raw1]
+        f1 = [f[:1].contiguous() for f in feats]
+        for i in range(10):
+            runner.forward_device(d1[i % 4], f1)
+        torch.cuda.synchronize()
+        ts = []
+        for i in range(a.latency_iters):
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record()
+            runner.forward_device(d1[i % 4], f1)
+            s1.record()
+            s1.synchronize()
+            ts.append(s0.elapsed_time(s1))
+        lat = {"p50_ms_per_window": float(np.median(ts)), "p90_ms_per_window": float(np.percentile(ts, 90)),
+               "events": N, "iters": a.latency_iters, "note": "B=1, inputs resident, includes the final count read-back"}
+
+    cpu = None
+    if not a.no_cpu_baseline and world == 1:
+        v, ms, cores, sample = cpu_reference_run(a, 2, 1)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "ms_per_window": ms}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": ms_total / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": workload_config(a),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": raw_bytes(raws[0]), "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e / a.steps},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "path_roofline": path_roofline,
+            "cpu_baseline": cpu, "latency": lat, "stage_ms_per_step": stage_ms,
+            "ms_per_window": ms_total / a.steps / B}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device (the sm_100a path has no CPU fallback); use --impl reference")
+        run_b200(a)
+
+
+if __name__ == "__main__":
+    main()

@@ -65,6 +65,7 @@ def _sig(L, name, restype, argtypes):
 def _declare(L):
     _sig(L, "evad_version", c_i, [])
     _sig(L, "evad_compiled_arch", c_i, [])
+    _sig(L, "evad_launch_count", ctypes.c_longlong, [])
     _sig(L, "evad_scan_ws_bytes", c_sz, [c_i64])
     _sig(L, "evad_exclusive_scan", c_i, [c_p, c_p, c_i64, c_p, c_p, c_sz, c_p])
     _sig(L, "evad_sort_ws_bytes", c_sz, [c_i64])

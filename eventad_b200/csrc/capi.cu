@@ -1,7 +1,11 @@
 // eventad_b200/csrc/capi.cu -- small C-ABI entry points that wrap the primitives (see include/eventad_b200.h).
 #include "common.cuh"
 
+long long g_evad_launches = 0;
+
 extern "C" int evad_version(void) { return 1; }
+
+extern "C" long long evad_launch_count(void) { return g_evad_launches; }
 
 extern "C" int evad_compiled_arch(void) {
 #ifdef EVAD_ARCH

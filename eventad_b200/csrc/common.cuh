@@ -6,10 +6,13 @@
 
 #include "../../include/eventad_b200.h"
 
+// every kernel launch of the library is followed by this macro: it also feeds evad_launch_count()
+extern long long g_evad_launches;
 #define EVAD_CHECK_LAUNCH()                                   \
     do {                                                      \
         cudaError_t e__ = cudaGetLastError();                 \
         if (e__ != cudaSuccess) return EVAD_ERR_LAUNCH;       \
+        ++g_evad_launches;                                    \
     } while (0)
 
 #define EVAD_TRY(expr)                                        \

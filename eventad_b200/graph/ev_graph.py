@@ -73,7 +73,9 @@ class AsyncGraph:
         cell_start = torch.empty(ncells + 2, dtype=torch.int32, device=dev) if want_cells else None
         nbytes = L.evad_graph_ws_bytes(n, self.batch_size, self.height, self.width, K)
         ws = self._ws.get(nbytes, dev)
-        rc = L.evad_graph_build(_lib.ptr(batch), _lib.ptr(pos), n, int(self.batch_size), int(self.height),
+        from .. import ops
+        with ops._timed("graph_build"):
+          rc = L.evad_graph_build(_lib.ptr(batch), _lib.ptr(pos), n, int(self.batch_size), int(self.height),
                                 int(self.width), int(self.radius), int(self.delta_t_us), int(self.max_queue_size), K,
                                 _lib.ptr(rowptr), _lib.ptr(src), _lib.ptr(num_edges), _lib.ptr(edge_index),
                                 max(n * K, 1), _lib.ptr(cell_perm), _lib.ptr(cell_start), _lib.ptr(self._status),

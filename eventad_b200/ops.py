@@ -20,6 +20,41 @@ def _ws(nbytes, device):
     return w.get(nbytes, device)
 
 
+class KernelTimer:
+    """Optional CUDA-event timing of the C-ABI calls, on the launching stream (bench.py's per-stage breakdown and the
+    roofline of the dominant kernel).  Disabled (None) by default."""
+
+    def __init__(self):
+        self.pairs = {}
+
+    def record(self, name):
+        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        self.pairs.setdefault(name, []).append(ev)
+        ev[0].record()
+        return ev[1]
+
+    def summary(self):
+        """name -> (launch groups, total ms); call after a synchronize."""
+        return {k: (len(v), sum(a.elapsed_time(b) for a, b in v)) for k, v in self.pairs.items()}
+
+
+TIMER = None
+
+
+class _timed:
+    def __init__(self, name):
+        self.name = name
+        self.stop = None
+
+    def __enter__(self):
+        if TIMER is not None:
+            self.stop = TIMER.record(self.name)
+
+    def __exit__(self, *a):
+        if self.stop is not None:
+            self.stop.record()
+
+
 def new_status(device):
     return torch.zeros(1, dtype=torch.int32, device=device)
 
@@ -89,9 +124,10 @@ def sample_concat(x, pos, batch_i32, feat_nhwc, width, height, append_pos=False,
         x = x.contiguous()
     pos = pos.contiguous()
     fb, fh, fw, fc = (feat_nhwc.shape if feat_nhwc is not None else (0, 0, 0, 0))
-    check(L.evad_sample_concat(ptr(x), x.stride(0) if x is not None else 0, cx, ptr(pos), pos.stride(0), ptr(batch_i32), n,
-                               ptr(n_dev), ptr(feat_nhwc), fb, fh, fw, fc, float(width), float(height), int(append_pos),
-                               ptr(out), ldo, stream()), "evad_sample_concat")
+    with _timed('sample_concat'):
+        check(L.evad_sample_concat(ptr(x), x.stride(0) if x is not None else 0, cx, ptr(pos), pos.stride(0), ptr(batch_i32), n,
+                                   ptr(n_dev), ptr(feat_nhwc), fb, fh, fw, fc, float(width), float(height), int(append_pos),
+                                   ptr(out), ldo, stream()), "evad_sample_concat")
     return out
 
 
@@ -176,11 +212,12 @@ def spline_conv_small(rowptr, src, n, x, cin, lut, mode, pseudo, epi, status, sk
     p = _pseudo_struct(**pseudo)
     e = _epi_struct(**epi)
     se = _epi_struct(**skip_epi) if skip_epi is not None else None
-    check(L.evad_spline_conv_small(ptr(rowptr), ptr(src), n, ptr(x), x.stride(0), cin, cin_pad, cout, ctypes.byref(p),
-                                   ctypes.byref(m), ptr(lut), ctypes.byref(e), ptr(out), out.stride(0),
-                                   ctypes.byref(se) if se is not None else None, ptr(skip_out),
-                                   skip_out.stride(0) if skip_out is not None else 0, ptr(status), stream()),
-          "evad_spline_conv_small")
+    with _timed(f'spline_conv_small_c{cin}'):
+        check(L.evad_spline_conv_small(ptr(rowptr), ptr(src), n, ptr(x), x.stride(0), cin, cin_pad, cout, ctypes.byref(p),
+                                       ctypes.byref(m), ptr(lut), ctypes.byref(e), ptr(out), out.stride(0),
+                                       ctypes.byref(se) if se is not None else None, ptr(skip_out),
+                                       skip_out.stride(0) if skip_out is not None else 0, ptr(status), stream()),
+              "evad_spline_conv_small")
     return out, skip_out
 
 
@@ -191,8 +228,9 @@ def spline_aggregate(rowptr, src, n_cap, n_dev, x, cin, mode, pseudo, status):
     A = torch.empty((max(n_cap, 1), lda), dtype=torch.float32, device=x.device)
     m = _mode_struct(mode)
     p = _pseudo_struct(**pseudo)
-    check(L.evad_spline_aggregate(ptr(rowptr), ptr(src), n_cap, ptr(n_dev), ptr(x), x.stride(0), cin, ctypes.byref(p),
-                                  ctypes.byref(m), ptr(A), lda, ptr(status), stream()), "evad_spline_aggregate")
+    with _timed('spline_aggregate'):
+        check(L.evad_spline_aggregate(ptr(rowptr), ptr(src), n_cap, ptr(n_dev), ptr(x), x.stride(0), cin, ctypes.byref(p),
+                                      ctypes.byref(m), ptr(A), lda, ptr(status), stream()), "evad_spline_aggregate")
     return A
 
 
@@ -204,8 +242,9 @@ def gemm_epilogue(A, W, m_cap, m_dev, epi, out=None, k=None):
     if out is None:
         out = torch.empty((max(m_cap, 1), n), dtype=torch.float32, device=A.device)
     e = _epi_struct(**epi)
-    check(L.evad_gemm_epilogue(ptr(A), A.stride(0), ptr(W), m_cap, ptr(m_dev), k, n, ctypes.byref(e), ptr(out),
-                               out.stride(0), stream()), "evad_gemm_epilogue")
+    with _timed('gemm_epilogue'):
+        check(L.evad_gemm_epilogue(ptr(A), A.stride(0), ptr(W), m_cap, ptr(m_dev), k, n, ctypes.byref(e), ptr(out),
+                                   out.stride(0), stream()), "evad_gemm_epilogue")
     return out
 
 
@@ -250,9 +289,10 @@ def voxel_pool(x, pos, batch_i32, rowptr, src, n_cap, n_dev, voxel_size, nv, bat
     ws = _ws(L.evad_voxel_pool_ws_bytes(n_cap, c_cap), dev)
     x = x.contiguous()
     pos = pos.contiguous()
-    check(L.evad_voxel_pool(ctypes.byref(P), n_cap, ptr(n_dev), ptr(pos), pos.stride(0), ptr(batch_i32), ptr(x),
-                            x.stride(0), cx, ptr(rowptr), ptr(src), c_cap, e_cap, ptr(cluster), ptr(n_out), ptr(x_out), ldo,
-                            ptr(pos_out), ptr(batch_out), ptr(rowptr_out), ptr(src_out), ptr(num_edges), ptr(status),
-                            ptr(ws), ws.numel(), stream()), "evad_voxel_pool")
+    with _timed('voxel_pool'):
+        check(L.evad_voxel_pool(ctypes.byref(P), n_cap, ptr(n_dev), ptr(pos), pos.stride(0), ptr(batch_i32), ptr(x),
+                                x.stride(0), cx, ptr(rowptr), ptr(src), c_cap, e_cap, ptr(cluster), ptr(n_out), ptr(x_out), ldo,
+                                ptr(pos_out), ptr(batch_out), ptr(rowptr_out), ptr(src_out), ptr(num_edges), ptr(status),
+                                ptr(ws), ws.numel(), stream()), "evad_voxel_pool")
     return dict(cluster=cluster, n_out=n_out, x=x_out, pos=pos_out, batch=batch_out, rowptr=rowptr_out, src=src_out,
                 num_edges=num_edges, c_cap=c_cap, e_cap=e_cap, status=status)

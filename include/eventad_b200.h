@@ -39,6 +39,8 @@ extern "C" {
 int evad_version(void);
 /* returns the SM architecture the library was compiled for (100) */
 int evad_compiled_arch(void);
+/* number of kernels this library has launched in this process (for bench.py's gpu_launches) */
+long long evad_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Primitives (exported for the unit tests).
