@@ -73,6 +73,11 @@ def _declare(L):
     _sig(L, "evad_graph_ws_bytes", c_sz, [c_i64, c_i, c_i, c_i, c_i])
     _sig(L, "evad_graph_build", c_i, [c_p, c_p, c_i64, c_i, c_i, c_i, c_i, c_i, c_i, c_i,
                                       c_p, c_p, c_p, c_p, c_i64, c_p, c_p, c_p, c_p, c_sz, c_p])
+    _sig(L, "evad_stream_state_bytes", c_sz, [c_i, c_i, c_i, c_i])
+    _sig(L, "evad_stream_reset", c_i, [c_p, c_i, c_i, c_i, c_i, c_p])
+    _sig(L, "evad_stream_ws_bytes", c_sz, [c_i64, c_i])
+    _sig(L, "evad_stream_append", c_i, [c_p, c_i, c_i, c_i, c_i, c_p, c_p, c_i64, c_i, c_i, c_i, c_i, c_i, c_i,
+                                        c_p, c_p, c_p, c_p, c_i64, c_p, c_p, c_sz, c_p])
     P = ctypes.POINTER
     _sig(L, "evad_spline_lut_build", c_i, [c_p, c_p, c_p, c_i, c_i, c_i, P(SplineModeT), c_p, c_p])
     _sig(L, "evad_spline_conv_small", c_i, [c_p, c_p, c_i64, c_p, c_i, c_i, c_i, c_i, P(PseudoT), P(SplineModeT), c_p,

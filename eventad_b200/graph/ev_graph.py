@@ -30,6 +30,7 @@ class AsyncGraph:
         self._ws = _lib.Workspace()
         self._status = None
         self._stream_state = None
+        self._history = []          # (batch, pos, base_index) of reset-mode calls, replayed if streaming starts
 
     def initialize(self, n_ev, device):
         self.edges = torch.zeros((2, 0), dtype=torch.long, device=device)
@@ -43,6 +44,7 @@ class AsyncGraph:
         self.min_index = 0
         self.csr = None
         self._stream_state = None
+        self._history = []
 
     # ------------------------------------------------------------------ device-resident build (no host sync)
     def build_csr(self, batch, pos, want_edge_index=False, want_cells=False):
@@ -98,6 +100,7 @@ class AsyncGraph:
 
         if self.max_index == 0 and self.min_index == 0 and self._stream_state is None:
             out = self.build_csr(batch, pos, want_edge_index=True)
+            self._history = [(batch, pos, 0)]
             self.all_timestamps = torch.cat([self.all_timestamps, pos[:, 2]])
             self.max_index += n_ev
             e = int(out["num_edges"].item())                    # the reference syncs here too (mask compaction)

@@ -210,6 +210,7 @@ class Net(torch.nn.Module):
         denorm = torch.tensor([int(width), int(height), int(time_window)], device=dev)
         pos_int = (denorm.view(1, -1) * pos + 1e-3).int()
         graph = gc.build_csr(batch_i32, pos_int)
+        gc.max_index, gc.all_timestamps, gc._history = n, pos_int[:, 2], [(batch_i32, pos_int, 0)]   # AsyncGraph bookkeeping
         status = gc._status
         rowptr, src = graph["rowptr"], graph["src"]
         f = feats_nhwc if self.use_image else [None] * 5

@@ -70,8 +70,8 @@ int evad_sort_pairs(uint32_t* keys_in, uint32_t* vals_in, uint32_t* keys_out, ui
  *   rowptr[N+1] int32, src[K*N] int32 (first E entries valid), num_edges[1] int32,
  *   edge_index (optional, may be NULL) int64 [2][edge_index_stride]: row 0 = src, row 1 = dst, first E columns.
  *   cell_perm (optional) int32[N]: event ids ordered by (b,y,x) pixel then id; cell_start (optional) int32[B*H*W+1].
- *   single_event_quirk: when N == 1 the reference ignores `batch` and inserts into sample 0
- *   (ev_graph.cu:152); the flag reproduces that.
+ *   (With N == 1 the reference inserts into sample 0 whatever `batch` says, ev_graph.cu:152; after a reset the
+ *   result is the self loop either way.  The streaming entry point below reproduces the quirk.)
  * ---------------------------------------------------------------------------------------------------------- */
 size_t evad_graph_ws_bytes(int64_t n_events, int batch_size, int height, int width, int max_neighbors);
 int evad_graph_build(const int32_t* batch, const int32_t* pos, int64_t n_events, int batch_size, int height,
@@ -79,6 +79,25 @@ int evad_graph_build(const int32_t* batch, const int32_t* pos, int64_t n_events,
                      int32_t* rowptr, int32_t* src, int32_t* num_edges, int64_t* edge_index,
                      int64_t edge_index_stride, int32_t* cell_perm, int32_t* cell_start, uint32_t* status,
                      void* ws, size_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Event-graph construction, streaming ("append") mode: EV_TGN.forward(reset=False)
+ * (src/dagr/model/layers/ev_tgn.py:45-56), AsyncGraph.forward growth path (src/dagr/graph/ev_graph.py:75-103),
+ * insert_in_queue_cuda / insert_in_queue_single_cuda / fill_edges_cuda with min_index > 0
+ * (src/dagr/graph/ev_graph.cu:15-80,130-212).  `state` is caller-owned device memory of evad_stream_state_bytes()
+ * holding a per-pixel ring [B*H*W][Q] of (event index, timestamp) plus insert counters; it replaces the reference's
+ * [B,Q,H,W] FIFO tensor.  New events get indices base_index .. base_index+n-1; edges are reported relative to
+ * min_index like the reference (SlidingWindowGraph.delete_nodes only bumps min_index, ev_graph.py:121-136).
+ * do_search = 0 only inserts (used to replay the events of a preceding reset-mode call into the ring).
+ * ---------------------------------------------------------------------------------------------------------- */
+size_t evad_stream_state_bytes(int batch_size, int height, int width, int max_queue_size);
+int evad_stream_reset(void* state, int batch_size, int height, int width, int max_queue_size, void* stream);
+size_t evad_stream_ws_bytes(int64_t n_events, int max_neighbors);
+int evad_stream_append(void* state, int batch_size, int height, int width, int max_queue_size, const int32_t* batch,
+                       const int32_t* pos, int64_t n_events, int base_index, int min_index, int radius,
+                       int delta_t_us, int max_neighbors, int do_search, int32_t* rowptr, int32_t* src,
+                       int32_t* num_edges, int64_t* edge_index, int64_t edge_index_stride, uint32_t* status, void* ws,
+                       size_t ws_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * SplineConv message passing.
