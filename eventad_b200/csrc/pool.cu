@@ -88,6 +88,10 @@ __device__ __forceinline__ float div_floor_f(float a, float b) {
 
 // ------------------------------------------------------------------------------------------------ per-voxel reduce
 // One CTA per output cluster.  x_out row = [reduced x (cx) | reduced sampled map (S.C) | pos_x, pos_y (if append_pos)].
+// Members are staged in chunks of PL_CHUNK: one thread per member resolves the node id and the (up to 8) trilinear
+// taps of the CNN map once; the channel threads then only do coalesced loads + FMAs.
+#define PL_CHUNK 32
+
 __global__ void __launch_bounds__(PL_THREADS) pool_reduce_kernel(
     const uint32_t* __restrict__ sidx, const int32_t* __restrict__ seg_start, const int32_t* __restrict__ n_out,
     const float* __restrict__ pos, int ld_pos, const int32_t* __restrict__ batch, const float* __restrict__ x, int ldx,
@@ -97,18 +101,58 @@ __global__ void __launch_bounds__(PL_THREADS) pool_reduce_kernel(
     if (c >= *n_out) return;
     const int s0 = seg_start[c], s1 = seg_start[c + 1];
     __shared__ float s_pos[2];
-    if (threadIdx.x == 0) {
-        // pool_pos = scatter mean: fp32 sums in ascending node order, then / count.clamp(min=1)
-        float sx = 0.f, sy = 0.f, st = 0.f;
-        for (int p = s0; p < s1; p++) {
-            const int64_t i = sidx[p];
-            sx = __fadd_rn(sx, pos[i * ld_pos]);
-            sy = __fadd_rn(sy, pos[i * ld_pos + 1]);
-            st = __fadd_rn(st, pos[i * ld_pos + 2]);
+    __shared__ int s_node[PL_CHUNK];
+    __shared__ int s_tap[PL_CHUNK][8];
+    __shared__ float s_wgt[PL_CHUNK][8];
+    const int ctot = cx + (S.feat ? S.C : 0);
+    const float cntf = fmaxf((float)(s1 - s0), 1.f);
+    float sx = 0.f, sy = 0.f, st = 0.f;                      // thread 0 only: serial position sums
+    float acc[2] = {0.f, 0.f};                               // up to 2 channels per thread (ctot <= 2*PL_THREADS)
+    for (int p0 = s0; p0 < s1; p0 += PL_CHUNK) {
+        const int cnt = min(PL_CHUNK, s1 - p0);
+        __syncthreads();
+        if (threadIdx.x < cnt) {
+            const int m = threadIdx.x;
+            const int64_t i = sidx[p0 + m];
+            s_node[m] = (int)i;
+            if (S.feat) sample_taps(S, pos[i * ld_pos], pos[i * ld_pos + 1], (float)batch[i], s_tap[m], s_wgt[m]);
         }
-        const float cnt = fmaxf((float)(s1 - s0), 1.f);
-        float mx = __fdiv_rn(sx, cnt), my = __fdiv_rn(sy, cnt);
-        const float mt = __fdiv_rn(st, cnt);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            // pool_pos = scatter mean: fp32 sums in ascending node order, then / count.clamp(min=1)
+            for (int m = 0; m < cnt; m++) {
+                const int64_t i = s_node[m];
+                sx = __fadd_rn(sx, pos[i * ld_pos]);
+                sy = __fadd_rn(sy, pos[i * ld_pos + 1]);
+                st = __fadd_rn(st, pos[i * ld_pos + 2]);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+            const int ch = threadIdx.x + u * PL_THREADS;
+            if (ch >= ctot) continue;
+            float a = acc[u];
+            for (int m = 0; m < cnt; m++) {
+                float v;
+                if (ch < cx) {
+                    v = x[(int64_t)s_node[m] * ldx + ch];
+                } else {
+                    v = 0.f;
+#pragma unroll
+                    for (int t = 0; t < 8; t++) {
+                        const int idx = s_tap[m][t];
+                        if (idx >= 0) v = fmaf(S.feat[(int64_t)idx * S.C + (ch - cx)], s_wgt[m][t], v);
+                    }
+                }
+                if (aggr_mean) a = __fadd_rn(a, v);
+                else a = (p0 == s0 && m == 0) ? v : fmaxf(a, v);
+            }
+            acc[u] = a;
+        }
+    }
+    if (threadIdx.x == 0) {
+        float mx = __fdiv_rn(sx, cntf), my = __fdiv_rn(sy, cntf);
+        const float mt = __fdiv_rn(st, cntf);
         // round_to_pixel: floor_divide(p + 1e-5, wh_inv) * wh_inv
         mx = __fmul_rn(div_floor_f(__fadd_rn(mx, 1e-5f), inv_w), inv_w);
         my = __fmul_rn(div_floor_f(__fadd_rn(my, 1e-5f), inv_h), inv_h);
@@ -119,20 +163,10 @@ __global__ void __launch_bounds__(PL_THREADS) pool_reduce_kernel(
         s_pos[0] = mx;
         s_pos[1] = my;
     }
-    const int ctot = cx + (S.feat ? S.C : 0);
-    const float cntf = fmaxf((float)(s1 - s0), 1.f);
-    for (int ch = threadIdx.x; ch < ctot; ch += PL_THREADS) {
-        float acc = 0.f;
-        for (int p = s0; p < s1; p++) {
-            const int64_t i = sidx[p];
-            float v;
-            if (ch < cx) v = x[i * ldx + ch];
-            else v = sample_feat(S, pos[i * ld_pos], pos[i * ld_pos + 1], (float)batch[i], ch - cx);
-            if (aggr_mean) acc = __fadd_rn(acc, v);
-            else acc = (p == s0) ? v : fmaxf(acc, v);
-        }
-        if (aggr_mean) acc = __fdiv_rn(acc, cntf);
-        x_out[(int64_t)c * ldo + ch] = acc;
+#pragma unroll
+    for (int u = 0; u < 2; u++) {
+        const int ch = threadIdx.x + u * PL_THREADS;
+        if (ch < ctot) x_out[(int64_t)c * ldo + ch] = aggr_mean ? __fdiv_rn(acc[u], cntf) : acc[u];
     }
     if (append_pos) {
         __syncthreads();
@@ -270,6 +304,7 @@ extern "C" int evad_voxel_pool(const evad_pool_params_t* p, int64_t n_cap, const
     const bool want_edges = rowptr_in && src_in && rowptr_out && src_out && num_edges_out;
     const int ctot = cx + (p->feat ? p->feat_c : 0);
     if (ldo < ctot + (p->append_pos ? 2 : 0)) return EVAD_ERR_ARG;
+    if (ctot > 2 * PL_THREADS) return EVAD_ERR_UNSUPPORTED;
     const long long kb = (long long)p->nvx * p->nvy * p->nvt * ((long long)p->batch_size + 1);
     if (kb >= (1ll << 31)) return EVAD_ERR_UNSUPPORTED;
     EvadArena a(ws, ws_bytes);

@@ -150,11 +150,111 @@ __global__ void __launch_bounds__((BM / TM) * (BN / TN)) gemm_epi_kernel(const f
     }
 }
 
+// N = 64 fast path: BM x 64 tile, BK = 16, 256 threads as 16 (rows) x 16 (column quads), TM = BM/16 rows x 4 columns
+// per thread; A is staged transposed so both operands are read with 128-bit shared loads (3 LDS.128 per 32 FFMA at
+// BM = 128); the next k-slab is prefetched into registers while the current one is multiplied.
+template <int BM>
+__global__ void __launch_bounds__(256) gemm64_kernel(const float* __restrict__ A, int64_t lda, const float* __restrict__ W,
+                                                     int64_t m, const int32_t* __restrict__ m_dev, int K,
+                                                     evad_epilogue_t E, float* __restrict__ out, int ldo) {
+    constexpr int TM = BM / 16;
+    constexpr int AV = (BM * GM_BK / 4 + 255) / 256;          // float4 loads of A per thread per slab
+    __shared__ __align__(16) float As[GM_BK][BM + 4];
+    __shared__ __align__(16) float Bs[GM_BK][64];
+    const int64_t mm = m_dev ? min((int64_t)*m_dev, m) : m;
+    const int64_t row0 = (int64_t)blockIdx.x * BM;
+    if (row0 >= mm) return;
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    float acc[TM][4];
+#pragma unroll
+    for (int a = 0; a < TM; a++) { acc[a][0] = acc[a][1] = acc[a][2] = acc[a][3] = 0.f; }
+    float4 ra[AV], rb;
+    auto load_slab = [&](int k0) {
+#pragma unroll
+        for (int v = 0; v < AV; v++) {
+            const int idx = tid + v * 256;
+            const int r = idx >> 2, kq = idx & 3;
+            const int64_t gr = row0 + r;
+            const int kk = k0 + kq * 4;
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (idx < BM * 4 && gr < mm) {
+                const float* p = A + gr * lda + kk;
+                if (kk + 3 < K) t = *reinterpret_cast<const float4*>(p);
+                else {
+                    if (kk < K) t.x = p[0];
+                    if (kk + 1 < K) t.y = p[1];
+                    if (kk + 2 < K) t.z = p[2];
+                }
+            }
+            ra[v] = t;
+        }
+        const int kb = k0 + (tid >> 4);
+        rb = (kb < K) ? *reinterpret_cast<const float4*>(W + (int64_t)kb * 64 + 4 * tx) : make_float4(0.f, 0.f, 0.f, 0.f);
+    };
+    auto store_slab = [&]() {
+#pragma unroll
+        for (int v = 0; v < AV; v++) {
+            const int idx = tid + v * 256;
+            const int r = idx >> 2, kq = idx & 3;
+            if (idx >= BM * 4) continue;
+            As[kq * 4 + 0][r] = ra[v].x; As[kq * 4 + 1][r] = ra[v].y;
+            As[kq * 4 + 2][r] = ra[v].z; As[kq * 4 + 3][r] = ra[v].w;
+        }
+        *reinterpret_cast<float4*>(&Bs[tid >> 4][4 * tx]) = rb;
+    };
+    load_slab(0);
+    for (int k0 = 0; k0 < K; k0 += GM_BK) {
+        store_slab();
+        __syncthreads();
+        if (k0 + GM_BK < K) load_slab(k0 + GM_BK);
+#pragma unroll
+        for (int kk = 0; kk < GM_BK; kk++) {
+            const float4 b4 = *reinterpret_cast<const float4*>(&Bs[kk][4 * tx]);
+            float av[TM];
+#pragma unroll
+            for (int a = 0; a < TM; a += 2) {
+                const float2 t = *reinterpret_cast<const float2*>(&As[kk][ty * TM + a]);
+                av[a] = t.x; av[a + 1] = t.y;
+            }
+#pragma unroll
+            for (int a = 0; a < TM; a++) {
+                acc[a][0] = fmaf(av[a], b4.x, acc[a][0]); acc[a][1] = fmaf(av[a], b4.y, acc[a][1]);
+                acc[a][2] = fmaf(av[a], b4.z, acc[a][2]); acc[a][3] = fmaf(av[a], b4.w, acc[a][3]);
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int a = 0; a < TM; a++) {
+        const int64_t gr = row0 + ty * TM + a;
+        if (gr >= mm) continue;
+        float v[4] = {acc[a][0], acc[a][1], acc[a][2], acc[a][3]};
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+            const int c = 4 * tx + b;
+            if (E.scale) v[b] = __fmul_rn(v[b], E.scale[c]);
+            if (E.shift) v[b] = __fadd_rn(v[b], E.shift[c]);
+            if (E.addend) v[b] = __fadd_rn(v[b], E.addend[gr * E.ld_add + c]);
+            if (E.relu) v[b] = fmaxf(v[b], 0.f);
+            out[gr * ldo + c] = v[b];
+        }
+    }
+}
+
 extern "C" int evad_gemm_epilogue(const float* A, int64_t lda, const float* W, int64_t m, const int32_t* m_dev, int k,
                                   int n, const evad_epilogue_t* epi_h, float* out, int ldo, void* stream) {
     if (!A || !W || !epi_h || !out || k < 1 || n < 1 || lda < k || ldo < n) return EVAD_ERR_ARG;
     if (m <= 0) return EVAD_OK;
     cudaStream_t st = (cudaStream_t)stream;
+    if (n == 64 && lda % 4 == 0 && (((uintptr_t)A | (uintptr_t)W) & 15) == 0) {
+        if (m >= 148 * 64) {
+            gemm64_kernel<128><<<evad_cdiv(m, 128), 256, 0, st>>>(A, lda, W, m, m_dev, k, *epi_h, out, ldo);
+        } else {
+            gemm64_kernel<32><<<evad_cdiv(m, 32), 256, 0, st>>>(A, lda, W, m, m_dev, k, *epi_h, out, ldo);
+        }
+        EVAD_CHECK_LAUNCH();
+        return EVAD_OK;
+    }
     if (m >= 148 * 64) {
         dim3 grid(evad_cdiv(m, 64), evad_cdiv(n, 64));
         gemm_epi_kernel<64, 64, 4, 4><<<grid, 256, 0, st>>>(A, lda, W, m, m_dev, k, n, *epi_h, out, ldo);

@@ -10,7 +10,7 @@
 #include "spline_common.cuh"
 
 #define SS_COUT 16
-#define SS_THREADS 256
+#define SS_THREADS 512
 #define SS_WARPS (SS_THREADS / 32)
 
 __global__ void lut_build_kernel(const float* __restrict__ weight, const float* __restrict__ root_w,
@@ -66,8 +66,14 @@ __device__ __forceinline__ float epi_apply(const evad_epilogue_t& E, float acc, 
     return v;
 }
 
+// Thread mapping: one warp per destination node; lane = (edge slot es = lane>>2, output quad q = lane&3).  Eight in-edges
+// are processed at once: the 4 lanes of a slot load the source row (5 x 128-bit, same address -> one transaction),
+// then per input channel one 128-bit LUT read feeds 4 FFMAs.  Odd slots walk channel pairs swapped, so the two
+// 64-byte LUT segments a quarter-warp reads in one LDS.128 wavefront always sit in different bank halves (the class
+// stride Cin_pad*16 floats is a multiple of 32 banks).  The root weight (and the skip Linear) ride along as one more
+// pseudo-edge whose source is the node itself.
 template <int CIN_PAD>
-__global__ void __launch_bounds__(SS_THREADS) spline_small_kernel(
+__global__ void __launch_bounds__(SS_THREADS, 2) spline_small_kernel(
     const int32_t* __restrict__ rowptr, const int32_t* __restrict__ src, int64_t n, const float* __restrict__ x,
     int ldx, EvadPseudo P, EvadSplineMode M, const float* __restrict__ lut, evad_epilogue_t E, float* __restrict__ out,
     int ldo, int has_skip, evad_epilogue_t ES, float* __restrict__ skip_out, int ld_skip, uint32_t* __restrict__ status) {
@@ -81,72 +87,74 @@ __global__ void __launch_bounds__(SS_THREADS) spline_small_kernel(
     }
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int half = lane >> 4, o = lane & 15;
+    const int es = lane >> 2, q = lane & 3, odd = es & 1;
     const int64_t stride = (int64_t)gridDim.x * SS_WARPS;
     for (int64_t i = (int64_t)blockIdx.x * SS_WARPS + warp; i < n; i += stride) {
-        const int r0 = rowptr[i], r1 = rowptr[i + 1];
-        float acc = 0.f;
-        for (int c0 = r0; c0 < r1; c0 += 32) {
-            const int cnt = min(32, r1 - c0);
-            int j = 0, cls = 0;
-            if (lane < cnt) {
-                j = src[c0 + lane];
+        const int r0 = rowptr[i];
+        const int deg = rowptr[i + 1] - r0;
+        float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;       // conv (+root) partial sums of this edge slot
+        float sk0 = 0.f, sk1 = 0.f, sk2 = 0.f, sk3 = 0.f;           // skip Linear (only the slot that owns the root)
+        for (int e0 = 0; e0 <= deg; e0 += 8) {                      // pseudo-edge `deg` = root / skip on x_i
+            const int e = e0 + es;
+            if (e > deg) continue;
+            const bool is_root = (e == deg);
+            int j, cls;
+            if (is_root) {
+                j = (int)i;
+                cls = nlut;
+            } else {
+                j = src[r0 + e];
                 float ax, ay;
-                evad_pseudo(P, c0 + lane, j, (int)i, &ax, &ay);
+                evad_pseudo(P, r0 + e, j, (int)i, &ax, &ay);
                 int ix, iy;
                 evad_lut_index(M, ax, ay, &ix, &iy, status);
                 cls = ix * M.ny + iy;
             }
-            for (int t = 0; t < cnt; t += 2) {
-                const int ee = t + half;
-                const int jj = __shfl_sync(0xffffffffu, j, ee & 31);
-                const int cc = __shfl_sync(0xffffffffu, cls, ee & 31);
-                if (ee < cnt) {
-                    float xr[CIN_PAD];
-                    const float4* xp = reinterpret_cast<const float4*>(x + (int64_t)jj * ldx);
+            float xr[CIN_PAD];
+            const float4* xp = reinterpret_cast<const float4*>(x + (int64_t)j * ldx);
 #pragma unroll
-                    for (int q = 0; q < CIN_PAD / 4; q++) {
-                        const float4 v = __ldg(xp + q);
-                        xr[4 * q] = v.x; xr[4 * q + 1] = v.y; xr[4 * q + 2] = v.z; xr[4 * q + 3] = v.w;
-                    }
-                    const float* w = lut_s + (cc * CIN_PAD) * SS_COUT + o;
-                    // the odd half-warp walks channel pairs swapped (c ^ 1): its 16 lanes then hit the other 16 banks
+            for (int k = 0; k < CIN_PAD / 4; k++) {
+                const float4 v = __ldg(xp + k);
+                // odd slots keep each channel pair swapped in registers
+                xr[4 * k] = odd ? v.y : v.x; xr[4 * k + 1] = odd ? v.x : v.y;
+                xr[4 * k + 2] = odd ? v.w : v.z; xr[4 * k + 3] = odd ? v.z : v.w;
+            }
+            const float* w = lut_s + (cls * CIN_PAD) * SS_COUT + 4 * q;
 #pragma unroll
-                    for (int c = 0; c < CIN_PAD; c += 2) {
-                        const float xa = half ? xr[c + 1] : xr[c];      // selects keep xr[] in registers
-                        const float xb = half ? xr[c] : xr[c + 1];
-                        acc = fmaf(w[(c + half) * SS_COUT], xa, acc);
-                        acc = fmaf(w[(c + 1 - half) * SS_COUT], xb, acc);
-                    }
+            for (int c = 0; c < CIN_PAD; c++) {
+                const int ci = c ^ odd;                              // channel whose value sits in xr[c]
+                const float4 w4 = *reinterpret_cast<const float4*>(w + ci * SS_COUT);
+                acc0 = fmaf(w4.x, xr[c], acc0); acc1 = fmaf(w4.y, xr[c], acc1);
+                acc2 = fmaf(w4.z, xr[c], acc2); acc3 = fmaf(w4.w, xr[c], acc3);
+            }
+            if (is_root && has_skip) {
+                const float* wk = w + CIN_PAD * SS_COUT;
+#pragma unroll
+                for (int c = 0; c < CIN_PAD; c++) {
+                    const int ci = c ^ odd;
+                    const float4 w4 = *reinterpret_cast<const float4*>(wk + ci * SS_COUT);
+                    sk0 = fmaf(w4.x, xr[c], sk0); sk1 = fmaf(w4.y, xr[c], sk1);
+                    sk2 = fmaf(w4.z, xr[c], sk2); sk3 = fmaf(w4.w, xr[c], sk3);
                 }
             }
         }
-        // root weight (and skip Linear) on x_i: half h takes channels c with (c & 1) == h
-        float acc2 = 0.f;
-        {
-            float xr[CIN_PAD];
-            const float4* xp = reinterpret_cast<const float4*>(x + i * ldx);
 #pragma unroll
-            for (int q = 0; q < CIN_PAD / 4; q++) {
-                const float4 v = __ldg(xp + q);
-                xr[4 * q] = v.x; xr[4 * q + 1] = v.y; xr[4 * q + 2] = v.z; xr[4 * q + 3] = v.w;
-            }
-            const float* wr = lut_s + (nlut * CIN_PAD) * SS_COUT + o;
-            const float* wk = wr + CIN_PAD * SS_COUT;
-#pragma unroll
-            for (int c = 0; c < CIN_PAD; c += 2) {
-                const int ci = c + half;
-                const float xv = half ? xr[c + 1] : xr[c];
-                acc = fmaf(wr[ci * SS_COUT], xv, acc);
-                if (has_skip) acc2 = fmaf(wk[ci * SS_COUT], xv, acc2);
-            }
+        for (int d = 4; d < 32; d <<= 1) {                          // reduce over the 8 edge slots
+            acc0 += __shfl_xor_sync(0xffffffffu, acc0, d); acc1 += __shfl_xor_sync(0xffffffffu, acc1, d);
+            acc2 += __shfl_xor_sync(0xffffffffu, acc2, d); acc3 += __shfl_xor_sync(0xffffffffu, acc3, d);
+            sk0 += __shfl_xor_sync(0xffffffffu, sk0, d); sk1 += __shfl_xor_sync(0xffffffffu, sk1, d);
+            sk2 += __shfl_xor_sync(0xffffffffu, sk2, d); sk3 += __shfl_xor_sync(0xffffffffu, sk3, d);
         }
-        acc += __shfl_xor_sync(0xffffffffu, acc, 16);
-        acc2 += __shfl_xor_sync(0xffffffffu, acc2, 16);
-        if (half == 0) {
-            out[i * ldo + o] = epi_apply(E, acc, i, o);
-        } else if (has_skip) {
-            skip_out[i * ld_skip + o] = epi_apply(ES, acc2, i, o);
+        if (es == 0) {
+            float4 o;
+            o.x = epi_apply(E, acc0, i, 4 * q); o.y = epi_apply(E, acc1, i, 4 * q + 1);
+            o.z = epi_apply(E, acc2, i, 4 * q + 2); o.w = epi_apply(E, acc3, i, 4 * q + 3);
+            *reinterpret_cast<float4*>(out + i * ldo + 4 * q) = o;
+        } else if (es == 1 && has_skip) {
+            float4 o;
+            o.x = epi_apply(ES, sk0, i, 4 * q); o.y = epi_apply(ES, sk1, i, 4 * q + 1);
+            o.z = epi_apply(ES, sk2, i, 4 * q + 2); o.w = epi_apply(ES, sk3, i, 4 * q + 3);
+            *reinterpret_cast<float4*>(skip_out + i * ld_skip + 4 * q) = o;
         }
     }
 }
@@ -183,7 +191,8 @@ extern "C" int evad_spline_conv_small(const int32_t* rowptr, const int32_t* src,
     if (!rowptr || !src || !x || !pseudo_h || !mode_h || !lut || !epi_h || !out || !status) return EVAD_ERR_ARG;
     if (cout != SS_COUT || cin_pad < cin || cin_pad % 4 != 0 || cin_pad > 32 || ldx % 4 != 0 || ldx < cin_pad)
         return EVAD_ERR_UNSUPPORTED;
-    if (((uintptr_t)x & 15) || ((uintptr_t)lut & 15)) return EVAD_ERR_ARG;
+    if (((uintptr_t)x & 15) || ((uintptr_t)lut & 15) || ((uintptr_t)out & 15) || ldo % 4 != 0) return EVAD_ERR_ARG;
+    if (skip_out && (((uintptr_t)skip_out & 15) || ld_skip % 4 != 0)) return EVAD_ERR_ARG;
     if (!mode_h->use_lut) return EVAD_ERR_UNSUPPORTED;
     if (n <= 0) return EVAD_OK;
     const int has_skip = skip_epi_h != nullptr && skip_out != nullptr;

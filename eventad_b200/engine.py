@@ -65,3 +65,59 @@ class EventBranchRunner:
             nbytes += sum(v.numel() * v.element_size() for v in h.values())
             host.append(h)
         return host, nbytes
+
+
+class GraphedForward:
+    """The fused event branch captured once in a CUDA graph for a fixed (events, windows) shape: one replay per call,
+    no per-kernel launch cost on the host.  Inputs are copied into static buffers; outputs are views of static
+    buffers that the next replay overwrites."""
+
+    def __init__(self, net, n_events_total, num_graphs, feats_like, width=320, height=240, time_window=1_000_000,
+                 device="cuda"):
+        from . import ops
+        self.net, self.dev = net, torch.device(device)
+        self.meta = (int(width), int(height), int(time_window), int(num_graphs))
+        n = int(n_events_total)
+        self.x = torch.zeros((n, 1), dtype=torch.float32, device=device)
+        self.pos = torch.zeros((n, 3), dtype=torch.float32, device=device)
+        self.batch = torch.zeros(n, dtype=torch.int32, device=device)
+        self.feats = [torch.zeros_like(f, device=device) for f in feats_like] if feats_like is not None else None
+        self.graph = None
+        self.res = None
+        self._ops = ops
+
+    def _enqueue(self):
+        w, h, tw, b = self.meta
+        f = [self._ops.to_channel_last(t) for t in self.feats] if self.feats is not None else None
+        return self.net.enqueue_fused(self.x, self.pos, self.batch, b, f, w, h, tw)
+
+    def load(self, data, feats):
+        self.x.copy_(data.x.view(-1, 1), non_blocking=True)
+        self.pos.copy_(data.pos, non_blocking=True)
+        self.batch.copy_(data.batch, non_blocking=True)
+        if self.feats is not None:
+            for d, s in zip(self.feats, feats):
+                d.copy_(s, non_blocking=True)
+
+    @torch.no_grad()
+    def capture(self, data, feats):
+        self.load(data, feats)
+        side = torch.cuda.Stream(device=self.dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):                           # warm-up: workspaces, cached LUTs / folded BN, func attributes
+                self._enqueue()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.res = self._enqueue()
+        return self
+
+    @torch.no_grad()
+    def __call__(self, data, feats, finalize=True):
+        if self.graph is None:
+            self.capture(data, feats)
+        self.load(data, feats)
+        self.graph.replay()
+        return self.net.finalize_fused(self.res) if finalize else self.res

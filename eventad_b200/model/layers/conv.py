@@ -10,10 +10,7 @@ from .spline_conv import MySplineConv, get_csr
 
 
 def _fold(bn_data, conv_bias=None):
-    scale, shift = ops.fold_bn(bn_data.module)
-    if conv_bias is not None:
-        shift = shift + conv_bias.detach().float() * scale
-    return scale, shift
+    return ops.fold_bn(bn_data.module, conv_bias)
 
 
 class ConvBlock(torch.nn.Module):

@@ -147,7 +147,11 @@ class MySplineConv(torch.nn.Module):
         out = ops.gemm_epilogue(A, self.wcat(), n_cap, n_dev, epi)
         skip = None
         if skip_epi is not None:
-            skip = ops.gemm_epilogue(x, skip_weight.detach().t().contiguous().float(), n_cap, n_dev, skip_epi, k=cin)
+            c = self._cache.get("skip_t")
+            if c is None or c[0] != (skip_weight._version, skip_weight.device):
+                c = self._cache["skip_t"] = ((skip_weight._version, skip_weight.device),
+                                             skip_weight.detach().t().contiguous().float())
+            skip = ops.gemm_epilogue(x, c[1], n_cap, n_dev, skip_epi, k=cin)
         return out, skip
 
     def forward(self, data):

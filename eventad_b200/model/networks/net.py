@@ -207,8 +207,11 @@ class Net(torch.nn.Module):
         gc = g.graph_creators
         gc.batch_size = max(gc.batch_size, num_graphs)
         gc.reset()
-        denorm = torch.tensor([int(width), int(height), int(time_window)], device=dev)
-        pos_int = (denorm.view(1, -1) * pos + 1e-3).int()
+        key = (int(width), int(height), int(time_window), dev)
+        if getattr(self, "_denorm_key", None) != key:          # cached: torch.tensor(list, device=...) cannot be captured
+            self._denorm = torch.tensor([int(width), int(height), int(time_window)], device=dev).view(1, -1)
+            self._denorm_key = key
+        pos_int = (self._denorm * pos + 1e-3).int()
         graph = gc.build_csr(batch_i32, pos_int)
         gc.max_index, gc.all_timestamps, gc._history = n, pos_int[:, 2], [(batch_i32, pos_int, 0)]   # AsyncGraph bookkeeping
         status = gc._status

@@ -179,11 +179,21 @@ def _epi_struct(scale=None, shift=None, addend=None, relu=False):
                      ld_add=addend.stride(0) if addend is not None else 0, relu=int(relu))
 
 
-def fold_bn(bn: torch.nn.BatchNorm1d):
-    """eval BatchNorm as y = x*scale + shift."""
-    scale = bn.weight / torch.sqrt(bn.running_var + bn.eps)
-    shift = bn.bias - bn.running_mean * scale
-    return scale.detach().float().contiguous(), shift.detach().float().contiguous()
+def fold_bn(bn: torch.nn.BatchNorm1d, conv_bias=None):
+    """eval BatchNorm (after an optional conv bias) as y = x*scale + shift; cached on the module until a tensor changes."""
+    key = (bn.weight._version, bn.bias._version, bn.running_mean._version, bn.running_var._version, bn.weight.device,
+           None if conv_bias is None else conv_bias._version)
+    c = getattr(bn, "_evad_fold", None)
+    if c is not None and c[0] == key:
+        return c[1], c[2]
+    with torch.no_grad():
+        scale = (bn.weight / torch.sqrt(bn.running_var + bn.eps)).float().contiguous()
+        shift = bn.bias - bn.running_mean * scale
+        if conv_bias is not None:
+            shift = shift + conv_bias.float() * scale
+        shift = shift.float().contiguous()
+    bn._evad_fold = (key, scale, shift)
+    return scale, shift
 
 
 # --------------------------------------------------------------------------------------------------- SplineConv

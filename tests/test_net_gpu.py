@@ -67,3 +67,24 @@ def test_extract_features_api():
     assert out4.x.shape[1] == 64 and out3.x.shape[1] == 64
     assert out4.x.shape[0] <= 36 * 2 and out4.pos.shape == (out4.x.shape[0], 3)
     assert torch.isfinite(out4.x).all()
+
+
+def test_cuda_graph_replay_matches_plain():
+    """The fused branch captured in one CUDA graph (engine.GraphedForward) gives the plain path's results on new inputs."""
+    from eventad_b200.engine import GraphedForward
+    model, args = make_backbone(seed=1, use_image=True)
+    model.cache_luts(320, 240, args.radius)
+    net = model.cuda().backbone
+    feats = [f.cuda() for f in synthetic.make_image_features(2, seed=4)]
+    d0 = make_data(6000, 2, seed=1, dist="C", device="cuda")
+    gf = GraphedForward(net, d0.pos.shape[0], 2, feats, device="cuda").capture(d0, feats)
+    for seed in (2, 3):
+        d = make_data(6000, 2, seed=seed, dist="C", device="cuda")
+        f2 = [f * (1.0 + 0.1 * seed) for f in feats]
+        with torch.no_grad():
+            plain = net(make_data(6000, 2, seed=seed, dist="C", device="cuda"), image_feat=f2)[0]
+        got = gf(d, f2)
+        for o, r in zip(got, plain):
+            assert torch.equal(o.batch, r.batch) and torch.equal(o.pos, r.pos)
+            assert torch.equal(o.edge_index, r.edge_index)
+            assert torch.equal(o.x, r.x)
