@@ -155,7 +155,8 @@ __global__ void __launch_bounds__((BM / TM) * (BN / TN)) gemm_epi_kernel(const f
 // BM = 128); the next k-slab is prefetched into registers while the current one is multiplied.
 template <int BM>
 __global__ void __launch_bounds__(256) gemm64_kernel(const float* __restrict__ A, int64_t lda, const float* __restrict__ W,
-                                                     int64_t m, const int32_t* __restrict__ m_dev, int K,
+                                                     int64_t m, const int32_t* __restrict__ m_dev, int K_total,
+                                                     int k_chunk, float* __restrict__ partial,
                                                      evad_epilogue_t E, float* __restrict__ out, int ldo) {
     constexpr int TM = BM / 16;
     constexpr int AV = (BM * GM_BK / 4 + 255) / 256;          // float4 loads of A per thread per slab
@@ -164,6 +165,9 @@ __global__ void __launch_bounds__(256) gemm64_kernel(const float* __restrict__ A
     const int64_t mm = m_dev ? min((int64_t)*m_dev, m) : m;
     const int64_t row0 = (int64_t)blockIdx.x * BM;
     if (row0 >= mm) return;
+    // split-K: blockIdx.y owns columns [kb0, K) of A / rows of W; partial sums go to `partial` (deterministic reduce)
+    const int kb0 = blockIdx.y * k_chunk;
+    const int K = min(K_total, kb0 + k_chunk);
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
     float acc[TM][4];
 #pragma unroll
@@ -202,8 +206,8 @@ __global__ void __launch_bounds__(256) gemm64_kernel(const float* __restrict__ A
         }
         *reinterpret_cast<float4*>(&Bs[tid >> 4][4 * tx]) = rb;
     };
-    load_slab(0);
-    for (int k0 = 0; k0 < K; k0 += GM_BK) {
+    load_slab(kb0);
+    for (int k0 = kb0; k0 < K; k0 += GM_BK) {
         store_slab();
         __syncthreads();
         if (k0 + GM_BK < K) load_slab(k0 + GM_BK);
@@ -229,6 +233,10 @@ __global__ void __launch_bounds__(256) gemm64_kernel(const float* __restrict__ A
         const int64_t gr = row0 + ty * TM + a;
         if (gr >= mm) continue;
         float v[4] = {acc[a][0], acc[a][1], acc[a][2], acc[a][3]};
+        if (partial) {
+            *reinterpret_cast<float4*>(partial + ((int64_t)blockIdx.y * m + gr) * 64 + 4 * tx) = make_float4(v[0], v[1], v[2], v[3]);
+            continue;
+        }
 #pragma unroll
         for (int b = 0; b < 4; b++) {
             const int c = 4 * tx + b;
@@ -241,17 +249,78 @@ __global__ void __launch_bounds__(256) gemm64_kernel(const float* __restrict__ A
     }
 }
 
+// sums the split-K partials in slice order (deterministic) and applies the epilogue
+__global__ void __launch_bounds__(256) gemm64_reduce_kernel(const float* __restrict__ partial, int splits, int64_t m,
+                                                            const int32_t* __restrict__ m_dev, evad_epilogue_t E,
+                                                            float* __restrict__ out, int ldo) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t mm = m_dev ? min((int64_t)*m_dev, m) : m;
+    const int64_t gr = t >> 4;
+    const int tx = (int)(t & 15);
+    if (gr >= mm) return;
+    float4 s4 = *reinterpret_cast<const float4*>(partial + gr * 64 + 4 * tx);
+    for (int y = 1; y < splits; y++) {
+        const float4 p = *reinterpret_cast<const float4*>(partial + ((int64_t)y * m + gr) * 64 + 4 * tx);
+        s4.x += p.x; s4.y += p.y; s4.z += p.z; s4.w += p.w;
+    }
+    float v[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+    for (int b = 0; b < 4; b++) {
+        const int c = 4 * tx + b;
+        if (E.scale) v[b] = __fmul_rn(v[b], E.scale[c]);
+        if (E.shift) v[b] = __fadd_rn(v[b], E.shift[c]);
+        if (E.addend) v[b] = __fadd_rn(v[b], E.addend[gr * E.ld_add + c]);
+        if (E.relu) v[b] = fmaxf(v[b], 0.f);
+        out[gr * ldo + c] = v[b];
+    }
+}
+
+// number of K slices for the small-M path (1 = unsplit); shared by the workspace query and the launcher
+static int gemm64_splits(int64_t m, int k, int* k_chunk) {
+    *k_chunk = k;
+    if (m >= 148 * 64) return 1;
+    const int mtiles = evad_cdiv(m, 32);
+    int splits = (2 * 148 + mtiles - 1) / mtiles;
+    const int max_splits_k = (k + 63) / 64;
+    if (splits > max_splits_k) splits = max_splits_k;
+    if (splits > 32) splits = 32;
+    if (splits < 2) return 1;
+    *k_chunk = ((k + splits - 1) / splits + GM_BK - 1) / GM_BK * GM_BK;   // multiple of 16 keeps A loads 16 B aligned
+    return (k + *k_chunk - 1) / *k_chunk;
+}
+
+extern "C" size_t evad_gemm_ws_bytes(int64_t m, int k, int n) {
+    if (n != 64 || m <= 0 || k < 1) return 256;
+    int kc;
+    const int splits = gemm64_splits(m, k, &kc);
+    return (splits > 1 ? (size_t)splits * (size_t)m * 64 * sizeof(float) : 0) + 256;
+}
+
 extern "C" int evad_gemm_epilogue(const float* A, int64_t lda, const float* W, int64_t m, const int32_t* m_dev, int k,
-                                  int n, const evad_epilogue_t* epi_h, float* out, int ldo, void* stream) {
+                                  int n, const evad_epilogue_t* epi_h, float* out, int ldo, void* ws, size_t ws_bytes,
+                                  void* stream) {
     if (!A || !W || !epi_h || !out || k < 1 || n < 1 || lda < k || ldo < n) return EVAD_ERR_ARG;
     if (m <= 0) return EVAD_OK;
     cudaStream_t st = (cudaStream_t)stream;
     if (n == 64 && lda % 4 == 0 && (((uintptr_t)A | (uintptr_t)W) & 15) == 0) {
         if (m >= 148 * 64) {
-            gemm64_kernel<128><<<evad_cdiv(m, 128), 256, 0, st>>>(A, lda, W, m, m_dev, k, *epi_h, out, ldo);
-        } else {
-            gemm64_kernel<32><<<evad_cdiv(m, 32), 256, 0, st>>>(A, lda, W, m, m_dev, k, *epi_h, out, ldo);
+            gemm64_kernel<128><<<evad_cdiv(m, 128), 256, 0, st>>>(A, lda, W, m, m_dev, k, k, nullptr, *epi_h, out, ldo);
+            EVAD_CHECK_LAUNCH();
+            return EVAD_OK;
         }
+        // small M (pooled graphs of a few windows): split K so that about two waves of CTAs exist
+        const int mtiles = evad_cdiv(m, 32);
+        int k_chunk;
+        const int splits = gemm64_splits(m, k, &k_chunk);
+        const size_t need = (size_t)splits * (size_t)m * 64 * sizeof(float);
+        if (splits < 2 || !ws || ws_bytes < need) {
+            gemm64_kernel<32><<<mtiles, 256, 0, st>>>(A, lda, W, m, m_dev, k, k, nullptr, *epi_h, out, ldo);
+            EVAD_CHECK_LAUNCH();
+            return EVAD_OK;
+        }
+        gemm64_kernel<32><<<dim3(mtiles, splits), 256, 0, st>>>(A, lda, W, m, m_dev, k, k_chunk, (float*)ws, *epi_h, out, ldo);
+        EVAD_CHECK_LAUNCH();
+        gemm64_reduce_kernel<<<evad_cdiv(m * 16, 256), 256, 0, st>>>((const float*)ws, splits, m, m_dev, *epi_h, out, ldo);
         EVAD_CHECK_LAUNCH();
         return EVAD_OK;
     }

@@ -231,9 +231,10 @@ class Net(torch.nn.Module):
             key_bound = p._nv[0] * p._nv[1] * p._nv[2] * (num_graphs + 1)
             c_cap = max(1, min(cur["n_cap"], key_bound))
             e_cap = max(1, min(cur["e_cap"], c_cap * 64))
+            cin_next = layers[k].in_channel
             r = ops.voxel_pool(cur["x"], cur["pos"], cur["batch"], cur["rowptr"], cur["src"], cur["n_cap"], cur["n_dev"],
                                p._vs, p._nv, num_graphs, p._inv_wh, p.aggr, width, height, f[k + 1], append_pos=True,
-                               c_cap=c_cap, e_cap=e_cap, status=status)
+                               ldo=(cin_next + 3) // 4 * 4, c_cap=c_cap, e_cap=e_cap, status=status)
             counts[2 * k:2 * k + 1].copy_(r["n_out"])
             counts[2 * k + 1:2 * k + 2].copy_(r["num_edges"])
             pseudo = dict(pos=r["pos"], two_m=two_m_of(p.transform.max), clamp01=False)

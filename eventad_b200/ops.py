@@ -252,9 +252,10 @@ def gemm_epilogue(A, W, m_cap, m_dev, epi, out=None, k=None):
     if out is None:
         out = torch.empty((max(m_cap, 1), n), dtype=torch.float32, device=A.device)
     e = _epi_struct(**epi)
+    ws = _ws(L.evad_gemm_ws_bytes(m_cap, k, n), A.device)
     with _timed('gemm_epilogue'):
         check(L.evad_gemm_epilogue(ptr(A), A.stride(0), ptr(W), m_cap, ptr(m_dev), k, n, ctypes.byref(e), ptr(out),
-                                   out.stride(0), stream()), "evad_gemm_epilogue")
+                                   out.stride(0), ptr(ws), ws.numel(), stream()), "evad_gemm_epilogue")
     return out
 
 

@@ -161,9 +161,11 @@ int evad_spline_aggregate(const int32_t* rowptr, const int32_t* src, int64_t n, 
                           int64_t lda, uint32_t* status, void* stream);
 
 /* General SplineConv, step 2 (also Linear): out[m, :] = epi(A[m, :K] @ W[K, N]) in fp32 on the CUDA cores. */
+size_t evad_gemm_ws_bytes(int64_t m, int k, int n);
+/* ws (optional, evad_gemm_ws_bytes): split-K partial sums for small m; without it the kernel runs unsplit. */
 int evad_gemm_epilogue(const float* A, int64_t lda, const float* W /*[K,N] row-major*/, int64_t m,
                        const int32_t* m_dev, int k, int n, const evad_epilogue_t* epi_h, float* out, int ldo,
-                       void* stream);
+                       void* ws, size_t ws_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Voxel-grid pooling.
