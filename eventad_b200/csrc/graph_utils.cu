@@ -189,6 +189,43 @@ __global__ void __launch_bounds__(256) sample_concat_kernel(const float* __restr
     out[t] = v;
 }
 
+// Vectorised variant (C % 4 == 0, channel-last map 16-byte aligned): one thread per (node, channel quad).  The up to 8
+// trilinear taps are resolved once per thread and each tap is one 128-bit load; accumulation order per channel is the
+// order of sample_feat (dz, dy, dx; out-of-bounds taps skipped), so both kernels give identical bits.
+__global__ void __launch_bounds__(256) sample_concat_quad_kernel(const float* __restrict__ x, int ldx, int cx,
+                                                                 const float* __restrict__ pos, int ld_pos,
+                                                                 const int32_t* __restrict__ batch, int64_t n_cap,
+                                                                 const int32_t* __restrict__ n_dev, PoolSample S,
+                                                                 int append_pos, float* __restrict__ out, int ldo) {
+    const int quads = S.C >> 2;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t n = n_dev ? min((int64_t)*n_dev, n_cap) : n_cap;
+    const int64_t i = t / quads;
+    const int q = (int)(t - i * quads);
+    if (i >= n) return;
+    const float px = pos[i * ld_pos], py = pos[i * ld_pos + 1];
+    int tap[8];
+    float wgt[8];
+    sample_taps(S, px, py, (float)batch[i], tap, wgt);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4* f4 = reinterpret_cast<const float4*>(S.feat);
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        if (tap[k] < 0) continue;
+        const float4 v = __ldg(f4 + (int64_t)tap[k] * quads + q);
+        acc.x = fmaf(v.x, wgt[k], acc.x); acc.y = fmaf(v.y, wgt[k], acc.y);
+        acc.z = fmaf(v.z, wgt[k], acc.z); acc.w = fmaf(v.w, wgt[k], acc.w);
+    }
+    float* o = out + i * ldo;
+    o[cx + 4 * q] = acc.x; o[cx + 4 * q + 1] = acc.y; o[cx + 4 * q + 2] = acc.z; o[cx + 4 * q + 3] = acc.w;
+    if (q == 0) {
+        for (int c = 0; c < cx; c++) o[c] = x[i * ldx + c];
+        int c = cx + S.C;
+        if (append_pos) { o[c] = px; o[c + 1] = py; c += 2; }
+        for (; c < ldo; c++) o[c] = 0.f;
+    }
+}
+
 extern "C" int evad_sample_concat(const float* x, int ldx, int cx, const float* pos, int ld_pos, const int32_t* batch,
                                   int64_t n_cap, const int32_t* n_dev, const float* feat, int feat_b, int feat_h,
                                   int feat_w, int feat_c, float width, float height, int append_pos, float* out,
@@ -198,9 +235,38 @@ extern "C" int evad_sample_concat(const float* x, int ldx, int cx, const float* 
     if (ldo < cx + cs + (append_pos ? 2 : 0)) return EVAD_ERR_ARG;
     if (n_cap == 0) return EVAD_OK;
     PoolSample S{feat, feat_b, feat_h, feat_w, feat_c, width, height};
+    if (feat && feat_c >= 4 && feat_c % 4 == 0 && ((uintptr_t)feat & 15) == 0) {
+        const int64_t threads = n_cap * (feat_c / 4);
+        sample_concat_quad_kernel<<<evad_cdiv(threads, 256), 256, 0, (cudaStream_t)stream>>>(
+            x, ldx, cx, pos, ld_pos, batch, n_cap, n_dev, S, append_pos, out, ldo);
+        EVAD_CHECK_LAUNCH();
+        return EVAD_OK;
+    }
     sample_concat_kernel<<<evad_cdiv(n_cap * ldo, 256), 256, 0, (cudaStream_t)stream>>>(x, ldx, cx, pos, ld_pos, batch,
                                                                                       n_cap, n_dev, S, append_pos, out,
                                                                                       ldo);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ denormalize_pos
+// ev_tgn.py:11-16: (pos * [W, H, T] + 1e-3).int() -- fp32 multiply, fp32 add, truncation.
+__global__ void __launch_bounds__(256) denormalize_kernel(const float* __restrict__ pos, int ld_pos, int64_t n, float w,
+                                                          float h, float t, int32_t* __restrict__ out) {
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= 3 * n) return;
+    const int64_t i = k / 3;
+    const int d = (int)(k - 3 * i);
+    const float s = d == 0 ? w : (d == 1 ? h : t);
+    out[k] = (int32_t)__fadd_rn(__fmul_rn(s, pos[i * ld_pos + d]), 1e-3f);
+}
+
+extern "C" int evad_denormalize_pos(const float* pos, int ld_pos, int64_t n, int width, int height, int time_window,
+                                    int32_t* pos_int, void* stream) {
+    if (!pos || !pos_int || n < 0 || ld_pos < 3) return EVAD_ERR_ARG;
+    if (n == 0) return EVAD_OK;
+    denormalize_kernel<<<evad_cdiv(3 * n, 256), 256, 0, (cudaStream_t)stream>>>(pos, ld_pos, n, (float)width, (float)height,
+                                                                              (float)time_window, pos_int);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }

@@ -172,6 +172,112 @@ __global__ void __launch_bounds__(PL_THREADS) pool_reduce_kernel(
         __syncthreads();
         if (threadIdx.x < 2) x_out[(int64_t)c * ldo + ctot + threadIdx.x] = s_pos[threadIdx.x];
     }
+    for (int ch = ctot + (append_pos ? 2 : 0) + threadIdx.x; ch < ldo; ch += PL_THREADS) x_out[(int64_t)c * ldo + ch] = 0.f;
+}
+
+// Warp-per-voxel variant (cx % 4 == 0, S.C % 4 == 0, 16-byte aligned rows): lanes own channel quads (128-bit loads of
+// x rows and of the channel-last CNN map), the members of a chunk are resolved one per lane (node id, position,
+// trilinear taps) and broadcast through warp-private shared memory / shuffles.  Arithmetic and its order are those of
+// pool_reduce_kernel (serial fp32 position sums in ascending node order, taps accumulated dz,dy,dx), so both kernels
+// produce identical bits.
+#define PRW_WARPS 8
+#define PRW_MAXQ 2                                          // channel quads per lane: ctot <= 256
+
+__global__ void __launch_bounds__(PRW_WARPS * 32) pool_reduce_warp_kernel(
+    const uint32_t* __restrict__ sidx, const int32_t* __restrict__ seg_start, const int32_t* __restrict__ n_out,
+    const float* __restrict__ pos, int ld_pos, const int32_t* __restrict__ batch, const float* __restrict__ x, int ldx,
+    int cx, PoolSample S, int aggr_mean, float inv_w, float inv_h, int append_pos, float* __restrict__ x_out, int ldo,
+    float* __restrict__ pos_out, int32_t* __restrict__ batch_out) {
+    __shared__ int s_node[PRW_WARPS][32];
+    __shared__ __align__(16) int s_tap[PRW_WARPS][32][8];
+    __shared__ __align__(16) float s_wgt[PRW_WARPS][32][8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c = blockIdx.x * PRW_WARPS + warp;
+    if (c >= *n_out) return;
+    const int s0 = seg_start[c], s1 = seg_start[c + 1];
+    const int qx = cx >> 2, qf = S.feat ? (S.C >> 2) : 0, nq = qx + qf;
+    const float cntf = fmaxf((float)(s1 - s0), 1.f);
+    const float4* f4 = reinterpret_cast<const float4*>(S.feat);
+    float sx = 0.f, sy = 0.f, st = 0.f;
+    float4 acc[PRW_MAXQ];
+#pragma unroll
+    for (int u = 0; u < PRW_MAXQ; u++) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int p0 = s0; p0 < s1; p0 += 32) {
+        const int cnt = min(32, s1 - p0);
+        float px = 0.f, py = 0.f, pt = 0.f;
+        __syncwarp();
+        if (lane < cnt) {
+            const int64_t i = sidx[p0 + lane];
+            px = pos[i * ld_pos]; py = pos[i * ld_pos + 1]; pt = pos[i * ld_pos + 2];
+            s_node[warp][lane] = (int)i;
+            if (S.feat) sample_taps(S, px, py, (float)batch[i], s_tap[warp][lane], s_wgt[warp][lane]);
+        }
+        __syncwarp();
+        for (int m = 0; m < cnt; m++) {                      // serial fp32 sums in ascending node order (all lanes)
+            sx = __fadd_rn(sx, __shfl_sync(0xffffffffu, px, m));
+            sy = __fadd_rn(sy, __shfl_sync(0xffffffffu, py, m));
+            st = __fadd_rn(st, __shfl_sync(0xffffffffu, pt, m));
+        }
+#pragma unroll
+        for (int u = 0; u < PRW_MAXQ; u++) {
+            const int q = lane + 32 * u;
+            if (q >= nq) continue;
+            float4 a = acc[u];
+            for (int m = 0; m < cnt; m++) {
+                float4 v;
+                if (q < qx) {
+                    v = __ldg(reinterpret_cast<const float4*>(x + (int64_t)s_node[warp][m] * ldx) + q);
+                } else {
+                    v = make_float4(0.f, 0.f, 0.f, 0.f);
+                    const int4 t0 = *reinterpret_cast<const int4*>(&s_tap[warp][m][0]);
+                    const int4 t1 = *reinterpret_cast<const int4*>(&s_tap[warp][m][4]);
+                    const float4 w0 = *reinterpret_cast<const float4*>(&s_wgt[warp][m][0]);
+                    const float4 w1 = *reinterpret_cast<const float4*>(&s_wgt[warp][m][4]);
+                    const int tp[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+                    const float wg[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+                    float4 fv[8];
+#pragma unroll
+                    for (int k = 0; k < 8; k++)
+                        if (tp[k] >= 0) fv[k] = __ldg(f4 + (int64_t)tp[k] * qf + (q - qx));
+#pragma unroll
+                    for (int k = 0; k < 8; k++) {
+                        if (tp[k] < 0) continue;
+                        v.x = fmaf(fv[k].x, wg[k], v.x); v.y = fmaf(fv[k].y, wg[k], v.y);
+                        v.z = fmaf(fv[k].z, wg[k], v.z); v.w = fmaf(fv[k].w, wg[k], v.w);
+                    }
+                }
+                if (aggr_mean) {
+                    a.x = __fadd_rn(a.x, v.x); a.y = __fadd_rn(a.y, v.y); a.z = __fadd_rn(a.z, v.z); a.w = __fadd_rn(a.w, v.w);
+                } else if (p0 == s0 && m == 0) {
+                    a = v;
+                } else {
+                    a.x = fmaxf(a.x, v.x); a.y = fmaxf(a.y, v.y); a.z = fmaxf(a.z, v.z); a.w = fmaxf(a.w, v.w);
+                }
+            }
+            acc[u] = a;
+        }
+    }
+    float mx = __fdiv_rn(sx, cntf), my = __fdiv_rn(sy, cntf);
+    const float mt = __fdiv_rn(st, cntf);
+    mx = __fmul_rn(div_floor_f(__fadd_rn(mx, 1e-5f), inv_w), inv_w);
+    my = __fmul_rn(div_floor_f(__fadd_rn(my, 1e-5f), inv_h), inv_h);
+    if (lane == 0) {
+        pos_out[(int64_t)c * 3] = mx;
+        pos_out[(int64_t)c * 3 + 1] = my;
+        pos_out[(int64_t)c * 3 + 2] = mt;
+        batch_out[c] = batch[sidx[s1 - 1]];
+    }
+    float* o = x_out + (int64_t)c * ldo;
+#pragma unroll
+    for (int u = 0; u < PRW_MAXQ; u++) {
+        const int q = lane + 32 * u;
+        if (q >= nq) continue;
+        float4 a = acc[u];
+        if (aggr_mean) { a.x = __fdiv_rn(a.x, cntf); a.y = __fdiv_rn(a.y, cntf); a.z = __fdiv_rn(a.z, cntf); a.w = __fdiv_rn(a.w, cntf); }
+        *reinterpret_cast<float4*>(o + 4 * q) = a;
+    }
+    if (append_pos && lane < 2) o[4 * nq + lane] = lane ? my : mx;
+    for (int ch = 4 * nq + (append_pos ? 2 : 0) + lane; ch < ldo; ch += 32) o[ch] = 0.f;     // row padding
 }
 
 // ------------------------------------------------------------------------------------------------ coarse edges
@@ -331,9 +437,18 @@ extern "C" int evad_voxel_pool(const evad_pool_params_t* p, int64_t n_cap, const
     pool_relabel_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(skey, sidx, w.flag, w.excl, n_cap, G.key_bound, cluster,
                                                          w.seg_start, n_out);
     EVAD_CHECK_LAUNCH();
-    pool_reduce_kernel<<<(unsigned)c_cap, PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, pos, ld_pos, batch, x, ldx, cx, S,
-                                                              p->aggr_mean, p->inv_w, p->inv_h, p->append_pos, x_out,
-                                                              ldo, pos_out, batch_out);
+    const bool quad_ok = cx % 4 == 0 && ldx % 4 == 0 && ldo % 4 == 0 && (((uintptr_t)x | (uintptr_t)x_out) & 15) == 0 &&
+                         (!p->feat || (p->feat_c % 4 == 0 && ((uintptr_t)p->feat & 15) == 0)) &&
+                         ctot <= 128 * PRW_MAXQ;
+    if (quad_ok) {
+        pool_reduce_warp_kernel<<<evad_cdiv(c_cap, PRW_WARPS), PRW_WARPS * 32, 0, st>>>(
+            sidx, w.seg_start, n_out, pos, ld_pos, batch, x, ldx, cx, S, p->aggr_mean, p->inv_w, p->inv_h, p->append_pos,
+            x_out, ldo, pos_out, batch_out);
+    } else {
+        pool_reduce_kernel<<<(unsigned)c_cap, PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, pos, ld_pos, batch, x, ldx, cx,
+                                                                  S, p->aggr_mean, p->inv_w, p->inv_h, p->append_pos,
+                                                                  x_out, ldo, pos_out, batch_out);
+    }
     EVAD_CHECK_LAUNCH();
     if (want_edges) {
         pool_edges_kernel<false><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, src_in,

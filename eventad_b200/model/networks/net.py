@@ -207,11 +207,7 @@ class Net(torch.nn.Module):
         gc = g.graph_creators
         gc.batch_size = max(gc.batch_size, num_graphs)
         gc.reset()
-        key = (int(width), int(height), int(time_window), dev)
-        if getattr(self, "_denorm_key", None) != key:          # cached: torch.tensor(list, device=...) cannot be captured
-            self._denorm = torch.tensor([int(width), int(height), int(time_window)], device=dev).view(1, -1)
-            self._denorm_key = key
-        pos_int = (self._denorm * pos + 1e-3).int()
+        pos_int = ops.denormalize_pos(pos, width, height, time_window)
         graph = gc.build_csr(batch_i32, pos_int)
         gc.max_index, gc.all_timestamps, gc._history = n, pos_int[:, 2], [(batch_i32, pos_int, 0)]   # AsyncGraph bookkeeping
         status = gc._status
@@ -234,9 +230,8 @@ class Net(torch.nn.Module):
             cin_next = layers[k].in_channel
             r = ops.voxel_pool(cur["x"], cur["pos"], cur["batch"], cur["rowptr"], cur["src"], cur["n_cap"], cur["n_dev"],
                                p._vs, p._nv, num_graphs, p._inv_wh, p.aggr, width, height, f[k + 1], append_pos=True,
-                               ldo=(cin_next + 3) // 4 * 4, c_cap=c_cap, e_cap=e_cap, status=status)
-            counts[2 * k:2 * k + 1].copy_(r["n_out"])
-            counts[2 * k + 1:2 * k + 2].copy_(r["num_edges"])
+                               ldo=(cin_next + 3) // 4 * 4, c_cap=c_cap, e_cap=e_cap, status=status,
+                               n_out=counts[2 * k:2 * k + 1], num_edges=counts[2 * k + 1:2 * k + 2])
             pseudo = dict(pos=r["pos"], two_m=two_m_of(p.transform.max), clamp01=False)
             xo = layers[k].run_fused(r["x"], r["rowptr"], r["src"], c_cap, r["n_out"], pseudo, status)
             cur = dict(x=xo, pos=r["pos"], batch=r["batch"], rowptr=r["rowptr"], src=r["src"], n_cap=c_cap,

@@ -104,6 +104,16 @@ def cartesian(pos, edge_index, two_m: float, clamp01: bool, num_edges=None, dims
     return out
 
 
+def denormalize_pos(pos, width, height, time_window):
+    """ev_tgn.py:11-16 in one launch: (pos * [W, H, T] + 1e-3).int()."""
+    L = _lib.lib()
+    pos = pos.contiguous()
+    out = torch.empty((pos.shape[0], 3), dtype=torch.int32, device=pos.device)
+    check(L.evad_denormalize_pos(ptr(pos), pos.stride(0), pos.shape[0], int(width), int(height), int(time_window), ptr(out),
+                                 stream()), "evad_denormalize_pos")
+    return out
+
+
 def to_channel_last(feat: torch.Tensor) -> torch.Tensor:
     """[B,C,h,w] -> contiguous [B,h,w,C] (the layout the sampling kernels read)."""
     return feat.permute(0, 2, 3, 1).contiguous()
@@ -267,7 +277,8 @@ def pool_geometry(voxel_size4: torch.Tensor, end4: torch.Tensor):
 
 
 def voxel_pool(x, pos, batch_i32, rowptr, src, n_cap, n_dev, voxel_size, nv, batch_size, inv_wh, aggr, width, height,
-               feat_nhwc=None, append_pos=False, ldo=None, c_cap=None, e_cap=None, status=None):
+               feat_nhwc=None, append_pos=False, ldo=None, c_cap=None, e_cap=None, status=None, n_out=None,
+               num_edges=None):
     """Returns dict(cluster, n_out, x, pos, batch, rowptr, src, num_edges); all arrays sized by c_cap / e_cap."""
     L = _lib.lib()
     dev = pos.device
@@ -283,15 +294,17 @@ def voxel_pool(x, pos, batch_i32, rowptr, src, n_cap, n_dev, voxel_size, nv, bat
     e_cap = max(int(e_cap), 1)
     status = status if status is not None else new_status(dev)
     cluster = torch.empty(max(n_cap, 1), dtype=torch.int32, device=dev)
-    n_out = torch.zeros(1, dtype=torch.int32, device=dev)
-    x_out = torch.empty((c_cap, ldo), dtype=torch.float32, device=dev)
-    if ldo > ctot:
-        x_out[:, ctot:].zero_()
+    if n_out is None:                                # callers may pass int32[1] cells (views of one counter block)
+        n_out = torch.zeros(1, dtype=torch.int32, device=dev)
+    x_out = torch.empty((c_cap, ldo), dtype=torch.float32, device=dev)      # row padding is zeroed by the kernel
     pos_out = torch.empty((c_cap, 3), dtype=torch.float32, device=dev)
     batch_out = torch.empty(c_cap, dtype=torch.int32, device=dev)
-    rowptr_out = torch.zeros(c_cap + 1, dtype=torch.int32, device=dev) if want_edges else None
+    rowptr_out = torch.empty(c_cap + 1, dtype=torch.int32, device=dev) if want_edges else None
     src_out = torch.empty(e_cap, dtype=torch.int32, device=dev) if want_edges else None
-    num_edges = torch.zeros(1, dtype=torch.int32, device=dev) if want_edges else None
+    if not want_edges:
+        num_edges = None
+    elif num_edges is None:
+        num_edges = torch.zeros(1, dtype=torch.int32, device=dev)
     fb, fh, fw, fc = (feat_nhwc.shape if feat_nhwc is not None else (0, 0, 0, 0))
     P = PoolParamsT(size_x=float(voxel_size[0]), size_y=float(voxel_size[1]), size_t=float(voxel_size[2]), nvx=nv[0],
                     nvy=nv[1], nvt=nv[2], batch_size=int(batch_size), inv_w=float(inv_wh[0]), inv_h=float(inv_wh[1]),

@@ -218,6 +218,9 @@ int evad_csr_to_coo(const int32_t* rowptr, const int32_t* src, int64_t n_cap, co
  * out[e, d] = (pos[row[e], d] - pos[col[e], d]) / two_m + 0.5 for d < dims. */
 int evad_cartesian(const float* pos, int ld_pos, int dims, const int64_t* edge_index, int64_t stride, int64_t e_cap,
                    const int32_t* num_edges, float two_m, int clamp01, float* out, void* stream);
+/* denormalize_pos (src/dagr/model/layers/ev_tgn.py:11-16): pos_int[i,d] = (int)(pos[i,d] * {W,H,T}[d] + 1e-3), fp32. */
+int evad_denormalize_pos(const float* pos, int ld_pos, int64_t n, int width, int height, int time_window,
+                         int32_t* pos_int, void* stream);
 /* sampling_skip + cat(x, pos[:, :2]) (net.py:15-17,116,122-123): out[i] = [x[i,:cx] | grid_sample(feat)(feat_c) |
  * pos_x, pos_y | zero padding]; feat is CHANNEL-LAST [feat_b, feat_h, feat_w, feat_c] or NULL. */
 int evad_sample_concat(const float* x, int ldx, int cx, const float* pos, int ld_pos, const int32_t* batch,
