@@ -56,6 +56,118 @@ __global__ void __launch_bounds__(AG_THREADS) spline_agg_kernel(const int32_t* _
     }
 }
 
+// Variant for 16-byte aligned rows (ldx % 4 == 0): the source rows of up to 16 in-edges are staged in warp-private
+// shared memory with 128-bit loads that are all in flight together (one memory latency per chunk instead of one per
+// edge); the taps are then walked in order and each tap row is summed in registers from the staged rows and written
+// straight to A (no shared accumulators, no zero fill / copy-out pass).  Per tap the contributions are added in
+// ascending edge order with separate fp32 multiply and add, exactly like spline_agg_kernel, so both give the same bits.
+#define AG2_WARPS 8
+#define AG2_EDGES 16
+
+template <int CPL>
+__global__ void __launch_bounds__(AG2_WARPS * 32) spline_agg2_kernel(const int32_t* __restrict__ rowptr,
+                                                                     const int32_t* __restrict__ src, int64_t n,
+                                                                     const int32_t* __restrict__ n_dev,
+                                                                     const float* __restrict__ x, int ldx, int cin,
+                                                                     EvadPseudo P, EvadSplineMode M, float* __restrict__ A,
+                                                                     int64_t lda, uint32_t* __restrict__ status) {
+    extern __shared__ __align__(16) float ag2_rows[];         // [AG2_WARPS][AG2_EDGES][ldx]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ntap = M.ks * M.ks;
+    const int qpr = ldx >> 2;                                 // 128-bit quads per row
+    float* xs = ag2_rows + (size_t)warp * AG2_EDGES * ldx;
+    const int64_t nn = n_dev ? min((int64_t)*n_dev, n) : n;
+    const int64_t stride = (int64_t)gridDim.x * AG2_WARPS;
+    for (int64_t i = (int64_t)blockIdx.x * AG2_WARPS + warp; i < nn; i += stride) {
+        const int r0 = rowptr[i], r1 = rowptr[i + 1];
+        float* a = A + i * lda;
+        bool first = true;
+        for (int e0 = r0; e0 < r1 || first; e0 += AG2_EDGES) {
+            const int cnt = max(0, min(AG2_EDGES, r1 - e0));
+            int j = 0, k[4] = {-1, -1, -1, -1};
+            float w[4] = {0.f, 0.f, 0.f, 0.f};
+            if (lane < cnt) {
+                j = src[e0 + lane];
+                float ax, ay;
+                evad_pseudo(P, e0 + lane, j, (int)i, &ax, &ay);
+                evad_taps(M, ax, ay, k, w, status);
+            }
+            __syncwarp();
+            for (int base = 0; base < cnt * qpr; base += 32) {   // uniform trip count: every lane takes part in the shuffle
+                const int idx = base + lane;
+                const bool ok = idx < cnt * qpr;
+                const int e = ok ? idx / qpr : 0, q = idx - e * qpr;
+                const int jj = __shfl_sync(0xffffffffu, j, e);
+                if (ok)
+                    reinterpret_cast<float4*>(xs)[idx] = __ldg(reinterpret_cast<const float4*>(x + (int64_t)jj * ldx) + q);
+            }
+            __syncwarp();
+            for (int tap = 0; tap < ntap; tap++) {
+                const float wt = k[0] == tap ? w[0] : (k[1] == tap ? w[1] : (k[2] == tap ? w[2] : w[3]));
+                const bool hit = k[0] == tap || k[1] == tap || k[2] == tap || k[3] == tap;
+                unsigned mask = __ballot_sync(0xffffffffu, hit);
+                float acc[CPL];
+#pragma unroll
+                for (int u = 0; u < CPL; u++) acc[u] = 0.f;
+                const bool any = mask != 0;
+                while (mask) {
+                    const int e = __ffs(mask) - 1;
+                    mask &= mask - 1;
+                    const float we = __shfl_sync(0xffffffffu, wt, e);
+                    const float* xr = xs + e * ldx;
+#pragma unroll
+                    for (int u = 0; u < CPL; u++) {
+                        const int c = lane + 32 * u;
+                        if (c < cin) acc[u] = __fadd_rn(acc[u], __fmul_rn(we, xr[c]));
+                    }
+                }
+                float* at = a + tap * cin;
+                if (first) {
+#pragma unroll
+                    for (int u = 0; u < CPL; u++) {
+                        const int c = lane + 32 * u;
+                        if (c < cin) at[c] = acc[u];
+                    }
+                } else if (any) {
+#pragma unroll
+                    for (int u = 0; u < CPL; u++) {
+                        const int c = lane + 32 * u;
+                        if (c < cin) at[c] = __fadd_rn(at[c], acc[u]);
+                    }
+                }
+            }
+            first = false;
+            __syncwarp();
+        }
+        const float* xi = x + i * ldx;
+#pragma unroll
+        for (int u = 0; u < CPL; u++) {
+            const int c = lane + 32 * u;
+            if (c < cin) a[ntap * cin + c] = xi[c];
+        }
+    }
+}
+
+template <int CPL>
+static int launch_agg2(const int32_t* rowptr, const int32_t* src, int64_t n, const int32_t* n_dev, const float* x, int ldx,
+                       int cin, const evad_pseudo_t& P, const evad_spline_mode_t& M, float* A, int64_t lda,
+                       uint32_t* status, cudaStream_t st) {
+    const size_t smem = (size_t)AG2_WARPS * AG2_EDGES * ldx * sizeof(float);
+    static size_t attr_bytes = 0;
+    if (smem > attr_bytes) {
+        if (cudaFuncSetAttribute(spline_agg2_kernel<CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
+            cudaSuccess)
+            return EVAD_ERR_LAUNCH;
+        attr_bytes = smem;
+    }
+    const int64_t want = (n + AG2_WARPS - 1) / AG2_WARPS;
+    const int64_t cap = 148 * 4;
+    const int grid = (int)(want < cap ? want : cap);
+    spline_agg2_kernel<CPL><<<grid, AG2_WARPS * 32, smem, st>>>(rowptr, src, n, n_dev, x, ldx, cin, P, M, A, lda, status);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
 extern "C" int evad_spline_aggregate(const int32_t* rowptr, const int32_t* src, int64_t n, const int32_t* n_dev,
                                      const float* x, int ldx, int cin, const evad_pseudo_t* pseudo_h,
                                      const evad_spline_mode_t* mode_h, float* A, int64_t lda, uint32_t* status,
@@ -65,6 +177,17 @@ extern "C" int evad_spline_aggregate(const int32_t* rowptr, const int32_t* src, 
     if (n <= 0) return EVAD_OK;
     const int ntap = mode_h->ks * mode_h->ks;
     if (lda < (int64_t)(ntap + 1) * cin) return EVAD_ERR_ARG;
+    if (ldx % 4 == 0 && ((uintptr_t)x & 15) == 0 && cin <= 160 && (size_t)AG2_WARPS * AG2_EDGES * ldx * 4 <= 200 * 1024) {
+        const int cpl = (cin + 31) / 32;
+        cudaStream_t st = (cudaStream_t)stream;
+        switch (cpl) {
+        case 1: return launch_agg2<1>(rowptr, src, n, n_dev, x, ldx, cin, *pseudo_h, *mode_h, A, lda, status, st);
+        case 2: return launch_agg2<2>(rowptr, src, n, n_dev, x, ldx, cin, *pseudo_h, *mode_h, A, lda, status, st);
+        case 3: return launch_agg2<3>(rowptr, src, n, n_dev, x, ldx, cin, *pseudo_h, *mode_h, A, lda, status, st);
+        case 4: return launch_agg2<4>(rowptr, src, n, n_dev, x, ldx, cin, *pseudo_h, *mode_h, A, lda, status, st);
+        default: return launch_agg2<5>(rowptr, src, n, n_dev, x, ldx, cin, *pseudo_h, *mode_h, A, lda, status, st);
+        }
+    }
     const size_t smem = (size_t)AG_WARPS * ntap * cin * sizeof(float);
     if (smem > 200 * 1024) return EVAD_ERR_UNSUPPORTED;
     static bool attr_done = false;

@@ -269,6 +269,29 @@ def gemm_epilogue(A, W, m_cap, m_dev, epi, out=None, k=None):
     return out
 
 
+def split_tf32(W):
+    """W fp32 -> (hi, lo) with hi = tf32(W), lo = tf32(W - hi): the operand form of evad_gemm64_tc."""
+    L = _lib.lib()
+    W = W.detach().float().contiguous()
+    hi, lo = torch.empty_like(W), torch.empty_like(W)
+    check(L.evad_split_tf32(ptr(W), W.numel(), ptr(hi), ptr(lo), stream()), "evad_split_tf32")
+    return hi, lo
+
+
+def gemm64_tc(A, Whi, Wlo, m_cap, m_dev, epi, out=None, k=None):
+    """out = epi(A[:, :k] @ W) on the tensor cores (3xTF32, fp32 accuracy); W = Whi + Wlo, [k, 64] row-major."""
+    L = _lib.lib()
+    k = k or Whi.shape[0]
+    if out is None:
+        out = torch.empty((max(m_cap, 1), 64), dtype=torch.float32, device=A.device)
+    e = _epi_struct(**epi)
+    ws = _ws(L.evad_gemm64_tc_ws_bytes(m_cap, k), A.device)
+    with _timed('gemm_epilogue'):
+        check(L.evad_gemm64_tc(ptr(A), A.stride(0), ptr(Whi), ptr(Wlo), m_cap, ptr(m_dev), k, ctypes.byref(e), ptr(out),
+                               out.stride(0), ptr(ws), ws.numel(), stream()), "evad_gemm64_tc")
+    return out
+
+
 # --------------------------------------------------------------------------------------------------- pooling
 def pool_geometry(voxel_size4: torch.Tensor, end4: torch.Tensor):
     """num_voxels per dimension exactly as torch_cluster computes them: ((end - start) / size).long() + 1, start = 0."""

@@ -167,6 +167,17 @@ int evad_gemm_epilogue(const float* A, int64_t lda, const float* W /*[K,N] row-m
                        const int32_t* m_dev, int k, int n, const evad_epilogue_t* epi_h, float* out, int ldo,
                        void* ws, size_t ws_bytes, void* stream);
 
+/* The same contraction on the tensor cores for N = 64 (csrc/gemm_tc.cu): every product is split into TF32 parts
+ * (a_hi + a_lo)(w_hi + w_lo) and accumulated in fp32 as a_lo*w_hi + a_hi*w_lo + a_hi*w_hi, so the result keeps fp32
+ * accuracy (rtol 1e-4 / atol 1e-5 parity bar).  evad_split_tf32 prepares w_hi / w_lo once per weight
+ * (spline_conv.py:64-78 `weight` [K,Cin,Cout] stacked with `lin.weight`^T, see MySplineConv.wcat).
+ * Requirements: lda % 4 == 0, A / Whi / Wlo 16-byte aligned, out 16-byte aligned with ldo % 4 == 0. */
+int evad_split_tf32(const float* w, int64_t n, float* hi, float* lo, void* stream);
+size_t evad_gemm64_tc_ws_bytes(int64_t m, int k);
+int evad_gemm64_tc(const float* A, int64_t lda, const float* Whi /*[K,64]*/, const float* Wlo /*[K,64]*/, int64_t m,
+                   const int32_t* m_dev, int k, const evad_epilogue_t* epi_h, float* out, int ldo, void* ws,
+                   size_t ws_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------------
  * Voxel-grid pooling.
  * Replaces Pooling.forward (src/dagr/model/layers/pooling.py:51-97): torch_cluster.grid_cluster on [x,y,t,batch],
