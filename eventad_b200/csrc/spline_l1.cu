@@ -1,0 +1,318 @@
+// eventad_b200/csrc/spline_l1.cu -- full-resolution SplineConv (layer 1: 19->16 and 16->16 on the event graph) as
+// tap aggregation in registers + tensor-core contraction, one persistent CTA per SM.
+//
+// Reference path replaced per call (paths relative to /root/reference/src/dagr/model):
+//   layers/spline_conv.py:39-47  message_lut (gather x_j, gather lut[ix,iy] = sum_s b_s W[k_s], einsum)
+//   PyG propagate sum aggregation + layers/spline_conv.py:72-76 root weight
+//   layers/conv.py:23-28,47-56   eval BatchNorm, activation, skip Linear + BatchNorm
+//
+// Why not the LUT gather (csrc/spline_small.cu): every edge needs its own Cin x Cout matrix, 1280 B of shared-memory
+// reads per edge -- ncu (profiles/r01_summary.md) shows that kernel bound by the LDS pipe and instruction issue, with
+// DRAM at 1 % of peak.  Here the sum is re-associated:
+//     out_i = sum_e (sum_s b_{e,s} W[k_{e,s}])^T x_e  =  sum_k W[k]^T (sum_e b_{e,k} x_e)  =  W_cat^T P_i
+// (1) P_i[k] = sum_e b_{e,k} x_e over the <= 15 kernel taps the integer pixel lattice can reach: one thread per
+//     (node, channel quad), 60 accumulators in registers, per edge one 128-bit gather of the source row and the 16 tap
+//     weights of the edge's lattice class (a 6.5 KB shared table); no per-edge weight matrices.
+// (2) out tile [128 nodes x 16] = P tile [128 x 16*Cin_pad] @ W_cat on the tensor cores (mma.sync m16n8k8, 3xTF32 so
+//     that fp32 accuracy is kept; W_cat hi/lo parts stay in shared memory for the life of the persistent CTA), root
+//     weight as one more tap slot, the skip Linear as a second small product, BatchNorm / skip add / ReLU in the epilogue.
+// The lattice class of every edge (the reference's (ix, iy) LUT index, computed with its fp32 arithmetic) is written
+// once per graph by evad_edge_class and shared by both convolutions of the layer.
+#include "spline_common.cuh"
+
+#define L1_NODES 128                  // nodes per tile
+#define L1_SLOTS 16                   // 15 tap slots + root
+#define L1_TW_LD 20                   // tap-weight table row stride (floats): consecutive classes hit distinct bank quads
+#define L1_LDB 24                     // W_cat row stride in shared memory (16 outputs + 8): bank = 8*t + g
+#define L1_LDC 20                     // C tile row stride
+
+// ------------------------------------------------------------------------------------------------ edge classes
+__global__ void __launch_bounds__(256) edge_class_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ src,
+                                                         int64_t n, EvadPseudo P, EvadSplineMode M,
+                                                         uint8_t* __restrict__ cls, uint32_t* __restrict__ status) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int r0 = rowptr[i], r1 = rowptr[i + 1];
+    for (int e = r0; e < r1; e++) {
+        float ax, ay;
+        evad_pseudo(P, e, src[e], (int)i, &ax, &ay);
+        int ix, iy;
+        evad_lut_index(M, ax, ay, &ix, &iy, status);
+        cls[e] = (uint8_t)(ix * M.ny + iy);
+    }
+}
+
+extern "C" int evad_edge_class(const int32_t* rowptr, const int32_t* src, int64_t n, const evad_pseudo_t* pseudo_h,
+                               const evad_spline_mode_t* mode_h, uint8_t* cls, uint32_t* status, void* stream) {
+    if (!rowptr || !src || !pseudo_h || !mode_h || !cls || !status) return EVAD_ERR_ARG;
+    if (!mode_h->use_lut || mode_h->nx * mode_h->ny > 256) return EVAD_ERR_UNSUPPORTED;
+    if (n <= 0) return EVAD_OK;
+    edge_class_kernel<<<evad_cdiv(n, 256), 256, 0, (cudaStream_t)stream>>>(rowptr, src, n, *pseudo_h, *mode_h, cls, status);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
+__device__ __forceinline__ uint32_t l1_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return r;
+}
+
+__device__ __forceinline__ void l1_mma(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+// A fragment (rows g / g+8 of an m16 tile, columns kk+t / kk+t+4) split into TF32 hi / lo parts
+__device__ __forceinline__ void l1_load_a(const float* __restrict__ As, int lda, int row, int kk, int g, int t,
+                                          uint32_t (&ah)[4], uint32_t (&al)[4]) {
+    const float* p = As + (row + g) * lda + kk + t;
+    const float v[4] = {p[0], p[8 * lda], p[4], p[8 * lda + 4]};
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        ah[q] = l1_tf32(v[q]);
+        al[q] = l1_tf32(__fsub_rn(v[q], __uint_as_float(ah[q])));
+    }
+}
+
+__device__ __forceinline__ float4 l1_epi(const evad_epilogue_t& E, float4 v, int64_t row, int c0) {
+    float r[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int b = 0; b < 4; b++) {
+        if (E.scale) r[b] = __fmul_rn(r[b], E.scale[c0 + b]);
+        if (E.shift) r[b] = __fadd_rn(r[b], E.shift[c0 + b]);
+        if (E.addend) r[b] = __fadd_rn(r[b], E.addend[row * E.ld_add + c0 + b]);
+        if (E.relu) r[b] = fmaxf(r[b], 0.f);
+    }
+    return make_float4(r[0], r[1], r[2], r[3]);
+}
+
+template <int CP>
+struct L1Cfg {
+    static constexpr int QN = CP / 4;                        // channel quads per node = threads per node
+    static constexpr int THREADS = L1_NODES * QN;
+    static constexpr int KR = 8 * CP;                        // P columns staged per round (8 slots)
+    static constexpr int LDA = KR + ((20 - KR % 32) + 32) % 32;   // == 20 (mod 32): conflict-free fragment loads
+    static constexpr int KTOT = L1_SLOTS * CP;
+    static constexpr int KS = (CP + 7) / 8 * 8;              // rows of the skip weight (zero padded)
+    static constexpr int A_FLOATS = L1_NODES * LDA;
+    static constexpr int B_FLOATS = KTOT * L1_LDB;
+    static constexpr int S_FLOATS = KS * L1_LDB;
+    static constexpr int C_FLOATS = 3 * L1_NODES * L1_LDC;
+    static size_t smem_bytes(int ncls) {
+        return (size_t)(A_FLOATS + 2 * B_FLOATS + 2 * S_FLOATS + C_FLOATS + ncls * L1_TW_LD) * sizeof(float);
+    }
+};
+
+template <int CP>
+__global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 1) spline_l1_kernel(
+    const int32_t* __restrict__ rowptr, const int32_t* __restrict__ src, const uint8_t* __restrict__ cls, int64_t n,
+    const float* __restrict__ x, int ldx, const float* __restrict__ tapw, int ncls, const float* __restrict__ Whi,
+    const float* __restrict__ Wlo, const float* __restrict__ Shi, const float* __restrict__ Slo, evad_epilogue_t E,
+    float* __restrict__ out, int ldo, evad_epilogue_t ES, float* __restrict__ skip_out, int ld_skip) {
+    using C = L1Cfg<CP>;
+    constexpr int QN = C::QN, LDA = C::LDA, KR = C::KR;
+    extern __shared__ __align__(16) float l1_smem[];
+    float* As = l1_smem;
+    float* Bh = As + C::A_FLOATS;
+    float* Bl = Bh + C::B_FLOATS;
+    float* Sh = Bl + C::B_FLOATS;
+    float* Sl = Sh + C::S_FLOATS;
+    float* Cs = Sl + C::S_FLOATS;
+    float* tw = Cs + C::C_FLOATS;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const bool has_skip = Shi != nullptr;
+
+    // one-time staging: weights (hi / lo), skip weights, tap-weight table; A tile zeroed (its pad columns stay zero)
+    for (int idx = tid; idx < C::KTOT * 4; idx += C::THREADS) {
+        const int r = idx >> 2, c4 = idx & 3;
+        *reinterpret_cast<float4*>(Bh + r * L1_LDB + 4 * c4) = __ldg(reinterpret_cast<const float4*>(Whi) + idx);
+        *reinterpret_cast<float4*>(Bl + r * L1_LDB + 4 * c4) = __ldg(reinterpret_cast<const float4*>(Wlo) + idx);
+    }
+    if (has_skip)
+        for (int idx = tid; idx < C::KS * 4; idx += C::THREADS) {
+            const int r = idx >> 2, c4 = idx & 3;
+            *reinterpret_cast<float4*>(Sh + r * L1_LDB + 4 * c4) = __ldg(reinterpret_cast<const float4*>(Shi) + idx);
+            *reinterpret_cast<float4*>(Sl + r * L1_LDB + 4 * c4) = __ldg(reinterpret_cast<const float4*>(Slo) + idx);
+        }
+    for (int idx = tid; idx < ncls * 4; idx += C::THREADS) {
+        const int r = idx >> 2, c4 = idx & 3;
+        *reinterpret_cast<float4*>(tw + r * L1_TW_LD + 4 * c4) = __ldg(reinterpret_cast<const float4*>(tapw) + idx);
+    }
+    for (int idx = tid; idx < C::A_FLOATS; idx += C::THREADS) As[idx] = 0.f;
+    __syncthreads();
+
+    const int node_l = tid / QN, q = tid - node_l * QN;
+    const int mt = warp & 7, kp = warp >> 3;                 // MMA role of warps 0..15: m16 tile, k half
+    const int64_t ntiles = (n + L1_NODES - 1) / L1_NODES;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        // ---------------------------------------------------------------- (1) tap aggregation in registers
+        const int64_t i = tile * L1_NODES + node_l;
+        const bool valid = i < n;
+        float4 acc[L1_SLOTS - 1];
+#pragma unroll
+        for (int s = 0; s < L1_SLOTS - 1; s++) acc[s] = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 xroot = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (valid) {
+            const int r0 = rowptr[i];
+            const int deg = rowptr[i + 1] - r0;
+            xroot = __ldg(reinterpret_cast<const float4*>(x + i * ldx) + q);
+            int c_next = 0, j_n2 = 0;
+            float4 x_next = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (deg > 0) {
+                c_next = cls[r0];
+                x_next = __ldg(reinterpret_cast<const float4*>(x + (int64_t)src[r0] * ldx) + q);
+                if (deg > 1) j_n2 = src[r0 + 1];
+            }
+            for (int e = 0; e < deg; e++) {
+                const float4 xq = x_next;
+                const float* twr = tw + c_next * L1_TW_LD;
+                if (e + 1 < deg) {                           // next edge's class and row in flight during the FMAs
+                    c_next = cls[r0 + e + 1];
+                    x_next = __ldg(reinterpret_cast<const float4*>(x + (int64_t)j_n2 * ldx) + q);
+                    if (e + 2 < deg) j_n2 = src[r0 + e + 2];
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const float4 w4 = *reinterpret_cast<const float4*>(twr + 4 * u);
+                    const float w[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+                    for (int b = 0; b < 4; b++) {
+                        const int s = 4 * u + b;
+                        if (s < L1_SLOTS - 1) {
+                            acc[s].x = fmaf(w[b], xq.x, acc[s].x); acc[s].y = fmaf(w[b], xq.y, acc[s].y);
+                            acc[s].z = fmaf(w[b], xq.z, acc[s].z); acc[s].w = fmaf(w[b], xq.w, acc[s].w);
+                        }
+                    }
+                }
+            }
+        }
+        // ---------------------------------------------------------------- (2) contraction, two rounds of 8 slots
+        float cacc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+        float sacc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll
+        for (int round = 0; round < 2; round++) {
+            float* arow = As + node_l * LDA + 4 * q;
+#pragma unroll
+            for (int s = 0; s < 8; s++) {
+                const int slot = round * 8 + s;
+                *reinterpret_cast<float4*>(arow + s * CP) = slot < L1_SLOTS - 1 ? acc[slot < L1_SLOTS - 1 ? slot : 0] : xroot;
+            }
+            __syncthreads();
+            if (warp < 16) {
+                float part[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll 2
+                for (int s = 0; s < CP / 2; s++) {
+                    const int kk = (kp * (CP / 2) + s) * 8;
+                    uint32_t ah[4], al[4];
+                    l1_load_a(As, LDA, mt * 16, kk, g, t, ah, al);
+                    const int krow = round * KR + kk;
+#pragma unroll
+                    for (int nt = 0; nt < 2; nt++) {
+                        const int o0 = (krow + t) * L1_LDB + nt * 8 + g, o1 = o0 + 4 * L1_LDB;
+                        const uint32_t bh[2] = {__float_as_uint(Bh[o0]), __float_as_uint(Bh[o1])};
+                        const uint32_t bl[2] = {__float_as_uint(Bl[o0]), __float_as_uint(Bl[o1])};
+                        l1_mma(part[nt], al, bh);
+                        l1_mma(part[nt], ah, bl);
+                        l1_mma(part[nt], ah, bh);
+                    }
+                }
+#pragma unroll
+                for (int nt = 0; nt < 2; nt++)
+#pragma unroll
+                    for (int b = 0; b < 4; b++) cacc[nt][b] += part[nt][b];
+                if (round == 1 && has_skip && kp == 1) {     // skip Linear on the root slot (slot 7 of this round)
+#pragma unroll
+                    for (int s = 0; s < C::KS / 8; s++) {
+                        uint32_t ah[4], al[4];
+                        l1_load_a(As, LDA, mt * 16, 7 * CP + 8 * s, g, t, ah, al);
+#pragma unroll
+                        for (int nt = 0; nt < 2; nt++) {
+                            const int o0 = (8 * s + t) * L1_LDB + nt * 8 + g, o1 = o0 + 4 * L1_LDB;
+                            const uint32_t bh[2] = {__float_as_uint(Sh[o0]), __float_as_uint(Sh[o1])};
+                            const uint32_t bl[2] = {__float_as_uint(Sl[o0]), __float_as_uint(Sl[o1])};
+                            l1_mma(sacc[nt], al, bh);
+                            l1_mma(sacc[nt], ah, bl);
+                            l1_mma(sacc[nt], ah, bh);
+                        }
+                    }
+                }
+                if (round == 1) {
+#pragma unroll
+                    for (int nt = 0; nt < 2; nt++)
+#pragma unroll
+                        for (int h = 0; h < 2; h++) {
+                            const int row = mt * 16 + g + 8 * h, col = nt * 8 + 2 * t;
+                            *reinterpret_cast<float2*>(Cs + (kp * L1_NODES + row) * L1_LDC + col) =
+                                make_float2(cacc[nt][2 * h], cacc[nt][2 * h + 1]);
+                            if (has_skip && kp == 1)
+                                *reinterpret_cast<float2*>(Cs + (2 * L1_NODES + row) * L1_LDC + col) =
+                                    make_float2(sacc[nt][2 * h], sacc[nt][2 * h + 1]);
+                        }
+                }
+            }
+            __syncthreads();
+        }
+        // ---------------------------------------------------------------- (3) epilogue: BN / skip add / ReLU
+        if (tid < 4 * L1_NODES) {
+            const int nl = tid >> 2, oq = tid & 3;
+            const int64_t io = tile * L1_NODES + nl;
+            if (io < n) {
+                const float4 c0 = *reinterpret_cast<const float4*>(Cs + nl * L1_LDC + 4 * oq);
+                const float4 c1 = *reinterpret_cast<const float4*>(Cs + (L1_NODES + nl) * L1_LDC + 4 * oq);
+                const float4 v = make_float4(c0.x + c1.x, c0.y + c1.y, c0.z + c1.z, c0.w + c1.w);
+                *reinterpret_cast<float4*>(out + io * ldo + 4 * oq) = l1_epi(E, v, io, 4 * oq);
+                if (has_skip) {
+                    const float4 sv = *reinterpret_cast<const float4*>(Cs + (2 * L1_NODES + nl) * L1_LDC + 4 * oq);
+                    *reinterpret_cast<float4*>(skip_out + io * ld_skip + 4 * oq) = l1_epi(ES, sv, io, 4 * oq);
+                }
+            }
+        }
+    }
+}
+
+template <int CP>
+static int launch_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* cls, int64_t n, const float* x, int ldx,
+                     const float* tapw, int ncls, const float* Whi, const float* Wlo, const float* Shi, const float* Slo,
+                     const evad_epilogue_t& E, float* out, int ldo, const evad_epilogue_t& ES, float* skip_out,
+                     int ld_skip, cudaStream_t st) {
+    const size_t smem = L1Cfg<CP>::smem_bytes(ncls);
+    if (smem > 227 * 1024) return EVAD_ERR_UNSUPPORTED;
+    static size_t attr_bytes = 0;
+    if (smem > attr_bytes) {
+        if (cudaFuncSetAttribute(spline_l1_kernel<CP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return EVAD_ERR_LAUNCH;
+        attr_bytes = smem;
+    }
+    const int64_t ntiles = (n + L1_NODES - 1) / L1_NODES;
+    const int grid = (int)(ntiles < 148 ? ntiles : 148);
+    spline_l1_kernel<CP><<<grid, L1Cfg<CP>::THREADS, smem, st>>>(rowptr, src, cls, n, x, ldx, tapw, ncls, Whi, Wlo, Shi, Slo,
+                                                                E, out, ldo, ES, skip_out, ld_skip);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
+extern "C" int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* cls, int64_t n,
+                                   const float* x, int ldx, int cin_pad, const float* tapw, int ncls, const float* Whi,
+                                   const float* Wlo, const float* Shi, const float* Slo, const evad_epilogue_t* epi_h,
+                                   float* out, int ldo, const evad_epilogue_t* skip_epi_h, float* skip_out, int ld_skip,
+                                   void* stream) {
+    if (!rowptr || !src || !cls || !x || !tapw || !Whi || !Wlo || !epi_h || !out) return EVAD_ERR_ARG;
+    if (cin_pad != 16 && cin_pad != 20) return EVAD_ERR_UNSUPPORTED;
+    if (ldx < cin_pad || ldx % 4 != 0 || ldo % 4 != 0 || ncls < 1 || ncls > 256) return EVAD_ERR_ARG;
+    if ((((uintptr_t)x | (uintptr_t)tapw | (uintptr_t)Whi | (uintptr_t)Wlo | (uintptr_t)out) & 15) != 0) return EVAD_ERR_ARG;
+    const bool has_skip = Shi && Slo && skip_epi_h && skip_out;
+    if (has_skip && ((((uintptr_t)Shi | (uintptr_t)Slo | (uintptr_t)skip_out) & 15) != 0 || ld_skip % 4 != 0))
+        return EVAD_ERR_ARG;
+    if (n <= 0) return EVAD_OK;
+    const evad_epilogue_t es = has_skip ? *skip_epi_h : *epi_h;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cin_pad == 20)
+        return launch_l1<20>(rowptr, src, cls, n, x, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
+                             has_skip ? Slo : nullptr, *epi_h, out, ldo, es, skip_out, ld_skip, st);
+    return launch_l1<16>(rowptr, src, cls, n, x, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
+                         has_skip ? Slo : nullptr, *epi_h, out, ldo, es, skip_out, ld_skip, st);
+}

@@ -62,11 +62,18 @@ class Layer(torch.nn.Module):
         s1, h1 = _fold(b1.norm, b1.conv.bias)
         s2, h2 = _fold(b2.norm, b2.conv.bias)
         ss, hs = _fold(b2.norm_skip, b2.lin.mlp.bias)
+        cls = None
+        if n_dev is None and b1.conv.small_ok() and b2.conv.small_ok() and b1.conv.l1_pack(b2.lin.mlp.weight) is not None:
+            # both convolutions of the layer see the same graph and lattice: one class byte per edge serves both
+            from .spline_conv import USE_L1
+            if USE_L1:
+                cls = ops.edge_class(rowptr, src, n_cap, b1.conv.mode(), pseudo, status)
         y, skip = b1.conv.run(x, rowptr, src, n_cap, n_dev, pseudo, dict(scale=s1, shift=h1, relu=relu), status,
-                              skip_weight=b2.lin.mlp.weight, skip_epi=dict(scale=ss, shift=hs))
+                              skip_weight=b2.lin.mlp.weight, skip_epi=dict(scale=ss, shift=hs), cls=cls)
         if not relu:
             y = b1.activation(y)
-        out, _ = b2.conv.run(y, rowptr, src, n_cap, n_dev, pseudo, dict(scale=s2, shift=h2, addend=skip, relu=relu), status)
+        out, _ = b2.conv.run(y, rowptr, src, n_cap, n_dev, pseudo, dict(scale=s2, shift=h2, addend=skip, relu=relu), status,
+                             cls=cls)
         if not relu:
             out = b2.activation(out)
         return out

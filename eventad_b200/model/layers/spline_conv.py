@@ -10,6 +10,9 @@ import torch
 from ... import ops
 
 
+USE_L1 = True       # tap aggregation + tensor-core contraction for the cout=16 layer (False: LUT-gather kernel)
+
+
 class _PyGLinear(torch.nn.Module):
     """torch_geometric.nn.dense.linear.Linear(in, out, bias=False): key `weight` [out, in]."""
 
@@ -132,13 +135,50 @@ class MySplineConv(torch.nn.Module):
             c = self._cache["lut"] = (key, lut)
         return c[1]
 
+    def l1_pack(self, skip_weight=None):
+        """Operands of evad_spline_conv_l1, or None when the layer does not fit it (cout 16, Cin_pad in {16, 20}, LUT
+        mode, at most 15 distinct kernel taps reachable from the integer lattice)."""
+        m = self.mode()
+        cin_pad = (self.in_channels + 3) // 4 * 4
+        if not (m["use_lut"] == 1 and self.out_channels == 16 and cin_pad in (16, 20) and m["nx"] * m["ny"] <= 256):
+            return None
+        key = self._versions(skip_weight)
+        c = self._cache.get("l1")
+        if c is not None and c[0] == key:
+            return c[1]
+        nx, ny, ks, dev = m["nx"], m["ny"], m["ks"], self.weight.device
+        tk, tw = m["tab_k"].cpu().long(), m["tab_w"].cpu().float()
+        kx, wx, ky, wy = tk[:nx], tw[:nx], tk[nx:], tw[nx:]
+        kk = kx[:, None, :, None] + ks * ky[None, :, None, :]            # [nx, ny, mx, my]
+        kk = torch.where(kk < 0, kk + ks * ks, kk)
+        b = wx[:, None, :, None] * wy[None, :, None, :]                  # fp32 products, as in init_lut
+        used = sorted(set(kk.flatten().tolist()))
+        pack = None
+        if len(used) <= 15:
+            slot = torch.full((ks * ks,), -1, dtype=torch.long)
+            slot[torch.tensor(used)] = torch.arange(len(used))
+            tapw = torch.zeros(nx * ny, 16)
+            tapw.index_put_((torch.arange(nx * ny).view(nx, ny, 1, 1).expand_as(kk), slot[kk]), b, accumulate=True)
+            cin = self.in_channels
+            W = torch.zeros(16, cin_pad, 16)
+            W[:len(used), :cin] = self.weight.detach().float().cpu()[used]
+            W[15, :cin] = self.lin.weight.detach().float().cpu().t()
+            whi, wlo = ops.split_tf32(W.view(16 * cin_pad, 16).to(dev))
+            pack = dict(tapw=tapw.to(dev).contiguous(), whi=whi, wlo=wlo, shi=None, slo=None, cin_pad=cin_pad)
+            if skip_weight is not None:
+                S = torch.zeros((cin_pad + 7) // 8 * 8, 16)
+                S[:cin] = skip_weight.detach().float().cpu().t()
+                pack["shi"], pack["slo"] = ops.split_tf32(S.to(dev))
+        self._cache["l1"] = (key, pack)
+        return pack
+
     def small_ok(self):
         m = self.mode()
         return (m["use_lut"] == 1 and self.out_channels == 16 and self.in_channels <= 32 and
                 (m["nx"] * m["ny"] + 2) * ((self.in_channels + 3) // 4 * 4) * 16 * 4 <= 227 * 1024)
 
     # ---- kernels ---------------------------------------------------------------------------------------------
-    def run(self, x, rowptr, src, n_cap, n_dev, pseudo, epi, status, skip_weight=None, skip_epi=None):
+    def run(self, x, rowptr, src, n_cap, n_dev, pseudo, epi, status, skip_weight=None, skip_epi=None, cls=None):
         """x [n_cap, >=Cin] float32 -> epi(conv(x)) [n_cap, Cout] (+ skip_epi(x @ skip_weight^T) when requested)."""
         cin = self.in_channels
         if self.small_ok() and n_dev is None:
@@ -148,6 +188,11 @@ class MySplineConv(torch.nn.Module):
                 xp = torch.zeros((x.shape[0], cin_pad), dtype=torch.float32, device=x.device)
                 xp[:, :cin] = x[:, :cin]
                 x = xp
+            pack = self.l1_pack(skip_weight) if USE_L1 else None
+            if pack is not None:
+                if cls is None:
+                    cls = ops.edge_class(rowptr, src, n_cap, self.mode(), pseudo, status)
+                return ops.spline_conv_l1(rowptr, src, cls, n_cap, x, cin, pack, epi, skip_epi)
             return ops.spline_conv_small(rowptr, src, n_cap, x, cin, self.small_lut(skip_weight), self.mode(), pseudo, epi,
                                          status, skip_epi)
         x = x.contiguous()

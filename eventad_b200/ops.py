@@ -241,6 +241,36 @@ def spline_conv_small(rowptr, src, n, x, cin, lut, mode, pseudo, epi, status, sk
     return out, skip_out
 
 
+def edge_class(rowptr, src, n, mode, pseudo, status):
+    """uint8 LUT class (ix*ny + iy) of every CSR slot (spline_conv.py:39-42)."""
+    L = _lib.lib()
+    cls = torch.empty(max(src.shape[0], 1), dtype=torch.uint8, device=src.device)
+    m = _mode_struct(mode)
+    p = _pseudo_struct(**pseudo)
+    with _timed('edge_class'):
+        check(L.evad_edge_class(ptr(rowptr), ptr(src), n, ctypes.byref(p), ctypes.byref(m), ptr(cls), ptr(status), stream()),
+              "evad_edge_class")
+    return cls
+
+
+def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None):
+    """Tap aggregation + tensor-core contraction, cout = 16.  pack = dict(tapw, whi, wlo, shi, slo, cin_pad)."""
+    L = _lib.lib()
+    out = torch.empty((n, 16), dtype=torch.float32, device=x.device)
+    has_skip = skip_epi is not None and pack.get("shi") is not None
+    skip_out = torch.empty((n, 16), dtype=torch.float32, device=x.device) if has_skip else None
+    e = _epi_struct(**epi)
+    se = _epi_struct(**skip_epi) if has_skip else None
+    with _timed(f'spline_conv_small_c{cin}'):
+        check(L.evad_spline_conv_l1(ptr(rowptr), ptr(src), ptr(cls), n, ptr(x), x.stride(0), pack["cin_pad"],
+                                    ptr(pack["tapw"]), pack["tapw"].shape[0], ptr(pack["whi"]), ptr(pack["wlo"]),
+                                    ptr(pack["shi"]) if has_skip else None, ptr(pack["slo"]) if has_skip else None,
+                                    ctypes.byref(e), ptr(out), out.stride(0), ctypes.byref(se) if has_skip else None,
+                                    ptr(skip_out), skip_out.stride(0) if has_skip else 0, stream()),
+              "evad_spline_conv_l1")
+    return out, skip_out
+
+
 def spline_aggregate(rowptr, src, n_cap, n_dev, x, cin, mode, pseudo, status):
     """A[i] = [per-tap aggregated sources (ks*ks*cin) | x_i (cin)]."""
     L = _lib.lib()

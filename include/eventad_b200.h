@@ -167,6 +167,21 @@ int evad_gemm_epilogue(const float* A, int64_t lda, const float* W /*[K,N] row-m
                        const int32_t* m_dev, int k, int n, const evad_epilogue_t* epi_h, float* out, int ldo,
                        void* ws, size_t ws_bytes, void* stream);
 
+/* Full-resolution SplineConv with cout = 16 (layer 1) as tap aggregation + tensor-core contraction (csrc/spline_l1.cu):
+ * replaces message_lut + propagate + root weight + BatchNorm/ReLU/skip (spline_conv.py:39-47,72-76; conv.py:23-28,47-56)
+ * like evad_spline_conv_small, without per-edge weight matrices.
+ *   evad_edge_class: cls[e] = ix*ny + iy, the reference's LUT index of edge e (spline_conv.py:39-42, fp32 arithmetic of
+ *     T.Cartesian + attr_remapping_matrix), one byte per CSR slot; shared by both convolutions of a Layer.
+ *   tapw [ncls][16]: basis value of lattice class c on compact tap slot s (0 for the taps the class does not touch;
+ *     slot 15 unused); Whi/Wlo [16*cin_pad][16]: TF32 hi/lo parts of the weight rows [slot][channel] (slot 15 = root
+ *     weight `lin`), Shi/Slo [roundup(cin_pad,8)][16]: skip Linear (optional).  cin_pad in {16, 20}; x rows zero padded. */
+int evad_edge_class(const int32_t* rowptr, const int32_t* src, int64_t n, const evad_pseudo_t* pseudo_h,
+                    const evad_spline_mode_t* mode_h, uint8_t* cls, uint32_t* status, void* stream);
+int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* cls, int64_t n, const float* x, int ldx,
+                        int cin_pad, const float* tapw, int ncls, const float* Whi, const float* Wlo, const float* Shi,
+                        const float* Slo, const evad_epilogue_t* epi_h, float* out, int ldo,
+                        const evad_epilogue_t* skip_epi_h, float* skip_out, int ld_skip, void* stream);
+
 /* The same contraction on the tensor cores for N = 64 (csrc/gemm_tc.cu): every product is split into TF32 parts
  * (a_hi + a_lo)(w_hi + w_lo) and accumulated in fp32 as a_lo*w_hi + a_hi*w_lo + a_hi*w_hi, so the result keeps fp32
  * accuracy (rtol 1e-4 / atol 1e-5 parity bar).  evad_split_tf32 prepares w_hi / w_lo once per weight
