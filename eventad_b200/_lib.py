@@ -72,7 +72,7 @@ def _declare(L):
     _sig(L, "evad_sort_pairs", c_i, [c_p, c_p, c_p, c_p, c_i64, c_i, c_p, c_sz, c_p])
     _sig(L, "evad_graph_ws_bytes", c_sz, [c_i64, c_i, c_i, c_i, c_i])
     _sig(L, "evad_graph_build", c_i, [c_p, c_p, c_i64, c_i, c_i, c_i, c_i, c_i, c_i, c_i,
-                                      c_p, c_p, c_p, c_p, c_i64, c_p, c_p, c_p, c_p, c_sz, c_p])
+                                      c_p, c_p, c_p, c_p, c_i64, c_p, c_p, c_p, c_p, c_p, c_sz, c_p])
     _sig(L, "evad_stream_state_bytes", c_sz, [c_i, c_i, c_i, c_i])
     _sig(L, "evad_stream_reset", c_i, [c_p, c_i, c_i, c_i, c_i, c_p])
     _sig(L, "evad_stream_ws_bytes", c_sz, [c_i64, c_i])
@@ -87,11 +87,11 @@ def _declare(L):
     _sig(L, "evad_gemm_ws_bytes", c_sz, [c_i64, c_i, c_i])
     _sig(L, "evad_gemm_epilogue", c_i, [c_p, c_i64, c_p, c_i64, c_p, c_i, c_i, P(EpilogueT), c_p, c_i, c_p, c_sz, c_p])
     _sig(L, "evad_edge_class", c_i, [c_p, c_p, c_i64, P(PseudoT), P(SplineModeT), c_p, c_p, c_p])
-    _sig(L, "evad_spline_conv_l1", c_i, [c_p, c_p, c_p, c_i64, c_p, c_i, c_i, c_p, c_i, c_p, c_p, c_p, c_p, P(EpilogueT),
+    _sig(L, "evad_spline_conv_l1", c_i, [c_p, c_p, c_p, c_p, c_i64, c_p, c_i, c_i, c_p, c_i, c_p, c_p, c_p, c_p, P(EpilogueT),
                                          c_p, c_i, P(EpilogueT), c_p, c_i, c_p])
     _sig(L, "evad_split_tf32", c_i, [c_p, c_i64, c_p, c_p, c_p])
     _sig(L, "evad_gemm64_tc_ws_bytes", c_sz, [c_i64, c_i])
-    _sig(L, "evad_gemm64_tc", c_i, [c_p, c_i64, c_p, c_p, c_i64, c_p, c_i, P(EpilogueT), c_p, c_i, c_p, c_sz, c_p])
+    _sig(L, "evad_gemm64_tc", c_i, [c_p, c_i64, c_p, c_i64, c_p, c_i, P(EpilogueT), c_p, c_i, c_p, c_sz, c_p])
     _sig(L, "evad_voxel_pool_ws_bytes", c_sz, [c_i64, c_i64])
     _sig(L, "evad_voxel_pool", c_i, [P(PoolParamsT), c_i64, c_p, c_p, c_i, c_p, c_p, c_i, c_i, c_p, c_p, c_i64, c_i64,
                                      c_p, c_p, c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_p])

@@ -9,7 +9,9 @@
 // which is the case north_star reserves tensor cores for.  fp32 parity (rtol 1e-4 / atol 1e-5) rules out plain TF32
 // (10-bit mantissa), so every product is split  a = a_hi + a_lo, w = w_hi + w_lo  (each part exactly a TF32 number) and
 // accumulated as  a_lo*w_hi + a_hi*w_lo + a_hi*w_hi  in fp32: 3 tensor-core MMAs per tile, ~2^-21 relative error.
-// W is split once per weight (evad_split_tf32); A is split in registers while the fragments are loaded.
+// Both operands are split in registers while the fragments are loaded (hi = upper 19 bits, lo = exact remainder, of
+// which the tensor core again reads the upper 19 bits), so W streams from L2 once as plain fp32.
+// evad_split_tf32 (round-to-nearest parts) serves kernels that keep a weight resident in shared memory (spline_l1.cu).
 #include "common.cuh"
 
 #define TG_BK 32
@@ -63,14 +65,13 @@ extern "C" int evad_split_tf32(const float* w, int64_t n, float* hi, float* lo, 
 // (summed in slice order by tg_reduce_kernel -- deterministic), otherwise the epilogue is applied here.
 template <int BM, int WM, int WN>
 __global__ void __launch_bounds__(TG_THREADS) gemm64_tf32x3_kernel(
-    const float* __restrict__ A, int64_t lda, const float* __restrict__ Whi, const float* __restrict__ Wlo, int64_t m,
+    const float* __restrict__ A, int64_t lda, const float* __restrict__ W, int64_t m,
     const int32_t* __restrict__ m_dev, int K_total, int k_chunk, float* __restrict__ partial, evad_epilogue_t E,
     float* __restrict__ out, int ldo) {
     constexpr int MT = BM / WM / 16, NT = 64 / WN / 8;
     extern __shared__ __align__(16) float tg_smem[];
     float* As = tg_smem;                                     // [STAGES][BM][LDA]
-    float* Bh = As + TG_STAGES * BM * TG_LDA;                // [STAGES][BK][LDB]
-    float* Bl = Bh + TG_STAGES * TG_BK * TG_LDB;
+    float* Bs = As + TG_STAGES * BM * TG_LDA;                // [STAGES][BK][LDB], fp32 W (split in registers)
     const int64_t mm = m_dev ? min((int64_t)*m_dev, m) : m;
     const int64_t row0 = (int64_t)blockIdx.x * BM;
     if (row0 >= mm) return;
@@ -95,8 +96,7 @@ __global__ void __launch_bounds__(TG_THREADS) gemm64_tf32x3_kernel(
             const int kk = k0 + r;
             const int bytes = kk < K ? 16 : 0;
             const int64_t off = bytes ? (int64_t)kk * 64 + 4 * c : 0;
-            tg_cp16(Bh + (slot * TG_BK + r) * TG_LDB + 4 * c, Whi + off, bytes);
-            tg_cp16(Bl + (slot * TG_BK + r) * TG_LDB + 4 * c, Wlo + off, bytes);
+            tg_cp16(Bs + (slot * TG_BK + r) * TG_LDB + 4 * c, W + off, bytes);
         }
     };
 
@@ -128,8 +128,7 @@ __global__ void __launch_bounds__(TG_THREADS) gemm64_tf32x3_kernel(
 #pragma unroll
             for (int b = 0; b < NT; b++) { part[a][b][0] = part[a][b][1] = part[a][b][2] = part[a][b][3] = 0.f; }
         const float* a_s = As + (slot * BM + wm * (BM / WM)) * TG_LDA;
-        const float* bh_s = Bh + slot * TG_BK * TG_LDB + wn * (64 / WN);
-        const float* bl_s = Bl + slot * TG_BK * TG_LDB + wn * (64 / WN);
+        const float* b_s = Bs + slot * TG_BK * TG_LDB + wn * (64 / WN);
 #pragma unroll
         for (int ks = 0; ks < TG_BK / 8; ks++) {
             const int kk = ks * 8;
@@ -140,15 +139,18 @@ __global__ void __launch_bounds__(TG_THREADS) gemm64_tf32x3_kernel(
                 const float v[4] = {p[0], p[8 * TG_LDA], p[4], p[8 * TG_LDA + 4]};
 #pragma unroll
                 for (int q = 0; q < 4; q++) {
-                    ah[mt][q] = tg_tf32(v[q]);
-                    al[mt][q] = tg_tf32(__fsub_rn(v[q], __uint_as_float(ah[mt][q])));
+                    // hi = upper 19 bits (what the tensor core reads of a TF32 operand), lo = exact remainder
+                    ah[mt][q] = __float_as_uint(v[q]) & 0xffffe000u;
+                    al[mt][q] = __float_as_uint(__fsub_rn(v[q], __uint_as_float(ah[mt][q])));
                 }
             }
 #pragma unroll
             for (int nt = 0; nt < NT; nt++) {
                 const int o0 = (kk + t) * TG_LDB + nt * 8 + g, o1 = o0 + 4 * TG_LDB;
-                const uint32_t bh[2] = {__float_as_uint(bh_s[o0]), __float_as_uint(bh_s[o1])};
-                const uint32_t bl[2] = {__float_as_uint(bl_s[o0]), __float_as_uint(bl_s[o1])};
+                const float w0 = b_s[o0], w1 = b_s[o1];
+                const uint32_t bh[2] = {__float_as_uint(w0) & 0xffffe000u, __float_as_uint(w1) & 0xffffe000u};
+                const uint32_t bl[2] = {__float_as_uint(__fsub_rn(w0, __uint_as_float(bh[0]))),
+                                        __float_as_uint(__fsub_rn(w1, __uint_as_float(bh[1])))};
 #pragma unroll
                 for (int mt = 0; mt < MT; mt++) {
                     tg_mma(part[mt][nt], al[mt], bh);
@@ -218,13 +220,13 @@ __global__ void __launch_bounds__(256) tg_reduce_kernel(const float* __restrict_
     *reinterpret_cast<float4*>(out + gr * ldo + 4 * tx) = make_float4(v[0], v[1], v[2], v[3]);
 }
 
-// tile height and number of K slices: enough CTAs for about two waves of the 148 SMs
+// tile height and number of K slices: enough CTAs to fill the resident slots of the 148 SMs
 static void tg_plan(int64_t m, int k, int* bm, int* splits, int* k_chunk) {
     *bm = (m >= 64 * 148) ? 64 : 32;
     const int mtiles = evad_cdiv(m, *bm);
     int s = 1;
-    if (mtiles < 2 * 148) {
-        s = (2 * 148 + mtiles - 1) / mtiles;
+    if (mtiles < 4 * 148) {                                  // 4 CTAs are resident per SM (55 KB of shared memory each)
+        s = (4 * 148 + mtiles - 1) / mtiles;
         const int max_s = (k + 4 * TG_BK - 1) / (4 * TG_BK);      // at least 4 slabs per slice
         if (s > max_s) s = max_s;
         if (s > 32) s = 32;
@@ -243,10 +245,10 @@ extern "C" size_t evad_gemm64_tc_ws_bytes(int64_t m, int k) {
 }
 
 template <int BM, int WM, int WN>
-static int tg_launch(const float* A, int64_t lda, const float* Whi, const float* Wlo, int64_t m, const int32_t* m_dev,
+static int tg_launch(const float* A, int64_t lda, const float* W, int64_t m, const int32_t* m_dev,
                      int k, int splits, int k_chunk, float* partial, const evad_epilogue_t& E, float* out, int ldo,
                      cudaStream_t st) {
-    const size_t smem = (size_t)(TG_STAGES * BM * TG_LDA + 2 * TG_STAGES * TG_BK * TG_LDB) * sizeof(float);
+    const size_t smem = (size_t)(TG_STAGES * BM * TG_LDA + TG_STAGES * TG_BK * TG_LDB) * sizeof(float);
     static bool attr_done = false;
     if (!attr_done) {
         if (cudaFuncSetAttribute(gemm64_tf32x3_kernel<BM, WM, WN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -255,17 +257,16 @@ static int tg_launch(const float* A, int64_t lda, const float* Whi, const float*
         attr_done = true;
     }
     dim3 grid(evad_cdiv(m, BM), splits);
-    gemm64_tf32x3_kernel<BM, WM, WN><<<grid, TG_THREADS, smem, st>>>(A, lda, Whi, Wlo, m, m_dev, k, k_chunk, partial, E,
+    gemm64_tf32x3_kernel<BM, WM, WN><<<grid, TG_THREADS, smem, st>>>(A, lda, W, m, m_dev, k, k_chunk, partial, E,
                                                                      out, ldo);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }
 
-extern "C" int evad_gemm64_tc(const float* A, int64_t lda, const float* Whi, const float* Wlo, int64_t m,
-                              const int32_t* m_dev, int k, const evad_epilogue_t* epi_h, float* out, int ldo, void* ws,
+extern "C" int evad_gemm64_tc(const float* A, int64_t lda, const float* W, int64_t m, const int32_t* m_dev, int k, const evad_epilogue_t* epi_h, float* out, int ldo, void* ws,
                               size_t ws_bytes, void* stream) {
-    if (!A || !Whi || !Wlo || !epi_h || !out || k < 1 || lda < k || ldo < 64) return EVAD_ERR_ARG;
-    if (lda % 4 != 0 || ldo % 2 != 0 || (((uintptr_t)A | (uintptr_t)Whi | (uintptr_t)Wlo) & 15) || ((uintptr_t)out & 7))
+    if (!A || !W || !epi_h || !out || k < 1 || lda < k || ldo < 64) return EVAD_ERR_ARG;
+    if (lda % 4 != 0 || ldo % 2 != 0 || (((uintptr_t)A | (uintptr_t)W) & 15) || ((uintptr_t)out & 7))
         return EVAD_ERR_UNSUPPORTED;
     if (m <= 0) return EVAD_OK;
     cudaStream_t st = (cudaStream_t)stream;
@@ -277,8 +278,8 @@ extern "C" int evad_gemm64_tc(const float* A, int64_t lda, const float* Whi, con
         if (ws && ws_bytes >= need) partial = (float*)ws;
         else { splits = 1; kc = (k + TG_BK - 1) / TG_BK * TG_BK; }
     }
-    if (bm == 64) EVAD_TRY((tg_launch<64, 2, 2>(A, lda, Whi, Wlo, m, m_dev, k, splits, kc, partial, *epi_h, out, ldo, st)));
-    else EVAD_TRY((tg_launch<32, 1, 4>(A, lda, Whi, Wlo, m, m_dev, k, splits, kc, partial, *epi_h, out, ldo, st)));
+    if (bm == 64) EVAD_TRY((tg_launch<64, 2, 2>(A, lda, W, m, m_dev, k, splits, kc, partial, *epi_h, out, ldo, st)));
+    else EVAD_TRY((tg_launch<32, 1, 4>(A, lda, W, m, m_dev, k, splits, kc, partial, *epi_h, out, ldo, st)));
     if (partial) {
         if (((uintptr_t)out & 15) || ldo % 4 != 0) return EVAD_ERR_UNSUPPORTED;
         tg_reduce_kernel<<<evad_cdiv(m * 16, 256), 256, 0, st>>>(partial, splits, m, m_dev, *epi_h, out, ldo);

@@ -59,6 +59,7 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
                                                              const int32_t* __restrict__ cell_start, int64_t n, int H,
                                                              int W, int radius, float delta_t, int Q, int K,
                                                              int32_t* __restrict__ nbr /*[n][K]*/,
+                                                             uint8_t* __restrict__ nbr_cls /*[n][K] or null*/,
                                                              uint32_t* __restrict__ count /*[n]*/) {
     int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
@@ -68,7 +69,10 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
     const int rem = c % (W * H);
     const int y = rem / W, x = rem - y * W;
     int32_t* out = nbr + (int64_t)i * K;
+    uint8_t* ocls = nbr_cls ? nbr_cls + (int64_t)i * K : nullptr;   // spiral offset class (dx + r) * (2r + 1) + (dy + r)
+    const int side = 2 * radius + 1;
     out[0] = i;                                               // self edge first (ev_graph.cu:43-46)
+    if (ocls) ocls[0] = (uint8_t)(radius * side + radius);
     int cnt = 1;
     // spiral walk of spiral.h:1-15 (layer starts at 1, leg 0)
     int sx = 0, sy = 0, layer = 1, leg = 0;
@@ -94,6 +98,7 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
                 for (int q = hi - 1; q >= lo; q--) {          // newest first
                     const int dt = ti - st[q];
                     if ((float)dt > delta_t) continue;        // NOT break (ev_graph.cu:69)
+                    if (ocls) ocls[cnt] = (uint8_t)((sx + radius) * side + (sy + radius));
                     out[cnt++] = (int)sidx[q];
                     if (cnt >= K) break;
                 }
@@ -113,7 +118,9 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
 __global__ void __launch_bounds__(256) g_compact_kernel(const int32_t* __restrict__ nbr, const uint32_t* __restrict__ rowptr_u,
                                                         int64_t n, int K, int32_t* __restrict__ rowptr,
                                                         int32_t* __restrict__ src, int32_t* __restrict__ num_edges,
-                                                        int64_t* __restrict__ edge_index, int64_t stride) {
+                                                        int64_t* __restrict__ edge_index, int64_t stride,
+                                                        const uint8_t* __restrict__ nbr_cls,
+                                                        uint8_t* __restrict__ edge_cls) {
     int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n * K) return;
     const int64_t i = t / K;
@@ -127,6 +134,7 @@ __global__ void __launch_bounds__(256) g_compact_kernel(const int32_t* __restric
         const int32_t j = nbr[t];
         src[r0 + k] = j;
         if (edge_index) { edge_index[r0 + k] = j; edge_index[stride + r0 + k] = i; }
+        if (edge_cls) edge_cls[r0 + k] = nbr_cls[t];
     }
 }
 
@@ -135,6 +143,7 @@ __global__ void g_empty_kernel(int32_t* rowptr, int32_t* num_edges) { rowptr[0] 
 struct GraphWs {
     uint32_t *k0, *v0, *k1, *v1, *count, *rowptr_u, *sort_tmp, *scan_tmp;
     int32_t *st, *nbr, *cell_start;
+    uint8_t* nbr_cls;
 };
 
 static size_t graph_ws_layout(EvadArena& a, int64_t n, int64_t ncells, int K, GraphWs* w) {
@@ -142,6 +151,7 @@ static size_t graph_ws_layout(EvadArena& a, int64_t n, int64_t ncells, int K, Gr
     w->k1 = a.take<uint32_t>(n); w->v1 = a.take<uint32_t>(n);
     w->st = a.take<int32_t>(n);
     w->nbr = a.take<int32_t>(n * K);
+    w->nbr_cls = a.take<uint8_t>(n * K);
     w->count = a.take<uint32_t>(n + 1);
     w->rowptr_u = a.take<uint32_t>(n + 1);
     w->cell_start = a.take<int32_t>(ncells + 2);
@@ -159,9 +169,11 @@ extern "C" size_t evad_graph_ws_bytes(int64_t n, int B, int H, int W, int K) {
 extern "C" int evad_graph_build(const int32_t* batch, const int32_t* pos, int64_t n, int B, int H, int W, int radius,
                                 int delta_t_us, int Q, int K, int32_t* rowptr, int32_t* src, int32_t* num_edges,
                                 int64_t* edge_index, int64_t edge_index_stride, int32_t* cell_perm,
-                                int32_t* cell_start_out, uint32_t* status, void* ws, size_t ws_bytes, void* stream) {
+                                int32_t* cell_start_out, uint8_t* edge_cls, uint32_t* status, void* ws, size_t ws_bytes,
+                                void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     if (n < 0 || B < 1 || H < 1 || W < 1 || radius < 0 || Q < 1 || K < 1 || K > 32) return EVAD_ERR_ARG;
+    if (edge_cls && (2 * radius + 1) * (2 * radius + 1) > 256) return EVAD_ERR_UNSUPPORTED;
     if (!rowptr || !src || !num_edges || !status) return EVAD_ERR_ARG;
     const int64_t ncells = (int64_t)B * H * W;
     if (ncells >= (1ll << 31) || n * K >= (1ll << 31)) return EVAD_ERR_UNSUPPORTED;
@@ -187,11 +199,12 @@ extern "C" int evad_graph_build(const int32_t* batch, const int32_t* pos, int64_
     g_cells_kernel<<<evad_cdiv(m, 256), 256, 0, st>>>(skey, sidx, pos, n, ncells, cell_start, w.st, cell_perm);
     EVAD_CHECK_LAUNCH();
     g_search_kernel<<<evad_cdiv(n, G_THREADS), G_THREADS, 0, st>>>(skey, sidx, w.st, cell_start, n, H, W, radius,
-                                                                  (float)delta_t_us, Q, K, w.nbr, w.count);
+                                                                  (float)delta_t_us, Q, K, w.nbr,
+                                                                  edge_cls ? w.nbr_cls : nullptr, w.count);
     EVAD_CHECK_LAUNCH();
     EVAD_TRY(evad_exclusive_scan_u32(w.count, w.rowptr_u, n, w.rowptr_u + n, w.scan_tmp, st));
     g_compact_kernel<<<evad_cdiv(n * K, 256), 256, 0, st>>>(w.nbr, w.rowptr_u, n, K, rowptr, src, num_edges,
-                                                          edge_index, edge_index_stride);
+                                                          edge_index, edge_index_stride, w.nbr_cls, edge_cls);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }

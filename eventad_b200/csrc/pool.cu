@@ -175,88 +175,150 @@ __global__ void __launch_bounds__(PL_THREADS) pool_reduce_kernel(
     for (int ch = ctot + (append_pos ? 2 : 0) + threadIdx.x; ch < ldo; ch += PL_THREADS) x_out[(int64_t)c * ldo + ch] = 0.f;
 }
 
-// Warp-per-voxel variant (cx % 4 == 0, S.C % 4 == 0, 16-byte aligned rows): lanes own channel quads (128-bit loads of
-// x rows and of the channel-last CNN map), the members of a chunk are resolved one per lane (node id, position,
-// trilinear taps) and broadcast through warp-private shared memory / shuffles.  Arithmetic and its order are those of
-// pool_reduce_kernel (serial fp32 position sums in ascending node order, taps accumulated dz,dy,dx), so both kernels
-// produce identical bits.
+// Warp-per-voxel variant (cx % 4 == 0, S.C % 4 == 0, 16-byte aligned rows).
+//  * members of a chunk (<= 32) are resolved one per lane: node id, position, trilinear taps;
+//  * node features: lane = member, one 128-bit row load per channel quad (all in flight together), then a butterfly
+//    max / sum over the lanes -- no per-member memory latency;
+//  * sampled CNN features: all members of a voxel sample the same few map cells (a voxel spans ~1.5 cells of the map
+//    at its stride), so the bounding window of the chunk (<= PRW_WIN cells) is staged once in warp-private shared
+//    memory and the member loop runs out of shared memory; lanes own channel quads, the two half-warps take alternate
+//    members.  Per channel the taps are accumulated dz,dy,dx with fmaf exactly like sample_feat, and max pooling is
+//    order independent, so max-pooled rows are bit-identical to pool_reduce_kernel; mean rows agree to rounding;
+//  * positions: serial fp32 sums in ascending node order (bit-exact with the oracle's CPU scatter_add).
 #define PRW_WARPS 8
-#define PRW_MAXQ 2                                          // channel quads per lane: ctot <= 256
+#define PRW_WIN 32
+
+__device__ __forceinline__ float4 prw_comb(float4 a, float4 b, int mean) {
+    if (mean) return make_float4(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z), __fadd_rn(a.w, b.w));
+    return make_float4(fmaxf(a.x, b.x), fmaxf(a.y, b.y), fmaxf(a.z, b.z), fmaxf(a.w, b.w));
+}
+
+__device__ __forceinline__ float4 prw_shfl_xor(float4 v, int d) {
+    return make_float4(__shfl_xor_sync(0xffffffffu, v.x, d), __shfl_xor_sync(0xffffffffu, v.y, d),
+                       __shfl_xor_sync(0xffffffffu, v.z, d), __shfl_xor_sync(0xffffffffu, v.w, d));
+}
 
 __global__ void __launch_bounds__(PRW_WARPS * 32) pool_reduce_warp_kernel(
     const uint32_t* __restrict__ sidx, const int32_t* __restrict__ seg_start, const int32_t* __restrict__ n_out,
     const float* __restrict__ pos, int ld_pos, const int32_t* __restrict__ batch, const float* __restrict__ x, int ldx,
     int cx, PoolSample S, int aggr_mean, float inv_w, float inv_h, int append_pos, float* __restrict__ x_out, int ldo,
     float* __restrict__ pos_out, int32_t* __restrict__ batch_out) {
-    __shared__ int s_node[PRW_WARPS][32];
-    __shared__ __align__(16) int s_tap[PRW_WARPS][32][8];
-    __shared__ __align__(16) float s_wgt[PRW_WARPS][32][8];
+    extern __shared__ __align__(16) float prw_smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int c = blockIdx.x * PRW_WARPS + warp;
     if (c >= *n_out) return;
+    const int qx = cx >> 2, qf = S.feat ? (S.C >> 2) : 0;
+    float* wbase = prw_smem + (size_t)warp * (PRW_WIN * 4 * qf + 512);
+    float4* s_win = reinterpret_cast<float4*>(wbase);                       // [PRW_WIN][qf] float4
+    int* s_tap = reinterpret_cast<int*>(wbase + PRW_WIN * 4 * qf);          // [32][8]
+    float* s_wgt = wbase + PRW_WIN * 4 * qf + 256;                          // [32][8]
     const int s0 = seg_start[c], s1 = seg_start[c + 1];
-    const int qx = cx >> 2, qf = S.feat ? (S.C >> 2) : 0, nq = qx + qf;
     const float cntf = fmaxf((float)(s1 - s0), 1.f);
     const float4* f4 = reinterpret_cast<const float4*>(S.feat);
+    const float ident = aggr_mean ? 0.f : -INFINITY;
+    const int groups = (qf > 0 && qf <= 16) ? 2 : 1, lg = 32 / groups;      // sampled part: lane groups over members
+    const int grp = lane / lg, ql = lane - grp * lg;
     float sx = 0.f, sy = 0.f, st = 0.f;
-    float4 acc[PRW_MAXQ];
+    float4 accx[2], accf[2];
 #pragma unroll
-    for (int u = 0; u < PRW_MAXQ; u++) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int u = 0; u < 2; u++) accx[u] = accf[u] = make_float4(ident, ident, ident, ident);
     for (int p0 = s0; p0 < s1; p0 += 32) {
         const int cnt = min(32, s1 - p0);
         float px = 0.f, py = 0.f, pt = 0.f;
+        int node = 0, bx = 0x7fffffff, by = 0x7fffffff, bz = 0x7fffffff;
+        int tap[8];
+        float wgt[8];
         __syncwarp();
         if (lane < cnt) {
-            const int64_t i = sidx[p0 + lane];
-            px = pos[i * ld_pos]; py = pos[i * ld_pos + 1]; pt = pos[i * ld_pos + 2];
-            s_node[warp][lane] = (int)i;
-            if (S.feat) sample_taps(S, px, py, (float)batch[i], s_tap[warp][lane], s_wgt[warp][lane]);
+            node = (int)sidx[p0 + lane];
+            px = pos[(int64_t)node * ld_pos]; py = pos[(int64_t)node * ld_pos + 1]; pt = pos[(int64_t)node * ld_pos + 2];
+            if (qf) sample_taps_base(S, px, py, (float)batch[node], tap, wgt, &bx, &by, &bz);
         }
-        __syncwarp();
-        for (int m = 0; m < cnt; m++) {                      // serial fp32 sums in ascending node order (all lanes)
+        // ---- node features: lane = member, butterfly over the lanes, lane (q & 31) keeps quad q
+        for (int q0 = 0; q0 < qx; q0 += 4) {
+            float4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                v[u] = make_float4(ident, ident, ident, ident);
+                if (q0 + u < qx && lane < cnt) v[u] = __ldg(reinterpret_cast<const float4*>(x + (int64_t)node * ldx) + q0 + u);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (q0 + u >= qx) break;
+#pragma unroll
+                for (int d = 16; d >= 1; d >>= 1) v[u] = prw_comb(v[u], prw_shfl_xor(v[u], d), aggr_mean);
+                const int q = q0 + u;
+                if (lane == (q & 31)) {
+                    if (q < 32) accx[0] = prw_comb(accx[0], v[u], aggr_mean);
+                    else accx[1] = prw_comb(accx[1], v[u], aggr_mean);
+                }
+            }
+        }
+        // ---- positions: serial fp32 sums in ascending node order (all lanes redundantly)
+        for (int m = 0; m < cnt; m++) {
             sx = __fadd_rn(sx, __shfl_sync(0xffffffffu, px, m));
             sy = __fadd_rn(sy, __shfl_sync(0xffffffffu, py, m));
             st = __fadd_rn(st, __shfl_sync(0xffffffffu, pt, m));
         }
-#pragma unroll
-        for (int u = 0; u < PRW_MAXQ; u++) {
-            const int q = lane + 32 * u;
-            if (q >= nq) continue;
-            float4 a = acc[u];
-            for (int m = 0; m < cnt; m++) {
-                float4 v;
-                if (q < qx) {
-                    v = __ldg(reinterpret_cast<const float4*>(x + (int64_t)s_node[warp][m] * ldx) + q);
-                } else {
-                    v = make_float4(0.f, 0.f, 0.f, 0.f);
-                    const int4 t0 = *reinterpret_cast<const int4*>(&s_tap[warp][m][0]);
-                    const int4 t1 = *reinterpret_cast<const int4*>(&s_tap[warp][m][4]);
-                    const float4 w0 = *reinterpret_cast<const float4*>(&s_wgt[warp][m][0]);
-                    const float4 w1 = *reinterpret_cast<const float4*>(&s_wgt[warp][m][4]);
-                    const int tp[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
-                    const float wg[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
-                    float4 fv[8];
-#pragma unroll
-                    for (int k = 0; k < 8; k++)
-                        if (tp[k] >= 0) fv[k] = __ldg(f4 + (int64_t)tp[k] * qf + (q - qx));
-#pragma unroll
-                    for (int k = 0; k < 8; k++) {
-                        if (tp[k] < 0) continue;
-                        v.x = fmaf(fv[k].x, wg[k], v.x); v.y = fmaf(fv[k].y, wg[k], v.y);
-                        v.z = fmaf(fv[k].z, wg[k], v.z); v.w = fmaf(fv[k].w, wg[k], v.w);
-                    }
-                }
-                if (aggr_mean) {
-                    a.x = __fadd_rn(a.x, v.x); a.y = __fadd_rn(a.y, v.y); a.z = __fadd_rn(a.z, v.z); a.w = __fadd_rn(a.w, v.w);
-                } else if (p0 == s0 && m == 0) {
-                    a = v;
-                } else {
-                    a.x = fmaxf(a.x, v.x); a.y = fmaxf(a.y, v.y); a.z = fmaxf(a.z, v.z); a.w = fmaxf(a.w, v.w);
-                }
+        if (!qf) continue;
+        // ---- sampled CNN features: window of the chunk in shared memory
+        const int xmin = __reduce_min_sync(0xffffffffu, bx), ymin = __reduce_min_sync(0xffffffffu, by),
+                  zmin = __reduce_min_sync(0xffffffffu, bz);
+        const int xmax = __reduce_max_sync(0xffffffffu, lane < cnt ? bx : (int)0x80000000),
+                  ymax = __reduce_max_sync(0xffffffffu, lane < cnt ? by : (int)0x80000000),
+                  zmax = __reduce_max_sync(0xffffffffu, lane < cnt ? bz : (int)0x80000000);
+        const int wx = xmax - xmin + 2, wy = ymax - ymin + 2, wz = zmax - zmin + 2;
+        const bool use_win = (long long)wx * wy * wz <= PRW_WIN;
+        if (use_win) {
+            const int ncell = wx * wy * wz;
+            for (int idx = lane; idx < ncell * qf; idx += 32) {
+                const int cell = idx / qf, q = idx - cell * qf;
+                const int cz = cell / (wx * wy), r = cell - cz * wx * wy, cy = r / wx, cxx = r - cy * wx;
+                const int gx = xmin + cxx, gy = ymin + cy, gz = zmin + cz;
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (gx >= 0 && gx < S.w && gy >= 0 && gy < S.h && gz >= 0 && gz < S.Bimg)
+                    v = __ldg(f4 + ((int64_t)(gz * S.h + gy) * S.w + gx) * qf + q);
+                s_win[idx] = v;
             }
-            acc[u] = a;
+        }
+        if (lane < cnt) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                int tl = tap[k];
+                if (use_win && tl >= 0)
+                    tl = ((bz - zmin + (k >> 2)) * wy + (by - ymin + ((k >> 1) & 1))) * wx + (bx - xmin + (k & 1));
+                s_tap[lane * 8 + k] = tl;
+                s_wgt[lane * 8 + k] = wgt[k];
+            }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+            const int q = ql + u * lg;
+            if (q >= qf) continue;
+            float4 a = accf[u];
+            for (int m = grp; m < cnt; m += groups) {
+                const int4 t0 = *reinterpret_cast<const int4*>(s_tap + m * 8), t1 = *reinterpret_cast<const int4*>(s_tap + m * 8 + 4);
+                const float4 w0 = *reinterpret_cast<const float4*>(s_wgt + m * 8), w1 = *reinterpret_cast<const float4*>(s_wgt + m * 8 + 4);
+                const int tp[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+                const float wg[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+                float4 fv[8];
+#pragma unroll
+                for (int k = 0; k < 8; k++)
+                    if (tp[k] >= 0) fv[k] = use_win ? s_win[tp[k] * qf + q] : __ldg(f4 + (int64_t)tp[k] * qf + q);
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    if (tp[k] < 0) continue;
+                    v.x = fmaf(fv[k].x, wg[k], v.x); v.y = fmaf(fv[k].y, wg[k], v.y);
+                    v.z = fmaf(fv[k].z, wg[k], v.z); v.w = fmaf(fv[k].w, wg[k], v.w);
+                }
+                a = prw_comb(a, v, aggr_mean);
+            }
+            accf[u] = a;
         }
     }
+    if (groups == 2) accf[0] = prw_comb(accf[0], prw_shfl_xor(accf[0], 16), aggr_mean);
     float mx = __fdiv_rn(sx, cntf), my = __fdiv_rn(sy, cntf);
     const float mt = __fdiv_rn(st, cntf);
     mx = __fmul_rn(div_floor_f(__fadd_rn(mx, 1e-5f), inv_w), inv_w);
@@ -269,26 +331,62 @@ __global__ void __launch_bounds__(PRW_WARPS * 32) pool_reduce_warp_kernel(
     }
     float* o = x_out + (int64_t)c * ldo;
 #pragma unroll
-    for (int u = 0; u < PRW_MAXQ; u++) {
+    for (int u = 0; u < 2; u++) {
         const int q = lane + 32 * u;
-        if (q >= nq) continue;
-        float4 a = acc[u];
-        if (aggr_mean) { a.x = __fdiv_rn(a.x, cntf); a.y = __fdiv_rn(a.y, cntf); a.z = __fdiv_rn(a.z, cntf); a.w = __fdiv_rn(a.w, cntf); }
-        *reinterpret_cast<float4*>(o + 4 * q) = a;
+        if (q < qx) {
+            float4 a = accx[u];
+            if (aggr_mean) { a.x = __fdiv_rn(a.x, cntf); a.y = __fdiv_rn(a.y, cntf); a.z = __fdiv_rn(a.z, cntf); a.w = __fdiv_rn(a.w, cntf); }
+            *reinterpret_cast<float4*>(o + 4 * q) = a;
+        }
+        const int qq = ql + u * lg;
+        if (grp == 0 && qq < qf) {
+            float4 a = accf[u];
+            if (aggr_mean) { a.x = __fdiv_rn(a.x, cntf); a.y = __fdiv_rn(a.y, cntf); a.z = __fdiv_rn(a.z, cntf); a.w = __fdiv_rn(a.w, cntf); }
+            *reinterpret_cast<float4*>(o + 4 * (qx + qq)) = a;
+        }
     }
+    const int nq = qx + qf;
     if (append_pos && lane < 2) o[4 * nq + lane] = lane ? my : mx;
     for (int ch = 4 * nq + (append_pos ? 2 : 0) + lane; ch < ldo; ch += 32) o[ch] = 0.f;     // row padding
 }
 
 // ------------------------------------------------------------------------------------------------ coarse edges
 // One CTA per destination cluster: mark cluster[src] of every in-edge of every member (self loops dropped) in a
-// shared-memory bitmap over [lo, hi]; FILL=false counts the distinct sources, FILL=true writes them (ascending).
+// shared-memory bitmap; FILL=false counts the distinct sources, FILL=true writes them (ascending).
+// Fast path (the common case): the sources of cluster c lie in the 4096-id window centred on c (dense ids follow the
+// voxel order, neighbours are a few voxel rows away), so ONE pass over the fine edges yields the bitmap; rows of at most
+// PL_ROWCAP sources are parked in `tmp` and the FILL launch only copies them to their CSR position.  Anything else
+// (sources outside the window, longer rows) takes the general path: id range first, then 4096-id chunks, in both launches.
+#define PL_ROWCAP 64
+
+// exclusive prefix of per-thread popcounts over the CTA (PL_THREADS = 128); returns the CTA total
+__device__ __forceinline__ uint32_t pool_popc_scan(uint32_t pc, uint32_t* s_warp, uint32_t* excl) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = pc;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += t;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t woff = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < PL_THREADS / 32; w++) {
+        if (w < warp) woff += s_warp[w];
+        total += s_warp[w];
+    }
+    *excl = woff + inc - pc;
+    __syncthreads();
+    return total;
+}
+
 template <bool FILL>
 __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
     const uint32_t* __restrict__ sidx, const int32_t* __restrict__ seg_start, const int32_t* __restrict__ n_out,
     const int32_t* __restrict__ rowptr_in, const int32_t* __restrict__ src_in, const int32_t* __restrict__ cluster,
     uint32_t* __restrict__ deg, const uint32_t* __restrict__ rowptr_out, int32_t* __restrict__ src_out, int64_t e_cap,
-    uint32_t* __restrict__ status) {
+    int32_t* __restrict__ tmp, uint8_t* __restrict__ parked, uint32_t* __restrict__ status) {
     const int c = blockIdx.x;
     const int nc = *n_out;
     if (c >= nc) {
@@ -296,9 +394,54 @@ __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
         return;
     }
     __shared__ uint32_t bits[PL_BITS / 32];
-    __shared__ int s_lo, s_hi;
+    __shared__ int s_lo, s_hi, s_oow;
     __shared__ uint32_t s_warp[PL_THREADS / 32 + 1];
+    if (FILL && parked[c]) {                                 // row parked by the counting launch: copy it into place
+        const uint32_t base = rowptr_out[c], cnt = rowptr_out[c + 1] - base;
+        for (uint32_t k = threadIdx.x; k < cnt; k += PL_THREADS) {
+            if ((int64_t)(base + k) < e_cap) src_out[base + k] = tmp[(int64_t)c * PL_ROWCAP + k];
+            else atomicOr(status, EVAD_STATUS_EDGE_OVERFLOW);
+        }
+        return;
+    }
     const int s0 = seg_start[c], s1 = seg_start[c + 1];
+    if (!FILL) {
+        bits[threadIdx.x] = 0u;
+        if (threadIdx.x == 0) s_oow = 0;
+        __syncthreads();
+        const int w0 = max(0, c - PL_BITS / 2);
+        bool oow = false;
+        for (int p = s0 + threadIdx.x; p < s1; p += PL_THREADS) {
+            const int i = (int)sidx[p];
+            for (int e = rowptr_in[i]; e < rowptr_in[i + 1]; e++) {
+                const int sc = cluster[src_in[e]];
+                const int r = sc - w0;
+                if (sc == c) continue;
+                if (r >= 0 && r < PL_BITS) atomicOr(&bits[r >> 5], 1u << (r & 31));
+                else oow = true;
+            }
+        }
+        if (oow) s_oow = 1;
+        __syncthreads();
+        if (!s_oow) {
+            uint32_t word = bits[threadIdx.x];
+            uint32_t off;
+            const uint32_t total = pool_popc_scan(__popc(word), s_warp, &off);
+            const bool park = total <= PL_ROWCAP;
+            if (park) {
+                while (word) {
+                    const int b = __ffs(word) - 1;
+                    word &= word - 1;
+                    tmp[(int64_t)c * PL_ROWCAP + off++] = w0 + threadIdx.x * 32 + b;
+                }
+            }
+            if (threadIdx.x == 0) { deg[c] = total; parked[c] = park ? 1 : 0; }
+            return;
+        }
+        if (threadIdx.x == 0) parked[c] = 0;
+        __syncthreads();
+    }
+    // ---- general path
     if (threadIdx.x == 0) { s_lo = 0x7fffffff; s_hi = -1; }
     __syncthreads();
     int lo = 0x7fffffff, hi = -1;
@@ -328,25 +471,10 @@ __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
         }
         __syncthreads();
         uint32_t word = bits[threadIdx.x];
-        const uint32_t pc = __popc(word);
-        // block exclusive scan of pc (4 warps)
-        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-        uint32_t inc = pc;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d) inc += t;
-        }
-        if (lane == 31) s_warp[warp] = inc;
-        __syncthreads();
-        uint32_t woff = 0, chunk_total = 0;
-#pragma unroll
-        for (int w = 0; w < PL_THREADS / 32; w++) {
-            if (w < warp) woff += s_warp[w];
-            chunk_total += s_warp[w];
-        }
+        uint32_t off;
+        const uint32_t chunk_total = pool_popc_scan(__popc(word), s_warp, &off);
         if (FILL) {
-            uint32_t o = base_out + total + woff + inc - pc;
+            uint32_t o = base_out + total + off;
             while (word) {
                 const int b = __ffs(word) - 1;
                 word &= word - 1;
@@ -356,7 +484,6 @@ __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
             }
         }
         total += chunk_total;
-        __syncthreads();
     }
     if (!FILL && threadIdx.x == 0) deg[c] = total;
 }
@@ -373,7 +500,8 @@ __global__ void pool_finish_edges_kernel(const uint32_t* __restrict__ rowptr_u, 
 // ------------------------------------------------------------------------------------------------ host side
 struct PoolWs {
     uint32_t *k0, *v0, *k1, *v1, *flag, *excl, *deg, *rowptr_u, *sort_tmp, *scan_tmp;
-    int32_t* seg_start;
+    int32_t *seg_start, *row_tmp;
+    uint8_t* parked;
 };
 
 static size_t pool_ws_layout(EvadArena& a, int64_t n_cap, int64_t c_cap, PoolWs* w) {
@@ -385,6 +513,8 @@ static size_t pool_ws_layout(EvadArena& a, int64_t n_cap, int64_t c_cap, PoolWs*
     w->seg_start = a.take<int32_t>(c_cap + 2);
     w->deg = a.take<uint32_t>(c_cap + 2);
     w->rowptr_u = a.take<uint32_t>(c_cap + 2);
+    w->row_tmp = a.take<int32_t>((size_t)(c_cap + 1) * PL_ROWCAP);
+    w->parked = a.take<uint8_t>(c_cap + 2);
     w->sort_tmp = a.take<uint32_t>(evad_sort_tmp_elems(n));
     const int64_t m = n > c_cap + 2 ? n : c_cap + 2;
     w->scan_tmp = a.take<uint32_t>(evad_scan_tmp_elems(m));
@@ -437,11 +567,20 @@ extern "C" int evad_voxel_pool(const evad_pool_params_t* p, int64_t n_cap, const
     pool_relabel_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(skey, sidx, w.flag, w.excl, n_cap, G.key_bound, cluster,
                                                          w.seg_start, n_out);
     EVAD_CHECK_LAUNCH();
+    const int qf_h = p->feat ? p->feat_c / 4 : 0;
+    const size_t prw_smem = (size_t)PRW_WARPS * (PRW_WIN * 4 * qf_h + 512) * sizeof(float);
     const bool quad_ok = cx % 4 == 0 && ldx % 4 == 0 && ldo % 4 == 0 && (((uintptr_t)x | (uintptr_t)x_out) & 15) == 0 &&
-                         (!p->feat || (p->feat_c % 4 == 0 && ((uintptr_t)p->feat & 15) == 0)) &&
-                         ctot <= 128 * PRW_MAXQ;
+                         (!p->feat || (p->feat_c % 4 == 0 && ((uintptr_t)p->feat & 15) == 0)) && cx <= 256 &&
+                         qf_h <= 64 && prw_smem <= 100 * 1024;
     if (quad_ok) {
-        pool_reduce_warp_kernel<<<evad_cdiv(c_cap, PRW_WARPS), PRW_WARPS * 32, 0, st>>>(
+        static size_t attr_bytes = 0;
+        if (prw_smem > attr_bytes) {
+            if (cudaFuncSetAttribute(pool_reduce_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prw_smem) !=
+                cudaSuccess)
+                return EVAD_ERR_LAUNCH;
+            attr_bytes = prw_smem;
+        }
+        pool_reduce_warp_kernel<<<evad_cdiv(c_cap, PRW_WARPS), PRW_WARPS * 32, prw_smem, st>>>(
             sidx, w.seg_start, n_out, pos, ld_pos, batch, x, ldx, cx, S, p->aggr_mean, p->inv_w, p->inv_h, p->append_pos,
             x_out, ldo, pos_out, batch_out);
     } else {
@@ -453,12 +592,12 @@ extern "C" int evad_voxel_pool(const evad_pool_params_t* p, int64_t n_cap, const
     if (want_edges) {
         pool_edges_kernel<false><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, src_in,
                                                                              cluster, w.deg, nullptr, nullptr, e_cap,
-                                                                             status);
+                                                                             w.row_tmp, w.parked, status);
         EVAD_CHECK_LAUNCH();
         EVAD_TRY(evad_exclusive_scan_u32(w.deg, w.rowptr_u, c_cap + 1, nullptr, w.scan_tmp, st));
         pool_edges_kernel<true><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, src_in,
                                                                             cluster, w.deg, w.rowptr_u, src_out, e_cap,
-                                                                            status);
+                                                                            w.row_tmp, w.parked, status);
         EVAD_CHECK_LAUNCH();
         pool_finish_edges_kernel<<<evad_cdiv(c_cap + 1, 256), 256, 0, st>>>(w.rowptr_u, n_out, c_cap, rowptr_out,
                                                                           num_edges_out);

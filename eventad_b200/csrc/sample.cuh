@@ -74,3 +74,31 @@ __device__ __forceinline__ void sample_taps(const PoolSample& S, float px, float
         wgt[t] = __fmul_rn(__fmul_rn(dx ? fx1 : fx0, dy ? fy1 : fy0), dz ? fz1 : fz0);
     }
 }
+
+
+// sample_taps plus the integer base cell (x0, y0, z0) of the 2x2x2 tap cube: tap t sits at (x0 + (t&1), y0 + ((t>>1)&1),
+// z0 + (t>>2)).  Used by the pooling kernel to stage the few map cells a voxel touches in shared memory.
+__device__ __forceinline__ void sample_taps_base(const PoolSample& S, float px, float py, float b, int* tap, float* wgt,
+                                                 int* bx, int* by, int* bz) {
+    float gx = __fmul_rn(px, S.width), gy = __fmul_rn(py, S.height);
+    gx = __fsub_rn(__fdiv_rn(__fmul_rn(2.f, gx), __fsub_rn(S.width, 1.f)), 1.f);
+    gy = __fsub_rn(__fdiv_rn(__fmul_rn(2.f, gy), __fsub_rn(S.height, 1.f)), 1.f);
+    const float bs = S.Bimg > 1 ? (float)S.Bimg : 2.f;
+    const float gb = __fsub_rn(__fdiv_rn(__fmul_rn(2.f, b), __fsub_rn(bs, 1.f)), 1.f);
+    const float ix = __fmul_rn(__fdiv_rn(__fadd_rn(gx, 1.f), 2.f), (float)(S.w - 1));
+    const float iy = __fmul_rn(__fdiv_rn(__fadd_rn(gy, 1.f), 2.f), (float)(S.h - 1));
+    const float iz = __fmul_rn(__fdiv_rn(__fadd_rn(gb, 1.f), 2.f), (float)(S.Bimg - 1));
+    const float x0 = floorf(ix), y0 = floorf(iy), z0 = floorf(iz);
+    const float fx1 = __fsub_rn(ix, x0), fy1 = __fsub_rn(iy, y0), fz1 = __fsub_rn(iz, z0);
+    const float fx0 = __fsub_rn(__fadd_rn(x0, 1.f), ix), fy0 = __fsub_rn(__fadd_rn(y0, 1.f), iy),
+                fz0 = __fsub_rn(__fadd_rn(z0, 1.f), iz);
+    *bx = (int)x0; *by = (int)y0; *bz = (int)z0;
+#pragma unroll
+    for (int t = 0; t < 8; t++) {
+        const int dz = t >> 2, dy = (t >> 1) & 1, dx = t & 1;
+        const int z = (int)z0 + dz, y = (int)y0 + dy, x = (int)x0 + dx;
+        const bool ok = z >= 0 && z < S.Bimg && y >= 0 && y < S.h && x >= 0 && x < S.w;
+        tap[t] = ok ? (z * S.h + y) * S.w + x : -1;
+        wgt[t] = __fmul_rn(__fmul_rn(dx ? fx1 : fx0, dy ? fy1 : fy0), dz ? fz1 : fz0);
+    }
+}

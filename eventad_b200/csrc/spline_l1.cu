@@ -1,5 +1,5 @@
 // eventad_b200/csrc/spline_l1.cu -- full-resolution SplineConv (layer 1: 19->16 and 16->16 on the event graph) as
-// tap aggregation in registers + tensor-core contraction, one persistent CTA per SM.
+// tap aggregation in registers + tensor-core contraction, two persistent CTAs per SM.
 //
 // Reference path replaced per call (paths relative to /root/reference/src/dagr/model):
 //   layers/spline_conv.py:39-47  message_lut (gather x_j, gather lut[ix,iy] = sum_s b_s W[k_s], einsum)
@@ -13,27 +13,32 @@
 // (1) P_i[k] = sum_e b_{e,k} x_e over the <= 15 kernel taps the integer pixel lattice can reach: one thread per
 //     (node, channel quad), 60 accumulators in registers, per edge one 128-bit gather of the source row and the 16 tap
 //     weights of the edge's lattice class (a 6.5 KB shared table); no per-edge weight matrices.
-// (2) out tile [128 nodes x 16] = P tile [128 x 16*Cin_pad] @ W_cat on the tensor cores (mma.sync m16n8k8, 3xTF32 so
+// (2) out tile [64 nodes x 16] = P tile [64 x 16*Cin_pad] @ W_cat on the tensor cores (mma.sync m16n8k8, 3xTF32 so
 //     that fp32 accuracy is kept; W_cat hi/lo parts stay in shared memory for the life of the persistent CTA), root
 //     weight as one more tap slot, the skip Linear as a second small product, BatchNorm / skip add / ReLU in the epilogue.
 // The lattice class of every edge (the reference's (ix, iy) LUT index, computed with its fp32 arithmetic) is written
 // once per graph by evad_edge_class and shared by both convolutions of the layer.
 #include "spline_common.cuh"
 
-#define L1_NODES 128                  // nodes per tile
+#define L1_NODES 64                   // nodes per tile; two CTAs per SM so that gather and MMA phases overlap
+#define L1_MMA_WARPS (L1_NODES / 16 * 2)   // (m16 tile, k half)
 #define L1_SLOTS 16                   // 15 tap slots + root
 #define L1_TW_LD 20                   // tap-weight table row stride (floats): consecutive classes hit distinct bank quads
-#define L1_LDB 24                     // W_cat row stride in shared memory (16 outputs + 8): bank = 8*t + g
+#define L1_LDB 16                     // W_cat row stride; column n of row k is stored at n ^ (((k >> 1) & 1) << 3): the
+                                      // four k rows of a B fragment then fall into four distinct 8-bank groups
 #define L1_LDC 20                     // C tile row stride
 
 // ------------------------------------------------------------------------------------------------ edge classes
+// 16 lanes per destination node: lane k takes CSR slots r0+k, r0+k+16, ... so that src / cls accesses are coalesced
 __global__ void __launch_bounds__(256) edge_class_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ src,
                                                          int64_t n, EvadPseudo P, EvadSplineMode M,
                                                          uint8_t* __restrict__ cls, uint32_t* __restrict__ status) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t i = t >> 4;
+    const int k = (int)(t & 15);
     if (i >= n) return;
     const int r0 = rowptr[i], r1 = rowptr[i + 1];
-    for (int e = r0; e < r1; e++) {
+    for (int e = r0 + k; e < r1; e += 16) {
         float ax, ay;
         evad_pseudo(P, e, src[e], (int)i, &ax, &ay);
         int ix, iy;
@@ -47,7 +52,7 @@ extern "C" int evad_edge_class(const int32_t* rowptr, const int32_t* src, int64_
     if (!rowptr || !src || !pseudo_h || !mode_h || !cls || !status) return EVAD_ERR_ARG;
     if (!mode_h->use_lut || mode_h->nx * mode_h->ny > 256) return EVAD_ERR_UNSUPPORTED;
     if (n <= 0) return EVAD_OK;
-    edge_class_kernel<<<evad_cdiv(n, 256), 256, 0, (cudaStream_t)stream>>>(rowptr, src, n, *pseudo_h, *mode_h, cls, status);
+    edge_class_kernel<<<evad_cdiv(n * 16, 256), 256, 0, (cudaStream_t)stream>>>(rowptr, src, n, *pseudo_h, *mode_h, cls, status);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }
@@ -71,9 +76,9 @@ __device__ __forceinline__ void l1_load_a(const float* __restrict__ As, int lda,
     const float* p = As + (row + g) * lda + kk + t;
     const float v[4] = {p[0], p[8 * lda], p[4], p[8 * lda + 4]};
 #pragma unroll
-    for (int q = 0; q < 4; q++) {
-        ah[q] = l1_tf32(v[q]);
-        al[q] = l1_tf32(__fsub_rn(v[q], __uint_as_float(ah[q])));
+    for (int q = 0; q < 4; q++) {                            // hi = upper 19 bits (what the tensor core reads); lo = exact rest,
+        ah[q] = __float_as_uint(v[q]) & 0xffffe000u;         // of which the MMA again reads the upper 19 bits
+        al[q] = __float_as_uint(__fsub_rn(v[q], __uint_as_float(ah[q])));
     }
 }
 
@@ -107,9 +112,9 @@ struct L1Cfg {
 };
 
 template <int CP>
-__global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 1) spline_l1_kernel(
-    const int32_t* __restrict__ rowptr, const int32_t* __restrict__ src, const uint8_t* __restrict__ cls, int64_t n,
-    const float* __restrict__ x, int ldx, const float* __restrict__ tapw, int ncls, const float* __restrict__ Whi,
+__global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 2) spline_l1_kernel(
+    const int32_t* __restrict__ rowptr, const int32_t* __restrict__ src, const uint8_t* __restrict__ cls,
+    const int32_t* __restrict__ perm, int64_t n, const float* __restrict__ x, int ldx, const float* __restrict__ tapw, int ncls, const float* __restrict__ Whi,
     const float* __restrict__ Wlo, const float* __restrict__ Shi, const float* __restrict__ Slo, evad_epilogue_t E,
     float* __restrict__ out, int ldo, evad_epilogue_t ES, float* __restrict__ skip_out, int ld_skip) {
     using C = L1Cfg<CP>;
@@ -129,14 +134,16 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 1) spline_l1_kernel(
     // one-time staging: weights (hi / lo), skip weights, tap-weight table; A tile zeroed (its pad columns stay zero)
     for (int idx = tid; idx < C::KTOT * 4; idx += C::THREADS) {
         const int r = idx >> 2, c4 = idx & 3;
-        *reinterpret_cast<float4*>(Bh + r * L1_LDB + 4 * c4) = __ldg(reinterpret_cast<const float4*>(Whi) + idx);
-        *reinterpret_cast<float4*>(Bl + r * L1_LDB + 4 * c4) = __ldg(reinterpret_cast<const float4*>(Wlo) + idx);
+        const int cs = (4 * c4) ^ (((r >> 1) & 1) << 3);
+        *reinterpret_cast<float4*>(Bh + r * L1_LDB + cs) = __ldg(reinterpret_cast<const float4*>(Whi) + idx);
+        *reinterpret_cast<float4*>(Bl + r * L1_LDB + cs) = __ldg(reinterpret_cast<const float4*>(Wlo) + idx);
     }
     if (has_skip)
         for (int idx = tid; idx < C::KS * 4; idx += C::THREADS) {
             const int r = idx >> 2, c4 = idx & 3;
-            *reinterpret_cast<float4*>(Sh + r * L1_LDB + 4 * c4) = __ldg(reinterpret_cast<const float4*>(Shi) + idx);
-            *reinterpret_cast<float4*>(Sl + r * L1_LDB + 4 * c4) = __ldg(reinterpret_cast<const float4*>(Slo) + idx);
+            const int cs = (4 * c4) ^ (((r >> 1) & 1) << 3);
+            *reinterpret_cast<float4*>(Sh + r * L1_LDB + cs) = __ldg(reinterpret_cast<const float4*>(Shi) + idx);
+            *reinterpret_cast<float4*>(Sl + r * L1_LDB + cs) = __ldg(reinterpret_cast<const float4*>(Slo) + idx);
         }
     for (int idx = tid; idx < ncls * 4; idx += C::THREADS) {
         const int r = idx >> 2, c4 = idx & 3;
@@ -146,12 +153,14 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 1) spline_l1_kernel(
     __syncthreads();
 
     const int node_l = tid / QN, q = tid - node_l * QN;
-    const int mt = warp & 7, kp = warp >> 3;                 // MMA role of warps 0..15: m16 tile, k half
+    const int mt = warp & (L1_NODES / 16 - 1), kp = warp / (L1_NODES / 16);   // MMA role of the first warps: m16 tile, k half
+    const int swz = ((t >> 1) & 1) << 3;                     // column swizzle of this lane's B-fragment rows
     const int64_t ntiles = (n + L1_NODES - 1) / L1_NODES;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         // ---------------------------------------------------------------- (1) tap aggregation in registers
-        const int64_t i = tile * L1_NODES + node_l;
-        const bool valid = i < n;
+        const int64_t ip = tile * L1_NODES + node_l;          // position in processing order (pixel order when perm)
+        const bool valid = ip < n;
+        const int64_t i = valid ? (perm ? (int64_t)perm[ip] : ip) : 0;
         float4 acc[L1_SLOTS - 1];
 #pragma unroll
         for (int s = 0; s < L1_SLOTS - 1; s++) acc[s] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -202,7 +211,7 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 1) spline_l1_kernel(
                 *reinterpret_cast<float4*>(arow + s * CP) = slot < L1_SLOTS - 1 ? acc[slot < L1_SLOTS - 1 ? slot : 0] : xroot;
             }
             __syncthreads();
-            if (warp < 16) {
+            if (warp < L1_MMA_WARPS) {
                 float part[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
 #pragma unroll 2
                 for (int s = 0; s < CP / 2; s++) {
@@ -212,7 +221,7 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 1) spline_l1_kernel(
                     const int krow = round * KR + kk;
 #pragma unroll
                     for (int nt = 0; nt < 2; nt++) {
-                        const int o0 = (krow + t) * L1_LDB + nt * 8 + g, o1 = o0 + 4 * L1_LDB;
+                        const int o0 = (krow + t) * L1_LDB + ((nt * 8 + g) ^ swz), o1 = o0 + 4 * L1_LDB;
                         const uint32_t bh[2] = {__float_as_uint(Bh[o0]), __float_as_uint(Bh[o1])};
                         const uint32_t bl[2] = {__float_as_uint(Bl[o0]), __float_as_uint(Bl[o1])};
                         l1_mma(part[nt], al, bh);
@@ -231,7 +240,7 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 1) spline_l1_kernel(
                         l1_load_a(As, LDA, mt * 16, 7 * CP + 8 * s, g, t, ah, al);
 #pragma unroll
                         for (int nt = 0; nt < 2; nt++) {
-                            const int o0 = (8 * s + t) * L1_LDB + nt * 8 + g, o1 = o0 + 4 * L1_LDB;
+                            const int o0 = (8 * s + t) * L1_LDB + ((nt * 8 + g) ^ swz), o1 = o0 + 4 * L1_LDB;
                             const uint32_t bh[2] = {__float_as_uint(Sh[o0]), __float_as_uint(Sh[o1])};
                             const uint32_t bl[2] = {__float_as_uint(Sl[o0]), __float_as_uint(Sl[o1])};
                             l1_mma(sacc[nt], al, bh);
@@ -259,8 +268,9 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 1) spline_l1_kernel(
         // ---------------------------------------------------------------- (3) epilogue: BN / skip add / ReLU
         if (tid < 4 * L1_NODES) {
             const int nl = tid >> 2, oq = tid & 3;
-            const int64_t io = tile * L1_NODES + nl;
-            if (io < n) {
+            const int64_t iop = tile * L1_NODES + nl;
+            if (iop < n) {
+                const int64_t io = perm ? (int64_t)perm[iop] : iop;
                 const float4 c0 = *reinterpret_cast<const float4*>(Cs + nl * L1_LDC + 4 * oq);
                 const float4 c1 = *reinterpret_cast<const float4*>(Cs + (L1_NODES + nl) * L1_LDC + 4 * oq);
                 const float4 v = make_float4(c0.x + c1.x, c0.y + c1.y, c0.z + c1.z, c0.w + c1.w);
@@ -275,12 +285,13 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 1) spline_l1_kernel(
 }
 
 template <int CP>
-static int launch_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* cls, int64_t n, const float* x, int ldx,
+static int launch_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* cls, const int32_t* perm, int64_t n,
+                     const float* x, int ldx,
                      const float* tapw, int ncls, const float* Whi, const float* Wlo, const float* Shi, const float* Slo,
                      const evad_epilogue_t& E, float* out, int ldo, const evad_epilogue_t& ES, float* skip_out,
                      int ld_skip, cudaStream_t st) {
     const size_t smem = L1Cfg<CP>::smem_bytes(ncls);
-    if (smem > 227 * 1024) return EVAD_ERR_UNSUPPORTED;
+    if (smem > 113 * 1024) return EVAD_ERR_UNSUPPORTED;      // two CTAs per SM
     static size_t attr_bytes = 0;
     if (smem > attr_bytes) {
         if (cudaFuncSetAttribute(spline_l1_kernel<CP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
@@ -288,15 +299,15 @@ static int launch_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* c
         attr_bytes = smem;
     }
     const int64_t ntiles = (n + L1_NODES - 1) / L1_NODES;
-    const int grid = (int)(ntiles < 148 ? ntiles : 148);
-    spline_l1_kernel<CP><<<grid, L1Cfg<CP>::THREADS, smem, st>>>(rowptr, src, cls, n, x, ldx, tapw, ncls, Whi, Wlo, Shi, Slo,
+    const int grid = (int)(ntiles < 2 * 148 ? ntiles : 2 * 148);
+    spline_l1_kernel<CP><<<grid, L1Cfg<CP>::THREADS, smem, st>>>(rowptr, src, cls, perm, n, x, ldx, tapw, ncls, Whi, Wlo, Shi, Slo,
                                                                 E, out, ldo, ES, skip_out, ld_skip);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }
 
-extern "C" int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* cls, int64_t n,
-                                   const float* x, int ldx, int cin_pad, const float* tapw, int ncls, const float* Whi,
+extern "C" int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* cls, const int32_t* perm,
+                                   int64_t n, const float* x, int ldx, int cin_pad, const float* tapw, int ncls, const float* Whi,
                                    const float* Wlo, const float* Shi, const float* Slo, const evad_epilogue_t* epi_h,
                                    float* out, int ldo, const evad_epilogue_t* skip_epi_h, float* skip_out, int ld_skip,
                                    void* stream) {
@@ -311,8 +322,8 @@ extern "C" int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, co
     const evad_epilogue_t es = has_skip ? *skip_epi_h : *epi_h;
     cudaStream_t st = (cudaStream_t)stream;
     if (cin_pad == 20)
-        return launch_l1<20>(rowptr, src, cls, n, x, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
+        return launch_l1<20>(rowptr, src, cls, perm, n, x, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
                              has_skip ? Slo : nullptr, *epi_h, out, ldo, es, skip_out, ld_skip, st);
-    return launch_l1<16>(rowptr, src, cls, n, x, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
+    return launch_l1<16>(rowptr, src, cls, perm, n, x, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
                          has_skip ? Slo : nullptr, *epi_h, out, ldo, es, skip_out, ld_skip, st);
 }

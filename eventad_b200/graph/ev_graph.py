@@ -47,7 +47,7 @@ class AsyncGraph:
         self._history = []
 
     # ------------------------------------------------------------------ device-resident build (no host sync)
-    def build_csr(self, batch, pos, want_edge_index=False, want_cells=False):
+    def build_csr(self, batch, pos, want_edge_index=False, want_cells=False, want_cls=False):
         """Enqueues evad_graph_build for a fresh graph.  Returns dict(rowptr, src, num_edges, edge_index, cell_perm,
         cell_start); all sizes are upper bounds, `num_edges` lives on the device."""
         if not (batch.is_cuda and pos.is_cuda):
@@ -73,6 +73,7 @@ class AsyncGraph:
         ncells = self.batch_size * self.height * self.width
         cell_perm = torch.empty(max(n, 1), dtype=torch.int32, device=dev) if want_cells else None
         cell_start = torch.empty(ncells + 2, dtype=torch.int32, device=dev) if want_cells else None
+        edge_cls = torch.empty(max(n * K, 1), dtype=torch.uint8, device=dev) if want_cls else None
         nbytes = L.evad_graph_ws_bytes(n, self.batch_size, self.height, self.width, K)
         ws = self._ws.get(nbytes, dev)
         from .. import ops
@@ -80,11 +81,12 @@ class AsyncGraph:
           rc = L.evad_graph_build(_lib.ptr(batch), _lib.ptr(pos), n, int(self.batch_size), int(self.height),
                                 int(self.width), int(self.radius), int(self.delta_t_us), int(self.max_queue_size), K,
                                 _lib.ptr(rowptr), _lib.ptr(src), _lib.ptr(num_edges), _lib.ptr(edge_index),
-                                max(n * K, 1), _lib.ptr(cell_perm), _lib.ptr(cell_start), _lib.ptr(self._status),
+                                max(n * K, 1), _lib.ptr(cell_perm), _lib.ptr(cell_start), _lib.ptr(edge_cls),
+                                _lib.ptr(self._status),
                                 _lib.ptr(ws), ws.numel(), _lib.stream())
         _lib.check(rc, "evad_graph_build")
         return dict(rowptr=rowptr, src=src, num_edges=num_edges, edge_index=edge_index, cell_perm=cell_perm,
-                    cell_start=cell_start)
+                    cell_start=cell_start, edge_cls=edge_cls)
 
     def forward(self, batch, pos, collect_edges=True):
         n_ev = len(batch)

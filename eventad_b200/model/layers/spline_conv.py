@@ -117,14 +117,6 @@ class MySplineConv(torch.nn.Module):
             c = self._cache["wcat"] = (key, w)
         return c[1]
 
-    def wcat_split(self):
-        """TF32 hi/lo parts of wcat() for the tensor-core contraction (out_channels == 64)."""
-        key = self._versions()
-        c = self._cache.get("wcat_split")
-        if c is None or c[0] != key:
-            c = self._cache["wcat_split"] = (key,) + ops.split_tf32(self.wcat())
-        return c[1], c[2]
-
     def small_lut(self, skip_weight=None):
         cin_pad = (self.in_channels + 3) // 4 * 4
         key = self._versions(skip_weight)
@@ -178,7 +170,8 @@ class MySplineConv(torch.nn.Module):
                 (m["nx"] * m["ny"] + 2) * ((self.in_channels + 3) // 4 * 4) * 16 * 4 <= 227 * 1024)
 
     # ---- kernels ---------------------------------------------------------------------------------------------
-    def run(self, x, rowptr, src, n_cap, n_dev, pseudo, epi, status, skip_weight=None, skip_epi=None, cls=None):
+    def run(self, x, rowptr, src, n_cap, n_dev, pseudo, epi, status, skip_weight=None, skip_epi=None, cls=None,
+            perm=None):
         """x [n_cap, >=Cin] float32 -> epi(conv(x)) [n_cap, Cout] (+ skip_epi(x @ skip_weight^T) when requested)."""
         cin = self.in_channels
         if self.small_ok() and n_dev is None:
@@ -192,15 +185,14 @@ class MySplineConv(torch.nn.Module):
             if pack is not None:
                 if cls is None:
                     cls = ops.edge_class(rowptr, src, n_cap, self.mode(), pseudo, status)
-                return ops.spline_conv_l1(rowptr, src, cls, n_cap, x, cin, pack, epi, skip_epi)
+                return ops.spline_conv_l1(rowptr, src, cls, n_cap, x, cin, pack, epi, skip_epi, perm=perm)
             return ops.spline_conv_small(rowptr, src, n_cap, x, cin, self.small_lut(skip_weight), self.mode(), pseudo, epi,
                                          status, skip_epi)
         x = x.contiguous()
         A = ops.spline_aggregate(rowptr, src, n_cap, n_dev, x, cin, self.mode(), pseudo, status)
         tc = self.out_channels == 64 and A.stride(0) % 4 == 0
         if tc:
-            whi, wlo = self.wcat_split()
-            out = ops.gemm64_tc(A, whi, wlo, n_cap, n_dev, epi)
+            out = ops.gemm64_tc(A, self.wcat(), n_cap, n_dev, epi)
         else:
             out = ops.gemm_epilogue(A, self.wcat(), n_cap, n_dev, epi)
         skip = None
@@ -208,10 +200,9 @@ class MySplineConv(torch.nn.Module):
             c = self._cache.get("skip_t")
             if c is None or c[0] != (skip_weight._version, skip_weight.device):
                 wt = skip_weight.detach().t().contiguous().float()
-                c = self._cache["skip_t"] = ((skip_weight._version, skip_weight.device), wt) + \
-                    (ops.split_tf32(wt) if wt.shape[1] == 64 else (None, None))
-            if c[2] is not None and x.stride(0) % 4 == 0 and x.data_ptr() % 16 == 0:
-                skip = ops.gemm64_tc(x, c[2], c[3], n_cap, n_dev, skip_epi, k=cin)
+                c = self._cache["skip_t"] = ((skip_weight._version, skip_weight.device), wt)
+            if c[1].shape[1] == 64 and x.stride(0) % 4 == 0 and x.data_ptr() % 16 == 0:
+                skip = ops.gemm64_tc(x, c[1], n_cap, n_dev, skip_epi, k=cin)
             else:
                 skip = ops.gemm_epilogue(x, c[1], n_cap, n_dev, skip_epi, k=cin)
         return out, skip

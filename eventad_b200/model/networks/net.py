@@ -208,7 +208,17 @@ class Net(torch.nn.Module):
         gc.batch_size = max(gc.batch_size, num_graphs)
         gc.reset()
         pos_int = ops.denormalize_pos(pos, width, height, time_window)
-        graph = gc.build_csr(batch_i32, pos_int)
+        # When the fp32 LUT index of an integer pixel offset is provably offset + r (exhaustive host check, cached), the
+        # spiral walk of the graph build already knows every edge's lattice class: no per-edge float pass is needed.
+        c1 = self.conv_block1.conv_block1.conv
+        ck = (int(width), int(height))
+        if getattr(self, "_offcls_key", None) != ck:
+            m = c1.mode()
+            self._offcls_ok = bool(m["use_lut"] == 1 and m["nx"] == m["ny"] == 2 * int(gc.radius) + 1 and
+                                   c1.l1_pack(self.conv_block1.conv_block2.lin.mlp.weight) is not None and
+                                   ops.offset_class_is_lut_class(m, two_m_of(self.edge_attrs.max), True, width, height))
+            self._offcls_key = ck
+        graph = gc.build_csr(batch_i32, pos_int, want_cells=True, want_cls=self._offcls_ok)   # cell_perm: pixel order
         gc.max_index, gc.all_timestamps, gc._history = n, pos_int[:, 2], [(batch_i32, pos_int, 0)]   # AsyncGraph bookkeeping
         status = gc._status
         rowptr, src = graph["rowptr"], graph["src"]
@@ -216,7 +226,10 @@ class Net(torch.nn.Module):
         cin1 = self.conv_block1.in_channel
         x0 = ops.sample_concat(x, pos, batch_i32, f[0], width, height, append_pos=True, ldo=(cin1 + 3) // 4 * 4)
         pseudo = dict(pos=pos, two_m=two_m_of(self.edge_attrs.max), clamp01=True)
-        xk = self.conv_block1.run_fused(x0, rowptr, src, n, None, pseudo, status)
+        # layer 1 walks the nodes in pixel order: neighbouring destinations share their sources, so the row gathers
+        # of a tile hit L1 instead of L2
+        xk = self.conv_block1.run_fused(x0, rowptr, src, n, None, pseudo, status, perm=graph["cell_perm"],
+                                        cls=graph["edge_cls"])
         counts = torch.zeros(12, dtype=torch.int32, device=dev)
         pools = [self.pool1, self.pool2, self.pool3, self.pool4]
         layers = [self.layer2, self.layer3, self.layer4, self.layer5]

@@ -241,6 +241,32 @@ def spline_conv_small(rowptr, src, n, x, cin, lut, mode, pseudo, epi, status, sk
     return out, skip_out
 
 
+def offset_class_is_lut_class(mode, two_m, clamp01, width, height):
+    """True when, for every pixel and every integer offset d in [-r, r], the reference's fp32 LUT index
+    (T.Cartesian attr -> attr_remapping_matrix -> +1e-3 -> long, spline_conv.py:39-42) equals d + r, i.e. when the
+    spiral-offset class bytes of evad_graph_build ARE the LUT classes.  Exhaustive over the lattice, same fp32 ops as
+    the kernels (positions are pixel / extent in fp32, buffers.py:33-44)."""
+    nx, ny = mode["nx"], mode["ny"]
+    r00, r02, r11, r12 = mode["r"]
+    tm = torch.tensor(float(two_m), dtype=torch.float32)
+    for ext, n1, coef, off in ((int(width), nx, r00, r02), (int(height), ny, r11, r12)):
+        r = (n1 - 1) // 2
+        pix = torch.arange(ext)
+        d = torch.arange(-r, r + 1)
+        pj_idx = pix[:, None] + d[None, :]
+        valid = (pj_idx >= 0) & (pj_idx < ext)
+        pi = pix.float() / torch.tensor(float(ext))
+        pj = pj_idx.clamp(0, ext - 1).float() / torch.tensor(float(ext))
+        a = (pj - pi[:, None]) / tm + torch.tensor(0.5)
+        if clamp01:
+            a = a.clamp(0, 1)
+        idx = (a * torch.tensor(coef, dtype=torch.float32) + torch.tensor(off, dtype=torch.float32) +
+               torch.tensor(1e-3, dtype=torch.float32)).long()
+        if not bool((idx == (d + r)[None, :])[valid].all()):
+            return False
+    return True
+
+
 def edge_class(rowptr, src, n, mode, pseudo, status):
     """uint8 LUT class (ix*ny + iy) of every CSR slot (spline_conv.py:39-42)."""
     L = _lib.lib()
@@ -253,7 +279,7 @@ def edge_class(rowptr, src, n, mode, pseudo, status):
     return cls
 
 
-def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None):
+def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None, perm=None):
     """Tap aggregation + tensor-core contraction, cout = 16.  pack = dict(tapw, whi, wlo, shi, slo, cin_pad)."""
     L = _lib.lib()
     out = torch.empty((n, 16), dtype=torch.float32, device=x.device)
@@ -262,7 +288,7 @@ def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None):
     e = _epi_struct(**epi)
     se = _epi_struct(**skip_epi) if has_skip else None
     with _timed(f'spline_conv_small_c{cin}'):
-        check(L.evad_spline_conv_l1(ptr(rowptr), ptr(src), ptr(cls), n, ptr(x), x.stride(0), pack["cin_pad"],
+        check(L.evad_spline_conv_l1(ptr(rowptr), ptr(src), ptr(cls), ptr(perm), n, ptr(x), x.stride(0), pack["cin_pad"],
                                     ptr(pack["tapw"]), pack["tapw"].shape[0], ptr(pack["whi"]), ptr(pack["wlo"]),
                                     ptr(pack["shi"]) if has_skip else None, ptr(pack["slo"]) if has_skip else None,
                                     ctypes.byref(e), ptr(out), out.stride(0), ctypes.byref(se) if has_skip else None,
@@ -308,16 +334,16 @@ def split_tf32(W):
     return hi, lo
 
 
-def gemm64_tc(A, Whi, Wlo, m_cap, m_dev, epi, out=None, k=None):
-    """out = epi(A[:, :k] @ W) on the tensor cores (3xTF32, fp32 accuracy); W = Whi + Wlo, [k, 64] row-major."""
+def gemm64_tc(A, W, m_cap, m_dev, epi, out=None, k=None):
+    """out = epi(A[:, :k] @ W) on the tensor cores (3xTF32, fp32 accuracy); W [k, 64] row-major fp32."""
     L = _lib.lib()
-    k = k or Whi.shape[0]
+    k = k or W.shape[0]
     if out is None:
         out = torch.empty((max(m_cap, 1), 64), dtype=torch.float32, device=A.device)
     e = _epi_struct(**epi)
     ws = _ws(L.evad_gemm64_tc_ws_bytes(m_cap, k), A.device)
     with _timed('gemm_epilogue'):
-        check(L.evad_gemm64_tc(ptr(A), A.stride(0), ptr(Whi), ptr(Wlo), m_cap, ptr(m_dev), k, ctypes.byref(e), ptr(out),
+        check(L.evad_gemm64_tc(ptr(A), A.stride(0), ptr(W), m_cap, ptr(m_dev), k, ctypes.byref(e), ptr(out),
                                out.stride(0), ptr(ws), ws.numel(), stream()), "evad_gemm64_tc")
     return out
 

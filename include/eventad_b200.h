@@ -77,8 +77,10 @@ size_t evad_graph_ws_bytes(int64_t n_events, int batch_size, int height, int wid
 int evad_graph_build(const int32_t* batch, const int32_t* pos, int64_t n_events, int batch_size, int height,
                      int width, int radius, int delta_t_us, int max_queue_size, int max_neighbors,
                      int32_t* rowptr, int32_t* src, int32_t* num_edges, int64_t* edge_index,
-                     int64_t edge_index_stride, int32_t* cell_perm, int32_t* cell_start, uint32_t* status,
-                     void* ws, size_t ws_bytes, void* stream);
+                     int64_t edge_index_stride, int32_t* cell_perm, int32_t* cell_start,
+                     uint8_t* edge_cls /* optional [K*N]: (dx + r) * (2r + 1) + (dy + r) of every CSR slot, the pixel
+                                          offset source - destination the spiral walk found the edge at */,
+                     uint32_t* status, void* ws, size_t ws_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Event-graph construction, streaming ("append") mode: EV_TGN.forward(reset=False)
@@ -177,21 +179,23 @@ int evad_gemm_epilogue(const float* A, int64_t lda, const float* W /*[K,N] row-m
  *     weight `lin`), Shi/Slo [roundup(cin_pad,8)][16]: skip Linear (optional).  cin_pad in {16, 20}; x rows zero padded. */
 int evad_edge_class(const int32_t* rowptr, const int32_t* src, int64_t n, const evad_pseudo_t* pseudo_h,
                     const evad_spline_mode_t* mode_h, uint8_t* cls, uint32_t* status, void* stream);
-int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* cls, int64_t n, const float* x, int ldx,
+int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* cls,
+                        const int32_t* perm /* optional processing order, e.g. cell_perm of evad_graph_build */,
+                        int64_t n, const float* x, int ldx,
                         int cin_pad, const float* tapw, int ncls, const float* Whi, const float* Wlo, const float* Shi,
                         const float* Slo, const evad_epilogue_t* epi_h, float* out, int ldo,
                         const evad_epilogue_t* skip_epi_h, float* skip_out, int ld_skip, void* stream);
 
 /* The same contraction on the tensor cores for N = 64 (csrc/gemm_tc.cu): every product is split into TF32 parts
  * (a_hi + a_lo)(w_hi + w_lo) and accumulated in fp32 as a_lo*w_hi + a_hi*w_lo + a_hi*w_hi, so the result keeps fp32
- * accuracy (rtol 1e-4 / atol 1e-5 parity bar).  evad_split_tf32 prepares w_hi / w_lo once per weight
- * (spline_conv.py:64-78 `weight` [K,Cin,Cout] stacked with `lin.weight`^T, see MySplineConv.wcat).
- * Requirements: lda % 4 == 0, A / Whi / Wlo 16-byte aligned, out 16-byte aligned with ldo % 4 == 0. */
+ * accuracy (rtol 1e-4 / atol 1e-5 parity bar); the split happens in registers.  W = spline_conv.py:64-78 `weight`
+ * [K,Cin,Cout] stacked with `lin.weight`^T (MySplineConv.wcat).  evad_split_tf32 writes round-to-nearest hi / lo parts
+ * of a weight for kernels that keep it resident in shared memory (evad_spline_conv_l1).
+ * Requirements: lda % 4 == 0, A / W 16-byte aligned, out 16-byte aligned with ldo % 4 == 0. */
 int evad_split_tf32(const float* w, int64_t n, float* hi, float* lo, void* stream);
 size_t evad_gemm64_tc_ws_bytes(int64_t m, int k);
-int evad_gemm64_tc(const float* A, int64_t lda, const float* Whi /*[K,64]*/, const float* Wlo /*[K,64]*/, int64_t m,
-                   const int32_t* m_dev, int k, const evad_epilogue_t* epi_h, float* out, int ldo, void* ws,
-                   size_t ws_bytes, void* stream);
+int evad_gemm64_tc(const float* A, int64_t lda, const float* W /*[K,64] row-major fp32*/, int64_t m, const int32_t* m_dev,
+                   int k, const evad_epilogue_t* epi_h, float* out, int ldo, void* ws, size_t ws_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Voxel-grid pooling.

@@ -152,3 +152,28 @@ def test_pooling(B, n, level, aggr):
     else:
         assert_close(out.x, ref.x, what="mean pool")
     assert torch.equal(out.edge_attr.cpu(), ref.edge_attr)
+
+
+@pytest.mark.parametrize("dist,B", [("U", 1), ("C", 3)])
+def test_spiral_offset_class_equals_lut_class(dist, B):
+    """The class bytes evad_graph_build derives from the spiral offset equal the reference's fp32 LUT index
+    (spline_conv.py:39-42) computed per edge by evad_edge_class, and the exhaustive host check agrees."""
+    from eventad_b200 import ops
+    from eventad_b200.graph.ev_graph import SlidingWindowGraph
+    from eventad_b200.model.layers.components import two_m_of
+    model, args = make_backbone(use_image=True)
+    model.cache_luts(320, 240, args.radius)
+    conv = model.backbone.conv_block1.conv_block1.conv.cuda()
+    d = make_data(30_000, B, seed=11, dist=dist, device="cuda")
+    pos_int = ops.denormalize_pos(d.pos, 320, 240, 1_000_000)
+    g = SlidingWindowGraph(width=320, height=240, batch_size=B, max_num_neighbors=16, max_queue_size=128, radius=4,
+                           delta_t_us=10_000)
+    out = g.build_csr(d.batch.int(), pos_int, want_cls=True)
+    e = int(out["num_edges"].item())
+    two_m = two_m_of(model.backbone.edge_attrs.max)
+    assert ops.offset_class_is_lut_class(conv.mode(), two_m, True, 320, 240)
+    status = ops.new_status(d.pos.device)
+    ref = ops.edge_class(out["rowptr"], out["src"], d.pos.shape[0], conv.mode(),
+                         dict(pos=d.pos.contiguous(), two_m=two_m, clamp01=True), status)
+    assert int(status.item()) == 0
+    assert torch.equal(out["edge_cls"][:e], ref[:e])
