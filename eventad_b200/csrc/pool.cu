@@ -208,10 +208,11 @@ __global__ void __launch_bounds__(PRW_WARPS * 32) pool_reduce_warp_kernel(
     const int c = blockIdx.x * PRW_WARPS + warp;
     if (c >= *n_out) return;
     const int qx = cx >> 2, qf = S.feat ? (S.C >> 2) : 0;
-    float* wbase = prw_smem + (size_t)warp * (PRW_WIN * 4 * qf + 512);
+    float* wbase = prw_smem + (size_t)warp * (PRW_WIN * 4 * qf + 544);
     float4* s_win = reinterpret_cast<float4*>(wbase);                       // [PRW_WIN][qf] float4
     int* s_tap = reinterpret_cast<int*>(wbase + PRW_WIN * 4 * qf);          // [32][8]
     float* s_wgt = wbase + PRW_WIN * 4 * qf + 256;                          // [32][8]
+    int* s_cell = reinterpret_cast<int*>(wbase + PRW_WIN * 4 * qf + 512);   // [32] flat map index of window cells
     const int s0 = seg_start[c], s1 = seg_start[c + 1];
     const float cntf = fmaxf((float)(s1 - s0), 1.f);
     const float4* f4 = reinterpret_cast<const float4*>(S.feat);
@@ -270,25 +271,38 @@ __global__ void __launch_bounds__(PRW_WARPS * 32) pool_reduce_warp_kernel(
         const int wx = xmax - xmin + 2, wy = ymax - ymin + 2, wz = zmax - zmin + 2;
         const bool use_win = (long long)wx * wy * wz <= PRW_WIN;
         if (use_win) {
+            // lane c resolves window cell c to its flat map index once (-1 outside the map); the copy loop then walks
+            // (cell, quad) incrementally -- no per-element divisions
             const int ncell = wx * wy * wz;
-            for (int idx = lane; idx < ncell * qf; idx += 32) {
-                const int cell = idx / qf, q = idx - cell * qf;
-                const int cz = cell / (wx * wy), r = cell - cz * wx * wy, cy = r / wx, cxx = r - cy * wx;
+            if (lane < ncell) {
+                const int cz = lane / (wx * wy), r = lane - cz * wx * wy, cy = r / wx, cxx = r - cy * wx;
                 const int gx = xmin + cxx, gy = ymin + cy, gz = zmin + cz;
+                s_cell[lane] = (gx >= 0 && gx < S.w && gy >= 0 && gy < S.h && gz >= 0 && gz < S.Bimg)
+                                   ? (gz * S.h + gy) * S.w + gx : -1;
+            }
+            __syncwarp();
+            int cell = lane / qf, q = lane - cell * qf;
+            const int dcell = 32 / qf, dq = 32 - dcell * qf;
+            for (int idx = lane; idx < ncell * qf; idx += 32) {
+                const int gcell = s_cell[cell];
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (gx >= 0 && gx < S.w && gy >= 0 && gy < S.h && gz >= 0 && gz < S.Bimg)
-                    v = __ldg(f4 + ((int64_t)(gz * S.h + gy) * S.w + gx) * qf + q);
+                if (gcell >= 0) v = __ldg(f4 + (int64_t)gcell * qf + q);
                 s_win[idx] = v;
+                q += dq; cell += dcell;
+                if (q >= qf) { q -= qf; cell++; }
             }
         }
         if (lane < cnt) {
+            // taps outside the map get weight 0 on a valid cell: fmaf(x, 0, v) == v, so the member loop is branch free
 #pragma unroll
             for (int k = 0; k < 8; k++) {
                 int tl = tap[k];
-                if (use_win && tl >= 0)
+                float wk = wgt[k];
+                if (tl < 0) { tl = 0; wk = 0.f; }
+                else if (use_win)
                     tl = ((bz - zmin + (k >> 2)) * wy + (by - ymin + ((k >> 1) & 1))) * wx + (bx - xmin + (k & 1));
-                s_tap[lane * 8 + k] = tl;
-                s_wgt[lane * 8 + k] = wgt[k];
+                s_tap[lane * 8 + k] = tl * qf;
+                s_wgt[lane * 8 + k] = wk;
             }
         }
         __syncwarp();
@@ -304,12 +318,10 @@ __global__ void __launch_bounds__(PRW_WARPS * 32) pool_reduce_warp_kernel(
                 const float wg[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
                 float4 fv[8];
 #pragma unroll
-                for (int k = 0; k < 8; k++)
-                    if (tp[k] >= 0) fv[k] = use_win ? s_win[tp[k] * qf + q] : __ldg(f4 + (int64_t)tp[k] * qf + q);
+                for (int k = 0; k < 8; k++) fv[k] = use_win ? s_win[tp[k] + q] : __ldg(f4 + tp[k] + q);
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
                 for (int k = 0; k < 8; k++) {
-                    if (tp[k] < 0) continue;
                     v.x = fmaf(fv[k].x, wg[k], v.x); v.y = fmaf(fv[k].y, wg[k], v.y);
                     v.z = fmaf(fv[k].z, wg[k], v.z); v.w = fmaf(fv[k].w, wg[k], v.w);
                 }
@@ -568,7 +580,7 @@ extern "C" int evad_voxel_pool(const evad_pool_params_t* p, int64_t n_cap, const
                                                          w.seg_start, n_out);
     EVAD_CHECK_LAUNCH();
     const int qf_h = p->feat ? p->feat_c / 4 : 0;
-    const size_t prw_smem = (size_t)PRW_WARPS * (PRW_WIN * 4 * qf_h + 512) * sizeof(float);
+    const size_t prw_smem = (size_t)PRW_WARPS * (PRW_WIN * 4 * qf_h + 544) * sizeof(float);
     const bool quad_ok = cx % 4 == 0 && ldx % 4 == 0 && ldo % 4 == 0 && (((uintptr_t)x | (uintptr_t)x_out) & 15) == 0 &&
                          (!p->feat || (p->feat_c % 4 == 0 && ((uintptr_t)p->feat & 15) == 0)) && cx <= 256 &&
                          qf_h <= 64 && prw_smem <= 100 * 1024;
