@@ -92,6 +92,8 @@ def _declare(L):
     _sig(L, "evad_split_tf32", c_i, [c_p, c_i64, c_p, c_p, c_p])
     _sig(L, "evad_gemm64_tc_ws_bytes", c_sz, [c_i64, c_i])
     _sig(L, "evad_gemm64_tc", c_i, [c_p, c_i64, c_p, c_i64, c_p, c_i, P(EpilogueT), c_p, c_i, c_p, c_sz, c_p])
+    _sig(L, "evad_gemm64_tc5_ws_bytes", c_sz, [c_i64, c_i])
+    _sig(L, "evad_gemm64_tc5", c_i, [c_p, c_i64, c_p, c_i64, c_i64, c_p, c_i, P(EpilogueT), c_p, c_i, c_p, c_sz, c_p])
     _sig(L, "evad_voxel_pool_ws_bytes", c_sz, [c_i64, c_i64])
     _sig(L, "evad_voxel_pool", c_i, [P(PoolParamsT), c_i64, c_p, c_p, c_i, c_p, c_p, c_i, c_i, c_p, c_p, c_i64, c_i64,
                                      c_p, c_p, c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_p])

@@ -54,6 +54,10 @@ size_t evad_sort_tmp_elems(long long n);
 int evad_sort_pairs_u32(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int iota_vals, long long n,
                         int key_bits, uint32_t* tmp, uint32_t** res_k, uint32_t** res_v, cudaStream_t st);
 
+// deterministic split-K reduce + epilogue for [m, 64] outputs (gemm_tc.cu): out = epi(sum_y partial[y][m][64])
+int evad_gemm64_reduce(const float* partial, int splits, int64_t m, const int32_t* m_dev, const evad_epilogue_t* E,
+                       float* out, int ldo, cudaStream_t st);
+
 __device__ __forceinline__ unsigned evad_lanemask_lt() {
     unsigned m;
     asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));

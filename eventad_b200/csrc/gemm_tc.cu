@@ -220,6 +220,14 @@ __global__ void __launch_bounds__(256) tg_reduce_kernel(const float* __restrict_
     *reinterpret_cast<float4*>(out + gr * ldo + 4 * tx) = make_float4(v[0], v[1], v[2], v[3]);
 }
 
+// shared with gemm_tc5.cu (declared in common.cuh)
+int evad_gemm64_reduce(const float* partial, int splits, int64_t m, const int32_t* m_dev, const evad_epilogue_t* E,
+                       float* out, int ldo, cudaStream_t st) {
+    tg_reduce_kernel<<<evad_cdiv(m * 16, 256), 256, 0, st>>>(partial, splits, m, m_dev, *E, out, ldo);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
 // tile height and number of K slices: enough CTAs to fill the resident slots of the 148 SMs
 static void tg_plan(int64_t m, int k, int* bm, int* splits, int* k_chunk) {
     *bm = (m >= 64 * 148) ? 64 : 32;

@@ -10,6 +10,9 @@ import torch
 from ... import ops
 
 
+USE_TC5 = True      # tcgen05 (UMMA / TMEM) contraction for the cout=64 layers (False: legacy mma.sync kernel)
+TC5_MIN_ROWS = 1024 # below this many rows the 128-row tcgen05 tiles leave SMs idle and the mma.sync kernel is faster
+                    # (tools/gemm_bench.py: 65 vs 94 us at 17920 x 2132, 11.8 vs 8.5 us at 140 x 3380)
 USE_L1 = True       # tap aggregation + tensor-core contraction for the cout=16 layer (False: LUT-gather kernel)
 
 
@@ -117,6 +120,14 @@ class MySplineConv(torch.nn.Module):
             c = self._cache["wcat"] = (key, w)
         return c[1]
 
+    def wcat_t(self):
+        """wcat() transposed and padded: [Cout, roundup4(K*Cin + Cin)], the operand layout of the tcgen05 kernel."""
+        key = self._versions()
+        c = self._cache.get("wcat_t")
+        if c is None or c[0] != key:
+            c = self._cache["wcat_t"] = (key, ops.transpose_pad_weight(self.wcat()))
+        return c[1]
+
     def small_lut(self, skip_weight=None):
         cin_pad = (self.in_channels + 3) // 4 * 4
         key = self._versions(skip_weight)
@@ -191,7 +202,9 @@ class MySplineConv(torch.nn.Module):
         x = x.contiguous()
         A = ops.spline_aggregate(rowptr, src, n_cap, n_dev, x, cin, self.mode(), pseudo, status)
         tc = self.out_channels == 64 and A.stride(0) % 4 == 0
-        if tc:
+        if tc and USE_TC5 and n_cap >= TC5_MIN_ROWS and A.data_ptr() % 16 == 0:
+            out = ops.gemm64_tc5(A, self.wcat_t(), n_cap, n_dev, epi, k=A.shape[1])
+        elif tc:
             out = ops.gemm64_tc(A, self.wcat(), n_cap, n_dev, epi)
         else:
             out = ops.gemm_epilogue(A, self.wcat(), n_cap, n_dev, epi)
@@ -200,8 +213,11 @@ class MySplineConv(torch.nn.Module):
             c = self._cache.get("skip_t")
             if c is None or c[0] != (skip_weight._version, skip_weight.device):
                 wt = skip_weight.detach().t().contiguous().float()
-                c = self._cache["skip_t"] = ((skip_weight._version, skip_weight.device), wt)
-            if c[1].shape[1] == 64 and x.stride(0) % 4 == 0 and x.data_ptr() % 16 == 0:
+                c = self._cache["skip_t"] = ((skip_weight._version, skip_weight.device), wt,
+                                             ops.transpose_pad_weight(wt) if wt.shape[1] == 64 else None)
+            if c[2] is not None and USE_TC5 and n_cap >= 8 * TC5_MIN_ROWS and x.stride(0) % 4 == 0 and x.data_ptr() % 16 == 0:
+                skip = ops.gemm64_tc5(x, c[2], n_cap, n_dev, skip_epi, k=cin)
+            elif c[1].shape[1] == 64 and x.stride(0) % 4 == 0 and x.data_ptr() % 16 == 0:
                 skip = ops.gemm64_tc(x, c[1], n_cap, n_dev, skip_epi, k=cin)
             else:
                 skip = ops.gemm_epilogue(x, c[1], n_cap, n_dev, skip_epi, k=cin)

@@ -348,6 +348,29 @@ def gemm64_tc(A, W, m_cap, m_dev, epi, out=None, k=None):
     return out
 
 
+def transpose_pad_weight(W):
+    """W [k, 64] -> Wt [64, ldw] (ldw = k rounded up to a multiple of 4, zero padded): operand of gemm64_tc5."""
+    k = W.shape[0]
+    ldw = (k + 3) // 4 * 4
+    wt = torch.zeros((W.shape[1], ldw), dtype=torch.float32, device=W.device)
+    wt[:, :k] = W.detach().float().t()
+    return wt
+
+
+def gemm64_tc5(A, Wt, m_cap, m_dev, epi, out=None, k=None):
+    """out = epi(A[:, :k] @ W) with tcgen05.mma (TMEM accumulator, 3xTF32); Wt = transpose_pad_weight(W)."""
+    L = _lib.lib()
+    k = k or Wt.shape[1]
+    if out is None:
+        out = torch.empty((max(m_cap, 1), 64), dtype=torch.float32, device=A.device)
+    e = _epi_struct(**epi)
+    ws = _ws(L.evad_gemm64_tc5_ws_bytes(m_cap, k), A.device)
+    with _timed('gemm_epilogue'):
+        check(L.evad_gemm64_tc5(ptr(A), A.stride(0), ptr(Wt), Wt.stride(0), m_cap, ptr(m_dev), k, ctypes.byref(e), ptr(out),
+                                out.stride(0), ptr(ws), ws.numel(), stream()), "evad_gemm64_tc5")
+    return out
+
+
 # --------------------------------------------------------------------------------------------------- pooling
 def pool_geometry(voxel_size4: torch.Tensor, end4: torch.Tensor):
     """num_voxels per dimension exactly as torch_cluster computes them: ((end - start) / size).long() + 1, start = 0."""

@@ -197,6 +197,14 @@ size_t evad_gemm64_tc_ws_bytes(int64_t m, int k);
 int evad_gemm64_tc(const float* A, int64_t lda, const float* W /*[K,64] row-major fp32*/, int64_t m, const int32_t* m_dev,
                    int k, const evad_epilogue_t* epi_h, float* out, int ldo, void* ws, size_t ws_bytes, void* stream);
 
+/* The same contraction on the 5th-generation tensor cores (csrc/gemm_tc5.cu): tcgen05.mma kind::tf32 with the
+ * accumulator in tensor memory, 128 x 64 tile per CTA, operands staged in the SWIZZLE_128B K-major shared-memory layout,
+ * 3xTF32 split as above.  Wt is W TRANSPOSED: [64, ldw] row-major (row n = the K weights of output n), ldw % 4 == 0,
+ * zero padded beyond K.  Requirements: lda % 4 == 0, ldo % 4 == 0, A / Wt / out 16-byte aligned. */
+size_t evad_gemm64_tc5_ws_bytes(int64_t m, int k);
+int evad_gemm64_tc5(const float* A, int64_t lda, const float* Wt, int64_t ldw, int64_t m, const int32_t* m_dev, int k,
+                    const evad_epilogue_t* epi_h, float* out, int ldo, void* ws, size_t ws_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------------
  * Voxel-grid pooling.
  * Replaces Pooling.forward (src/dagr/model/layers/pooling.py:51-97): torch_cluster.grid_cluster on [x,y,t,batch],
