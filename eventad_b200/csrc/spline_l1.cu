@@ -169,21 +169,22 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 2) spline_l1_kernel(
             const int r0 = rowptr[i];
             const int deg = rowptr[i + 1] - r0;
             xroot = __ldg(reinterpret_cast<const float4*>(x + i * ldx) + q);
+            // software pipeline without branches: the class and row of edge e+1 and the source id of edge e+2 are in
+            // flight while the 60 FMAs of edge e run; indices are clamped to the last edge (a redundant, valid load)
+            const int last = r0 + max(deg - 1, 0);
             int c_next = 0, j_n2 = 0;
             float4 x_next = make_float4(0.f, 0.f, 0.f, 0.f);
             if (deg > 0) {
                 c_next = cls[r0];
                 x_next = __ldg(reinterpret_cast<const float4*>(x + (int64_t)src[r0] * ldx) + q);
-                if (deg > 1) j_n2 = src[r0 + 1];
+                j_n2 = src[min(r0 + 1, last)];
             }
             for (int e = 0; e < deg; e++) {
                 const float4 xq = x_next;
                 const float* twr = tw + c_next * L1_TW_LD;
-                if (e + 1 < deg) {                           // next edge's class and row in flight during the FMAs
-                    c_next = cls[r0 + e + 1];
-                    x_next = __ldg(reinterpret_cast<const float4*>(x + (int64_t)j_n2 * ldx) + q);
-                    if (e + 2 < deg) j_n2 = src[r0 + e + 2];
-                }
+                c_next = cls[min(r0 + e + 1, last)];
+                x_next = __ldg(reinterpret_cast<const float4*>(x + (int64_t)j_n2 * ldx) + q);
+                j_n2 = src[min(r0 + e + 2, last)];
 #pragma unroll
                 for (int u = 0; u < 4; u++) {
                     const float4 w4 = *reinterpret_cast<const float4*>(twr + 4 * u);

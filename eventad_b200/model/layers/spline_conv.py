@@ -188,7 +188,7 @@ class MySplineConv(torch.nn.Module):
         if self.small_ok() and n_dev is None:
             cin_pad = (cin + 3) // 4 * 4
             # rows must be 16-byte aligned and zero beyond Cin; a [n, cin_pad] input is trusted to be zero padded
-            if not (x.stride(1) == 1 and x.stride(0) % 4 == 0 and x.data_ptr() % 16 == 0 and x.shape[1] == cin_pad):
+            if not (x.stride(1) == 1 and x.stride(0) % 4 == 0 and x.data_ptr() % 16 == 0 and x.shape[1] >= cin_pad):
                 xp = torch.zeros((x.shape[0], cin_pad), dtype=torch.float32, device=x.device)
                 xp[:, :cin] = x[:, :cin]
                 x = xp
