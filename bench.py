@@ -51,36 +51,57 @@ def workload_config(a):
 
 # ------------------------------------------------------------------------------------------------ clocks sampler
 class ClockSampler:
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled DURING the timed regions: NVML polled every 5 ms from a thread (the timed
+    region of the default run is ~70 ms, too short for `nvidia-smi -lms`); falls back to one nvidia-smi query."""
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index=0):
-        self.rows, self.proc, self.index = [], None, index
+        self.index, self.sm, self.bits, self.max_mhz, self.run, self.thread, self.nvml = index, [], 0, None, False, None, None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
-                                         stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = int(vis.split(",")[self.index]) if vis and vis.split(",")[self.index].isdigit() else self.index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
         except Exception:
-            self.proc = None
+            self.nvml = None
+            return
+        self.run = True
+        self.thread = threading.Thread(target=self._poll, daemon=True)
+        self.thread.start()
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+    def _poll(self):
+        n = self.nvml
+        while self.run:
+            try:
+                self.sm.append(float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM)))
+                self.bits |= int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+            except Exception:
+                pass
+            time.sleep(0.005)
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower() == "active" for r in self.rows)]
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+        if self.nvml is None:
+            try:
+                q = "clocks.sm,clocks.max.sm"
+                r = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                   capture_output=True, text=True, timeout=20).stdout.split(",")
+                return {"sm_mhz": float(r[0]), "sm_max_mhz": float(r[1]), "reasons": [], "samples": 1,
+                        "source": "nvidia-smi after the timed region (NVML python binding unavailable)"}
+            except Exception:
+                return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.run = False
+        self.thread.join(timeout=1.0)
+        n = self.nvml
+        masks = [getattr(n, "nvmlClocksThrottleReasonHwSlowdown", 0x8), getattr(n, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+                 getattr(n, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20), getattr(n, "nvmlClocksThrottleReasonSwPowerCap", 0x4)]
+        reasons = [nm for nm, m in zip(self.NAMES, masks) if self.bits & m]
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.max_mhz, "reasons": reasons,
+                "samples": len(self.sm), "source": "NVML polled every 5 ms across the device-timed and end-to-end timed regions"}
 
 
 # ------------------------------------------------------------------------------------------------ CPU reference arm
@@ -183,8 +204,6 @@ def run_b200(a):
     ops.TIMER = None
     ms_total = e0.elapsed_time(e1)
     stage = timer.summary()
-    clocks = sampler.stop() if rank == 0 else None
-
     # ---- end to end through the public call: pinned host events -> H2D -> format_data -> forward -> D2H results
     for i in range(min(a.warmup, 3)):
         runner.infer(raws[i % n_sets], feats)
@@ -196,6 +215,7 @@ def run_b200(a):
     e1.record()
     barrier()
     ms_e2e = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
 
     t = torch.tensor([ms_total, ms_e2e], device=dev, dtype=torch.float64)
     if world > 1:
@@ -226,18 +246,26 @@ def run_b200(a):
     E = float(np.mean(e_sets))
     Ntot = float(events_per_step)
     stage_ms = {k: v[1] / a.steps for k, v in stage.items()}
-    dom = "spline_conv_small_c19"
+    dom = "spline_conv_l1_c19"
     dom_ms = stage_ms.get(dom, None)
-    # algorithmic bytes of one conv1a launch: x0 rows 80 B + pos 12 B + rowptr 4 B read per
-    # node, src 4 B per edge, conv output 64 B + skip output 64 B written per node; gathers counted once
-    dom_bytes = Ntot * (80 + 12 + 4 + 64 + 64) + 4 * E
+    # algorithmic bytes of one conv1a launch: per node the x0 row (80 B), rowptr (4 B) and pixel-order
+    # index (4 B) read, conv output 64 B + skip output 64 B written; per edge the source index (4 B) and the offset-class
+    # byte (1 B); gathered rows counted once
+    dom_bytes = Ntot * (80 + 4 + 4 + 64 + 64) + 5 * E
+    # DRAM bytes of the same launch from the committed `ncu --set full` capture (profiles/r01c_spline_l1_full_raw.csv:
+    # dram__bytes_read.sum 126 MB + dram__bytes_write.sum 71 MB at 8 x 100k uniform events), scaled per event
+    ncu_traffic = 197.0e6 / 800000.0 * Ntot if a.dist == "U" else None
     roofline = None
     if dom_ms:
         ach = dom_bytes / (dom_ms * 1e-3) / 1e9
-        roofline = {"bound": "hbm", "kernel": "spline_small_kernel<20> (conv_block1.conv_block1: 19->16 LUT conv + BN + ReLU + skip Linear/BN)",
-                    "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+        roofline = {"bound": "hbm", "kernel": "spline_l1_kernel<20> (conv_block1.conv_block1: 19->16 LUT conv + BN + ReLU + skip Linear/BN; "
+                                              "register tap aggregation + 3xTF32 mma contraction, one launch)",
+                    "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": ncu_traffic,
                     "peak_source": peak_kind, "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": dom_ms,
-                    "share_of_step": dom_ms / (ms_total / a.steps)}
+                    "share_of_step": dom_ms / (ms_total / a.steps),
+                    "note": "ncu: DRAM 3.9 % of peak, L1 data pipe 64 %, issue slots 52 % -- the kernel is bound by the LSU/issue "
+                            "work of the 15-tap aggregation (60 FFMA + 32 other instructions per edge and thread), not by HBM; "
+                            "see profiles/r01c_summary.md"}
     n1 = 2240.0 * B                                              # pool-1 nodes (upper bound without the t==T extras)
     path_bytes = 1200 * Ntot + 108 * E + 1100 * n1                # SURVEY.md 8(d) module-boundary model
     path_ach = path_bytes / (ms_total / a.steps * 1e-3) / 1e9

@@ -287,7 +287,7 @@ def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None, perm=N
     skip_out = torch.empty((n, 16), dtype=torch.float32, device=x.device) if has_skip else None
     e = _epi_struct(**epi)
     se = _epi_struct(**skip_epi) if has_skip else None
-    with _timed(f'spline_conv_small_c{cin}'):
+    with _timed(f'spline_conv_l1_c{cin}'):
         check(L.evad_spline_conv_l1(ptr(rowptr), ptr(src), ptr(cls), ptr(perm), n, ptr(x), x.stride(0), pack["cin_pad"],
                                     ptr(pack["tapw"]), pack["tapw"].shape[0], ptr(pack["whi"]), ptr(pack["wlo"]),
                                     ptr(pack["shi"]) if has_skip else None, ptr(pack["slo"]) if has_skip else None,
