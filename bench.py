@@ -182,7 +182,19 @@ def run_b200(a):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # ---- `value`: the fused branch captured once in a CUDA graph (fixed events x windows shape; all data-dependent sizes
+    #      live in device counters), inputs resident in HBM: per step 3 device copies into the graph's static inputs,
+    #      one replay, one read-back of the 13 counters.  CNN maps are consumed in place.
+    from eventad_b200.engine import GraphedForward, StreamedRunner
+    gfd = GraphedForward(runner.net, N * B, B, feats, device=dev, static_feats=True)
+    c0 = L.evad_launch_count()
+    gfd.capture(datas[0], feats)
+    launches_per_replay = (L.evad_launch_count() - c0) // 3            # 2 warm-up passes + the captured one
+
     def step_device(i):
+        return gfd(datas[i % n_sets], feats)
+
+    def step_plain(i):
         return runner.forward_device(datas[i % n_sets], feats)
 
     for i in range(a.warmup):
@@ -191,27 +203,41 @@ def run_b200(a):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    timer = ops.KernelTimer()
-    ops.TIMER = timer
-    launches0 = L.evad_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(a.steps):
         step_device(a.warmup + i)
     e1.record()
     barrier()
-    launches = L.evad_launch_count() - launches0
-    ops.TIMER = None
     ms_total = e0.elapsed_time(e1)
-    stage = timer.summary()
-    # ---- end to end through the public call: pinned host events -> H2D -> format_data -> forward -> D2H results
+    launches = launches_per_replay * a.steps
+
+    # ---- the same steps as plain stream launches, with CUDA events around every C-ABI call: per-stage times for the
+    #      roofline block (the graph replay cannot be timed per kernel from the host)
     for i in range(min(a.warmup, 3)):
-        runner.infer(raws[i % n_sets], feats)
+        step_plain(i)
+    barrier()
+    timer = ops.KernelTimer()
+    ops.TIMER = timer
+    e0.record()
+    for i in range(a.steps):
+        step_plain(a.warmup + i)
+    e1.record()
+    barrier()
+    ops.TIMER = None
+    ms_plain = e0.elapsed_time(e1)
+    stage = timer.summary()
+
+    # ---- end to end through the public serving call: pinned raw host events -> H2D (copy stream, one step ahead) ->
+    #      format_data kernel -> graph replay -> D2H of out3 / out4.  Every step's H2D and D2H are inside the timed region.
+    sr = StreamedRunner(runner, N * B, B, feats, static_feats=True)
+    for _ in sr.run([raws[i % n_sets] for i in range(max(min(a.warmup, 3), 1))], feats):
+        pass
     barrier()
     d2h = 0
     e0.record()
-    for i in range(a.steps):
-        _, d2h = runner.infer(raws[(a.warmup + i) % n_sets], feats)
+    for _, d2h in sr.run((raws[(a.warmup + i) % n_sets] for i in range(a.steps)), feats):
+        pass
     e1.record()
     barrier()
     ms_e2e = e0.elapsed_time(e1)
@@ -246,6 +272,7 @@ def run_b200(a):
     E = float(np.mean(e_sets))
     Ntot = float(events_per_step)
     stage_ms = {k: v[1] / a.steps for k, v in stage.items()}
+    ms_plain_step = ms_plain / a.steps
     dom = "spline_conv_l1_c19"
     dom_ms = stage_ms.get(dom, None)
     # algorithmic bytes of one conv1a launch: per node the x0 row (80 B), rowptr (4 B) and pixel-order
@@ -262,7 +289,7 @@ def run_b200(a):
                                               "register tap aggregation + 3xTF32 mma contraction, one launch)",
                     "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": ncu_traffic,
                     "peak_source": peak_kind, "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": dom_ms,
-                    "share_of_step": dom_ms / (ms_total / a.steps),
+                    "share_of_step": dom_ms / ms_plain_step,
                     "note": "ncu: DRAM 3.9 % of peak, L1 data pipe 64 %, issue slots 52 % -- the kernel is bound by the LSU/issue "
                             "work of the 15-tap aggregation (60 FFMA + 32 other instructions per edge and thread), not by HBM; "
                             "see profiles/r01c_summary.md"}
@@ -318,7 +345,9 @@ def run_b200(a):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": raw_bytes(raws[0]), "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / a.steps},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "path_roofline": path_roofline,
-            "cpu_baseline": cpu, "latency": lat, "stage_ms_per_step": stage_ms,
+            "cpu_baseline": cpu, "latency": lat, "stage_ms_per_step": stage_ms, "plain_launch_ms_per_step": ms_plain_step,
+            "mode": "value: CUDA-graph replay per step (inputs resident); e2e: double-buffered H2D on a copy stream + "
+                    "format_data kernel + graph replay + D2H; stage_ms/roofline: plain stream launches with CUDA events",
             "ms_per_window": ms_total / a.steps / B}
     print(json.dumps(line), flush=True)
     if world > 1:

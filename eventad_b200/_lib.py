@@ -102,6 +102,7 @@ def _declare(L):
     _sig(L, "evad_csr_to_coo_ws_bytes", c_sz, [c_i64])
     _sig(L, "evad_csr_to_coo", c_i, [c_p, c_p, c_i64, c_p, c_i64, c_p, c_i, c_p, c_i64, c_p, c_p, c_sz, c_p])
     _sig(L, "evad_cartesian", c_i, [c_p, c_i, c_i, c_p, c_i64, c_i64, c_p, c_f, c_i, c_p, c_p])
+    _sig(L, "evad_format_events", c_i, [c_p, c_p, c_p, c_p, c_i64, c_i, c_i, c_i, c_p, c_p, c_p, c_p])
     _sig(L, "evad_denormalize_pos", c_i, [c_p, c_i, c_i64, c_i, c_i, c_i, c_p, c_p])
     _sig(L, "evad_sample_concat", c_i, [c_p, c_i, c_i, c_p, c_i, c_p, c_i64, c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_f,
                                         c_i, c_p, c_i, c_p])

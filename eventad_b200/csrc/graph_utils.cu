@@ -249,6 +249,37 @@ extern "C" int evad_sample_concat(const float* x, int ldx, int cx, const float* 
     return EVAD_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ format_events
+// utils/buffers.py:33-44 (format_data) on the raw Data layout of data/utils.py:6-20: pos int16 [N,2], t int32 [N],
+// x int8 [N,1] (polarity), batch int64 [N]  ->  x float32, pos = cat([pos, t]) / [W, H, T] (integer true division = fp32
+// divide of the converted operands), batch int32.  One launch instead of six torch kernels.
+__global__ void __launch_bounds__(256) format_events_kernel(const int16_t* __restrict__ pos_xy, const int32_t* __restrict__ t,
+                                                            const int8_t* __restrict__ pol, const int64_t* __restrict__ batch64,
+                                                            int64_t n, float w, float h, float tw, float* __restrict__ x,
+                                                            float* __restrict__ pos, int32_t* __restrict__ batch) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const short2 xy = reinterpret_cast<const short2*>(pos_xy)[i];
+    pos[3 * i] = __fdiv_rn((float)xy.x, w);
+    pos[3 * i + 1] = __fdiv_rn((float)xy.y, h);
+    pos[3 * i + 2] = __fdiv_rn((float)t[i], tw);
+    x[i] = (float)pol[i];
+    batch[i] = batch64 ? (int32_t)batch64[i] : 0;
+}
+
+extern "C" int evad_format_events(const int16_t* pos_xy, const int32_t* t, const int8_t* polarity, const int64_t* batch64,
+                                  int64_t n, int width, int height, int time_window, float* x, float* pos, int32_t* batch,
+                                  void* stream) {
+    if (!pos_xy || !t || !polarity || !x || !pos || !batch || n < 0 || width <= 0 || height <= 0 || time_window <= 0)
+        return EVAD_ERR_ARG;
+    if (((uintptr_t)pos_xy & 3) != 0) return EVAD_ERR_ARG;
+    if (n == 0) return EVAD_OK;
+    format_events_kernel<<<evad_cdiv(n, 256), 256, 0, (cudaStream_t)stream>>>(pos_xy, t, polarity, batch64, n, (float)width,
+                                                                          (float)height, (float)time_window, x, pos, batch);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ denormalize_pos
 // ev_tgn.py:11-16: (pos * [W, H, T] + 1e-3).int() -- fp32 multiply, fp32 add, truncation.
 __global__ void __launch_bounds__(256) denormalize_kernel(const float* __restrict__ pos, int ld_pos, int64_t n, float w,

@@ -104,6 +104,27 @@ def cartesian(pos, edge_index, two_m: float, clamp01: bool, num_edges=None, dims
     return out
 
 
+def format_events(pos_xy, t, polarity, batch64, width, height, time_window, out=None):
+    """utils/buffers.py:33-44 (format_data) in one launch: raw int16 / int32 / int8 / int64 event arrays on the device ->
+    (x float32 [n,1], pos float32 [n,3] normalised, batch int32 [n]); `out` = preallocated (x, pos, batch)."""
+    L = _lib.lib()
+    n = t.shape[0]
+    dev = t.device
+    assert pos_xy.dtype == torch.int16 and t.dtype == torch.int32 and polarity.dtype == torch.int8
+    assert batch64 is None or batch64.dtype == torch.int64
+    pos_xy, t, polarity = pos_xy.contiguous(), t.contiguous(), polarity.contiguous()
+    if out is None:
+        out = (torch.empty((n, 1), dtype=torch.float32, device=dev), torch.empty((n, 3), dtype=torch.float32, device=dev),
+               torch.empty(n, dtype=torch.int32, device=dev))
+    x, pos, batch = out
+    assert x.is_contiguous() and pos.is_contiguous() and batch.is_contiguous() and x.numel() >= n and pos.shape[0] >= n
+    with _timed('format_events'):
+        check(L.evad_format_events(ptr(pos_xy), ptr(t), ptr(polarity), ptr(batch64.contiguous()) if batch64 is not None else None,
+                                   n, int(width), int(height), int(time_window), ptr(x), ptr(pos), ptr(batch), stream()),
+              "evad_format_events")
+    return out
+
+
 def denormalize_pos(pos, width, height, time_window):
     """ev_tgn.py:11-16 in one launch: (pos * [W, H, T] + 1e-3).int()."""
     L = _lib.lib()

@@ -257,6 +257,11 @@ int evad_csr_to_coo(const int32_t* rowptr, const int32_t* src, int64_t n_cap, co
 int evad_cartesian(const float* pos, int ld_pos, int dims, const int64_t* edge_index, int64_t stride, int64_t e_cap,
                    const int32_t* num_edges, float two_m, int clamp01, float* out, void* stream);
 /* denormalize_pos (src/dagr/model/layers/ev_tgn.py:11-16): pos_int[i,d] = (int)(pos[i,d] * {W,H,T}[d] + 1e-3), fp32. */
+/* format_data (src/dagr/utils/buffers.py:33-44) on the raw event layout of src/dagr/data/utils.py:6-20:
+ * pos_xy int16 [n,2], t int32 [n], polarity int8 [n], batch64 int64 [n] (NULL = all zero)  ->  x float32 [n,1],
+ * pos float32 [n,3] = cat([pos, t]) / [width, height, time_window], batch int32 [n]. */
+int evad_format_events(const int16_t* pos_xy, const int32_t* t, const int8_t* polarity, const int64_t* batch64, int64_t n,
+                       int width, int height, int time_window, float* x, float* pos, int32_t* batch, void* stream);
 int evad_denormalize_pos(const float* pos, int ld_pos, int64_t n, int width, int height, int time_window,
                          int32_t* pos_int, void* stream);
 /* sampling_skip + cat(x, pos[:, :2]) (net.py:15-17,116,122-123): out[i] = [x[i,:cx] | grid_sample(feat)(feat_c) |

@@ -88,3 +88,42 @@ def test_cuda_graph_replay_matches_plain():
             assert torch.equal(o.batch, r.batch) and torch.equal(o.pos, r.pos)
             assert torch.equal(o.edge_index, r.edge_index)
             assert torch.equal(o.x, r.x)
+
+
+def test_format_events_matches_format_data():
+    """evad_format_events == utils/buffers.py:33-44 on the raw Data layout (int16 pos, int32 t, int8 x, int64 batch),
+    bit for bit, including the fp32 division of the converted integers."""
+    from eventad_b200 import ops
+    g = torch.Generator().manual_seed(11)
+    n = 70_001
+    pos = torch.stack([torch.randint(0, 320, (n,), generator=g), torch.randint(0, 240, (n,), generator=g)], 1).to(torch.int16)
+    t = torch.randint(0, 1_000_001, (n,), generator=g).to(torch.int32)
+    x = (torch.randint(0, 2, (n, 1), generator=g) * 2 - 1).to(torch.int8)
+    batch = torch.sort(torch.randint(0, 5, (n,), generator=g)).values
+    normalizer = torch.tensor([320, 240, 1_000_000])
+    ref_pos = torch.cat([pos, t.view(-1, 1)], dim=-1) / normalizer
+    gx, gpos, gbatch = ops.format_events(pos.cuda(), t.cuda(), x.view(-1).cuda(), batch.cuda(), 320, 240, 1_000_000)
+    assert gpos.dtype == ref_pos.dtype == torch.float32
+    assert torch.equal(gpos.cpu(), ref_pos) and torch.equal(gx.cpu(), x.float()) and torch.equal(gbatch.cpu(), batch.int())
+    _, _, b0 = ops.format_events(pos.cuda(), t.cuda(), x.view(-1).cuda(), None, 320, 240, 1_000_000)
+    assert int(b0.abs().sum()) == 0
+
+
+def test_streamed_runner_matches_infer():
+    """The double-buffered serving loop (copy stream + format kernel + graph replay) returns what the plain end-to-end
+    call returns, batch after batch, also when a staging slot is reused."""
+    from eventad_b200.engine import EventBranchRunner, StreamedRunner, pin_raw
+    model, args = make_backbone(seed=2, use_image=True)
+    model.cache_luts(320, 240, args.radius)
+    runner = EventBranchRunner(model, "cuda")
+    feats = [f.cuda().contiguous(memory_format=torch.channels_last) for f in synthetic.make_image_features(2, seed=6)]
+    raws = [pin_raw(synthetic.make_batch(5000, 2, seed=40 + s, dist="C")) for s in range(5)]
+    sr = StreamedRunner(runner, 10_000, 2, feats)
+    got = list(sr.run(raws, feats))
+    assert len(got) == 5
+    for raw, (host, nbytes) in zip(raws, got):
+        ref, ref_bytes = runner.infer(raw, feats)
+        assert nbytes == ref_bytes
+        for o, r in zip(host, ref):
+            for key in ("x", "pos", "batch"):
+                assert torch.equal(o[key], r[key]), key
