@@ -128,17 +128,54 @@ def cpu_reference_run(a, steps, warmup):
     return a.events / (ms * 1e-3) / 1e6, ms, cores, sample
 
 
+def ref_cuda_graph_stage(a, iters=5):
+    """the reference's OWN CUDA graph builder (src/dagr/graph/ev_graph.cu compiled unmodified into
+    oracle/_ref/ev_graph_cuda.so) timed on the GPU for the graph stage of one window, with the host glue of
+    graph/utils.py:6-23 / ev_graph.py:45-103 (reset fill, sort, unique, insert, fill_edges, mask); the reference has no
+    GPU code for the other stages without PyG.  None when there is no GPU or the module was not built."""
+    if not torch.cuda.is_available():
+        return None
+    from eventad_b200 import synthetic
+    from tests.util import RefGraph, load_ref_graph_module
+    m = load_ref_graph_module()
+    if m is None:
+        return None
+    raw = synthetic.make_batch(a.events, 1, seed=100, dist=a.dist)
+    W, H = raw["width"], raw["height"]
+    pos = np.concatenate([raw["pos"].astype(np.int32), raw["t"].reshape(-1, 1)], 1).astype(np.int32)
+    bt, pt = torch.from_numpy(raw["batch"].astype(np.int32)).cuda(), torch.from_numpy(pos).cuda()
+    ts, edges = [], 0
+    for it in range(iters + 2):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        g = RefGraph(m, W, H, 1, 16, 128, 4, 10000)           # reset(): queue refilled with -1 (ev_graph.py:45-50)
+        edges = g.forward(bt, pt).shape[1]
+        e1.record()
+        torch.cuda.synchronize()
+        if it >= 2:
+            ts.append(e0.elapsed_time(e1))
+    ms = float(np.median(ts))
+    return {"ms_per_window": ms, "Mevents_per_s": a.events / ms / 1e3, "edges": int(edges), "events": a.events,
+            "what": "reference ev_graph.cu (unmodified, sm_100a) + torch sort/unique/mask glue, graph stage only, B=1"}
+
+
 def run_reference(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     steps, warmup = max(1, min(a.steps, 5)), max(1, min(a.warmup, 1))
     v, ms, cores, sample = cpu_reference_run(a, steps, warmup)
+    try:
+        ref_cuda = ref_cuda_graph_stage(a)
+    except Exception as ex:                                       # report, do not hide
+        ref_cuda = {"error": repr(ex)[:200]}
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": steps,
             "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": workload_config(a),
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "ref_cuda_graph_stage": ref_cuda,
             "note": "the reference has no CPU path for the graph builder and its PyG stack is not installable here; "
                     "this is the CPU restatement in oracle/ (kind=port), timed with all host threads"}
     print(json.dumps(line), flush=True)
