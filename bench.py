@@ -33,7 +33,7 @@ def parse():
     p.add_argument("--warmup", type=int, default=5)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--events", type=int, default=100_000, help="events per 50 ms window")
-    p.add_argument("--windows", type=int, default=8, help="windows per step (batch)")
+    p.add_argument("--windows", type=int, default=64, help="windows per step (batch); BASELINE configs[2]: 64 clips x 100k-event windows")
     p.add_argument("--dist", default="U", choices=["U", "C"])
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--latency-iters", type=int, default=100)

@@ -198,6 +198,41 @@ __device__ __forceinline__ float4 prw_shfl_xor(float4 v, int d) {
                        __shfl_xor_sync(0xffffffffu, v.z, d), __shfl_xor_sync(0xffffffffu, v.w, d));
 }
 
+// member loop of one lane group: channel quad q of members grp, grp + groups, ... of the chunk; NT taps per member
+// (dz, dy, dx order, fmaf chain as in sample_feat), from the staged window (WIN) or straight from the map
+template <bool WIN, int NT>
+__device__ __forceinline__ float4 prw_members(float4 a, const int* __restrict__ s_tap, const float* __restrict__ s_wgt,
+                                              const float4* __restrict__ s_win, const float4* __restrict__ f4, int q, int grp,
+                                              int cnt, int groups, int aggr_mean) {
+    for (int m = grp; m < cnt; m += groups) {
+        int tp[8];
+        float wg[8];
+        {
+            const int4 t0 = *reinterpret_cast<const int4*>(s_tap + m * 8);
+            const float4 w0 = *reinterpret_cast<const float4*>(s_wgt + m * 8);
+            tp[0] = t0.x; tp[1] = t0.y; tp[2] = t0.z; tp[3] = t0.w;
+            wg[0] = w0.x; wg[1] = w0.y; wg[2] = w0.z; wg[3] = w0.w;
+        }
+        if (NT == 8) {
+            const int4 t1 = *reinterpret_cast<const int4*>(s_tap + m * 8 + 4);
+            const float4 w1 = *reinterpret_cast<const float4*>(s_wgt + m * 8 + 4);
+            tp[4] = t1.x; tp[5] = t1.y; tp[6] = t1.z; tp[7] = t1.w;
+            wg[4] = w1.x; wg[5] = w1.y; wg[6] = w1.z; wg[7] = w1.w;
+        }
+        float4 fv[NT];
+#pragma unroll
+        for (int k = 0; k < NT; k++) fv[k] = WIN ? s_win[tp[k] + q] : __ldg(f4 + tp[k] + q);
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < NT; k++) {
+            v.x = fmaf(fv[k].x, wg[k], v.x); v.y = fmaf(fv[k].y, wg[k], v.y);
+            v.z = fmaf(fv[k].z, wg[k], v.z); v.w = fmaf(fv[k].w, wg[k], v.w);
+        }
+        a = prw_comb(a, v, aggr_mean);
+    }
+    return a;
+}
+
 __global__ void __launch_bounds__(PRW_WARPS * 32) pool_reduce_warp_kernel(
     const uint32_t* __restrict__ sidx, const int32_t* __restrict__ seg_start, const int32_t* __restrict__ n_out,
     const float* __restrict__ pos, int ld_pos, const int32_t* __restrict__ batch, const float* __restrict__ x, int ldx,
@@ -268,7 +303,12 @@ __global__ void __launch_bounds__(PRW_WARPS * 32) pool_reduce_warp_kernel(
         const int xmax = __reduce_max_sync(0xffffffffu, lane < cnt ? bx : (int)0x80000000),
                   ymax = __reduce_max_sync(0xffffffffu, lane < cnt ? by : (int)0x80000000),
                   zmax = __reduce_max_sync(0xffffffffu, lane < cnt ? bz : (int)0x80000000);
-        const int wx = xmax - xmin + 2, wy = ymax - ymin + 2, wz = zmax - zmin + 2;
+        // taps 4..7 are the dz = 1 plane: with the batch index as depth coordinate their weights are exactly 0 for every
+        // member (fmaf(x, 0, v) == v), so the common case stages one plane less and runs a 4-tap loop -- bit-identical
+        bool hi0 = true;
+        if (lane < cnt) hi0 = wgt[4] == 0.f && wgt[5] == 0.f && wgt[6] == 0.f && wgt[7] == 0.f;
+        const bool four = __all_sync(0xffffffffu, hi0);
+        const int wx = xmax - xmin + 2, wy = ymax - ymin + 2, wz = zmax - zmin + (four ? 1 : 2);
         const bool use_win = (long long)wx * wy * wz <= PRW_WIN;
         if (use_win) {
             // lane c resolves window cell c to its flat map index once (-1 outside the map); the copy loop then walks
@@ -310,24 +350,14 @@ __global__ void __launch_bounds__(PRW_WARPS * 32) pool_reduce_warp_kernel(
         for (int u = 0; u < 2; u++) {
             const int q = ql + u * lg;
             if (q >= qf) continue;
-            float4 a = accf[u];
-            for (int m = grp; m < cnt; m += groups) {
-                const int4 t0 = *reinterpret_cast<const int4*>(s_tap + m * 8), t1 = *reinterpret_cast<const int4*>(s_tap + m * 8 + 4);
-                const float4 w0 = *reinterpret_cast<const float4*>(s_wgt + m * 8), w1 = *reinterpret_cast<const float4*>(s_wgt + m * 8 + 4);
-                const int tp[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
-                const float wg[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
-                float4 fv[8];
-#pragma unroll
-                for (int k = 0; k < 8; k++) fv[k] = use_win ? s_win[tp[k] + q] : __ldg(f4 + tp[k] + q);
-                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-                for (int k = 0; k < 8; k++) {
-                    v.x = fmaf(fv[k].x, wg[k], v.x); v.y = fmaf(fv[k].y, wg[k], v.y);
-                    v.z = fmaf(fv[k].z, wg[k], v.z); v.w = fmaf(fv[k].w, wg[k], v.w);
-                }
-                a = prw_comb(a, v, aggr_mean);
+            if (four) {
+                if (use_win) accf[u] = prw_members<true, 4>(accf[u], s_tap, s_wgt, s_win, f4, q, grp, cnt, groups, aggr_mean);
+                else accf[u] = prw_members<false, 4>(accf[u], s_tap, s_wgt, s_win, f4, q, grp, cnt, groups, aggr_mean);
+            } else if (use_win) {
+                accf[u] = prw_members<true, 8>(accf[u], s_tap, s_wgt, s_win, f4, q, grp, cnt, groups, aggr_mean);
+            } else {
+                accf[u] = prw_members<false, 8>(accf[u], s_tap, s_wgt, s_win, f4, q, grp, cnt, groups, aggr_mean);
             }
-            accf[u] = a;
         }
     }
     if (groups == 2) accf[0] = prw_comb(accf[0], prw_shfl_xor(accf[0], 16), aggr_mean);
