@@ -42,7 +42,7 @@ class PoolParamsT(ctypes.Structure):
     _fields_ = [("size_x", c_f), ("size_y", c_f), ("size_t", c_f), ("nvx", c_i), ("nvy", c_i), ("nvt", c_i),
                 ("batch_size", c_i), ("inv_w", c_f), ("inv_h", c_f), ("aggr_mean", c_i), ("append_pos", c_i),
                 ("feat", c_p), ("feat_b", c_i), ("feat_h", c_i), ("feat_w", c_i), ("feat_c", c_i),
-                ("width", c_f), ("height", c_f)]
+                ("width", c_f), ("height", c_f), ("ell_stride", c_i)]
 
 
 def lib():
@@ -73,6 +73,8 @@ def _declare(L):
     _sig(L, "evad_graph_ws_bytes", c_sz, [c_i64, c_i, c_i, c_i, c_i])
     _sig(L, "evad_graph_build", c_i, [c_p, c_p, c_i64, c_i, c_i, c_i, c_i, c_i, c_i, c_i,
                                       c_p, c_p, c_p, c_p, c_i64, c_p, c_p, c_p, c_p, c_p, c_sz, c_p])
+    _sig(L, "evad_graph_build_rows", c_i, [c_p, c_p, c_i64, c_i, c_i, c_i, c_i, c_i, c_i, c_i,
+                                           c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_p])
     _sig(L, "evad_stream_state_bytes", c_sz, [c_i, c_i, c_i, c_i])
     _sig(L, "evad_stream_reset", c_i, [c_p, c_i, c_i, c_i, c_i, c_p])
     _sig(L, "evad_stream_ws_bytes", c_sz, [c_i64, c_i])
@@ -87,7 +89,7 @@ def _declare(L):
     _sig(L, "evad_gemm_ws_bytes", c_sz, [c_i64, c_i, c_i])
     _sig(L, "evad_gemm_epilogue", c_i, [c_p, c_i64, c_p, c_i64, c_p, c_i, c_i, P(EpilogueT), c_p, c_i, c_p, c_sz, c_p])
     _sig(L, "evad_edge_class", c_i, [c_p, c_p, c_i64, P(PseudoT), P(SplineModeT), c_p, c_p, c_p])
-    _sig(L, "evad_spline_conv_l1", c_i, [c_p, c_p, c_p, c_p, c_i64, c_p, c_i, c_i, c_p, c_i, c_p, c_p, c_p, c_p, P(EpilogueT),
+    _sig(L, "evad_spline_conv_l1", c_i, [c_p, c_p, c_p, c_p, c_i, c_i64, c_p, c_i, c_i, c_p, c_i, c_p, c_p, c_p, c_p, P(EpilogueT),
                                          c_p, c_i, P(EpilogueT), c_p, c_i, c_p])
     _sig(L, "evad_split_tf32", c_i, [c_p, c_i64, c_p, c_p, c_p])
     _sig(L, "evad_gemm64_tc_ws_bytes", c_sz, [c_i64, c_i])

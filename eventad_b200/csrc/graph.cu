@@ -166,6 +166,26 @@ extern "C" size_t evad_graph_ws_bytes(int64_t n, int B, int H, int W, int K) {
     return graph_ws_layout(a, n > 0 ? n : 1, (int64_t)B * H * W, K, &w) + 256;
 }
 
+// keys -> pixel sort -> cell table -> spiral search into fixed-stride rows nbr[n][K] / nbr_cls[n][K] / count[n]
+static int graph_rows(const int32_t* batch, const int32_t* pos, int64_t n, int B, int H, int W, int radius, int delta_t_us,
+                      int Q, int K, const GraphWs& w, int32_t* cell_start, int32_t* cell_perm, int32_t* nbr,
+                      uint8_t* nbr_cls, uint32_t* count, uint32_t* status, cudaStream_t st) {
+    const int64_t ncells = (int64_t)B * H * W;
+    g_keys_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(batch, pos, n, B, H, W, w.k0, status);
+    EVAD_CHECK_LAUNCH();
+    int key_bits = 1;
+    while ((1ll << key_bits) < ncells) key_bits++;
+    uint32_t *skey, *sidx;
+    EVAD_TRY(evad_sort_pairs_u32(w.k0, w.v0, w.k1, w.v1, 1, n, key_bits, w.sort_tmp, &skey, &sidx, st));
+    const int64_t m = (ncells + 1 > n) ? ncells + 1 : n;
+    g_cells_kernel<<<evad_cdiv(m, 256), 256, 0, st>>>(skey, sidx, pos, n, ncells, cell_start, w.st, cell_perm);
+    EVAD_CHECK_LAUNCH();
+    g_search_kernel<<<evad_cdiv(n, G_THREADS), G_THREADS, 0, st>>>(skey, sidx, w.st, cell_start, n, H, W, radius,
+                                                                  (float)delta_t_us, Q, K, nbr, nbr_cls, count);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
 extern "C" int evad_graph_build(const int32_t* batch, const int32_t* pos, int64_t n, int B, int H, int W, int radius,
                                 int delta_t_us, int Q, int K, int32_t* rowptr, int32_t* src, int32_t* num_edges,
                                 int64_t* edge_index, int64_t edge_index_stride, int32_t* cell_perm,
@@ -188,23 +208,33 @@ extern "C" int evad_graph_build(const int32_t* batch, const int32_t* pos, int64_
     graph_ws_layout(a, n, ncells, K, &w);
     if (!a.ok) return EVAD_ERR_WORKSPACE;
     int32_t* cell_start = cell_start_out ? cell_start_out : w.cell_start;
-
-    g_keys_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(batch, pos, n, B, H, W, w.k0, status);
-    EVAD_CHECK_LAUNCH();
-    int key_bits = 1;
-    while ((1ll << key_bits) < ncells) key_bits++;
-    uint32_t *skey, *sidx;
-    EVAD_TRY(evad_sort_pairs_u32(w.k0, w.v0, w.k1, w.v1, 1, n, key_bits, w.sort_tmp, &skey, &sidx, st));
-    const int64_t m = (ncells + 1 > n) ? ncells + 1 : n;
-    g_cells_kernel<<<evad_cdiv(m, 256), 256, 0, st>>>(skey, sidx, pos, n, ncells, cell_start, w.st, cell_perm);
-    EVAD_CHECK_LAUNCH();
-    g_search_kernel<<<evad_cdiv(n, G_THREADS), G_THREADS, 0, st>>>(skey, sidx, w.st, cell_start, n, H, W, radius,
-                                                                  (float)delta_t_us, Q, K, w.nbr,
-                                                                  edge_cls ? w.nbr_cls : nullptr, w.count);
-    EVAD_CHECK_LAUNCH();
+    EVAD_TRY(graph_rows(batch, pos, n, B, H, W, radius, delta_t_us, Q, K, w, cell_start, cell_perm, w.nbr,
+                        edge_cls ? w.nbr_cls : nullptr, w.count, status, st));
     EVAD_TRY(evad_exclusive_scan_u32(w.count, w.rowptr_u, n, w.rowptr_u + n, w.scan_tmp, st));
     g_compact_kernel<<<evad_cdiv(n * K, 256), 256, 0, st>>>(w.nbr, w.rowptr_u, n, K, rowptr, src, num_edges,
                                                           edge_index, edge_index_stride, w.nbr_cls, edge_cls);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
+}
+
+// The same graph as fixed-stride rows, without the scan + compaction into a CSR: row i = nbr[i*K .. i*K + count[i]).
+extern "C" int evad_graph_build_rows(const int32_t* batch, const int32_t* pos, int64_t n, int B, int H, int W, int radius,
+                                     int delta_t_us, int Q, int K, int32_t* nbr, int32_t* count, uint8_t* nbr_cls,
+                                     int32_t* cell_perm, int32_t* cell_start_out, uint32_t* status, void* ws,
+                                     size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n < 0 || B < 1 || H < 1 || W < 1 || radius < 0 || Q < 1 || K < 1 || K > 32) return EVAD_ERR_ARG;
+    if (nbr_cls && (2 * radius + 1) * (2 * radius + 1) > 256) return EVAD_ERR_UNSUPPORTED;
+    if (!nbr || !count || !status) return EVAD_ERR_ARG;
+    const int64_t ncells = (int64_t)B * H * W;
+    if (ncells >= (1ll << 31) || n * K >= (1ll << 31)) return EVAD_ERR_UNSUPPORTED;
+    if (n == 0) return EVAD_OK;
+    if (!batch || !pos || !ws) return EVAD_ERR_ARG;
+    EvadArena a(ws, ws_bytes);
+    GraphWs w;
+    graph_ws_layout(a, n, ncells, K, &w);
+    if (!a.ok) return EVAD_ERR_WORKSPACE;
+    int32_t* cell_start = cell_start_out ? cell_start_out : w.cell_start;
+    return graph_rows(batch, pos, n, B, H, W, radius, delta_t_us, Q, K, w, cell_start, cell_perm, nbr, nbr_cls,
+                      reinterpret_cast<uint32_t*>(count), status, st);
 }

@@ -401,6 +401,14 @@ __global__ void __launch_bounds__(PRW_WARPS * 32) pool_reduce_warp_kernel(
 // (sources outside the window, longer rows) takes the general path: id range first, then 4096-id chunks, in both launches.
 #define PL_ROWCAP 64
 
+// fine-graph rows: CSR (in_stride == 0, rowptr[n+1]) or fixed-stride rows (in_stride > 0, rowptr[i] = row length)
+__device__ __forceinline__ int pl_row_begin(const int32_t* __restrict__ rowptr, int in_stride, int i) {
+    return in_stride > 0 ? i * in_stride : rowptr[i];
+}
+__device__ __forceinline__ int pl_row_end(const int32_t* __restrict__ rowptr, int in_stride, int i) {
+    return in_stride > 0 ? i * in_stride + rowptr[i] : rowptr[i + 1];
+}
+
 // exclusive prefix of per-thread popcounts over the CTA (PL_THREADS = 128); returns the CTA total
 __device__ __forceinline__ uint32_t pool_popc_scan(uint32_t pc, uint32_t* s_warp, uint32_t* excl) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -426,7 +434,7 @@ __device__ __forceinline__ uint32_t pool_popc_scan(uint32_t pc, uint32_t* s_warp
 template <bool FILL>
 __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
     const uint32_t* __restrict__ sidx, const int32_t* __restrict__ seg_start, const int32_t* __restrict__ n_out,
-    const int32_t* __restrict__ rowptr_in, const int32_t* __restrict__ src_in, const int32_t* __restrict__ cluster,
+    const int32_t* __restrict__ rowptr_in, int in_stride, const int32_t* __restrict__ src_in, const int32_t* __restrict__ cluster,
     uint32_t* __restrict__ deg, const uint32_t* __restrict__ rowptr_out, int32_t* __restrict__ src_out, int64_t e_cap,
     int32_t* __restrict__ tmp, uint8_t* __restrict__ parked, uint32_t* __restrict__ status) {
     const int c = blockIdx.x;
@@ -455,7 +463,7 @@ __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
         bool oow = false;
         for (int p = s0 + threadIdx.x; p < s1; p += PL_THREADS) {
             const int i = (int)sidx[p];
-            for (int e = rowptr_in[i]; e < rowptr_in[i + 1]; e++) {
+            for (int e = pl_row_begin(rowptr_in, in_stride, i), e1 = pl_row_end(rowptr_in, in_stride, i); e < e1; e++) {
                 const int sc = cluster[src_in[e]];
                 const int r = sc - w0;
                 if (sc == c) continue;
@@ -489,7 +497,7 @@ __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
     int lo = 0x7fffffff, hi = -1;
     for (int p = s0 + threadIdx.x; p < s1; p += PL_THREADS) {
         const int i = (int)sidx[p];
-        for (int e = rowptr_in[i]; e < rowptr_in[i + 1]; e++) {
+        for (int e = pl_row_begin(rowptr_in, in_stride, i), e1 = pl_row_end(rowptr_in, in_stride, i); e < e1; e++) {
             const int sc = cluster[src_in[e]];
             if (sc != c) { lo = min(lo, sc); hi = max(hi, sc); }
         }
@@ -505,7 +513,7 @@ __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
         __syncthreads();
         for (int p = s0 + threadIdx.x; p < s1; p += PL_THREADS) {
             const int i = (int)sidx[p];
-            for (int e = rowptr_in[i]; e < rowptr_in[i + 1]; e++) {
+            for (int e = pl_row_begin(rowptr_in, in_stride, i), e1 = pl_row_end(rowptr_in, in_stride, i); e < e1; e++) {
                 const int sc = cluster[src_in[e]];
                 const int r = sc - w0;
                 if (sc != c && r >= 0 && r < PL_BITS) atomicOr(&bits[r >> 5], 1u << (r & 31));
@@ -632,12 +640,12 @@ extern "C" int evad_voxel_pool(const evad_pool_params_t* p, int64_t n_cap, const
     }
     EVAD_CHECK_LAUNCH();
     if (want_edges) {
-        pool_edges_kernel<false><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, src_in,
+        pool_edges_kernel<false><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, p->ell_stride, src_in,
                                                                              cluster, w.deg, nullptr, nullptr, e_cap,
                                                                              w.row_tmp, w.parked, status);
         EVAD_CHECK_LAUNCH();
         EVAD_TRY(evad_exclusive_scan_u32(w.deg, w.rowptr_u, c_cap + 1, nullptr, w.scan_tmp, st));
-        pool_edges_kernel<true><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, src_in,
+        pool_edges_kernel<true><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, p->ell_stride, src_in,
                                                                             cluster, w.deg, w.rowptr_u, src_out, e_cap,
                                                                             w.row_tmp, w.parked, status);
         EVAD_CHECK_LAUNCH();

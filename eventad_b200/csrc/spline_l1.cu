@@ -114,7 +114,7 @@ struct L1Cfg {
 template <int CP>
 __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 2) spline_l1_kernel(
     const int32_t* __restrict__ rowptr, const int32_t* __restrict__ src, const uint8_t* __restrict__ cls,
-    const int32_t* __restrict__ perm, int64_t n, const float* __restrict__ x, int ldx, const float* __restrict__ tapw, int ncls, const float* __restrict__ Whi,
+    const int32_t* __restrict__ perm, int ell_stride, int64_t n, const float* __restrict__ x, int ldx, const float* __restrict__ tapw, int ncls, const float* __restrict__ Whi,
     const float* __restrict__ Wlo, const float* __restrict__ Shi, const float* __restrict__ Slo, evad_epilogue_t E,
     float* __restrict__ out, int ldo, evad_epilogue_t ES, float* __restrict__ skip_out, int ld_skip) {
     using C = L1Cfg<CP>;
@@ -166,8 +166,9 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 2) spline_l1_kernel(
         for (int s = 0; s < L1_SLOTS - 1; s++) acc[s] = make_float4(0.f, 0.f, 0.f, 0.f);
         float4 xroot = make_float4(0.f, 0.f, 0.f, 0.f);
         if (valid) {
-            const int r0 = rowptr[i];
-            const int deg = rowptr[i + 1] - r0;
+            // CSR (rowptr[n+1]) or fixed-stride rows (ell_stride > 0: rowptr[i] = length of row i at i * ell_stride)
+            const int r0 = ell_stride > 0 ? (int)i * ell_stride : rowptr[i];
+            const int deg = ell_stride > 0 ? rowptr[i] : rowptr[i + 1] - r0;
             xroot = __ldg(reinterpret_cast<const float4*>(x + i * ldx) + q);
             // software pipeline without branches: the class and row of edge e+1 and the source id of edge e+2 are in
             // flight while the 60 FMAs of edge e run; indices are clamped to the last edge (a redundant, valid load)
@@ -286,7 +287,7 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 2) spline_l1_kernel(
 }
 
 template <int CP>
-static int launch_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* cls, const int32_t* perm, int64_t n,
+static int launch_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* cls, const int32_t* perm, int ell_stride, int64_t n,
                      const float* x, int ldx,
                      const float* tapw, int ncls, const float* Whi, const float* Wlo, const float* Shi, const float* Slo,
                      const evad_epilogue_t& E, float* out, int ldo, const evad_epilogue_t& ES, float* skip_out,
@@ -301,19 +302,20 @@ static int launch_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* c
     }
     const int64_t ntiles = (n + L1_NODES - 1) / L1_NODES;
     const int grid = (int)(ntiles < 2 * 148 ? ntiles : 2 * 148);
-    spline_l1_kernel<CP><<<grid, L1Cfg<CP>::THREADS, smem, st>>>(rowptr, src, cls, perm, n, x, ldx, tapw, ncls, Whi, Wlo, Shi, Slo,
+    spline_l1_kernel<CP><<<grid, L1Cfg<CP>::THREADS, smem, st>>>(rowptr, src, cls, perm, ell_stride, n, x, ldx, tapw, ncls, Whi, Wlo, Shi, Slo,
                                                                 E, out, ldo, ES, skip_out, ld_skip);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }
 
 extern "C" int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* cls, const int32_t* perm,
-                                   int64_t n, const float* x, int ldx, int cin_pad, const float* tapw, int ncls, const float* Whi,
+                                   int ell_stride, int64_t n, const float* x, int ldx, int cin_pad, const float* tapw, int ncls, const float* Whi,
                                    const float* Wlo, const float* Shi, const float* Slo, const evad_epilogue_t* epi_h,
                                    float* out, int ldo, const evad_epilogue_t* skip_epi_h, float* skip_out, int ld_skip,
                                    void* stream) {
     if (!rowptr || !src || !cls || !x || !tapw || !Whi || !Wlo || !epi_h || !out) return EVAD_ERR_ARG;
     if (cin_pad != 16 && cin_pad != 20) return EVAD_ERR_UNSUPPORTED;
+    if (ell_stride < 0 || (ell_stride > 0 && n * ell_stride >= (1ll << 31))) return EVAD_ERR_ARG;
     if (ldx < cin_pad || ldx % 4 != 0 || ldo % 4 != 0 || ncls < 1 || ncls > 256) return EVAD_ERR_ARG;
     if ((((uintptr_t)x | (uintptr_t)tapw | (uintptr_t)Whi | (uintptr_t)Wlo | (uintptr_t)out) & 15) != 0) return EVAD_ERR_ARG;
     const bool has_skip = Shi && Slo && skip_epi_h && skip_out;
@@ -323,8 +325,8 @@ extern "C" int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, co
     const evad_epilogue_t es = has_skip ? *skip_epi_h : *epi_h;
     cudaStream_t st = (cudaStream_t)stream;
     if (cin_pad == 20)
-        return launch_l1<20>(rowptr, src, cls, perm, n, x, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
+        return launch_l1<20>(rowptr, src, cls, perm, ell_stride, n, x, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
                              has_skip ? Slo : nullptr, *epi_h, out, ldo, es, skip_out, ld_skip, st);
-    return launch_l1<16>(rowptr, src, cls, perm, n, x, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
+    return launch_l1<16>(rowptr, src, cls, perm, ell_stride, n, x, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
                          has_skip ? Slo : nullptr, *epi_h, out, ldo, es, skip_out, ld_skip, st);
 }

@@ -88,6 +88,35 @@ class AsyncGraph:
         return dict(rowptr=rowptr, src=src, num_edges=num_edges, edge_index=edge_index, cell_perm=cell_perm,
                     cell_start=cell_start, edge_cls=edge_cls)
 
+    def build_rows(self, batch, pos, want_cls=True):
+        """Enqueues evad_graph_build_rows for a fresh graph: fixed-stride rows nbr [n, K] / count [n] / nbr_cls [n, K]
+        (+ cell_perm), no scan and no compaction.  Same edges and order as build_csr."""
+        if not (batch.is_cuda and pos.is_cuda):
+            raise RuntimeError("batch must be a CUDA tensor")
+        assert batch.dtype == torch.int32, [type(batch), batch.dtype]
+        batch, pos = batch.contiguous(), pos.contiguous()
+        if pos.dtype != torch.int32:
+            pos = pos.int()
+        dev, n = batch.device, batch.shape[0]
+        if self.device is None:
+            self.device = dev
+            self.initialize(n, dev)
+        K = int(self.max_num_neighbors)
+        L = _lib.lib()
+        nbr = torch.empty((max(n, 1), K), dtype=torch.int32, device=dev)
+        count = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+        nbr_cls = torch.empty((max(n, 1), K), dtype=torch.uint8, device=dev) if want_cls else None
+        cell_perm = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+        ws = self._ws.get(L.evad_graph_ws_bytes(n, self.batch_size, self.height, self.width, K), dev)
+        from .. import ops
+        with ops._timed("graph_build"):
+            rc = L.evad_graph_build_rows(_lib.ptr(batch), _lib.ptr(pos), n, int(self.batch_size), int(self.height),
+                                         int(self.width), int(self.radius), int(self.delta_t_us), int(self.max_queue_size),
+                                         K, _lib.ptr(nbr), _lib.ptr(count), _lib.ptr(nbr_cls), _lib.ptr(cell_perm), None,
+                                         _lib.ptr(self._status), _lib.ptr(ws), ws.numel(), _lib.stream())
+        _lib.check(rc, "evad_graph_build_rows")
+        return dict(nbr=nbr, count=count, nbr_cls=nbr_cls, cell_perm=cell_perm, K=K)
+
     def forward(self, batch, pos, collect_edges=True):
         n_ev = len(batch)
         if self.device is None:

@@ -56,7 +56,7 @@ class Layer(torch.nn.Module):
         self.conv_block2 = ConvBlockWithSkip(out_channels, out_channels, in_channels, args=args)
 
     # fused eval path on raw tensors (used by Layer.forward and by the fused Net.forward)
-    def run_fused(self, x, rowptr, src, n_cap, n_dev, pseudo, status, perm=None, cls=None):
+    def run_fused(self, x, rowptr, src, n_cap, n_dev, pseudo, status, perm=None, cls=None, ell_stride=0):
         b1, b2 = self.conv_block1, self.conv_block2
         relu = b1.activation is torch.nn.functional.relu
         s1, h1 = _fold(b1.norm, b1.conv.bias)
@@ -68,11 +68,12 @@ class Layer(torch.nn.Module):
             if USE_L1:
                 cls = ops.edge_class(rowptr, src, n_cap, b1.conv.mode(), pseudo, status)
         y, skip = b1.conv.run(x, rowptr, src, n_cap, n_dev, pseudo, dict(scale=s1, shift=h1, relu=relu), status,
-                              skip_weight=b2.lin.mlp.weight, skip_epi=dict(scale=ss, shift=hs), cls=cls, perm=perm)
+                              skip_weight=b2.lin.mlp.weight, skip_epi=dict(scale=ss, shift=hs), cls=cls, perm=perm,
+                              ell_stride=ell_stride)
         if not relu:
             y = b1.activation(y)
         out, _ = b2.conv.run(y, rowptr, src, n_cap, n_dev, pseudo, dict(scale=s2, shift=h2, addend=skip, relu=relu), status,
-                             cls=cls, perm=perm)
+                             cls=cls, perm=perm, ell_stride=ell_stride)
         if not relu:
             out = b2.activation(out)
         return out

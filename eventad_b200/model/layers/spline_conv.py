@@ -182,7 +182,7 @@ class MySplineConv(torch.nn.Module):
 
     # ---- kernels ---------------------------------------------------------------------------------------------
     def run(self, x, rowptr, src, n_cap, n_dev, pseudo, epi, status, skip_weight=None, skip_epi=None, cls=None,
-            perm=None):
+            perm=None, ell_stride=0):
         """x [n_cap, >=Cin] float32 -> epi(conv(x)) [n_cap, Cout] (+ skip_epi(x @ skip_weight^T) when requested)."""
         cin = self.in_channels
         if self.small_ok() and n_dev is None:
@@ -195,8 +195,11 @@ class MySplineConv(torch.nn.Module):
             pack = self.l1_pack(skip_weight) if USE_L1 else None
             if pack is not None:
                 if cls is None:
+                    assert ell_stride == 0
                     cls = ops.edge_class(rowptr, src, n_cap, self.mode(), pseudo, status)
-                return ops.spline_conv_l1(rowptr, src, cls, n_cap, x, cin, pack, epi, skip_epi, perm=perm)
+                return ops.spline_conv_l1(rowptr, src, cls, n_cap, x, cin, pack, epi, skip_epi, perm=perm,
+                                          ell_stride=ell_stride)
+            assert ell_stride == 0, "fixed-stride rows are only read by the layer-1 tensor-core kernel"
             return ops.spline_conv_small(rowptr, src, n_cap, x, cin, self.small_lut(skip_weight), self.mode(), pseudo, epi,
                                          status, skip_epi)
         x = x.contiguous()

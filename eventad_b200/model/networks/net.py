@@ -218,22 +218,29 @@ class Net(torch.nn.Module):
                                    c1.l1_pack(self.conv_block1.conv_block2.lin.mlp.weight) is not None and
                                    ops.offset_class_is_lut_class(m, two_m_of(self.edge_attrs.max), True, width, height))
             self._offcls_key = ck
-        graph = gc.build_csr(batch_i32, pos_int, want_cells=True, want_cls=self._offcls_ok)   # cell_perm: pixel order
+        cin1 = self.conv_block1.in_channel
+        f = feats_nhwc if self.use_image else [None] * 5
+        pseudo = dict(pos=pos, two_m=two_m_of(self.edge_attrs.max), clamp01=True)
+        if self._offcls_ok and n > 0:
+            # fixed-stride rows straight from the spiral search: layer 1 and pool 1 read them in place, so the fine graph
+            # is never scanned / compacted into a CSR (the reference's `edges[:, edges[1] >= 0]`, graph/utils.py:23)
+            graph = gc.build_rows(batch_i32, pos_int, want_cls=True)
+            rowptr, src, ell = graph["count"], graph["nbr"].view(-1), graph["K"]
+            cls1 = graph["nbr_cls"].view(-1)
+        else:
+            graph = gc.build_csr(batch_i32, pos_int, want_cells=True, want_cls=False)
+            rowptr, src, ell, cls1 = graph["rowptr"], graph["src"], 0, None
         gc.max_index, gc.all_timestamps, gc._history = n, pos_int[:, 2], [(batch_i32, pos_int, 0)]   # AsyncGraph bookkeeping
         status = gc._status
-        rowptr, src = graph["rowptr"], graph["src"]
-        f = feats_nhwc if self.use_image else [None] * 5
-        cin1 = self.conv_block1.in_channel
         x0 = ops.sample_concat(x, pos, batch_i32, f[0], width, height, append_pos=True, ldo=(cin1 + 3) // 4 * 4)
-        pseudo = dict(pos=pos, two_m=two_m_of(self.edge_attrs.max), clamp01=True)
         # layer 1 walks the nodes in pixel order: neighbouring destinations share their sources, so the row gathers
         # of a tile hit L1 instead of L2
-        xk = self.conv_block1.run_fused(x0, rowptr, src, n, None, pseudo, status, perm=graph["cell_perm"],
-                                        cls=graph["edge_cls"])
+        xk = self.conv_block1.run_fused(x0, rowptr, src, n, None, pseudo, status, perm=graph["cell_perm"], cls=cls1,
+                                        ell_stride=ell)
         counts = torch.zeros(12, dtype=torch.int32, device=dev)
         pools = [self.pool1, self.pool2, self.pool3, self.pool4]
         layers = [self.layer2, self.layer3, self.layer4, self.layer5]
-        cur = dict(x=xk, pos=pos, batch=batch_i32, rowptr=rowptr, src=src, n_cap=n, n_dev=None, e_cap=src.shape[0])
+        cur = dict(x=xk, pos=pos, batch=batch_i32, rowptr=rowptr, src=src, n_cap=n, n_dev=None, e_cap=src.shape[0], ell=ell)
         outs = []
         for k in range(4):
             p = pools[k]
@@ -244,7 +251,8 @@ class Net(torch.nn.Module):
             r = ops.voxel_pool(cur["x"], cur["pos"], cur["batch"], cur["rowptr"], cur["src"], cur["n_cap"], cur["n_dev"],
                                p._vs, p._nv, num_graphs, p._inv_wh, p.aggr, width, height, f[k + 1], append_pos=True,
                                ldo=(cin_next + 3) // 4 * 4, c_cap=c_cap, e_cap=e_cap, status=status,
-                               n_out=counts[2 * k:2 * k + 1], num_edges=counts[2 * k + 1:2 * k + 2])
+                               n_out=counts[2 * k:2 * k + 1], num_edges=counts[2 * k + 1:2 * k + 2],
+                               ell_stride=cur.get("ell", 0))
             pseudo = dict(pos=r["pos"], two_m=two_m_of(p.transform.max), clamp01=False)
             xo = layers[k].run_fused(r["x"], r["rowptr"], r["src"], c_cap, r["n_out"], pseudo, status)
             cur = dict(x=xo, pos=r["pos"], batch=r["batch"], rowptr=r["rowptr"], src=r["src"], n_cap=c_cap,

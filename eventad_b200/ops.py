@@ -300,8 +300,9 @@ def edge_class(rowptr, src, n, mode, pseudo, status):
     return cls
 
 
-def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None, perm=None):
-    """Tap aggregation + tensor-core contraction, cout = 16.  pack = dict(tapw, whi, wlo, shi, slo, cin_pad)."""
+def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None, perm=None, ell_stride=0):
+    """Tap aggregation + tensor-core contraction, cout = 16.  pack = dict(tapw, whi, wlo, shi, slo, cin_pad).
+    ell_stride > 0: fixed-stride rows (graph build_rows): rowptr = row lengths [n], src / cls rows at i * ell_stride."""
     L = _lib.lib()
     out = torch.empty((n, 16), dtype=torch.float32, device=x.device)
     has_skip = skip_epi is not None and pack.get("shi") is not None
@@ -309,7 +310,7 @@ def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None, perm=N
     e = _epi_struct(**epi)
     se = _epi_struct(**skip_epi) if has_skip else None
     with _timed(f'spline_conv_l1_c{cin}'):
-        check(L.evad_spline_conv_l1(ptr(rowptr), ptr(src), ptr(cls), ptr(perm), n, ptr(x), x.stride(0), pack["cin_pad"],
+        check(L.evad_spline_conv_l1(ptr(rowptr), ptr(src), ptr(cls), ptr(perm), int(ell_stride), n, ptr(x), x.stride(0), pack["cin_pad"],
                                     ptr(pack["tapw"]), pack["tapw"].shape[0], ptr(pack["whi"]), ptr(pack["wlo"]),
                                     ptr(pack["shi"]) if has_skip else None, ptr(pack["slo"]) if has_skip else None,
                                     ctypes.byref(e), ptr(out), out.stride(0), ctypes.byref(se) if has_skip else None,
@@ -401,8 +402,9 @@ def pool_geometry(voxel_size4: torch.Tensor, end4: torch.Tensor):
 
 def voxel_pool(x, pos, batch_i32, rowptr, src, n_cap, n_dev, voxel_size, nv, batch_size, inv_wh, aggr, width, height,
                feat_nhwc=None, append_pos=False, ldo=None, c_cap=None, e_cap=None, status=None, n_out=None,
-               num_edges=None):
-    """Returns dict(cluster, n_out, x, pos, batch, rowptr, src, num_edges); all arrays sized by c_cap / e_cap."""
+               num_edges=None, ell_stride=0):
+    """Returns dict(cluster, n_out, x, pos, batch, rowptr, src, num_edges); all arrays sized by c_cap / e_cap.
+    ell_stride > 0: the fine graph comes as fixed-stride rows (rowptr = row lengths [n], src rows at i * ell_stride)."""
     L = _lib.lib()
     dev = pos.device
     cx = x.shape[1]
@@ -432,7 +434,7 @@ def voxel_pool(x, pos, batch_i32, rowptr, src, n_cap, n_dev, voxel_size, nv, bat
     P = PoolParamsT(size_x=float(voxel_size[0]), size_y=float(voxel_size[1]), size_t=float(voxel_size[2]), nvx=nv[0],
                     nvy=nv[1], nvt=nv[2], batch_size=int(batch_size), inv_w=float(inv_wh[0]), inv_h=float(inv_wh[1]),
                     aggr_mean=int(aggr == "mean"), append_pos=int(append_pos), feat=ptr(feat_nhwc), feat_b=fb, feat_h=fh,
-                    feat_w=fw, feat_c=fc, width=float(width), height=float(height))
+                    feat_w=fw, feat_c=fc, width=float(width), height=float(height), ell_stride=int(ell_stride))
     ws = _ws(L.evad_voxel_pool_ws_bytes(n_cap, c_cap), dev)
     x = x.contiguous()
     pos = pos.contiguous()

@@ -81,6 +81,15 @@ int evad_graph_build(const int32_t* batch, const int32_t* pos, int64_t n_events,
                      uint8_t* edge_cls /* optional [K*N]: (dx + r) * (2r + 1) + (dy + r) of every CSR slot, the pixel
                                           offset source - destination the spiral walk found the edge at */,
                      uint32_t* status, void* ws, size_t ws_bytes, void* stream);
+/* The same graph as FIXED-STRIDE ROWS, without the prefix scan and the compaction into a CSR: row i =
+ * nbr[i*K .. i*K + count[i]) in the reference's edge order for destination i (self loop first), nbr_cls the matching
+ * offset-class bytes (optional).  evad_spline_conv_l1 and evad_voxel_pool read this layout directly (ell_stride = K);
+ * the reference's mask compaction `edges[:, edges[1] >= 0]` (graph/utils.py:23) is what evad_graph_build adds on top.
+ * Workspace: evad_graph_ws_bytes. */
+int evad_graph_build_rows(const int32_t* batch, const int32_t* pos, int64_t n_events, int batch_size, int height,
+                          int width, int radius, int delta_t_us, int max_queue_size, int max_neighbors, int32_t* nbr,
+                          int32_t* count, uint8_t* nbr_cls, int32_t* cell_perm, int32_t* cell_start, uint32_t* status,
+                          void* ws, size_t ws_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Event-graph construction, streaming ("append") mode: EV_TGN.forward(reset=False)
@@ -181,6 +190,8 @@ int evad_edge_class(const int32_t* rowptr, const int32_t* src, int64_t n, const 
                     const evad_spline_mode_t* mode_h, uint8_t* cls, uint32_t* status, void* stream);
 int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* cls,
                         const int32_t* perm /* optional processing order, e.g. cell_perm of evad_graph_build */,
+                        int ell_stride /* 0: CSR, rowptr[n+1]; K > 0: fixed-stride rows of evad_graph_build_rows,
+                                          rowptr[i] = length of row i, src / cls row i at i*K */,
                         int64_t n, const float* x, int ldx,
                         int cin_pad, const float* tapw, int ncls, const float* Whi, const float* Wlo, const float* Shi,
                         const float* Slo, const evad_epilogue_t* epi_h, float* out, int ldo,
@@ -224,6 +235,8 @@ typedef struct {
     const float* feat;            /* optional CHANNEL-LAST CNN map [feat_b, feat_h, feat_w, feat_c], or NULL */
     int feat_b, feat_h, feat_w, feat_c;
     float width, height;          /* data.width[0], data.height[0] */
+    int ell_stride;               /* 0: rowptr_in is a CSR row pointer [n+1]; K > 0: the fine graph comes as fixed-stride
+                                     rows (evad_graph_build_rows): row i = src_in[i*K .. i*K + rowptr_in[i]) */
 } evad_pool_params_t;
 
 size_t evad_voxel_pool_ws_bytes(int64_t n_cap, int64_t c_cap);

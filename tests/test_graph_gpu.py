@@ -81,3 +81,28 @@ def test_empty_and_errors():
     bad = torch.tensor([[40, 1, 5], [1, 1, 6]], dtype=torch.int32, device="cuda")      # x outside the sensor
     with pytest.raises(RuntimeError):
         g.forward(torch.zeros(2, dtype=torch.int32, device="cuda"), bad, delete_nodes=False)
+
+
+@pytest.mark.parametrize("n,B,dist", [(30_000, 2, "C"), (100_000, 1, "U"), (1, 1, "U")])
+def test_fixed_stride_rows_equal_the_compacted_graph(n, B, dist):
+    """evad_graph_build_rows (no scan / compaction) holds exactly the rows of evad_graph_build, slot for slot, and the
+    offset-class bytes of both agree."""
+    from eventad_b200.graph.ev_graph import SlidingWindowGraph
+    raw = synthetic.make_batch(n, B, seed=5, dist=dist)
+    pos = np.concatenate([raw["pos"].astype(np.int32), raw["t"].reshape(-1, 1)], 1).astype(np.int32)
+    bt, pt = torch.from_numpy(raw["batch"].astype(np.int32)).cuda(), torch.from_numpy(pos).cuda()
+    mk = lambda: SlidingWindowGraph(width=raw["width"], height=raw["height"], batch_size=B, max_num_neighbors=16,
+                                    max_queue_size=128, radius=4, delta_t_us=10000)
+    g1, g2 = mk(), mk()
+    g1.reset(); g2.reset()
+    csr = g1.build_csr(bt, pt, want_cells=True, want_cls=True)
+    rows = g2.build_rows(bt, pt, want_cls=True)
+    N = bt.shape[0]
+    rowptr = csr["rowptr"].cpu().numpy()
+    cnt = rows["count"].cpu().numpy()[:N]
+    assert np.array_equal(np.diff(rowptr[:N + 1]), cnt)
+    E = int(csr["num_edges"].item())
+    mask = np.arange(16)[None, :] < cnt[:, None]
+    assert np.array_equal(rows["nbr"].cpu().numpy()[:N][mask], csr["src"].cpu().numpy()[:E])
+    assert np.array_equal(rows["nbr_cls"].cpu().numpy()[:N][mask], csr["edge_cls"].cpu().numpy()[:E])
+    assert torch.equal(rows["cell_perm"][:N], csr["cell_perm"][:N])
