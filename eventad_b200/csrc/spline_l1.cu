@@ -111,7 +111,26 @@ struct L1Cfg {
     }
 };
 
-template <int CP>
+// one edge of the tap aggregation: acc[s] += tapw[class][s] * x_src for the 15 tap slots
+__device__ __forceinline__ void l1_edge_fma(float4 (&acc)[L1_SLOTS - 1], const float* __restrict__ twr, const float4 xq) {
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        const float4 w4 = *reinterpret_cast<const float4*>(twr + 4 * u);
+        const float w[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+            const int s = 4 * u + b;
+            if (s < L1_SLOTS - 1) {
+                acc[s].x = fmaf(w[b], xq.x, acc[s].x); acc[s].y = fmaf(w[b], xq.y, acc[s].y);
+                acc[s].z = fmaf(w[b], xq.z, acc[s].z); acc[s].w = fmaf(w[b], xq.w, acc[s].w);
+            }
+        }
+    }
+}
+
+// ROWS16: the graph comes as fixed-stride rows of 16 slots (evad_graph_build_rows): source ids are read four at a time
+// (one 128-bit load per group) and the class bytes one word per group, instead of two scalar loads per edge and thread.
+template <int CP, bool ROWS16>
 __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 2) spline_l1_kernel(
     const int32_t* __restrict__ rowptr, const int32_t* __restrict__ src, const uint8_t* __restrict__ cls,
     const int32_t* __restrict__ perm, int ell_stride, int64_t n, const float* __restrict__ x, int ldx, const float* __restrict__ tapw, int ncls, const float* __restrict__ Whi,
@@ -165,7 +184,37 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 2) spline_l1_kernel(
 #pragma unroll
         for (int s = 0; s < L1_SLOTS - 1; s++) acc[s] = make_float4(0.f, 0.f, 0.f, 0.f);
         float4 xroot = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (valid) {
+        if (valid && ROWS16) {
+            const int deg = rowptr[i];
+            const int4* srow = reinterpret_cast<const int4*>(src) + i * 4;
+            const uint32_t* crow = reinterpret_cast<const uint32_t*>(cls) + i * 4;
+            if (deg > 0) {
+                int4 s_cur = __ldg(srow);
+                uint32_t c_cur = __ldg(crow);
+                float4 x_next = __ldg(reinterpret_cast<const float4*>(x + (int64_t)s_cur.x * ldx) + q);
+#pragma unroll 1
+                for (int g = 0; 4 * g < deg; g++) {
+                    int4 s_next = s_cur;
+                    uint32_t c_next = c_cur;
+                    if (4 * (g + 1) < deg) {                  // next group of source ids / class bytes: in flight for 4 edges
+                        s_next = __ldg(srow + g + 1);
+                        c_next = __ldg(crow + g + 1);
+                    }
+                    const int sj[5] = {s_cur.x, s_cur.y, s_cur.z, s_cur.w, s_next.x};
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        const int e = 4 * g + k;
+                        if (e >= deg) break;
+                        const float4 xq = x_next;
+                        if (e + 1 < deg) x_next = __ldg(reinterpret_cast<const float4*>(x + (int64_t)sj[k + 1] * ldx) + q);
+                        l1_edge_fma(acc, tw + ((c_cur >> (8 * k)) & 0xffu) * L1_TW_LD, xq);
+                    }
+                    s_cur = s_next;
+                    c_cur = c_next;
+                }
+            }
+            xroot = __ldg(reinterpret_cast<const float4*>(x + i * ldx) + q);
+        } else if (valid) {
             // CSR (rowptr[n+1]) or fixed-stride rows (ell_stride > 0: rowptr[i] = length of row i at i * ell_stride)
             const int r0 = ell_stride > 0 ? (int)i * ell_stride : rowptr[i];
             const int deg = ell_stride > 0 ? rowptr[i] : rowptr[i + 1] - r0;
@@ -186,19 +235,7 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 2) spline_l1_kernel(
                 c_next = cls[min(r0 + e + 1, last)];
                 x_next = __ldg(reinterpret_cast<const float4*>(x + (int64_t)j_n2 * ldx) + q);
                 j_n2 = src[min(r0 + e + 2, last)];
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const float4 w4 = *reinterpret_cast<const float4*>(twr + 4 * u);
-                    const float w[4] = {w4.x, w4.y, w4.z, w4.w};
-#pragma unroll
-                    for (int b = 0; b < 4; b++) {
-                        const int s = 4 * u + b;
-                        if (s < L1_SLOTS - 1) {
-                            acc[s].x = fmaf(w[b], xq.x, acc[s].x); acc[s].y = fmaf(w[b], xq.y, acc[s].y);
-                            acc[s].z = fmaf(w[b], xq.z, acc[s].z); acc[s].w = fmaf(w[b], xq.w, acc[s].w);
-                        }
-                    }
-                }
+                l1_edge_fma(acc, twr, xq);
             }
         }
         // ---------------------------------------------------------------- (2) contraction, two rounds of 8 slots
@@ -286,7 +323,7 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 2) spline_l1_kernel(
     }
 }
 
-template <int CP>
+template <int CP, bool ROWS16>
 static int launch_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* cls, const int32_t* perm, int ell_stride, int64_t n,
                      const float* x, int ldx,
                      const float* tapw, int ncls, const float* Whi, const float* Wlo, const float* Shi, const float* Slo,
@@ -296,13 +333,13 @@ static int launch_l1(const int32_t* rowptr, const int32_t* src, const uint8_t* c
     if (smem > 113 * 1024) return EVAD_ERR_UNSUPPORTED;      // two CTAs per SM
     static size_t attr_bytes = 0;
     if (smem > attr_bytes) {
-        if (cudaFuncSetAttribute(spline_l1_kernel<CP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        if (cudaFuncSetAttribute(spline_l1_kernel<CP, ROWS16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
             return EVAD_ERR_LAUNCH;
         attr_bytes = smem;
     }
     const int64_t ntiles = (n + L1_NODES - 1) / L1_NODES;
     const int grid = (int)(ntiles < 2 * 148 ? ntiles : 2 * 148);
-    spline_l1_kernel<CP><<<grid, L1Cfg<CP>::THREADS, smem, st>>>(rowptr, src, cls, perm, ell_stride, n, x, ldx, tapw, ncls, Whi, Wlo, Shi, Slo,
+    spline_l1_kernel<CP, ROWS16><<<grid, L1Cfg<CP>::THREADS, smem, st>>>(rowptr, src, cls, perm, ell_stride, n, x, ldx, tapw, ncls, Whi, Wlo, Shi, Slo,
                                                                 E, out, ldo, ES, skip_out, ld_skip);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
@@ -324,9 +361,11 @@ extern "C" int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, co
     if (n <= 0) return EVAD_OK;
     const evad_epilogue_t es = has_skip ? *skip_epi_h : *epi_h;
     cudaStream_t st = (cudaStream_t)stream;
-    if (cin_pad == 20)
-        return launch_l1<20>(rowptr, src, cls, perm, ell_stride, n, x, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
-                             has_skip ? Slo : nullptr, *epi_h, out, ldo, es, skip_out, ld_skip, st);
-    return launch_l1<16>(rowptr, src, cls, perm, ell_stride, n, x, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
-                         has_skip ? Slo : nullptr, *epi_h, out, ldo, es, skip_out, ld_skip, st);
+    const bool rows16 = ell_stride == 16 && (((uintptr_t)src | (uintptr_t)cls) & 15) == 0;
+#define L1_LAUNCH(CP_, R_)                                                                                              \
+    launch_l1<CP_, R_>(rowptr, src, cls, perm, ell_stride, n, x, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,   \
+                       has_skip ? Slo : nullptr, *epi_h, out, ldo, es, skip_out, ld_skip, st)
+    if (cin_pad == 20) return rows16 ? L1_LAUNCH(20, true) : L1_LAUNCH(20, false);
+    return rows16 ? L1_LAUNCH(16, true) : L1_LAUNCH(16, false);
+#undef L1_LAUNCH
 }
