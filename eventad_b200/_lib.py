@@ -42,7 +42,7 @@ class PoolParamsT(ctypes.Structure):
     _fields_ = [("size_x", c_f), ("size_y", c_f), ("size_t", c_f), ("nvx", c_i), ("nvy", c_i), ("nvt", c_i),
                 ("batch_size", c_i), ("inv_w", c_f), ("inv_h", c_f), ("aggr_mean", c_i), ("append_pos", c_i),
                 ("feat", c_p), ("feat_b", c_i), ("feat_h", c_i), ("feat_w", c_i), ("feat_c", c_i),
-                ("width", c_f), ("height", c_f), ("ell_stride", c_i)]
+                ("width", c_f), ("height", c_f), ("ell_stride", c_i), ("self_loop", c_i)]
 
 
 def lib():

@@ -434,8 +434,8 @@ __device__ __forceinline__ uint32_t pool_popc_scan(uint32_t pc, uint32_t* s_warp
 template <bool FILL>
 __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
     const uint32_t* __restrict__ sidx, const int32_t* __restrict__ seg_start, const int32_t* __restrict__ n_out,
-    const int32_t* __restrict__ rowptr_in, int in_stride, const int32_t* __restrict__ src_in, const int32_t* __restrict__ cluster,
-    uint32_t* __restrict__ deg, const uint32_t* __restrict__ rowptr_out, int32_t* __restrict__ src_out, int64_t e_cap,
+    const int32_t* __restrict__ rowptr_in, int in_stride, int keep_self, const int32_t* __restrict__ src_in,
+    const int32_t* __restrict__ cluster, uint32_t* __restrict__ deg, const uint32_t* __restrict__ rowptr_out, int32_t* __restrict__ src_out, int64_t e_cap,
     int32_t* __restrict__ tmp, uint8_t* __restrict__ parked, uint32_t* __restrict__ status) {
     const int c = blockIdx.x;
     const int nc = *n_out;
@@ -466,7 +466,7 @@ __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
             for (int e = pl_row_begin(rowptr_in, in_stride, i), e1 = pl_row_end(rowptr_in, in_stride, i); e < e1; e++) {
                 const int sc = cluster[src_in[e]];
                 const int r = sc - w0;
-                if (sc == c) continue;
+                if (sc == c && !keep_self) continue;             // Pooling(self_loop=False) drops them (pooling.py:60-63)
                 if (r >= 0 && r < PL_BITS) atomicOr(&bits[r >> 5], 1u << (r & 31));
                 else oow = true;
             }
@@ -499,7 +499,7 @@ __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
         const int i = (int)sidx[p];
         for (int e = pl_row_begin(rowptr_in, in_stride, i), e1 = pl_row_end(rowptr_in, in_stride, i); e < e1; e++) {
             const int sc = cluster[src_in[e]];
-            if (sc != c) { lo = min(lo, sc); hi = max(hi, sc); }
+            if (sc != c || keep_self) { lo = min(lo, sc); hi = max(hi, sc); }
         }
     }
     atomicMin(&s_lo, lo);
@@ -516,7 +516,7 @@ __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
             for (int e = pl_row_begin(rowptr_in, in_stride, i), e1 = pl_row_end(rowptr_in, in_stride, i); e < e1; e++) {
                 const int sc = cluster[src_in[e]];
                 const int r = sc - w0;
-                if (sc != c && r >= 0 && r < PL_BITS) atomicOr(&bits[r >> 5], 1u << (r & 31));
+                if ((sc != c || keep_self) && r >= 0 && r < PL_BITS) atomicOr(&bits[r >> 5], 1u << (r & 31));
             }
         }
         __syncthreads();
@@ -640,12 +640,12 @@ extern "C" int evad_voxel_pool(const evad_pool_params_t* p, int64_t n_cap, const
     }
     EVAD_CHECK_LAUNCH();
     if (want_edges) {
-        pool_edges_kernel<false><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, p->ell_stride, src_in,
+        pool_edges_kernel<false><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, p->ell_stride, p->self_loop, src_in,
                                                                              cluster, w.deg, nullptr, nullptr, e_cap,
                                                                              w.row_tmp, w.parked, status);
         EVAD_CHECK_LAUNCH();
         EVAD_TRY(evad_exclusive_scan_u32(w.deg, w.rowptr_u, c_cap + 1, nullptr, w.scan_tmp, st));
-        pool_edges_kernel<true><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, p->ell_stride, src_in,
+        pool_edges_kernel<true><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, p->ell_stride, p->self_loop, src_in,
                                                                             cluster, w.deg, w.rowptr_u, src_out, e_cap,
                                                                             w.row_tmp, w.parked, status);
         EVAD_CHECK_LAUNCH();

@@ -31,8 +31,6 @@ class Pooling(torch.nn.Module):
         self.bn = None
         if in_channels > 0:
             self.bn = BatchNormData(in_channels)
-        if keep_temporal_ordering or self_loop:
-            raise NotImplementedError("keep_temporal_ordering / self_loop are off on the EventAD path (SURVEY A.1)")
         # host copies of the geometry (fp32 values exactly as torch_cluster sees them)
         self._vs = [float(v) for v in self.voxel_size]
         self._nv = ops.pool_geometry(self.voxel_size, self.end)
@@ -51,7 +49,7 @@ class Pooling(torch.nn.Module):
             status=None, e_cap=None, width=None, height=None):
         return ops.voxel_pool(x, pos, batch_i32, rowptr, src, n_cap, n_dev, self._vs, self._nv, batch_size, self._inv_wh,
                               self.aggr, width or self.width, height or self.height, feat_nhwc, append_pos, ldo,
-                              e_cap=e_cap, status=status)
+                              e_cap=e_cap, status=status, self_loop=self.self_loop)
 
     def forward(self, data):
         if data.x.shape[0] == 0:
@@ -81,6 +79,14 @@ class Pooling(torch.nn.Module):
         new_data._csr = dict(rowptr=r["rowptr"][:n_out + 1], src=r["src"][:max(e, 1)], eid=eid[:max(e, 1)],
                              edge_index_ptr=(edge_index.data_ptr(), tuple(edge_index.shape)))
         new_data.cluster = r["cluster"][:n].long()
+        if self.keep_temporal_ordering:
+            # pooling.py:69-72: keep the coarse edges whose destination voxel holds a later event than the source voxel
+            t_max = torch.full((max(n_out, 1),), float("-inf"), dtype=pos.dtype, device=dev)
+            t_max.scatter_reduce_(0, new_data.cluster, pos[:, -1].contiguous(), reduce="amax", include_self=True)
+            if e > 0:
+                t_src, t_dst = t_max[edge_index]
+                new_data.edge_index = edge_index[:, t_dst > t_src]
+                del new_data._csr                            # the cached CSR describes the unfiltered edges
         if hasattr(data, "height"):
             new_data.height = data.height
             new_data.width = data.width

@@ -402,7 +402,7 @@ def pool_geometry(voxel_size4: torch.Tensor, end4: torch.Tensor):
 
 def voxel_pool(x, pos, batch_i32, rowptr, src, n_cap, n_dev, voxel_size, nv, batch_size, inv_wh, aggr, width, height,
                feat_nhwc=None, append_pos=False, ldo=None, c_cap=None, e_cap=None, status=None, n_out=None,
-               num_edges=None, ell_stride=0):
+               num_edges=None, ell_stride=0, self_loop=False):
     """Returns dict(cluster, n_out, x, pos, batch, rowptr, src, num_edges); all arrays sized by c_cap / e_cap.
     ell_stride > 0: the fine graph comes as fixed-stride rows (rowptr = row lengths [n], src rows at i * ell_stride)."""
     L = _lib.lib()
@@ -434,7 +434,7 @@ def voxel_pool(x, pos, batch_i32, rowptr, src, n_cap, n_dev, voxel_size, nv, bat
     P = PoolParamsT(size_x=float(voxel_size[0]), size_y=float(voxel_size[1]), size_t=float(voxel_size[2]), nvx=nv[0],
                     nvy=nv[1], nvt=nv[2], batch_size=int(batch_size), inv_w=float(inv_wh[0]), inv_h=float(inv_wh[1]),
                     aggr_mean=int(aggr == "mean"), append_pos=int(append_pos), feat=ptr(feat_nhwc), feat_b=fb, feat_h=fh,
-                    feat_w=fw, feat_c=fc, width=float(width), height=float(height), ell_stride=int(ell_stride))
+                    feat_w=fw, feat_c=fc, width=float(width), height=float(height), ell_stride=int(ell_stride), self_loop=int(bool(self_loop)))
     ws = _ws(L.evad_voxel_pool_ws_bytes(n_cap, c_cap), dev)
     x = x.contiguous()
     pos = pos.contiguous()

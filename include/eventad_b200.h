@@ -237,6 +237,7 @@ typedef struct {
     float width, height;          /* data.width[0], data.height[0] */
     int ell_stride;               /* 0: rowptr_in is a CSR row pointer [n+1]; K > 0: the fine graph comes as fixed-stride
                                      rows (evad_graph_build_rows): row i = src_in[i*K .. i*K + rowptr_in[i]) */
+    int self_loop;                /* Pooling(self_loop=True): coarse self loops are kept (pooling.py:59-60) */
 } evad_pool_params_t;
 
 size_t evad_voxel_pool_ws_bytes(int64_t n_cap, int64_t c_cap);

@@ -114,8 +114,9 @@ def consecutive_cluster(src):
     return unique, inv, perm, counts
 
 
-def pooling(x, pos, batch, edge_index, voxel_size3, width, height, batch_size_ctor, transform_max, aggr="max"):
-    """Pooling.forward (layers/pooling.py:51-97), keep_temporal_ordering=False, self_loop=False, no bn.
+def pooling(x, pos, batch, edge_index, voxel_size3, width, height, batch_size_ctor, transform_max, aggr="max",
+            keep_temporal_ordering=False, self_loop=False):
+    """Pooling.forward (layers/pooling.py:51-97), no bn.
     voxel_size3 = [sx, sy, 1] (pooling.py:24).  Returns a namespace with x,pos,batch,edge_index,edge_attr,cluster."""
     voxel_size = voxel_size3
     start = torch.Tensor([0, 0, 0, 0])
@@ -125,11 +126,19 @@ def pooling(x, pos, batch, edge_index, voxel_size3, width, height, batch_size_ct
     raw_cluster = ops.grid_cluster(pos4, torch.cat([voxel_size, torch.Tensor([1])]), start, end)
     unique_clusters, cluster, perm, _ = consecutive_cluster(raw_cluster)
     e = cluster[edge_index]
-    e = e[:, e[0] != e[1]]
-    if e.shape[1] > 0:
+    if self_loop:                                                     # pooling.py:59-60
         e = e.unique(dim=-1)
+    else:
+        e = e[:, e[0] != e[1]]
+        if e.shape[1] > 0:
+            e = e.unique(dim=-1)
     new_batch = batch[perm]
     new_pos = ops.scatter_mean(pos, cluster)
+    if keep_temporal_ordering:                                        # pooling.py:69-72 (torch_scatter.scatter_max)
+        t_max = torch.full((int(cluster.max()) + 1,), float("-inf"), dtype=pos.dtype)
+        t_max = t_max.scatter_reduce(0, cluster, pos[:, -1], reduce="amax", include_self=True)
+        t_src, t_dst = t_max[e]
+        e = e[:, t_dst > t_src]
     if aggr == "max":
         new_x = ops.scatter_max(x, cluster)
     else:

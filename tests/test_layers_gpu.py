@@ -154,6 +154,43 @@ def test_pooling(B, n, level, aggr):
     assert torch.equal(out.edge_attr.cpu(), ref.edge_attr)
 
 
+@pytest.mark.parametrize("level,self_loop,keep_t", [(0, True, False), (0, False, True), (1, True, True), (2, True, False)])
+def test_pooling_options(level, self_loop, keep_t):
+    """Pooling(self_loop=..., keep_temporal_ordering=...) (pooling.py:59-63,69-72) vs the oracle, bit-exact edges.  The
+    level-1 / level-2 inputs are coarse graphs without self loops, where (c, c) appears only if two members are linked."""
+    from eventad_b200.data import Batch
+    from eventad_b200.model.layers.components import Cartesian
+    from eventad_b200.model.layers.pooling import Pooling
+    from oracle import dagr_layers
+    from oracle.dagr_net import compute_pooling_at_each_layer
+    model, args = make_backbone(use_image=False)
+    B, n = 2, 12_000
+    d = make_data(n, B, seed=8, dist="C")
+    ei = _graph(d, args)
+    voxels = compute_pooling_at_each_layer(args.pooling_dim_at_output, 4)
+    x = torch.randn(d.pos.shape[0], 8, generator=torch.Generator().manual_seed(3))
+    pos, batch = d.pos, d.batch
+    for lv in range(level):                          # walk down to the requested level with the oracle (default options)
+        tm = [model.backbone.pool1, model.backbone.pool2, model.backbone.pool3][lv].transform.max
+        r = dagr_layers.pooling(x, pos, batch, ei, voxels[lv], 320, 240, args.batch_size, tm, "max")
+        x, pos, batch, ei = r.x, r.pos, r.batch, r.edge_index
+    tmax = [model.backbone.pool1, model.backbone.pool2, model.backbone.pool3][level].transform.max
+    ref = dagr_layers.pooling(x, pos, batch, ei, voxels[level], 320, 240, args.batch_size, tmax, "max",
+                              keep_temporal_ordering=keep_t, self_loop=self_loop)
+    pool = Pooling(voxels[level], width=320, height=240, batch_size=args.batch_size,
+                   transform=Cartesian(norm=True, cat=False, max_value=tmax), aggr="max",
+                   keep_temporal_ordering=keep_t, self_loop=self_loop).cuda()
+    data = Batch(x=x.cuda(), pos=pos.cuda(), batch=batch.cuda(), edge_index=ei.cuda())
+    data.width, data.height = d.width, d.height
+    out = pool(data)
+    assert torch.equal(out.cluster.cpu(), ref.cluster)
+    assert torch.equal(out.edge_index.cpu(), ref.edge_index)
+    assert torch.equal(out.x.cpu(), ref.x) and torch.equal(out.pos.cpu(), ref.pos)
+    assert torch.equal(out.edge_attr.cpu(), ref.edge_attr)
+    if self_loop and not keep_t:                     # (c, c) has t_dst == t_src and does not survive the temporal filter
+        assert bool((ref.edge_index[0] == ref.edge_index[1]).any())
+
+
 @pytest.mark.parametrize("dist,B", [("U", 1), ("C", 3)])
 def test_spiral_offset_class_equals_lut_class(dist, B):
     """The class bytes evad_graph_build derives from the spiral offset equal the reference's fp32 LUT index
