@@ -15,69 +15,11 @@
 //   one thread issues 12 tcgen05.mma and commits them to the slab's mbarrier -> (two slabs in flight) ->
 //   tcgen05.ld of the accumulator rows (one row per thread), BatchNorm / skip add / ReLU epilogue, or raw split-K
 //   partials that gemm_tc.cu's deterministic reduce kernel sums.
-#include "common.cuh"
+#include "tc5.cuh"
 
-#define T5_BM 128
-#define T5_BN 64
-#define T5_BK 32                                             // floats per slab = 128 bytes = one swizzle row
 #define T5_THREADS 256
-#define T5_A_BYTES (T5_BM * 128)                             // 16 KB
-#define T5_B_BYTES (T5_BN * 128)                             // 8 KB
-#define T5_OB_BYTES (2 * T5_A_BYTES + 2 * T5_B_BYTES)        // operand buffer: A_hi, A_lo, W_hi, W_lo = 48 KB
 #define T5_RAW_BYTES (T5_A_BYTES + T5_B_BYTES)               // raw fp32 slab: 24 KB
 #define T5_RAW_STAGES 4
-#define T5_TMEM_COLS 128                                     // two 64-column accumulator buffers
-
-
-// ---- PTX wrappers (sm_100a) ----
-__device__ __forceinline__ uint32_t t5_smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void t5_cp16(uint32_t dst, const void* gmem, int src_bytes) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(gmem), "r"(src_bytes));
-}
-__device__ __forceinline__ void t5_commit_group() { asm volatile("cp.async.commit_group;"); }
-template <int N>
-__device__ __forceinline__ void t5_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-__device__ __forceinline__ void t5_mbar_init(uint32_t bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void t5_mbar_wait(uint32_t bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "T5_WAIT:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra T5_DONE;\n\t"
-        "bra T5_WAIT;\n\t"
-        "T5_DONE:\n\t"
-        "}\n" ::"r"(bar), "r"(parity)
-        : "memory");
-}
-
-// 64-bit shared-memory matrix descriptor: K-major operand tile, 128-byte swizzle, rows of 128 bytes, 8-row groups
-// 1024 bytes apart (cute::UMMA::SmemDescriptor: start >> 4 | LBO(16 B) << 16 | SBO(1024 B) << 32 | version 1 << 46 |
-// SWIZZLE_128B (2) << 61).  The tile base is 1024-byte aligned; a K step of 8 floats advances the start by 32 bytes.
-__device__ __forceinline__ uint64_t t5_desc(uint32_t smem_addr) {
-    return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
-}
-
-// instruction descriptor (cute::UMMA::InstrDescriptor): D = F32 (1 << 4), A = B = TF32 (2 << 7, 2 << 10), both K-major,
-// N = 64 (N >> 3 at bit 17), M = 128 (M >> 4 at bit 24)
-#define T5_IDESC ((1u << 4) | (2u << 7) | (2u << 10) | ((T5_BN >> 3) << 17) | ((T5_BM >> 4) << 24))
-
-__device__ __forceinline__ void t5_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
-        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(T5_IDESC), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void t5_mma_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
 
 // A [m, lda] row-major; Wt [64, ldw] = W transposed (row n holds the K weights of output n, zero padded to ldw).
 // Shared memory: a T5_RAW_STAGES-deep ring of raw fp32 slabs filled by cp.async (enough bytes in flight to cover the

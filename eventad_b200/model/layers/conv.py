@@ -13,6 +13,20 @@ def _fold(bn_data, conv_bias=None):
     return ops.fold_bn(bn_data.module, conv_bias)
 
 
+def _same_mode(a, b):
+    """True when two convolutions evaluate the same basis for an edge (kernel size, LUT geometry and tables)."""
+    if a is b:
+        return True
+    for k in a:
+        va, vb = a[k], b.get(k)
+        if isinstance(va, torch.Tensor):
+            if not (isinstance(vb, torch.Tensor) and va.shape == vb.shape and bool(torch.equal(va, vb.to(va.device)))):
+                return False
+        elif va != vb:
+            return False
+    return True
+
+
 class ConvBlock(torch.nn.Module):
     def __init__(self, in_channels: int, out_channels: int, args, degree=1) -> None:
         super(ConvBlock, self).__init__()
@@ -67,12 +81,21 @@ class Layer(torch.nn.Module):
             from .spline_conv import USE_L1
             if USE_L1:
                 cls = ops.edge_class(rowptr, src, n_cap, b1.conv.mode(), pseudo, status)
-        y, skip = b1.conv.run(x, rowptr, src, n_cap, n_dev, pseudo, dict(scale=s1, shift=h1, relu=relu), status,
+        lists = None
+        from .spline_conv import FUSED_MIN_ROWS, USE_FUSED
+        m1, m2 = b1.conv.mode(), b2.conv.mode()
+        sm = getattr(self, "_same_mode_cache", None)
+        if sm is None or sm[0] is not m1 or sm[1] is not m2:  # compared once per LUT (the comparison synchronises)
+            sm = self._same_mode_cache = (m1, m2, _same_mode(m1, m2))
+        if USE_FUSED and b1.conv.out_channels == 64 and b2.conv.out_channels == 64 and n_cap >= FUSED_MIN_ROWS and sm[2]:
+            # both convolutions see the same graph and pseudo-coordinates: one tap-sorted entry list serves both
+            lists = ops.spline_tap_lists(rowptr, src, n_cap, n_dev, src.shape[0], b1.conv.mode(), pseudo, status)
+        y, skip = b1.conv.run(x, rowptr, src, n_cap, n_dev, pseudo, dict(scale=s1, shift=h1, relu=relu), status, lists=lists,
                               skip_weight=b2.lin.mlp.weight, skip_epi=dict(scale=ss, shift=hs), cls=cls, perm=perm,
                               ell_stride=ell_stride)
         if not relu:
             y = b1.activation(y)
-        out, _ = b2.conv.run(y, rowptr, src, n_cap, n_dev, pseudo, dict(scale=s2, shift=h2, addend=skip, relu=relu), status,
+        out, _ = b2.conv.run(y, rowptr, src, n_cap, n_dev, pseudo, dict(scale=s2, shift=h2, addend=skip, relu=relu), status, lists=lists,
                              cls=cls, perm=perm, ell_stride=ell_stride)
         if not relu:
             out = b2.activation(out)

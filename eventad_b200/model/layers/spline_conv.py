@@ -14,6 +14,9 @@ USE_TC5 = True      # tcgen05 (UMMA / TMEM) contraction for the cout=64 layers (
 TC5_MIN_ROWS = 1024 # below this many rows the 128-row tcgen05 tiles leave SMs idle and the mma.sync kernel is faster
                     # (tools/gemm_bench.py: 65 vs 94 us at 17920 x 2132, 11.8 vs 8.5 us at 140 x 3380)
 USE_L1 = True       # tap aggregation + tensor-core contraction for the cout=16 layer (False: LUT-gather kernel)
+USE_FUSED = False   # pooled layers: tap aggregation + tcgen05 contraction in ONE kernel (csrc/spline_tc5.cu): parity-tested, at
+                    # best equal to aggregate + GEMM (profiles/r01d_summary.md): the per-tap CTA barrier waits for the longest row
+FUSED_MIN_ROWS = 1024
 
 
 class _PyGLinear(torch.nn.Module):
@@ -128,6 +131,14 @@ class MySplineConv(torch.nn.Module):
             c = self._cache["wcat_t"] = (key, ops.transpose_pad_weight(self.wcat()))
         return c[1]
 
+    def fused_pack(self, ldx):
+        """(Wt_hi, Wt_lo, cp) of evad_spline_conv64_fused for inputs with row stride ldx."""
+        key = self._versions() + (int(ldx),)
+        c = self._cache.get("fused")
+        if c is None or c[0] != key:
+            c = self._cache["fused"] = (key, ops.pack_fused_weight(self.weight, self.lin.weight, ldx))
+        return c[1]
+
     def small_lut(self, skip_weight=None):
         cin_pad = (self.in_channels + 3) // 4 * 4
         key = self._versions(skip_weight)
@@ -182,7 +193,7 @@ class MySplineConv(torch.nn.Module):
 
     # ---- kernels ---------------------------------------------------------------------------------------------
     def run(self, x, rowptr, src, n_cap, n_dev, pseudo, epi, status, skip_weight=None, skip_epi=None, cls=None,
-            perm=None, ell_stride=0):
+            perm=None, ell_stride=0, lists=None):
         """x [n_cap, >=Cin] float32 -> epi(conv(x)) [n_cap, Cout] (+ skip_epi(x @ skip_weight^T) when requested)."""
         cin = self.in_channels
         if self.small_ok() and n_dev is None:
@@ -203,9 +214,19 @@ class MySplineConv(torch.nn.Module):
             return ops.spline_conv_small(rowptr, src, n_cap, x, cin, self.small_lut(skip_weight), self.mode(), pseudo, epi,
                                          status, skip_epi)
         x = x.contiguous()
-        A = ops.spline_aggregate(rowptr, src, n_cap, n_dev, x, cin, self.mode(), pseudo, status)
-        tc = self.out_channels == 64 and A.stride(0) % 4 == 0
-        if tc and USE_TC5 and n_cap >= TC5_MIN_ROWS and A.data_ptr() % 16 == 0:
+        fused = (USE_FUSED and self.out_channels == 64 and self.K <= 32 and n_cap >= FUSED_MIN_ROWS and
+                 x.stride(0) % 4 == 0 and x.data_ptr() % 16 == 0 and x.shape[1] == x.stride(0) and x.shape[1] - cin < 4)
+        if fused:
+            if lists is None:
+                lists = ops.spline_tap_lists(rowptr, src, n_cap, n_dev, src.shape[0], self.mode(), pseudo, status)
+            out = ops.spline_conv64_fused(lists, x, n_cap, n_dev, self.fused_pack(x.stride(0)), epi)
+            A = None
+        else:
+            A = ops.spline_aggregate(rowptr, src, n_cap, n_dev, x, cin, self.mode(), pseudo, status)
+        tc = self.out_channels == 64 and A is not None and A.stride(0) % 4 == 0
+        if fused:
+            pass
+        elif tc and USE_TC5 and n_cap >= TC5_MIN_ROWS and A.data_ptr() % 16 == 0:
             out = ops.gemm64_tc5(A, self.wcat_t(), n_cap, n_dev, epi, k=A.shape[1])
         elif tc:
             out = ops.gemm64_tc(A, self.wcat(), n_cap, n_dev, epi)

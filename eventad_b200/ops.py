@@ -393,6 +393,49 @@ def gemm64_tc5(A, Wt, m_cap, m_dev, epi, out=None, k=None):
     return out
 
 
+def spline_tap_lists(rowptr, src, n_cap, n_dev, e_cap, mode, pseudo, status):
+    """Per-node tap-sorted (source, basis value) entries of a pooled graph: dict(tptr [n_cap, ntap+1], ent [4*e_cap, 2],
+    ntap); one pass per graph, shared by the convolutions that see the same graph and pseudo-coordinates."""
+    L = _lib.lib()
+    ntap = mode["ks"] ** 2
+    dev = rowptr.device
+    tptr = torch.empty((max(n_cap, 1), ntap + 1), dtype=torch.int32, device=dev)
+    ent = torch.empty((4 * max(int(e_cap), 1), 2), dtype=torch.int32, device=dev)
+    m = _mode_struct(mode)
+    p = _pseudo_struct(**pseudo)
+    with _timed('spline_aggregate'):
+        check(L.evad_spline_tap_lists(ptr(rowptr), ptr(src), n_cap, ptr(n_dev), ctypes.byref(p), ctypes.byref(m), ptr(tptr),
+                                      ptr(ent), ptr(status), stream()), "evad_spline_tap_lists")
+    return dict(tptr=tptr, ent=ent, ntap=ntap)
+
+
+def pack_fused_weight(weight, lin_weight, ldx):
+    """[K, Cin, Cout=64] spline weight + [Cout, Cin] root weight -> (Wt_hi, Wt_lo, cp): transposed, tap-major with
+    cp = roundup8(ldx) zero-padded columns per tap, split into TF32 parts."""
+    ntap, cin, cout = weight.shape
+    cp = (int(ldx) + 7) // 8 * 8
+    wt = torch.zeros((cout, ntap + 1, cp), dtype=torch.float32, device=weight.device)
+    wt[:, :ntap, :cin] = weight.detach().float().permute(2, 0, 1)
+    wt[:, ntap, :cin] = lin_weight.detach().float()
+    hi, lo = split_tf32(wt.view(cout, (ntap + 1) * cp))
+    return hi, lo, cp
+
+
+def spline_conv64_fused(lists, x, n_cap, n_dev, wpack, epi, out=None):
+    """out = epi(SplineConv(x)) with Cout = 64 through evad_spline_conv64_fused; wpack = pack_fused_weight(...)."""
+    L = _lib.lib()
+    hi, lo, cp = wpack
+    if out is None:
+        out = torch.empty((max(n_cap, 1), 64), dtype=torch.float32, device=x.device)
+    e = _epi_struct(**epi)
+    ws = _ws(L.evad_spline_conv64_fused_ws_bytes(n_cap, lists["ntap"]), x.device)
+    with _timed('gemm_epilogue'):
+        check(L.evad_spline_conv64_fused(ptr(lists["tptr"]), ptr(lists["ent"]), ptr(x), x.stride(0), n_cap, ptr(n_dev),
+                                         lists["ntap"], cp, ptr(hi), ptr(lo), hi.stride(0), ctypes.byref(e), ptr(out),
+                                         out.stride(0), ptr(ws), ws.numel(), stream()), "evad_spline_conv64_fused")
+    return out
+
+
 # --------------------------------------------------------------------------------------------------- pooling
 def pool_geometry(voxel_size4: torch.Tensor, end4: torch.Tensor):
     """num_voxels per dimension exactly as torch_cluster computes them: ((end - start) / size).long() + 1, start = 0."""

@@ -217,6 +217,24 @@ int evad_gemm64_tc5(const float* A, int64_t lda, const float* Wt, int64_t ldw, i
                     const evad_epilogue_t* epi_h, float* out, int ldo, void* ws, size_t ws_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * SplineConv with Cout = 64 as one kernel (csrc/spline_tc5.cu): per-tap aggregation in registers feeding tcgen05.mma
+ * (kind::tf32, 3xTF32, TMEM accumulator) -- evad_spline_aggregate + evad_gemm64_tc5 without the [n, 26*Cin] operand in HBM.
+ *   evad_spline_tap_lists: per node the (source, basis value) entries of its in-edges grouped by kernel tap
+ *     (spline_conv.py:39-42 LUT index or torch_spline_conv.spline_basis, as evad_spline_aggregate evaluates them);
+ *     tptr [n, ntap+1] int32 entry offsets, entries [4 * rowptr[n]] (int32 source, fp32 basis value) pairs; one pass per
+ *     graph, shared by the two convolutions of a Layer.
+ *   evad_spline_conv64_fused: out = epi(sum_k W_k^T A_k + W_root^T x); x rows zero padded to ldx; Wt_hi / Wt_lo
+ *     [64, ldw]: TF32 parts (evad_split_tf32) of the transposed stacked weight, `cp` (multiple of 8, >= ldx) columns per
+ *     tap in the order taps 0..ntap-1, root; zero in the padding columns. */
+int evad_spline_tap_lists(const int32_t* rowptr, const int32_t* src, int64_t n, const int32_t* n_dev,
+                          const evad_pseudo_t* pseudo_h, const evad_spline_mode_t* mode_h, int32_t* tptr, void* entries,
+                          uint32_t* status, void* stream);
+size_t evad_spline_conv64_fused_ws_bytes(int64_t n, int ntap);
+int evad_spline_conv64_fused(const int32_t* tptr, const void* entries, const float* x, int ldx, int64_t n,
+                             const int32_t* n_dev, int ntap, int cp, const float* Wt_hi, const float* Wt_lo, int64_t ldw,
+                             const evad_epilogue_t* epi_h, float* out, int ldo, void* ws, size_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * Voxel-grid pooling.
  * Replaces Pooling.forward (src/dagr/model/layers/pooling.py:51-97): torch_cluster.grid_cluster on [x,y,t,batch],
  * consecutive_cluster, cluster[edge_index] + self-loop drop + unique(dim=-1), pool_pos, scatter_max / _avg_pool_x,
