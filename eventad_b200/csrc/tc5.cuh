@@ -37,6 +37,10 @@ __device__ __forceinline__ void t5_mbar_wait(uint32_t bar, uint32_t parity) {
         : "memory");
 }
 
+__device__ __forceinline__ void t5_mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
 // 64-bit shared-memory matrix descriptor: K-major operand tile, 128-byte swizzle, rows of 128 bytes, 8-row groups
 // 1024 bytes apart (cute::UMMA::SmemDescriptor: start >> 4 | LBO(16 B) << 16 | SBO(1024 B) << 32 | version 1 << 46 |
 // SWIZZLE_128B (2) << 61).  The tile base is 1024-byte aligned; a K step of 8 floats advances the start by 32 bytes.
