@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(PL_THREADS) pool_reduce_kernel(
 //    order independent, so max-pooled rows are bit-identical to pool_reduce_kernel; mean rows agree to rounding;
 //  * positions: serial fp32 sums in ascending node order (bit-exact with the oracle's CPU scatter_add).
 #define PRW_WARPS 8
-#define PRW_WIN 32
+#define PRW_WIN 16                    // window cells staged per warp: a voxel spans ~1.5 map cells per axis, single plane
 
 __device__ __forceinline__ float4 prw_comb(float4 a, float4 b, int mean) {
     if (mean) return make_float4(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z), __fadd_rn(a.w, b.w));
@@ -233,7 +233,7 @@ __device__ __forceinline__ float4 prw_members(float4 a, const int* __restrict__ 
     return a;
 }
 
-__global__ void __launch_bounds__(PRW_WARPS * 32) pool_reduce_warp_kernel(
+__global__ void __launch_bounds__(PRW_WARPS * 32, 3) pool_reduce_warp_kernel(
     const uint32_t* __restrict__ sidx, const int32_t* __restrict__ seg_start, const int32_t* __restrict__ n_out,
     const float* __restrict__ pos, int ld_pos, const int32_t* __restrict__ batch, const float* __restrict__ x, int ldx,
     int cx, PoolSample S, int aggr_mean, float inv_w, float inv_h, int append_pos, float* __restrict__ x_out, int ldo,
