@@ -243,18 +243,19 @@ __global__ void __launch_bounds__(PRW_WARPS * 32, 3) pool_reduce_warp_kernel(
     const int c = blockIdx.x * PRW_WARPS + warp;
     if (c >= *n_out) return;
     const int qx = cx >> 2, qf = S.feat ? (S.C >> 2) : 0;
-    float* wbase = prw_smem + (size_t)warp * (PRW_WIN * 4 * qf + 544);
+    float* wbase = prw_smem + (size_t)warp * (PRW_WIN * 4 * qf + 640);
     float4* s_win = reinterpret_cast<float4*>(wbase);                       // [PRW_WIN][qf] float4
     int* s_tap = reinterpret_cast<int*>(wbase + PRW_WIN * 4 * qf);          // [32][8]
     float* s_wgt = wbase + PRW_WIN * 4 * qf + 256;                          // [32][8]
     int* s_cell = reinterpret_cast<int*>(wbase + PRW_WIN * 4 * qf + 512);   // [32] flat map index of window cells
+    float* s_pos = wbase + PRW_WIN * 4 * qf + 544;                          // [32][3] member positions of the chunk
     const int s0 = seg_start[c], s1 = seg_start[c + 1];
     const float cntf = fmaxf((float)(s1 - s0), 1.f);
     const float4* f4 = reinterpret_cast<const float4*>(S.feat);
     const float ident = aggr_mean ? 0.f : -INFINITY;
     const int groups = (qf > 0 && qf <= 16) ? 2 : 1, lg = 32 / groups;      // sampled part: lane groups over members
     const int grp = lane / lg, ql = lane - grp * lg;
-    float sx = 0.f, sy = 0.f, st = 0.f;
+    float psum = 0.f;                                        // lane d < 3: running sum of position component d
     float4 accx[2], accf[2];
 #pragma unroll
     for (int u = 0; u < 2; u++) accx[u] = accf[u] = make_float4(ident, ident, ident, ident);
@@ -290,12 +291,13 @@ __global__ void __launch_bounds__(PRW_WARPS * 32, 3) pool_reduce_warp_kernel(
                 }
             }
         }
-        // ---- positions: serial fp32 sums in ascending node order (all lanes redundantly)
-        for (int m = 0; m < cnt; m++) {
-            sx = __fadd_rn(sx, __shfl_sync(0xffffffffu, px, m));
-            sy = __fadd_rn(sy, __shfl_sync(0xffffffffu, py, m));
-            st = __fadd_rn(st, __shfl_sync(0xffffffffu, pt, m));
-        }
+        // ---- positions: serial fp32 sums in ascending node order; lane d < 3 sums component d from shared memory
+        //      (one load + one add per member instead of three shuffles + three adds)
+        if (lane < cnt) { s_pos[3 * lane] = px; s_pos[3 * lane + 1] = py; s_pos[3 * lane + 2] = pt; }
+        __syncwarp();
+        if (lane < 3)
+            for (int m = 0; m < cnt; m++) psum = __fadd_rn(psum, s_pos[3 * m + lane]);
+        __syncwarp();
         if (!qf) continue;
         // ---- sampled CNN features: window of the chunk in shared memory
         const int xmin = __reduce_min_sync(0xffffffffu, bx), ymin = __reduce_min_sync(0xffffffffu, by),
@@ -361,6 +363,8 @@ __global__ void __launch_bounds__(PRW_WARPS * 32, 3) pool_reduce_warp_kernel(
         }
     }
     if (groups == 2) accf[0] = prw_comb(accf[0], prw_shfl_xor(accf[0], 16), aggr_mean);
+    const float sx = __shfl_sync(0xffffffffu, psum, 0), sy = __shfl_sync(0xffffffffu, psum, 1),
+                st = __shfl_sync(0xffffffffu, psum, 2);
     float mx = __fdiv_rn(sx, cntf), my = __fdiv_rn(sy, cntf);
     const float mt = __fdiv_rn(st, cntf);
     mx = __fmul_rn(div_floor_f(__fadd_rn(mx, 1e-5f), inv_w), inv_w);
@@ -618,7 +622,7 @@ extern "C" int evad_voxel_pool(const evad_pool_params_t* p, int64_t n_cap, const
                                                          w.seg_start, n_out);
     EVAD_CHECK_LAUNCH();
     const int qf_h = p->feat ? p->feat_c / 4 : 0;
-    const size_t prw_smem = (size_t)PRW_WARPS * (PRW_WIN * 4 * qf_h + 544) * sizeof(float);
+    const size_t prw_smem = (size_t)PRW_WARPS * (PRW_WIN * 4 * qf_h + 640) * sizeof(float);
     const bool quad_ok = cx % 4 == 0 && ldx % 4 == 0 && ldo % 4 == 0 && (((uintptr_t)x | (uintptr_t)x_out) & 15) == 0 &&
                          (!p->feat || (p->feat_c % 4 == 0 && ((uintptr_t)p->feat & 15) == 0)) && cx <= 256 &&
                          qf_h <= 64 && prw_smem <= 100 * 1024;
