@@ -243,6 +243,8 @@ __global__ void __launch_bounds__(PRW_WARPS * 32, 3) pool_reduce_warp_kernel(
     const int c = blockIdx.x * PRW_WARPS + warp;
     if (c >= *n_out) return;
     const int qx = cx >> 2, qf = S.feat ? (S.C >> 2) : 0;
+    int qxp = 1;
+    while (qxp < qx) qxp <<= 1;                              // lanes per member in the node-feature pass (qx <= 32)
     float* wbase = prw_smem + (size_t)warp * (PRW_WIN * 4 * qf + 640);
     float4* s_win = reinterpret_cast<float4*>(wbase);                       // [PRW_WIN][qf] float4
     int* s_tap = reinterpret_cast<int*>(wbase + PRW_WIN * 4 * qf);          // [32][8]
@@ -271,23 +273,35 @@ __global__ void __launch_bounds__(PRW_WARPS * 32, 3) pool_reduce_warp_kernel(
             px = pos[(int64_t)node * ld_pos]; py = pos[(int64_t)node * ld_pos + 1]; pt = pos[(int64_t)node * ld_pos + 2];
             if (qf) sample_taps_base(S, px, py, (float)batch[node], tap, wgt, &bx, &by, &bz);
         }
-        // ---- node features: lane = member, butterfly over the lanes, lane (q & 31) keeps quad q
-        for (int q0 = 0; q0 < qx; q0 += 4) {
-            float4 v[4];
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                v[u] = make_float4(ident, ident, ident, ident);
-                if (q0 + u < qx && lane < cnt) v[u] = __ldg(reinterpret_cast<const float4*>(x + (int64_t)node * ldx) + q0 + u);
+        // ---- node features: lane = (member slot, channel quad): qxp = qx rounded up to a power of two lanes per member,
+        //      32 / qxp members per pass, one 128-bit row load each, running max / sum in registers; the member slots
+        //      are folded by a butterfly once per voxel (below).  More than 32 quads: lane = member, butterfly per quad.
+        if (qx <= 32) {
+            const int ms = lane / qxp, quad = lane - ms * qxp, mpp = 32 / qxp;
+            for (int m0 = 0; m0 < cnt; m0 += mpp) {
+                const int m = m0 + ms;
+                const int nd = __shfl_sync(0xffffffffu, node, m & 31);
+                if (m < cnt && quad < qx)
+                    accx[0] = prw_comb(accx[0], __ldg(reinterpret_cast<const float4*>(x + (int64_t)nd * ldx) + quad), aggr_mean);
             }
+        } else {
+            for (int q0 = 0; q0 < qx; q0 += 4) {
+                float4 v[4];
 #pragma unroll
-            for (int u = 0; u < 4; u++) {
-                if (q0 + u >= qx) break;
+                for (int u = 0; u < 4; u++) {
+                    v[u] = make_float4(ident, ident, ident, ident);
+                    if (q0 + u < qx && lane < cnt) v[u] = __ldg(reinterpret_cast<const float4*>(x + (int64_t)node * ldx) + q0 + u);
+                }
 #pragma unroll
-                for (int d = 16; d >= 1; d >>= 1) v[u] = prw_comb(v[u], prw_shfl_xor(v[u], d), aggr_mean);
-                const int q = q0 + u;
-                if (lane == (q & 31)) {
-                    if (q < 32) accx[0] = prw_comb(accx[0], v[u], aggr_mean);
-                    else accx[1] = prw_comb(accx[1], v[u], aggr_mean);
+                for (int u = 0; u < 4; u++) {
+                    if (q0 + u >= qx) break;
+#pragma unroll
+                    for (int d = 16; d >= 1; d >>= 1) v[u] = prw_comb(v[u], prw_shfl_xor(v[u], d), aggr_mean);
+                    const int q = q0 + u;
+                    if (lane == (q & 31)) {
+                        if (q < 32) accx[0] = prw_comb(accx[0], v[u], aggr_mean);
+                        else accx[1] = prw_comb(accx[1], v[u], aggr_mean);
+                    }
                 }
             }
         }
@@ -362,6 +376,8 @@ __global__ void __launch_bounds__(PRW_WARPS * 32, 3) pool_reduce_warp_kernel(
             }
         }
     }
+    if (qx <= 32)
+        for (int d = qxp; d < 32; d <<= 1) accx[0] = prw_comb(accx[0], prw_shfl_xor(accx[0], d), aggr_mean);
     if (groups == 2) accf[0] = prw_comb(accf[0], prw_shfl_xor(accf[0], 16), aggr_mean);
     const float sx = __shfl_sync(0xffffffffu, psum, 0), sy = __shfl_sync(0xffffffffu, psum, 1),
                 st = __shfl_sync(0xffffffffu, psum, 2);
