@@ -483,6 +483,27 @@ __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
         bool oow = false;
         for (int p = s0 + threadIdx.x; p < s1; p += PL_THREADS) {
             const int i = (int)sidx[p];
+            if (in_stride == 16) {
+                // fixed-stride rows of 16 slots: four source ids per 128-bit load, their four cluster gathers in flight
+                const int deg = rowptr_in[i];
+                const int4* row = reinterpret_cast<const int4*>(src_in) + (int64_t)i * 4;
+                for (int g = 0; 4 * g < deg; g++) {
+                    const int4 s4 = __ldg(row + g);
+                    const int sj[4] = {s4.x, s4.y, s4.z, s4.w};
+                    int scs[4];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) scs[k] = 4 * g + k < deg ? cluster[sj[k]] : c;
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        if (4 * g + k >= deg) break;
+                        const int sc = scs[k], r = sc - w0;
+                        if (sc == c && !keep_self) continue;
+                        if (r >= 0 && r < PL_BITS) atomicOr(&bits[r >> 5], 1u << (r & 31));
+                        else oow = true;
+                    }
+                }
+                continue;
+            }
             for (int e = pl_row_begin(rowptr_in, in_stride, i), e1 = pl_row_end(rowptr_in, in_stride, i); e < e1; e++) {
                 const int sc = cluster[src_in[e]];
                 const int r = sc - w0;
