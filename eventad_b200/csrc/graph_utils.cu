@@ -211,7 +211,8 @@ __global__ void __launch_bounds__(256) sample_concat_quad_kernel(const float* __
     const float4* f4 = reinterpret_cast<const float4*>(S.feat);
 #pragma unroll
     for (int k = 0; k < 8; k++) {
-        if (tap[k] < 0) continue;
+        // zero weights (the whole dz = 1 plane when the depth coordinate is the integer batch index): fmaf(v, 0, acc) == acc
+        if (tap[k] < 0 || wgt[k] == 0.f) continue;
         const float4 v = __ldg(f4 + (int64_t)tap[k] * quads + q);
         acc.x = fmaf(v.x, wgt[k], acc.x); acc.y = fmaf(v.y, wgt[k], acc.y);
         acc.z = fmaf(v.z, wgt[k], acc.z); acc.w = fmaf(v.w, wgt[k], acc.w);
