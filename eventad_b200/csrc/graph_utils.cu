@@ -227,6 +227,46 @@ __global__ void __launch_bounds__(256) sample_concat_quad_kernel(const float* __
     }
 }
 
+// Layer-1 shape (one polarity channel + 16 sampled channels + position, rows of 20 floats): one thread per node builds
+// the whole row in registers -- taps resolved once per node instead of once per channel quad, and the row leaves as five
+// 128-bit stores instead of twenty 32-bit ones.
+template <int CX, int C, int LDO>
+__global__ void __launch_bounds__(256) sample_concat_row_kernel(const float* __restrict__ x, int ldx,
+                                                                const float* __restrict__ pos, int ld_pos,
+                                                                const int32_t* __restrict__ batch, int64_t n_cap,
+                                                                const int32_t* __restrict__ n_dev, PoolSample S,
+                                                                int append_pos, float* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t n = n_dev ? min((int64_t)*n_dev, n_cap) : n_cap;
+    if (i >= n) return;
+    const float px = pos[i * ld_pos], py = pos[i * ld_pos + 1];
+    int tap[8];
+    float wgt[8];
+    sample_taps(S, px, py, (float)batch[i], tap, wgt);
+    float row[LDO];
+#pragma unroll
+    for (int c = 0; c < LDO; c++) row[c] = 0.f;
+#pragma unroll
+    for (int c = 0; c < CX; c++) row[c] = x[i * ldx + c];
+    const float4* f4 = reinterpret_cast<const float4*>(S.feat);
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        if (tap[k] < 0 || wgt[k] == 0.f) continue;            // fmaf(v, 0, acc) == acc: same bits as the chain with it
+#pragma unroll
+        for (int q = 0; q < C / 4; q++) {
+            const float4 v = __ldg(f4 + (int64_t)tap[k] * (C / 4) + q);
+            row[CX + 4 * q] = fmaf(v.x, wgt[k], row[CX + 4 * q]);
+            row[CX + 4 * q + 1] = fmaf(v.y, wgt[k], row[CX + 4 * q + 1]);
+            row[CX + 4 * q + 2] = fmaf(v.z, wgt[k], row[CX + 4 * q + 2]);
+            row[CX + 4 * q + 3] = fmaf(v.w, wgt[k], row[CX + 4 * q + 3]);
+        }
+    }
+    if (append_pos) { row[CX + C] = px; row[CX + C + 1] = py; }
+    float4* o = reinterpret_cast<float4*>(out + i * LDO);
+#pragma unroll
+    for (int c = 0; c < LDO / 4; c++) o[c] = make_float4(row[4 * c], row[4 * c + 1], row[4 * c + 2], row[4 * c + 3]);
+}
+
 extern "C" int evad_sample_concat(const float* x, int ldx, int cx, const float* pos, int ld_pos, const int32_t* batch,
                                   int64_t n_cap, const int32_t* n_dev, const float* feat, int feat_b, int feat_h,
                                   int feat_w, int feat_c, float width, float height, int append_pos, float* out,
@@ -236,6 +276,12 @@ extern "C" int evad_sample_concat(const float* x, int ldx, int cx, const float* 
     if (ldo < cx + cs + (append_pos ? 2 : 0)) return EVAD_ERR_ARG;
     if (n_cap == 0) return EVAD_OK;
     PoolSample S{feat, feat_b, feat_h, feat_w, feat_c, width, height};
+    if (feat && cx == 1 && feat_c == 16 && ldo == 20 && (((uintptr_t)feat | (uintptr_t)out) & 15) == 0) {
+        sample_concat_row_kernel<1, 16, 20><<<evad_cdiv(n_cap, 256), 256, 0, (cudaStream_t)stream>>>(
+            x, ldx, pos, ld_pos, batch, n_cap, n_dev, S, append_pos, out);
+        EVAD_CHECK_LAUNCH();
+        return EVAD_OK;
+    }
     if (feat && feat_c >= 4 && feat_c % 4 == 0 && ((uintptr_t)feat & 15) == 0) {
         const int64_t threads = n_cap * (feat_c / 4);
         sample_concat_quad_kernel<<<evad_cdiv(threads, 256), 256, 0, (cudaStream_t)stream>>>(
