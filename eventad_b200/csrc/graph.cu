@@ -61,6 +61,24 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
                                                              int32_t* __restrict__ nbr /*[n][K]*/,
                                                              uint8_t* __restrict__ nbr_cls /*[n][K] or null*/,
                                                              uint32_t* __restrict__ count /*[n]*/) {
+    // spiral walk of spiral.h:1-15 (layer starts at 1, leg 0), tabulated once per CTA: the per-thread state machine cost
+    // more instructions per cell visit than the visit itself
+    extern __shared__ int8_t g_spiral[];                      // [nsp] dx, then [nsp] dy
+    const int nsp = (2 * radius + 1) * (2 * radius + 1);
+    if (threadIdx.x == 0) {
+        int sx = 0, sy = 0, layer = 1, leg = 0;
+        for (int s = 0; s < nsp; s++) {
+            g_spiral[s] = (int8_t)sx;
+            g_spiral[nsp + s] = (int8_t)sy;
+            switch (leg) {
+            case 0: ++sx; if (sx == layer) ++leg; break;
+            case 1: ++sy; if (sy == layer) ++leg; break;
+            case 2: --sx; if (-sx == layer) ++leg; break;
+            default: --sy; if (-sy == layer) { leg = 0; ++layer; } break;
+            }
+        }
+    }
+    __syncthreads();
     int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     const int i = (int)sidx[p];
@@ -74,12 +92,10 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
     out[0] = i;                                               // self edge first (ev_graph.cu:43-46)
     if (ocls) ocls[0] = (uint8_t)(radius * side + radius);
     int cnt = 1;
-    // spiral walk of spiral.h:1-15 (layer starts at 1, leg 0)
-    int sx = 0, sy = 0, layer = 1, leg = 0;
-    const int nsp = (2 * radius + 1) * (2 * radius + 1);
     for (int s = 0; s < nsp && cnt < K; s++) {
+        const int sx = g_spiral[s], sy = g_spiral[nsp + s];
         const int xn = x + sx, yn = y + sy;
-        if (xn >= 0 && yn >= 0 && xn < W && yn < H) {
+        if ((unsigned)xn < (unsigned)W && (unsigned)yn < (unsigned)H) {
             const int c2 = c + sy * W + sx;
             const int s0 = cell_start[c2], s1 = cell_start[c2 + 1];
             if (s1 > s0) {
@@ -103,12 +119,6 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
                     if (cnt >= K) break;
                 }
             }
-        }
-        switch (leg) {
-        case 0: ++sx; if (sx == layer) ++leg; break;
-        case 1: ++sy; if (sy == layer) ++leg; break;
-        case 2: --sx; if (-sx == layer) ++leg; break;
-        default: --sy; if (-sy == layer) { leg = 0; ++layer; } break;
         }
     }
     count[i] = (uint32_t)cnt;
@@ -180,7 +190,7 @@ static int graph_rows(const int32_t* batch, const int32_t* pos, int64_t n, int B
     const int64_t m = (ncells + 1 > n) ? ncells + 1 : n;
     g_cells_kernel<<<evad_cdiv(m, 256), 256, 0, st>>>(skey, sidx, pos, n, ncells, cell_start, w.st, cell_perm);
     EVAD_CHECK_LAUNCH();
-    g_search_kernel<<<evad_cdiv(n, G_THREADS), G_THREADS, 0, st>>>(skey, sidx, w.st, cell_start, n, H, W, radius,
+    g_search_kernel<<<evad_cdiv(n, G_THREADS), G_THREADS, 2 * (2 * radius + 1) * (2 * radius + 1), st>>>(skey, sidx, w.st, cell_start, n, H, W, radius,
                                                                   (float)delta_t_us, Q, K, nbr, nbr_cls, count);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
@@ -194,6 +204,7 @@ extern "C" int evad_graph_build(const int32_t* batch, const int32_t* pos, int64_
     cudaStream_t st = (cudaStream_t)stream;
     if (n < 0 || B < 1 || H < 1 || W < 1 || radius < 0 || Q < 1 || K < 1 || K > 32) return EVAD_ERR_ARG;
     if (edge_cls && (2 * radius + 1) * (2 * radius + 1) > 256) return EVAD_ERR_UNSUPPORTED;
+    if (radius > 64) return EVAD_ERR_UNSUPPORTED;            // spiral table of the search kernel: 2 (2r+1)^2 bytes of smem
     if (!rowptr || !src || !num_edges || !status) return EVAD_ERR_ARG;
     const int64_t ncells = (int64_t)B * H * W;
     if (ncells >= (1ll << 31) || n * K >= (1ll << 31)) return EVAD_ERR_UNSUPPORTED;
@@ -225,6 +236,7 @@ extern "C" int evad_graph_build_rows(const int32_t* batch, const int32_t* pos, i
     cudaStream_t st = (cudaStream_t)stream;
     if (n < 0 || B < 1 || H < 1 || W < 1 || radius < 0 || Q < 1 || K < 1 || K > 32) return EVAD_ERR_ARG;
     if (nbr_cls && (2 * radius + 1) * (2 * radius + 1) > 256) return EVAD_ERR_UNSUPPORTED;
+    if (radius > 64) return EVAD_ERR_UNSUPPORTED;
     if (!nbr || !count || !status) return EVAD_ERR_ARG;
     const int64_t ncells = (int64_t)B * H * W;
     if (ncells >= (1ll << 31) || n * K >= (1ll << 31)) return EVAD_ERR_UNSUPPORTED;
