@@ -128,6 +128,13 @@ __device__ __forceinline__ void l1_edge_fma(float4 (&acc)[L1_SLOTS - 1], const f
     }
 }
 
+__device__ __forceinline__ void l1_cp16(uint32_t dst, const float* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void l1_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void l1_cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 // ROWS16: the graph comes as fixed-stride rows of 16 slots (evad_graph_build_rows): source ids are read four at a time
 // (one 128-bit load per group) and the class bytes one word per group, instead of two scalar loads per edge and thread.
 template <int CP, bool ROWS16>
@@ -138,6 +145,7 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 2) spline_l1_kernel(
     float* __restrict__ out, int ldo, evad_epilogue_t ES, float* __restrict__ skip_out, int ld_skip) {
     using C = L1Cfg<CP>;
     constexpr int QN = C::QN, LDA = C::LDA, KR = C::KR;
+    constexpr bool RING = ROWS16 && CP <= 16;               // cp.async row ring: pays where the register budget allows (128 regs)
     extern __shared__ __align__(16) float l1_smem[];
     float* As = l1_smem;
     float* Bh = As + C::A_FLOATS;
@@ -175,22 +183,80 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 2) spline_l1_kernel(
     const int mt = warp & (L1_NODES / 16 - 1), kp = warp / (L1_NODES / 16);   // MMA role of the first warps: m16 tile, k half
     const int swz = ((t >> 1) & 1) << 3;                     // column swizzle of this lane's B-fragment rows
     const int64_t ntiles = (n + L1_NODES - 1) / L1_NODES;
+    // ROWS16: the head of a node's row (its id, length, first four sources / classes and its own features) is a chain
+    // of three dependent loads; it is fetched for the NEXT tile while this tile's contraction runs (hd_*).
+    int hd_i = 0, hd_deg = 0;
+    int4 hd_s0 = make_int4(0, 0, 0, 0);
+    uint32_t hd_c0 = 0;
+    float4 hd_xroot = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ROWS16) {
+        const int64_t ip0 = (int64_t)blockIdx.x * L1_NODES + node_l;
+        if (ip0 < n) {
+            hd_i = perm ? perm[ip0] : (int)ip0;
+            hd_deg = rowptr[hd_i];
+            hd_s0 = __ldg(reinterpret_cast<const int4*>(src) + (int64_t)hd_i * 4);
+            hd_c0 = __ldg(reinterpret_cast<const uint32_t*>(cls) + (int64_t)hd_i * 4);
+            hd_xroot = __ldg(reinterpret_cast<const float4*>(x + (int64_t)hd_i * ldx) + q);
+        }
+    }
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         // ---------------------------------------------------------------- (1) tap aggregation in registers
         const int64_t ip = tile * L1_NODES + node_l;          // position in processing order (pixel order when perm)
         const bool valid = ip < n;
-        const int64_t i = valid ? (perm ? (int64_t)perm[ip] : ip) : 0;
+        const int64_t i = ROWS16 ? (int64_t)hd_i : valid ? (perm ? (int64_t)perm[ip] : ip) : 0;
+        const int64_t ip_n = ip + (int64_t)gridDim.x * L1_NODES;   // this thread's node of the block's next tile
         float4 acc[L1_SLOTS - 1];
 #pragma unroll
         for (int s = 0; s < L1_SLOTS - 1; s++) acc[s] = make_float4(0.f, 0.f, 0.f, 0.f);
         float4 xroot = make_float4(0.f, 0.f, 0.f, 0.f);
         if (valid && ROWS16) {
-            const int deg = rowptr[i];
+            const int deg = hd_deg;
             const int4* srow = reinterpret_cast<const int4*>(src) + i * 4;
             const uint32_t* crow = reinterpret_cast<const uint32_t*>(cls) + i * 4;
-            if (deg > 0) {
-                int4 s_cur = __ldg(srow);
-                uint32_t c_cur = __ldg(crow);
+            xroot = hd_xroot;
+            if (deg > 0 && RING) {
+                // Source rows travel global -> shared by cp.async into a 4-slot ring made of this thread's own cells of
+                // the A tile (idle until the rounds below, and rewritten there), four edges ahead of their use: the
+                // gather latency is covered without holding the rows in registers.
+                float* ring = As + node_l * LDA + 4 * q;
+                const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring);
+                const float* xq_base = x + 4 * q;
+                int4 s_next = hd_s0;
+                uint32_t c_cur = hd_c0;
+                {
+                    const int s0[4] = {s_next.x, s_next.y, s_next.z, s_next.w};
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        if (k < deg) l1_cp16(ring_s + k * CP * 4, xq_base + (int64_t)s0[k] * ldx);
+                        l1_cp_commit();
+                    }
+                }
+                if (deg > 4) s_next = __ldg(srow + 1);
+#pragma unroll 1
+                for (int g = 0; 4 * g < deg; g++) {
+                    int4 s_nn = s_next;
+                    uint32_t c_next = c_cur;
+                    if (4 * (g + 1) < deg) c_next = __ldg(crow + g + 1);
+                    if (4 * (g + 2) < deg) s_nn = __ldg(srow + g + 2);
+                    const int sj[4] = {s_next.x, s_next.y, s_next.z, s_next.w};
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        const int e = 4 * g + k;
+                        if (e >= deg) break;
+                        l1_cp_wait<3>();
+                        const float4 xq = *reinterpret_cast<const float4*>(ring + k * CP);
+                        l1_edge_fma(acc, tw + ((c_cur >> (8 * k)) & 0xffu) * L1_TW_LD, xq);
+                        if (e + 4 < deg) l1_cp16(ring_s + k * CP * 4, xq_base + (int64_t)sj[k] * ldx);
+                        l1_cp_commit();
+                    }
+                    s_next = s_nn;
+                    c_cur = c_next;
+                }
+            }
+            if (deg > 0 && !RING) {
+                // rows prefetched one edge ahead in registers
+                int4 s_cur = hd_s0;
+                uint32_t c_cur = hd_c0;
                 float4 x_next = __ldg(reinterpret_cast<const float4*>(x + (int64_t)s_cur.x * ldx) + q);
 #pragma unroll 1
                 for (int g = 0; 4 * g < deg; g++) {
@@ -213,7 +279,6 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 2) spline_l1_kernel(
                     c_cur = c_next;
                 }
             }
-            xroot = __ldg(reinterpret_cast<const float4*>(x + i * ldx) + q);
         } else if (valid) {
             // CSR (rowptr[n+1]) or fixed-stride rows (ell_stride > 0: rowptr[i] = length of row i at i * ell_stride)
             const int r0 = ell_stride > 0 ? (int)i * ell_stride : rowptr[i];
@@ -238,6 +303,7 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 2) spline_l1_kernel(
                 l1_edge_fma(acc, twr, xq);
             }
         }
+        if (ROWS16) hd_i = ip_n < n ? (perm ? perm[ip_n] : (int)ip_n) : -1;   // next tile's node: in flight over round 0
         // ---------------------------------------------------------------- (2) contraction, two rounds of 8 slots
         float cacc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
         float sacc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
@@ -248,6 +314,17 @@ __global__ void __launch_bounds__(L1Cfg<CP>::THREADS, 2) spline_l1_kernel(
             for (int s = 0; s < 8; s++) {
                 const int slot = round * 8 + s;
                 *reinterpret_cast<float4*>(arow + s * CP) = slot < L1_SLOTS - 1 ? acc[slot < L1_SLOTS - 1 ? slot : 0] : xroot;
+            }
+            if (ROWS16 && round == 1) {                      // next tile's row head: in flight over round 1 (accumulators are dead now)
+                hd_deg = 0;
+                if (hd_i >= 0) {
+                    hd_deg = rowptr[hd_i];
+                    hd_s0 = __ldg(reinterpret_cast<const int4*>(src) + (int64_t)hd_i * 4);
+                    hd_c0 = __ldg(reinterpret_cast<const uint32_t*>(cls) + (int64_t)hd_i * 4);
+                    hd_xroot = __ldg(reinterpret_cast<const float4*>(x + (int64_t)hd_i * ldx) + q);
+                } else {
+                    hd_i = 0;
+                }
             }
             __syncthreads();
             if (warp < L1_MMA_WARPS) {
