@@ -5,6 +5,8 @@ sm_100a kernels (csrc/spline_small.cu, csrc/spline_general.cu).  There is no PyT
 """
 import math
 
+import os
+
 import torch
 
 from ... import ops
@@ -14,7 +16,7 @@ USE_TC5 = True      # tcgen05 (UMMA / TMEM) contraction for the cout=64 layers (
 TC5_MIN_ROWS = 1024 # below this many rows the 128-row tcgen05 tiles leave SMs idle and the mma.sync kernel is faster
                     # (tools/gemm_bench.py: 65 vs 94 us at 17920 x 2132, 11.8 vs 8.5 us at 140 x 3380)
 USE_L1 = True       # tap aggregation + tensor-core contraction for the cout=16 layer (False: LUT-gather kernel)
-USE_FUSED = False   # pooled layers: tap aggregation + tcgen05 contraction in ONE kernel (csrc/spline_tc5.cu): parity-tested, at
+USE_FUSED = os.environ.get("EVAD_FUSED", "0") == "1"   # pooled layers: tap aggregation + tcgen05 contraction in ONE kernel (csrc/spline_tc5.cu): parity-tested, at
                     # best equal to aggregate + GEMM (profiles/r01d_summary.md): the per-tap CTA barrier waits for the longest row
 FUSED_MIN_ROWS = 1024
 
