@@ -446,3 +446,319 @@ extern "C" int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, co
     return rows16 ? L1_LAUNCH(16, true) : L1_LAUNCH(16, false);
 #undef L1_LAUNCH
 }
+
+// ================================================================================================================
+// Variant with the tap aggregation on the tensor cores as well (fixed-stride rows of 16 only).
+//
+// Per destination node the aggregation P_i[slot][c] = sum_e tapw[class_e][slot] * x_{src_e}[c] is itself a small
+// product: [16 slots x 16 row positions] @ [16 row positions x Cin].  One warp computes it per node with
+// mma.sync.m16n8k8 (M = slots, K = row positions in two steps of 8, N = channels in tiles of 8):
+//   A fragment = tap weights of the lane's four row positions (t, t+4, t+8, t+12), read from a shared table laid out
+//     as (slot g, slot g+8) pairs; both operands are split into TF32 hi / lo parts in registers (3xTF32): three MMAs
+//     per (k step, n tile) -- 12 (Cin 16) or 18 (Cin 20) per node where the register variant above issues
+//     16 x QN x 60 FFMA;
+//   B fragment = the source rows gathered straight from global memory.  The MMA column -> channel map is free, so
+//     column j of tiles 0 / 1 is channel 2j / 2j+1: a lane fetches both with one 64-bit load and a row is 64
+//     contiguous bytes per request; tile 2 (Cin 20) is channels 16..19.
+//   D fragment: lane (g, t) ends up with slots g and g+8 of channels 4t..4t+3, i.e. one 128-bit store each into the
+//     [32 nodes x 16*Cin] shared P tile; slot 15 is overwritten with the node's own row (root weight).
+// The tile is 32 nodes (four per warp) with all 16 slots resident, so the contraction is a single pass split four ways
+// along K over the eight warps (two m16 tiles x four k quarters); partial sums are added in the epilogue.
+#define L1M_NODES 32
+#define L1M_THREADS 256
+#define L1M_TW_LD 24                  // floats per class row of the paired tap table: 8 x (slot g, slot g+8) + pad
+
+template <int CP>
+struct L1MCfg {
+    static constexpr int KTOT = L1_SLOTS * CP;
+    static constexpr int LDA = KTOT + ((20 - KTOT % 32) + 32) % 32;   // == 20 (mod 32)
+    static constexpr int KS = (CP + 7) / 8 * 8;
+    static constexpr int NT = (CP + 7) / 8;                  // channel tiles of the aggregation MMA
+    static constexpr int A_FLOATS = L1M_NODES * LDA;
+    static constexpr int B_FLOATS = KTOT * L1_LDB;
+    static constexpr int S_FLOATS = KS * L1_LDB;
+    static constexpr int C_FLOATS = 5 * L1M_NODES * L1_LDC;  // four k-quarter partials + skip
+    static size_t smem_bytes(int ncls) {
+        return (size_t)(A_FLOATS + 2 * B_FLOATS + 2 * S_FLOATS + C_FLOATS + (ncls + 1) * L1M_TW_LD) * sizeof(float);
+    }
+};
+
+struct L1MHead {                      // what a lane keeps of one node's row: id, length, its 4 sources, the class words
+    int i, deg;
+    int s[4];
+    uint4 c;
+};
+
+template <int CP>
+__global__ void __launch_bounds__(L1M_THREADS, 2) spline_l1_mma_kernel(
+    const int32_t* __restrict__ count, const int32_t* __restrict__ src, const uint8_t* __restrict__ cls,
+    const int32_t* __restrict__ perm, int64_t n, const float* __restrict__ x, int ldx, const float* __restrict__ tapw,
+    int ncls, const float* __restrict__ Whi, const float* __restrict__ Wlo, const float* __restrict__ Shi,
+    const float* __restrict__ Slo, evad_epilogue_t E, float* __restrict__ out, int ldo, evad_epilogue_t ES,
+    float* __restrict__ skip_out, int ld_skip) {
+    using C = L1MCfg<CP>;
+    constexpr int LDA = C::LDA, NT = C::NT;
+    extern __shared__ __align__(16) float l1_smem[];
+    float* As = l1_smem;
+    float* Bh = As + C::A_FLOATS;
+    float* Bl = Bh + C::B_FLOATS;
+    float* Sh = Bl + C::B_FLOATS;
+    float* Sl = Sh + C::S_FLOATS;
+    float* Cs = Sl + C::S_FLOATS;
+    float* tw = Cs + C::C_FLOATS;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const bool has_skip = Shi != nullptr;
+
+    for (int idx = tid; idx < C::KTOT * 4; idx += L1M_THREADS) {
+        const int r = idx >> 2, c4 = idx & 3;
+        const int cs = (4 * c4) ^ (((r >> 1) & 1) << 3);
+        *reinterpret_cast<float4*>(Bh + r * L1_LDB + cs) = __ldg(reinterpret_cast<const float4*>(Whi) + idx);
+        *reinterpret_cast<float4*>(Bl + r * L1_LDB + cs) = __ldg(reinterpret_cast<const float4*>(Wlo) + idx);
+    }
+    if (has_skip)
+        for (int idx = tid; idx < C::KS * 4; idx += L1M_THREADS) {
+            const int r = idx >> 2, c4 = idx & 3;
+            const int cs = (4 * c4) ^ (((r >> 1) & 1) << 3);
+            *reinterpret_cast<float4*>(Sh + r * L1_LDB + cs) = __ldg(reinterpret_cast<const float4*>(Shi) + idx);
+            *reinterpret_cast<float4*>(Sl + r * L1_LDB + cs) = __ldg(reinterpret_cast<const float4*>(Slo) + idx);
+        }
+    // paired tap table: row c = (tapw[c][0], tapw[c][8]), (tapw[c][1], tapw[c][9]), ...; row ncls = zeros (empty slots)
+    for (int idx = tid; idx < (ncls + 1) * 8; idx += L1M_THREADS) {
+        const int r = idx >> 3, k = idx & 7;
+        float2 v = make_float2(0.f, 0.f);
+        if (r < ncls) v = make_float2(__ldg(tapw + r * L1_SLOTS + k), __ldg(tapw + r * L1_SLOTS + k + 8));
+        *reinterpret_cast<float2*>(tw + r * L1M_TW_LD + 2 * k) = v;
+    }
+    for (int idx = tid; idx < C::A_FLOATS; idx += L1M_THREADS) As[idx] = 0.f;
+    __syncthreads();
+
+    const int mt = warp & 1, kq = warp >> 1;                 // contraction role: m16 tile, k quarter
+    const int swz = ((t >> 1) & 1) << 3;
+    const int64_t ntiles = (n + L1M_NODES - 1) / L1M_NODES;
+    const uint32_t tw_zero = (uint32_t)ncls;
+
+    L1MHead hd[4];
+    auto load_heads = [&](int64_t tile) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int64_t ip = tile * L1M_NODES + warp * 4 + k;
+            hd[k].i = -1;
+            hd[k].deg = 0;
+            hd[k].c = make_uint4(0, 0, 0, 0);
+#pragma unroll
+            for (int j = 0; j < 4; j++) hd[k].s[j] = 0;
+            if (ip < n) {
+                const int i = perm ? perm[ip] : (int)ip;
+                hd[k].i = i;
+                hd[k].deg = count[i];
+                hd[k].c = __ldg(reinterpret_cast<const uint4*>(cls) + i);
+#pragma unroll
+                for (int j = 0; j < 4; j++) hd[k].s[j] = __ldg(src + (int64_t)i * 16 + 4 * j + t);
+            }
+        }
+    };
+    if ((int64_t)blockIdx.x < ntiles) load_heads(blockIdx.x);
+
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        // ---------------------------------------------------------------- (1) tap aggregation: one node per warp at a time
+        float2 xa[2][4];                                     // [buffer][row position j]: channels 2g, 2g+1
+        float xb[2][4];                                      // channel 16 + g (Cin 20)
+        float4 xr[2];                                        // the node's own row (lanes g == 7): channels 4t..4t+3
+        float2 xr2[2];                                       //   and 16+2t, 17+2t
+        auto gather = [&](int k, int buf) {
+            const int i = hd[k].i < 0 ? 0 : hd[k].i;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int sj = (4 * j + t) < hd[k].deg ? hd[k].s[j] : i;   // empty slots read the node's own (valid) row
+                const float* row = x + (int64_t)sj * ldx;
+                xa[buf][j] = __ldg(reinterpret_cast<const float2*>(row) + g);
+                if (CP > 16) xb[buf][j] = g < 4 ? __ldg(row + 16 + g) : 0.f;
+            }
+            xr[buf] = make_float4(0.f, 0.f, 0.f, 0.f);
+            xr2[buf] = make_float2(0.f, 0.f);
+            if (g == 7 && hd[k].i >= 0) {
+                xr[buf] = __ldg(reinterpret_cast<const float4*>(x + (int64_t)i * ldx) + t);
+                if (CP > 16 && t < 2) xr2[buf] = __ldg(reinterpret_cast<const float2*>(x + (int64_t)i * ldx + 16) + t);
+            }
+        };
+        gather(0, 0);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int buf = k & 1;
+            if (k + 1 < 4) gather(k + 1, buf ^ 1);
+            const uint32_t cw[4] = {hd[k].c.x, hd[k].c.y, hd[k].c.z, hd[k].c.w};
+            float d[NT][4];
+#pragma unroll
+            for (int nt = 0; nt < NT; nt++)
+#pragma unroll
+                for (int b = 0; b < 4; b++) d[nt][b] = 0.f;
+#pragma unroll
+            for (int ks = 0; ks < 2; ks++) {
+                uint32_t ah[4], al[4];
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int j = 2 * ks + h;
+                    const uint32_t c = (4 * j + t) < hd[k].deg ? ((cw[j] >> (8 * t)) & 0xffu) : tw_zero;
+                    const float2 w = *reinterpret_cast<const float2*>(tw + c * L1M_TW_LD + 2 * g);
+                    ah[2 * h] = __float_as_uint(w.x) & 0xffffe000u;
+                    ah[2 * h + 1] = __float_as_uint(w.y) & 0xffffe000u;
+                    al[2 * h] = __float_as_uint(__fsub_rn(w.x, __uint_as_float(ah[2 * h])));
+                    al[2 * h + 1] = __float_as_uint(__fsub_rn(w.y, __uint_as_float(ah[2 * h + 1])));
+                }
+#pragma unroll
+                for (int nt = 0; nt < NT; nt++) {
+                    float v[2];
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        const int j = 2 * ks + h;
+                        v[h] = nt == 0 ? xa[buf][j].x : nt == 1 ? xa[buf][j].y : xb[buf][j];
+                    }
+                    uint32_t bh[2], bl[2];
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        bh[h] = __float_as_uint(v[h]) & 0xffffe000u;
+                        bl[h] = __float_as_uint(__fsub_rn(v[h], __uint_as_float(bh[h])));
+                    }
+                    l1_mma(d[nt], al, bh);
+                    l1_mma(d[nt], ah, bl);
+                    l1_mma(d[nt], ah, bh);
+                }
+            }
+            float* arow = As + (warp * 4 + k) * LDA;
+            float4 v0 = make_float4(d[0][0], d[1][0], d[0][1], d[1][1]);
+            float4 v1 = make_float4(d[0][2], d[1][2], d[0][3], d[1][3]);
+            if (g == 7) v1 = xr[buf];
+            *reinterpret_cast<float4*>(arow + g * CP + 4 * t) = v0;
+            *reinterpret_cast<float4*>(arow + (g + 8) * CP + 4 * t) = v1;
+            if (CP > 16 && t < 2) {
+                float2 u0 = make_float2(d[NT - 1][0], d[NT - 1][1]);
+                float2 u1 = make_float2(d[NT - 1][2], d[NT - 1][3]);
+                if (g == 7) u1 = xr2[buf];
+                *reinterpret_cast<float2*>(arow + g * CP + 16 + 2 * t) = u0;
+                *reinterpret_cast<float2*>(arow + (g + 8) * CP + 16 + 2 * t) = u1;
+            }
+        }
+        // next tile's row heads: in flight over the contraction
+        if (tile + gridDim.x < ntiles) load_heads(tile + gridDim.x);
+        __syncthreads();
+        // ---------------------------------------------------------------- (2) contraction P tile @ W_cat, k quarter per warp
+        {
+            float part[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll 2
+            for (int s = 0; s < CP / 2; s++) {
+                const int kk = (kq * (CP / 2) + s) * 8;
+                uint32_t ah[4], al[4];
+                l1_load_a(As, LDA, mt * 16, kk, g, t, ah, al);
+#pragma unroll
+                for (int nt = 0; nt < 2; nt++) {
+                    const int o0 = (kk + t) * L1_LDB + ((nt * 8 + g) ^ swz), o1 = o0 + 4 * L1_LDB;
+                    const uint32_t bh[2] = {__float_as_uint(Bh[o0]), __float_as_uint(Bh[o1])};
+                    const uint32_t bl[2] = {__float_as_uint(Bl[o0]), __float_as_uint(Bl[o1])};
+                    l1_mma(part[nt], al, bh);
+                    l1_mma(part[nt], ah, bl);
+                    l1_mma(part[nt], ah, bh);
+                }
+            }
+#pragma unroll
+            for (int nt = 0; nt < 2; nt++)
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int row = mt * 16 + g + 8 * h, col = nt * 8 + 2 * t;
+                    *reinterpret_cast<float2*>(Cs + (kq * L1M_NODES + row) * L1_LDC + col) =
+                        make_float2(part[nt][2 * h], part[nt][2 * h + 1]);
+                }
+            if (has_skip && kq == 3) {                       // skip Linear on the root slot
+                float sacc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll
+                for (int s = 0; s < C::KS / 8; s++) {
+                    uint32_t ah[4], al[4];
+                    l1_load_a(As, LDA, mt * 16, (L1_SLOTS - 1) * CP + 8 * s, g, t, ah, al);
+#pragma unroll
+                    for (int nt = 0; nt < 2; nt++) {
+                        const int o0 = (8 * s + t) * L1_LDB + ((nt * 8 + g) ^ swz), o1 = o0 + 4 * L1_LDB;
+                        const uint32_t bh[2] = {__float_as_uint(Sh[o0]), __float_as_uint(Sh[o1])};
+                        const uint32_t bl[2] = {__float_as_uint(Sl[o0]), __float_as_uint(Sl[o1])};
+                        l1_mma(sacc[nt], al, bh);
+                        l1_mma(sacc[nt], ah, bl);
+                        l1_mma(sacc[nt], ah, bh);
+                    }
+                }
+#pragma unroll
+                for (int nt = 0; nt < 2; nt++)
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        const int row = mt * 16 + g + 8 * h, col = nt * 8 + 2 * t;
+                        *reinterpret_cast<float2*>(Cs + (4 * L1M_NODES + row) * L1_LDC + col) =
+                            make_float2(sacc[nt][2 * h], sacc[nt][2 * h + 1]);
+                    }
+            }
+        }
+        __syncthreads();
+        // ---------------------------------------------------------------- (3) epilogue: BN / skip add / ReLU
+        if (tid < 4 * L1M_NODES) {
+            const int nl = tid >> 2, oq = tid & 3;
+            const int64_t iop = tile * L1M_NODES + nl;
+            if (iop < n) {
+                const int64_t io = perm ? (int64_t)perm[iop] : iop;
+                float4 v = *reinterpret_cast<const float4*>(Cs + nl * L1_LDC + 4 * oq);
+#pragma unroll
+                for (int p = 1; p < 4; p++) {
+                    const float4 c = *reinterpret_cast<const float4*>(Cs + (p * L1M_NODES + nl) * L1_LDC + 4 * oq);
+                    v.x += c.x; v.y += c.y; v.z += c.z; v.w += c.w;
+                }
+                *reinterpret_cast<float4*>(out + io * ldo + 4 * oq) = l1_epi(E, v, io, 4 * oq);
+                if (has_skip) {
+                    const float4 sv = *reinterpret_cast<const float4*>(Cs + (4 * L1M_NODES + nl) * L1_LDC + 4 * oq);
+                    *reinterpret_cast<float4*>(skip_out + io * ld_skip + 4 * oq) = l1_epi(ES, sv, io, 4 * oq);
+                }
+            }
+        }
+    }
+}
+
+template <int CP>
+static int launch_l1_mma(const int32_t* count, const int32_t* src, const uint8_t* cls, const int32_t* perm, int64_t n,
+                         const float* x, int ldx, const float* tapw, int ncls, const float* Whi, const float* Wlo,
+                         const float* Shi, const float* Slo, const evad_epilogue_t& E, float* out, int ldo,
+                         const evad_epilogue_t& ES, float* skip_out, int ld_skip, cudaStream_t st) {
+    const size_t smem = L1MCfg<CP>::smem_bytes(ncls);
+    if (smem > 113 * 1024) return EVAD_ERR_UNSUPPORTED;      // two CTAs per SM
+    static size_t attr_bytes = 0;
+    if (smem > attr_bytes) {
+        if (cudaFuncSetAttribute(spline_l1_mma_kernel<CP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return EVAD_ERR_LAUNCH;
+        attr_bytes = smem;
+    }
+    const int64_t ntiles = (n + L1M_NODES - 1) / L1M_NODES;
+    const int grid = (int)(ntiles < 2 * 148 ? ntiles : 2 * 148);
+    spline_l1_mma_kernel<CP><<<grid, L1M_THREADS, smem, st>>>(count, src, cls, perm, n, x, ldx, tapw, ncls, Whi, Wlo, Shi, Slo,
+                                                               E, out, ldo, ES, skip_out, ld_skip);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
+extern "C" int evad_spline_conv_l1_mma(const int32_t* count, const int32_t* nbr, const uint8_t* nbr_cls, const int32_t* perm,
+                                       int64_t n, const float* x, int ldx, int cin_pad, const float* tapw, int ncls,
+                                       const float* Whi, const float* Wlo, const float* Shi, const float* Slo,
+                                       const evad_epilogue_t* epi_h, float* out, int ldo,
+                                       const evad_epilogue_t* skip_epi_h, float* skip_out, int ld_skip, void* stream) {
+    if (!count || !nbr || !nbr_cls || !x || !tapw || !Whi || !Wlo || !epi_h || !out) return EVAD_ERR_ARG;
+    if (cin_pad != 16 && cin_pad != 20) return EVAD_ERR_UNSUPPORTED;
+    if (n * 16 >= (1ll << 31)) return EVAD_ERR_ARG;
+    if (ldx < cin_pad || ldx % 4 != 0 || ldo % 4 != 0 || ncls < 1 || ncls > 256) return EVAD_ERR_ARG;
+    if ((((uintptr_t)x | (uintptr_t)tapw | (uintptr_t)Whi | (uintptr_t)Wlo | (uintptr_t)out | (uintptr_t)nbr |
+          (uintptr_t)nbr_cls) & 15) != 0)
+        return EVAD_ERR_ARG;
+    const bool has_skip = Shi && Slo && skip_epi_h && skip_out;
+    if (has_skip && ((((uintptr_t)Shi | (uintptr_t)Slo | (uintptr_t)skip_out) & 15) != 0 || ld_skip % 4 != 0))
+        return EVAD_ERR_ARG;
+    if (n <= 0) return EVAD_OK;
+    const evad_epilogue_t es = has_skip ? *skip_epi_h : *epi_h;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cin_pad == 20)
+        return launch_l1_mma<20>(count, nbr, nbr_cls, perm, n, x, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
+                                 has_skip ? Slo : nullptr, *epi_h, out, ldo, es, skip_out, ld_skip, st);
+    return launch_l1_mma<16>(count, nbr, nbr_cls, perm, n, x, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
+                             has_skip ? Slo : nullptr, *epi_h, out, ldo, es, skip_out, ld_skip, st);
+}

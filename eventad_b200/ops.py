@@ -3,6 +3,7 @@ torch CUDA stream; sizes that depend on the data stay on the device (int32 cells
 tensor.  No function here has a CPU or PyTorch fallback."""
 import ctypes
 import math
+import os
 
 import torch
 
@@ -300,6 +301,10 @@ def edge_class(rowptr, src, n, mode, pseudo, status):
     return cls
 
 
+# EVAD_L1_MMA=0: keep the tap aggregation of layer 1 on the FFMA pipe (evad_spline_conv_l1) for A/B measurements
+USE_L1_MMA = os.environ.get("EVAD_L1_MMA", "1") != "0"
+
+
 def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None, perm=None, ell_stride=0):
     """Tap aggregation + tensor-core contraction, cout = 16.  pack = dict(tapw, whi, wlo, shi, slo, cin_pad).
     ell_stride > 0: fixed-stride rows (graph build_rows): rowptr = row lengths [n], src / cls rows at i * ell_stride."""
@@ -309,6 +314,16 @@ def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None, perm=N
     skip_out = torch.empty((n, 16), dtype=torch.float32, device=x.device) if has_skip else None
     e = _epi_struct(**epi)
     se = _epi_struct(**skip_epi) if has_skip else None
+    if (USE_L1_MMA and ell_stride == 16 and src.data_ptr() % 16 == 0 and
+            cls.data_ptr() % 16 == 0):
+        with _timed(f'spline_conv_l1_c{cin}'):
+            check(L.evad_spline_conv_l1_mma(ptr(rowptr), ptr(src), ptr(cls), ptr(perm), n, ptr(x), x.stride(0), pack["cin_pad"],
+                                            ptr(pack["tapw"]), pack["tapw"].shape[0], ptr(pack["whi"]), ptr(pack["wlo"]),
+                                            ptr(pack["shi"]) if has_skip else None, ptr(pack["slo"]) if has_skip else None,
+                                            ctypes.byref(e), ptr(out), out.stride(0), ctypes.byref(se) if has_skip else None,
+                                            ptr(skip_out), skip_out.stride(0) if has_skip else 0, stream()),
+                  "evad_spline_conv_l1_mma")
+        return out, skip_out
     with _timed(f'spline_conv_l1_c{cin}'):
         check(L.evad_spline_conv_l1(ptr(rowptr), ptr(src), ptr(cls), ptr(perm), int(ell_stride), n, ptr(x), x.stride(0), pack["cin_pad"],
                                     ptr(pack["tapw"]), pack["tapw"].shape[0], ptr(pack["whi"]), ptr(pack["wlo"]),

@@ -196,6 +196,16 @@ int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, const uint8_t
                         int cin_pad, const float* tapw, int ncls, const float* Whi, const float* Wlo, const float* Shi,
                         const float* Slo, const evad_epilogue_t* epi_h, float* out, int ldo,
                         const evad_epilogue_t* skip_epi_h, float* skip_out, int ld_skip, void* stream);
+/* The same layer with the tap aggregation on the tensor cores too (one mma.sync product [16 slots x 16 row positions] @
+ * [16 row positions x cin_pad] per node, csrc/spline_l1.cu second half).  Reads only the fixed-stride rows of
+ * evad_graph_build_rows (K = 16: count[i], nbr / nbr_cls row i at 16*i, 16-byte aligned).  Tap weights and features
+ * are both split into TF32 hi / lo parts (3xTF32).  Same operands, epilogues and result (rtol 1e-4 / atol 1e-5) as
+ * evad_spline_conv_l1. */
+int evad_spline_conv_l1_mma(const int32_t* count, const int32_t* nbr, const uint8_t* nbr_cls, const int32_t* perm,
+                            int64_t n, const float* x, int ldx, int cin_pad, const float* tapw, int ncls,
+                            const float* Whi, const float* Wlo, const float* Shi, const float* Slo,
+                            const evad_epilogue_t* epi_h, float* out, int ldo, const evad_epilogue_t* skip_epi_h,
+                            float* skip_out, int ld_skip, void* stream);
 
 /* The same contraction on the tensor cores for N = 64 (csrc/gemm_tc.cu): every product is split into TF32 parts
  * (a_hi + a_lo)(w_hi + w_lo) and accumulated in fp32 as a_lo*w_hi + a_hi*w_lo + a_hi*w_hi, so the result keeps fp32

@@ -1,0 +1,117 @@
+"""evad_spline_conv_l1_mma (tap aggregation on the tensor cores) against an fp64 evaluation of the same sum on the CPU and
+against evad_spline_conv_l1 (FFMA aggregation), on synthetic fixed-stride rows: ragged row lengths (0..16), node counts
+that are not a multiple of the 32-node tile, both channel widths, with and without the skip Linear, with and without a
+processing order.  Semantics: spline_conv.py:39-47,72-76 (LUT message, sum aggregation, root weight) + conv.py:23-28,47-56
+(eval BatchNorm folded to scale/shift, ReLU, skip Linear).  Bars: 2e-6 + 2e-5*|ref| + 1e-6*sum|terms| against fp64
+(outputs are 320-term sums with cancellation), rtol 1e-4 / atol 1e-5 between the two variants."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _case(n, cin, with_skip, with_perm, seed, full_rows=False):
+    from eventad_b200 import ops
+    g = torch.Generator().manual_seed(seed)
+    cin_pad = (cin + 3) // 4 * 4
+    ncls = 81
+    count = torch.full((n,), 16, dtype=torch.int32) if full_rows else torch.randint(0, 17, (n,), generator=g).int()
+    nbr = torch.randint(0, n, (n, 16), generator=g).int()
+    cls = torch.randint(0, ncls, (n, 16), generator=g).to(torch.uint8)
+    # slots beyond count hold garbage in the real layout (torch.empty): make it hostile
+    dead = torch.arange(16)[None, :] >= count[:, None]
+    nbr[dead] = 2**31 - 1
+    cls[dead] = 255
+    # degree-1 basis products: four non-zero taps per class out of 15 slots, (1-a, a) x (1-b, b) with arbitrary fractions
+    tapw = torch.zeros(ncls, 16)
+    for c in range(ncls):
+        slots = torch.randperm(15, generator=g)[:4]
+        a, b = torch.rand(2, generator=g)
+        tapw[c, slots] = torch.stack([(1 - a) * (1 - b), a * (1 - b), (1 - a) * b, a * b])
+    x = torch.zeros(n, cin_pad)
+    x[:, :cin] = torch.randn(n, cin, generator=g) * 3
+    W = torch.zeros(16, cin_pad, 16)
+    W[:, :cin] = torch.randn(16, cin, 16, generator=g) * 0.3
+    S = torch.zeros((cin_pad + 7) // 8 * 8, 16)
+    S[:cin] = torch.randn(cin, 16, generator=g) * 0.3
+    scale, shift = torch.rand(16, generator=g) + 0.5, torch.randn(16, generator=g)
+    sscale, sshift = torch.rand(16, generator=g) + 0.5, torch.randn(16, generator=g)
+    perm = torch.randperm(n, generator=g).int() if with_perm else None
+
+    # fp64 reference: P_i[s] = sum_e tapw[cls_e][s] x_src ; slot 15 = x_i ; out = relu(scale * (P_i . W) + shift)
+    xd, Wd = x.double(), W.double()
+    P = torch.zeros(n, 16, cin_pad, dtype=torch.float64)
+    for e in range(16):
+        live = (e < count).double()[:, None, None]
+        j = nbr[:, e].long().clamp(0, n - 1)
+        P += live * tapw[cls[:, e].long().clamp(0, ncls - 1)].double()[:, :, None] * xd[j][:, None, :]
+    P[:, 15] = xd
+    ref = torch.relu(torch.einsum("nsc,sco->no", P, Wd) * scale.double() + shift.double())
+    mag = torch.einsum("nsc,sco->no", P.abs(), Wd.abs()) * scale.double()   # sum of |terms|: the scale of cancellation errors
+    ref_skip = (xd[:, :S.shape[0]] if cin_pad >= S.shape[0] else torch.nn.functional.pad(xd, (0, S.shape[0] - cin_pad))) \
+        @ S.double() * sscale.double() + sshift.double()
+
+    dev = "cuda"
+    whi, wlo = ops.split_tf32(W.view(16 * cin_pad, 16).to(dev))
+    pack = dict(tapw=tapw.to(dev), whi=whi, wlo=wlo, shi=None, slo=None, cin_pad=cin_pad)
+    if with_skip:
+        pack["shi"], pack["slo"] = ops.split_tf32(S.to(dev))
+    epi = dict(scale=scale.to(dev), shift=shift.to(dev), relu=True)
+    sepi = dict(scale=sscale.to(dev), shift=sshift.to(dev)) if with_skip else None
+    args = (count.to(dev), nbr.to(dev).view(-1), cls.to(dev).view(-1), n, x.to(dev), cin, pack, epi, sepi)
+    kw = dict(perm=perm.to(dev) if perm is not None else None, ell_stride=16)
+    res = {}
+    for flag in (True, False):
+        old = ops.USE_L1_MMA
+        ops.USE_L1_MMA = flag
+        try:
+            res[flag] = ops.spline_conv_l1(*args, **kw)
+        finally:
+            ops.USE_L1_MMA = old
+    torch.cuda.synchronize()
+    for flag, (out, skip) in res.items():
+        err = (out.double().cpu() - ref).abs()
+        assert bool((err <= 2e-6 + 2e-5 * ref.abs() + 1e-6 * mag).all()), (flag, float(err.max()), float((err / mag).max()))
+        if with_skip:
+            serr = (skip.double().cpu() - ref_skip).abs()
+            assert bool((serr <= 2e-6 + 2e-5 * ref_skip.abs()).all()), (flag, float(serr.max()))
+        else:
+            assert skip is None
+    torch.testing.assert_close(res[True][0], res[False][0], rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("n,cin,with_skip,with_perm", [(1, 19, True, False), (31, 16, False, True), (33, 19, True, True),
+                                                       (4096, 16, False, False), (10_007, 19, True, True),
+                                                       (20_000, 16, True, True), (70_001, 20, False, True)])
+def test_l1_mma_matches_fp64_and_ffma_variant(n, cin, with_skip, with_perm):
+    _case(n, cin, with_skip, with_perm, seed=n % 7)
+
+
+def test_l1_mma_full_rows():
+    _case(5000, 19, True, True, seed=3, full_rows=True)
+
+
+def test_l1_mma_rejects_what_it_cannot_read():
+    """C-ABI argument checks: misaligned rows, unsupported channel width."""
+    import ctypes
+    from eventad_b200 import _lib
+    L = _lib.lib()
+    dev = "cuda"
+    n = 64
+    count = torch.zeros(n, dtype=torch.int32, device=dev)
+    nbr = torch.zeros(n * 16 + 4, dtype=torch.int32, device=dev)
+    cls = torch.zeros(n * 16 + 16, dtype=torch.uint8, device=dev)
+    x = torch.zeros(n, 16, device=dev)
+    tapw = torch.zeros(81, 16, device=dev)
+    w = torch.zeros(256, 16, device=dev)
+    out = torch.empty(n, 16, device=dev)
+    e = _lib.EpilogueT()
+
+    def call(nbr_t, cin_pad):
+        return L.evad_spline_conv_l1_mma(_lib.ptr(count), _lib.ptr(nbr_t), _lib.ptr(cls), None, n, _lib.ptr(x), 16, cin_pad,
+                                         _lib.ptr(tapw), 81, _lib.ptr(w), _lib.ptr(w), None, None, ctypes.byref(e),
+                                         _lib.ptr(out), 16, None, None, 0, _lib.stream())
+    assert call(nbr, 16) == 0
+    assert call(nbr[1:], 16) != 0          # rows not 16-byte aligned
+    assert call(nbr, 24) != 0              # channel width without a kernel
+    torch.cuda.synchronize()
