@@ -464,6 +464,12 @@ extern "C" int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, co
 //     [32 nodes x 16*Cin] shared P tile; slot 15 is overwritten with the node's own row (root weight).
 // The tile is 32 nodes (four per warp) with all 16 slots resident, so the contraction is a single pass split four ways
 // along K over the eight warps (two m16 tiles x four k quarters); partial sums are added in the epilogue.
+// Shared-memory layouts are chosen for the fragment loads of the contraction (ncu: the L1 data pipe bounds this kernel):
+//   P tile columns: [16 slots][channels 0..15] then [16 slots][channels 16..19] (slot stride 16 / 4: the D-fragment
+//     stores are conflict free), row stride == 8 (mod 32); a lane's two k columns of a k step are ADJACENT (k order
+//     inside a step is free), so an A fragment is two 64-bit loads;
+//   weights: fragment major, one float4 (hi k0, hi k1, lo k0, lo k1) per (k step, n tile, lane): a B fragment with both
+//     TF32 parts is one conflict-free 128-bit load.
 #define L1M_NODES 32
 #define L1M_THREADS 256
 #define L1M_TW_LD 24                  // floats per class row of the paired tap table: 8 x (slot g, slot g+8) + pad
@@ -471,23 +477,47 @@ extern "C" int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, co
 template <int CP>
 struct L1MCfg {
     static constexpr int KTOT = L1_SLOTS * CP;
-    static constexpr int LDA = KTOT + ((20 - KTOT % 32) + 32) % 32;   // == 20 (mod 32)
-    static constexpr int KS = (CP + 7) / 8 * 8;
+    static constexpr int LDA = KTOT + ((8 - KTOT % 32) + 32) % 32;    // == 8 (mod 32)
+    static constexpr int KSTEPS = KTOT / 8;
+    static constexpr int SSTEPS = (CP + 7) / 8;              // k steps of the skip Linear
     static constexpr int NT = (CP + 7) / 8;                  // channel tiles of the aggregation MMA
     static constexpr int A_FLOATS = L1M_NODES * LDA;
-    static constexpr int B_FLOATS = KTOT * L1_LDB;
-    static constexpr int S_FLOATS = KS * L1_LDB;
+    static constexpr int B_FLOATS = KSTEPS * 2 * 32 * 4;
+    static constexpr int S_FLOATS = SSTEPS * 2 * 32 * 4;
     static constexpr int C_FLOATS = 5 * L1M_NODES * L1_LDC;  // four k-quarter partials + skip
     static size_t smem_bytes(int ncls) {
-        return (size_t)(A_FLOATS + 2 * B_FLOATS + 2 * S_FLOATS + C_FLOATS + (ncls + 1) * L1M_TW_LD) * sizeof(float);
+        return (size_t)(A_FLOATS + B_FLOATS + S_FLOATS + C_FLOATS + (ncls + 1) * L1M_TW_LD) * sizeof(float);
+    }
+    // P tile column -> row of W_cat ([slot][channel], channel stride CP)
+    __host__ __device__ static constexpr int wrow(int k) {
+        return k < 256 ? (k >> 4) * CP + (k & 15) : ((k - 256) >> 2) * CP + 16 + ((k - 256) & 3);
     }
 };
 
-struct L1MHead {                      // what a lane keeps of one node's row: id, length, its 4 sources, the class words
+struct L1MHead {                      // what a lane keeps of one node's row: id, length, its 4 sources and their classes
     int i, deg;
     int s[4];
-    uint4 c;
+    uint32_t c;                       // class bytes of row positions t, t+4, t+8, t+12
 };
+
+__device__ __forceinline__ void l1m_mma(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// A fragment of the contraction: rows g / g+8, the lane's two adjacent columns of the k step at kk
+__device__ __forceinline__ void l1m_load_a(const float* __restrict__ As, int lda, int row, int kk, int g, int t,
+                                           uint32_t (&ah)[4], uint32_t (&al)[4]) {
+    const float2 p0 = *reinterpret_cast<const float2*>(As + (row + g) * lda + kk + 2 * t);
+    const float2 p1 = *reinterpret_cast<const float2*>(As + (row + g + 8) * lda + kk + 2 * t);
+    const float v[4] = {p0.x, p1.x, p0.y, p1.y};
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        ah[q] = __float_as_uint(v[q]) & 0xffffe000u;
+        al[q] = __float_as_uint(__fsub_rn(v[q], __uint_as_float(ah[q])));
+    }
+}
 
 template <int CP>
 __global__ void __launch_bounds__(L1M_THREADS, 2) spline_l1_mma_kernel(
@@ -500,28 +530,38 @@ __global__ void __launch_bounds__(L1M_THREADS, 2) spline_l1_mma_kernel(
     constexpr int LDA = C::LDA, NT = C::NT;
     extern __shared__ __align__(16) float l1_smem[];
     float* As = l1_smem;
-    float* Bh = As + C::A_FLOATS;
-    float* Bl = Bh + C::B_FLOATS;
-    float* Sh = Bl + C::B_FLOATS;
-    float* Sl = Sh + C::S_FLOATS;
-    float* Cs = Sl + C::S_FLOATS;
+    float4* Wf = reinterpret_cast<float4*>(As + C::A_FLOATS);
+    float4* Sf = Wf + C::B_FLOATS / 4;
+    float* Cs = reinterpret_cast<float*>(Sf + C::S_FLOATS / 4);
     float* tw = Cs + C::C_FLOATS;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
     const bool has_skip = Shi != nullptr;
 
-    for (int idx = tid; idx < C::KTOT * 4; idx += L1M_THREADS) {
-        const int r = idx >> 2, c4 = idx & 3;
-        const int cs = (4 * c4) ^ (((r >> 1) & 1) << 3);
-        *reinterpret_cast<float4*>(Bh + r * L1_LDB + cs) = __ldg(reinterpret_cast<const float4*>(Whi) + idx);
-        *reinterpret_cast<float4*>(Bl + r * L1_LDB + cs) = __ldg(reinterpret_cast<const float4*>(Wlo) + idx);
+    // one-time staging.  Weight fragments: entry (ks, nt, lane) = W_cat rows of P columns 8ks+2t, 8ks+2t+1, column 8nt+g
+    for (int idx = tid; idx < C::KSTEPS * 64; idx += L1M_THREADS) {
+        const int ks = idx >> 6, nt = (idx >> 5) & 1, l = idx & 31;
+        const int r0 = C::wrow(8 * ks + 2 * (l & 3)), r1 = C::wrow(8 * ks + 2 * (l & 3) + 1), col = 8 * nt + (l >> 2);
+        Wf[idx] = make_float4(__ldg(Whi + r0 * 16 + col), __ldg(Whi + r1 * 16 + col), __ldg(Wlo + r0 * 16 + col),
+                              __ldg(Wlo + r1 * 16 + col));
     }
     if (has_skip)
-        for (int idx = tid; idx < C::KS * 4; idx += L1M_THREADS) {
-            const int r = idx >> 2, c4 = idx & 3;
-            const int cs = (4 * c4) ^ (((r >> 1) & 1) << 3);
-            *reinterpret_cast<float4*>(Sh + r * L1_LDB + cs) = __ldg(reinterpret_cast<const float4*>(Shi) + idx);
-            *reinterpret_cast<float4*>(Sl + r * L1_LDB + cs) = __ldg(reinterpret_cast<const float4*>(Slo) + idx);
+        for (int idx = tid; idx < C::SSTEPS * 64; idx += L1M_THREADS) {
+            // skip k steps 0, 1 read the root slot's channels 0..15 (P columns 240..255); step 2 (Cin 20) reads columns
+            // 312..319 = slots 14, 15 of the second block: only the slot-15 half carries skip weights
+            const int s = idx >> 6, nt = (idx >> 5) & 1, l = idx & 31, col = 8 * nt + (l >> 2);
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            const int k0 = 2 * (l & 3);
+            if (s < 2) {
+                const int c0 = 8 * s + k0;
+                v = make_float4(__ldg(Shi + c0 * 16 + col), __ldg(Shi + (c0 + 1) * 16 + col), __ldg(Slo + c0 * 16 + col),
+                                __ldg(Slo + (c0 + 1) * 16 + col));
+            } else if (k0 >= 4) {
+                const int c0 = 16 + k0 - 4;
+                v = make_float4(__ldg(Shi + c0 * 16 + col), __ldg(Shi + (c0 + 1) * 16 + col), __ldg(Slo + c0 * 16 + col),
+                                __ldg(Slo + (c0 + 1) * 16 + col));
+            }
+            Sf[idx] = v;
         }
     // paired tap table: row c = (tapw[c][0], tapw[c][8]), (tapw[c][1], tapw[c][9]), ...; row ncls = zeros (empty slots)
     for (int idx = tid; idx < (ncls + 1) * 8; idx += L1M_THREADS) {
@@ -534,9 +574,12 @@ __global__ void __launch_bounds__(L1M_THREADS, 2) spline_l1_mma_kernel(
     __syncthreads();
 
     const int mt = warp & 1, kq = warp >> 1;                 // contraction role: m16 tile, k quarter
-    const int swz = ((t >> 1) & 1) << 3;
     const int64_t ntiles = (n + L1M_NODES - 1) / L1M_NODES;
     const uint32_t tw_zero = (uint32_t)ncls;
+    const float* xg = x + 2 * g;                             // lane bases of the row gathers (offsets fit 32 bits)
+    const float* xg16 = x + 16 + g;
+    const float* xt = x + 4 * t;
+    const uint32_t uldx = (uint32_t)ldx;
 
     L1MHead hd[4];
     auto load_heads = [&](int64_t tile) {
@@ -545,49 +588,54 @@ __global__ void __launch_bounds__(L1M_THREADS, 2) spline_l1_mma_kernel(
             const int64_t ip = tile * L1M_NODES + warp * 4 + k;
             hd[k].i = -1;
             hd[k].deg = 0;
-            hd[k].c = make_uint4(0, 0, 0, 0);
+            hd[k].c = 0;
 #pragma unroll
             for (int j = 0; j < 4; j++) hd[k].s[j] = 0;
             if (ip < n) {
                 const int i = perm ? perm[ip] : (int)ip;
                 hd[k].i = i;
                 hd[k].deg = count[i];
-                hd[k].c = __ldg(reinterpret_cast<const uint4*>(cls) + i);
+                const uint4 cw = __ldg(reinterpret_cast<const uint4*>(cls) + i);
+                hd[k].c = __byte_perm(__byte_perm(cw.x, cw.y, t | ((4 + t) << 4)), __byte_perm(cw.z, cw.w, t | ((4 + t) << 4)),
+                                      0x5410);
+                const int32_t* srow = src + ((uint32_t)i * 16u + (uint32_t)t);
 #pragma unroll
-                for (int j = 0; j < 4; j++) hd[k].s[j] = __ldg(src + (int64_t)i * 16 + 4 * j + t);
+                for (int j = 0; j < 4; j++) hd[k].s[j] = __ldg(srow + 4 * j);
             }
         }
     };
-    if ((int64_t)blockIdx.x < ntiles) load_heads(blockIdx.x);
+    float2 xa[2][4];                                         // [buffer][row position j]: channels 2g, 2g+1
+    float xb[2][4];                                          // channel 16 + g (Cin 20)
+    float4 xr[2];                                            // the node's own row (lanes g == 7): channels 4t..4t+3
+    float2 xr2[2];                                           //   and 16+2t, 17+2t
+    auto gather = [&](int k, int buf) {
+        const int i = hd[k].i < 0 ? 0 : hd[k].i;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int sj = (4 * j + t) < hd[k].deg ? hd[k].s[j] : i;   // empty slots read the node's own (valid) row
+            const uint32_t off = (uint32_t)sj * uldx;
+            xa[buf][j] = __ldg(reinterpret_cast<const float2*>(xg + off));
+            if (CP > 16) xb[buf][j] = g < 4 ? __ldg(xg16 + off) : 0.f;
+        }
+        xr[buf] = make_float4(0.f, 0.f, 0.f, 0.f);
+        xr2[buf] = make_float2(0.f, 0.f);
+        if (g == 7 && hd[k].i >= 0) {
+            const uint32_t off = (uint32_t)i * uldx;
+            xr[buf] = __ldg(reinterpret_cast<const float4*>(xt + off));
+            if (CP > 16 && t < 2) xr2[buf] = __ldg(reinterpret_cast<const float2*>(x + off + 16 + 2 * t));
+        }
+    };
+    if ((int64_t)blockIdx.x < ntiles) {
+        load_heads(blockIdx.x);
+        gather(0, 0);
+    }
 
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         // ---------------------------------------------------------------- (1) tap aggregation: one node per warp at a time
-        float2 xa[2][4];                                     // [buffer][row position j]: channels 2g, 2g+1
-        float xb[2][4];                                      // channel 16 + g (Cin 20)
-        float4 xr[2];                                        // the node's own row (lanes g == 7): channels 4t..4t+3
-        float2 xr2[2];                                       //   and 16+2t, 17+2t
-        auto gather = [&](int k, int buf) {
-            const int i = hd[k].i < 0 ? 0 : hd[k].i;
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const int sj = (4 * j + t) < hd[k].deg ? hd[k].s[j] : i;   // empty slots read the node's own (valid) row
-                const float* row = x + (int64_t)sj * ldx;
-                xa[buf][j] = __ldg(reinterpret_cast<const float2*>(row) + g);
-                if (CP > 16) xb[buf][j] = g < 4 ? __ldg(row + 16 + g) : 0.f;
-            }
-            xr[buf] = make_float4(0.f, 0.f, 0.f, 0.f);
-            xr2[buf] = make_float2(0.f, 0.f);
-            if (g == 7 && hd[k].i >= 0) {
-                xr[buf] = __ldg(reinterpret_cast<const float4*>(x + (int64_t)i * ldx) + t);
-                if (CP > 16 && t < 2) xr2[buf] = __ldg(reinterpret_cast<const float2*>(x + (int64_t)i * ldx + 16) + t);
-            }
-        };
-        gather(0, 0);
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             const int buf = k & 1;
             if (k + 1 < 4) gather(k + 1, buf ^ 1);
-            const uint32_t cw[4] = {hd[k].c.x, hd[k].c.y, hd[k].c.z, hd[k].c.w};
             float d[NT][4];
 #pragma unroll
             for (int nt = 0; nt < NT; nt++)
@@ -599,66 +647,66 @@ __global__ void __launch_bounds__(L1M_THREADS, 2) spline_l1_mma_kernel(
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
                     const int j = 2 * ks + h;
-                    const uint32_t c = (4 * j + t) < hd[k].deg ? ((cw[j] >> (8 * t)) & 0xffu) : tw_zero;
+                    const uint32_t c = (4 * j + t) < hd[k].deg ? ((hd[k].c >> (8 * j)) & 0xffu) : tw_zero;
                     const float2 w = *reinterpret_cast<const float2*>(tw + c * L1M_TW_LD + 2 * g);
                     ah[2 * h] = __float_as_uint(w.x) & 0xffffe000u;
                     ah[2 * h + 1] = __float_as_uint(w.y) & 0xffffe000u;
                     al[2 * h] = __float_as_uint(__fsub_rn(w.x, __uint_as_float(ah[2 * h])));
                     al[2 * h + 1] = __float_as_uint(__fsub_rn(w.y, __uint_as_float(ah[2 * h + 1])));
                 }
+                uint32_t bh[NT][2], bl[NT][2];
 #pragma unroll
-                for (int nt = 0; nt < NT; nt++) {
-                    float v[2];
+                for (int nt = 0; nt < NT; nt++)
 #pragma unroll
                     for (int h = 0; h < 2; h++) {
                         const int j = 2 * ks + h;
-                        v[h] = nt == 0 ? xa[buf][j].x : nt == 1 ? xa[buf][j].y : xb[buf][j];
+                        const float v = nt == 0 ? xa[buf][j].x : nt == 1 ? xa[buf][j].y : xb[buf][j];
+                        bh[nt][h] = __float_as_uint(v) & 0xffffe000u;
+                        bl[nt][h] = __float_as_uint(__fsub_rn(v, __uint_as_float(bh[nt][h])));
                     }
-                    uint32_t bh[2], bl[2];
+                // product by product over the channel tiles: consecutive MMAs are independent
 #pragma unroll
-                    for (int h = 0; h < 2; h++) {
-                        bh[h] = __float_as_uint(v[h]) & 0xffffe000u;
-                        bl[h] = __float_as_uint(__fsub_rn(v[h], __uint_as_float(bh[h])));
-                    }
-                    l1_mma(d[nt], al, bh);
-                    l1_mma(d[nt], ah, bl);
-                    l1_mma(d[nt], ah, bh);
-                }
+                for (int nt = 0; nt < NT; nt++) l1m_mma(d[nt], al, bh[nt][0], bh[nt][1]);
+#pragma unroll
+                for (int nt = 0; nt < NT; nt++) l1m_mma(d[nt], ah, bl[nt][0], bl[nt][1]);
+#pragma unroll
+                for (int nt = 0; nt < NT; nt++) l1m_mma(d[nt], ah, bh[nt][0], bh[nt][1]);
             }
             float* arow = As + (warp * 4 + k) * LDA;
             float4 v0 = make_float4(d[0][0], d[1][0], d[0][1], d[1][1]);
             float4 v1 = make_float4(d[0][2], d[1][2], d[0][3], d[1][3]);
             if (g == 7) v1 = xr[buf];
-            *reinterpret_cast<float4*>(arow + g * CP + 4 * t) = v0;
-            *reinterpret_cast<float4*>(arow + (g + 8) * CP + 4 * t) = v1;
+            *reinterpret_cast<float4*>(arow + g * 16 + 4 * t) = v0;
+            *reinterpret_cast<float4*>(arow + (g + 8) * 16 + 4 * t) = v1;
             if (CP > 16 && t < 2) {
                 float2 u0 = make_float2(d[NT - 1][0], d[NT - 1][1]);
                 float2 u1 = make_float2(d[NT - 1][2], d[NT - 1][3]);
                 if (g == 7) u1 = xr2[buf];
-                *reinterpret_cast<float2*>(arow + g * CP + 16 + 2 * t) = u0;
-                *reinterpret_cast<float2*>(arow + (g + 8) * CP + 16 + 2 * t) = u1;
+                *reinterpret_cast<float2*>(arow + 256 + g * 4 + 2 * t) = u0;
+                *reinterpret_cast<float2*>(arow + 256 + (g + 8) * 4 + 2 * t) = u1;
             }
         }
-        // next tile's row heads: in flight over the contraction
-        if (tile + gridDim.x < ntiles) load_heads(tile + gridDim.x);
+        // next tile's row heads: in flight over the first half of the contraction
+        const bool more = tile + gridDim.x < ntiles;
+        if (more) load_heads(tile + gridDim.x);
         __syncthreads();
         // ---------------------------------------------------------------- (2) contraction P tile @ W_cat, k quarter per warp
         {
             float part[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
-#pragma unroll 2
-            for (int s = 0; s < CP / 2; s++) {
-                const int kk = (kq * (CP / 2) + s) * 8;
-                uint32_t ah[4], al[4];
-                l1_load_a(As, LDA, mt * 16, kk, g, t, ah, al);
+            constexpr int KQ = C::KSTEPS / 4;
 #pragma unroll
-                for (int nt = 0; nt < 2; nt++) {
-                    const int o0 = (kk + t) * L1_LDB + ((nt * 8 + g) ^ swz), o1 = o0 + 4 * L1_LDB;
-                    const uint32_t bh[2] = {__float_as_uint(Bh[o0]), __float_as_uint(Bh[o1])};
-                    const uint32_t bl[2] = {__float_as_uint(Bl[o0]), __float_as_uint(Bl[o1])};
-                    l1_mma(part[nt], al, bh);
-                    l1_mma(part[nt], ah, bl);
-                    l1_mma(part[nt], ah, bh);
-                }
+            for (int s = 0; s < KQ; s++) {
+                if (s == KQ / 2 && more) gather(0, 0);       // first node of the next tile: rows in flight over the rest
+                const int ks = kq * KQ + s;
+                uint32_t ah[4], al[4];
+                l1m_load_a(As, LDA, mt * 16, ks * 8, g, t, ah, al);
+                const float4 w0 = Wf[(ks * 2 + 0) * 32 + lane], w1 = Wf[(ks * 2 + 1) * 32 + lane];
+                l1m_mma(part[0], al, __float_as_uint(w0.x), __float_as_uint(w0.y));
+                l1m_mma(part[1], al, __float_as_uint(w1.x), __float_as_uint(w1.y));
+                l1m_mma(part[0], ah, __float_as_uint(w0.z), __float_as_uint(w0.w));
+                l1m_mma(part[1], ah, __float_as_uint(w1.z), __float_as_uint(w1.w));
+                l1m_mma(part[0], ah, __float_as_uint(w0.x), __float_as_uint(w0.y));
+                l1m_mma(part[1], ah, __float_as_uint(w1.x), __float_as_uint(w1.y));
             }
 #pragma unroll
             for (int nt = 0; nt < 2; nt++)
@@ -671,18 +719,16 @@ __global__ void __launch_bounds__(L1M_THREADS, 2) spline_l1_mma_kernel(
             if (has_skip && kq == 3) {                       // skip Linear on the root slot
                 float sacc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
 #pragma unroll
-                for (int s = 0; s < C::KS / 8; s++) {
+                for (int s = 0; s < C::SSTEPS; s++) {
                     uint32_t ah[4], al[4];
-                    l1_load_a(As, LDA, mt * 16, (L1_SLOTS - 1) * CP + 8 * s, g, t, ah, al);
-#pragma unroll
-                    for (int nt = 0; nt < 2; nt++) {
-                        const int o0 = (8 * s + t) * L1_LDB + ((nt * 8 + g) ^ swz), o1 = o0 + 4 * L1_LDB;
-                        const uint32_t bh[2] = {__float_as_uint(Sh[o0]), __float_as_uint(Sh[o1])};
-                        const uint32_t bl[2] = {__float_as_uint(Sl[o0]), __float_as_uint(Sl[o1])};
-                        l1_mma(sacc[nt], al, bh);
-                        l1_mma(sacc[nt], ah, bl);
-                        l1_mma(sacc[nt], ah, bh);
-                    }
+                    l1m_load_a(As, LDA, mt * 16, s < 2 ? 240 + 8 * s : 312, g, t, ah, al);
+                    const float4 w0 = Sf[(s * 2 + 0) * 32 + lane], w1 = Sf[(s * 2 + 1) * 32 + lane];
+                    l1m_mma(sacc[0], al, __float_as_uint(w0.x), __float_as_uint(w0.y));
+                    l1m_mma(sacc[1], al, __float_as_uint(w1.x), __float_as_uint(w1.y));
+                    l1m_mma(sacc[0], ah, __float_as_uint(w0.z), __float_as_uint(w0.w));
+                    l1m_mma(sacc[1], ah, __float_as_uint(w1.z), __float_as_uint(w1.w));
+                    l1m_mma(sacc[0], ah, __float_as_uint(w0.x), __float_as_uint(w0.y));
+                    l1m_mma(sacc[1], ah, __float_as_uint(w1.x), __float_as_uint(w1.y));
                 }
 #pragma unroll
                 for (int nt = 0; nt < 2; nt++)
@@ -745,7 +791,7 @@ extern "C" int evad_spline_conv_l1_mma(const int32_t* count, const int32_t* nbr,
                                        const evad_epilogue_t* skip_epi_h, float* skip_out, int ld_skip, void* stream) {
     if (!count || !nbr || !nbr_cls || !x || !tapw || !Whi || !Wlo || !epi_h || !out) return EVAD_ERR_ARG;
     if (cin_pad != 16 && cin_pad != 20) return EVAD_ERR_UNSUPPORTED;
-    if (n * 16 >= (1ll << 31)) return EVAD_ERR_ARG;
+    if (n * 16 >= (1ll << 31) || n * (int64_t)ldx >= (1ll << 32)) return EVAD_ERR_ARG;   // 32-bit row offsets in the kernel
     if (ldx < cin_pad || ldx % 4 != 0 || ldo % 4 != 0 || ncls < 1 || ncls > 256) return EVAD_ERR_ARG;
     if ((((uintptr_t)x | (uintptr_t)tapw | (uintptr_t)Whi | (uintptr_t)Wlo | (uintptr_t)out | (uintptr_t)nbr |
           (uintptr_t)nbr_cls) & 15) != 0)

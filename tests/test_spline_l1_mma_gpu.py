@@ -48,8 +48,9 @@ def _case(n, cin, with_skip, with_perm, seed, full_rows=False):
     P[:, 15] = xd
     ref = torch.relu(torch.einsum("nsc,sco->no", P, Wd) * scale.double() + shift.double())
     mag = torch.einsum("nsc,sco->no", P.abs(), Wd.abs()) * scale.double()   # sum of |terms|: the scale of cancellation errors
-    ref_skip = (xd[:, :S.shape[0]] if cin_pad >= S.shape[0] else torch.nn.functional.pad(xd, (0, S.shape[0] - cin_pad))) \
-        @ S.double() * sscale.double() + sshift.double()
+    xs = xd[:, :S.shape[0]] if cin_pad >= S.shape[0] else torch.nn.functional.pad(xd, (0, S.shape[0] - cin_pad))
+    ref_skip = xs @ S.double() * sscale.double() + sshift.double()
+    smag = xs.abs() @ S.double().abs() * sscale.double()
 
     dev = "cuda"
     whi, wlo = ops.split_tf32(W.view(16 * cin_pad, 16).to(dev))
@@ -74,10 +75,13 @@ def _case(n, cin, with_skip, with_perm, seed, full_rows=False):
         assert bool((err <= 2e-6 + 2e-5 * ref.abs() + 1e-6 * mag).all()), (flag, float(err.max()), float((err / mag).max()))
         if with_skip:
             serr = (skip.double().cpu() - ref_skip).abs()
-            assert bool((serr <= 2e-6 + 2e-5 * ref_skip.abs()).all()), (flag, float(serr.max()))
+            assert bool((serr <= 2e-6 + 2e-5 * ref_skip.abs() + 1e-6 * smag).all()), (flag, float(serr.max()))
         else:
             assert skip is None
-    torch.testing.assert_close(res[True][0], res[False][0], rtol=1e-4, atol=1e-5)
+    # the two variants sum the same 320 terms in different orders: north_star's rtol 1e-4 / atol 1e-5 plus the
+    # cancellation term of the fp64 bar (the synthetic features here are far larger than real layer inputs)
+    diff = (res[True][0] - res[False][0]).abs().double().cpu()
+    assert bool((diff <= 1e-5 + 1e-4 * ref.abs() + 2e-6 * mag).all()), float(diff.max())
 
 
 @pytest.mark.parametrize("n,cin,with_skip,with_perm", [(1, 19, True, False), (31, 16, False, True), (33, 19, True, True),
