@@ -473,6 +473,7 @@ extern "C" int evad_spline_conv_l1(const int32_t* rowptr, const int32_t* src, co
 #define L1M_NODES 32
 #define L1M_THREADS 256
 #define L1M_TW_LD 24                  // floats per class row of the paired tap table: 8 x (slot g, slot g+8) + pad
+#define L1M_AUX 128                   // words: node ids of the tile [2 parities][32] + epilogue scale / shift [4][16]
 
 template <int CP>
 struct L1MCfg {
@@ -486,7 +487,7 @@ struct L1MCfg {
     static constexpr int S_FLOATS = SSTEPS * 2 * 32 * 4;
     static constexpr int C_FLOATS = 5 * L1M_NODES * L1_LDC;  // four k-quarter partials + skip
     static size_t smem_bytes(int ncls) {
-        return (size_t)(A_FLOATS + B_FLOATS + S_FLOATS + C_FLOATS + (ncls + 1) * L1M_TW_LD) * sizeof(float);
+        return (size_t)(A_FLOATS + B_FLOATS + S_FLOATS + C_FLOATS + (ncls + 1) * L1M_TW_LD + L1M_AUX) * sizeof(float);
     }
     // P tile column -> row of W_cat ([slot][channel], channel stride CP)
     __host__ __device__ static constexpr int wrow(int k) {
@@ -534,10 +535,17 @@ __global__ void __launch_bounds__(L1M_THREADS, 2) spline_l1_mma_kernel(
     float4* Sf = Wf + C::B_FLOATS / 4;
     float* Cs = reinterpret_cast<float*>(Sf + C::S_FLOATS / 4);
     float* tw = Cs + C::C_FLOATS;
+    int* ids = reinterpret_cast<int*>(tw + (ncls + 1) * L1M_TW_LD);
+    float* epc = reinterpret_cast<float*>(ids + 64);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
     const bool has_skip = Shi != nullptr;
 
+    if (tid < 64) {                                          // epilogue constants: scale (1 when absent), shift (0 when absent)
+        const int c = tid & 15, w = tid >> 4;
+        const float* pq = w == 0 ? E.scale : w == 1 ? E.shift : w == 2 ? ES.scale : ES.shift;
+        epc[tid] = pq ? pq[c] : (w & 1) ? 0.f : 1.f;
+    }
     // one-time staging.  Weight fragments: entry (ks, nt, lane) = W_cat rows of P columns 8ks+2t, 8ks+2t+1, column 8nt+g
     for (int idx = tid; idx < C::KSTEPS * 64; idx += L1M_THREADS) {
         const int ks = idx >> 6, nt = (idx >> 5) & 1, l = idx & 31;
@@ -581,28 +589,43 @@ __global__ void __launch_bounds__(L1M_THREADS, 2) spline_l1_mma_kernel(
     const float* xt = x + 4 * t;
     const uint32_t uldx = (uint32_t)ldx;
 
+    // Row heads travel in three steps so that no load is waited for where it is issued: node ids (perm) two tiles
+    // ahead, row length / sources / class words one tile ahead (issued after the aggregation, from the ids that are
+    // already there), class bytes packed and the first node's rows gathered in the middle of the contraction.
     L1MHead hd[4];
-    auto load_heads = [&](int64_t tile) {
+    uint4 craw[4];
+    int inext[4];
+    auto load_ids = [&](int64_t tile) {
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             const int64_t ip = tile * L1M_NODES + warp * 4 + k;
-            hd[k].i = -1;
+            inext[k] = -1;
+            if (tile < ntiles && ip < n) inext[k] = perm ? perm[ip] : (int)ip;
+        }
+    };
+    auto load_heads = [&]() {
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int i = inext[k];
+            hd[k].i = i;
             hd[k].deg = 0;
-            hd[k].c = 0;
+            craw[k] = make_uint4(0, 0, 0, 0);
 #pragma unroll
             for (int j = 0; j < 4; j++) hd[k].s[j] = 0;
-            if (ip < n) {
-                const int i = perm ? perm[ip] : (int)ip;
-                hd[k].i = i;
+            if (i >= 0) {
                 hd[k].deg = count[i];
-                const uint4 cw = __ldg(reinterpret_cast<const uint4*>(cls) + i);
-                hd[k].c = __byte_perm(__byte_perm(cw.x, cw.y, t | ((4 + t) << 4)), __byte_perm(cw.z, cw.w, t | ((4 + t) << 4)),
-                                      0x5410);
+                craw[k] = __ldg(reinterpret_cast<const uint4*>(cls) + i);
                 const int32_t* srow = src + ((uint32_t)i * 16u + (uint32_t)t);
 #pragma unroll
                 for (int j = 0; j < 4; j++) hd[k].s[j] = __ldg(srow + 4 * j);
             }
         }
+    };
+    auto pack_classes = [&]() {
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            hd[k].c = __byte_perm(__byte_perm(craw[k].x, craw[k].y, t | ((4 + t) << 4)),
+                                  __byte_perm(craw[k].z, craw[k].w, t | ((4 + t) << 4)), 0x5410);
     };
     float2 xa[2][4];                                         // [buffer][row position j]: channels 2g, 2g+1
     float xb[2][4];                                          // channel 16 + g (Cin 20)
@@ -625,12 +648,21 @@ __global__ void __launch_bounds__(L1M_THREADS, 2) spline_l1_mma_kernel(
             if (CP > 16 && t < 2) xr2[buf] = __ldg(reinterpret_cast<const float2*>(x + off + 16 + 2 * t));
         }
     };
-    if ((int64_t)blockIdx.x < ntiles) {
-        load_heads(blockIdx.x);
-        gather(0, 0);
-    }
+    load_ids(blockIdx.x);
+    load_heads();
+    pack_classes();
+    gather(0, 0);
+    load_ids((int64_t)blockIdx.x + gridDim.x);
 
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    int par = 0;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 32) {
+        if (lane < 4) {                                      // this tile's node ids for the epilogue threads
+            int idv = hd[0].i;
+            if (lane == 1) idv = hd[1].i;
+            if (lane == 2) idv = hd[2].i;
+            if (lane == 3) idv = hd[3].i;
+            ids[par + warp * 4 + lane] = idv;
+        }
         // ---------------------------------------------------------------- (1) tap aggregation: one node per warp at a time
 #pragma unroll
         for (int k = 0; k < 4; k++) {
@@ -686,17 +718,30 @@ __global__ void __launch_bounds__(L1M_THREADS, 2) spline_l1_mma_kernel(
                 *reinterpret_cast<float2*>(arow + 256 + (g + 8) * 4 + 2 * t) = u1;
             }
         }
-        // next tile's row heads: in flight over the first half of the contraction
+        // next tile's row heads (their node ids arrived a tile ago): in flight over the first half of the contraction;
+        // the node ids of the tile after that: in flight over a whole tile
         const bool more = tile + gridDim.x < ntiles;
-        if (more) load_heads(tile + gridDim.x);
+        load_heads();
+        load_ids(tile + 2 * (int64_t)gridDim.x);
         __syncthreads();
+        // epilogue threads fetch their addend row now: it lands during the contraction
+        const int e_nl = tid >> 2, e_oq = tid & 3;
+        int e_io = -1;
+        float4 e_add = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (tid < 4 * L1M_NODES) {
+            e_io = ids[par + e_nl];
+            if (e_io >= 0 && E.addend) e_add = __ldg(reinterpret_cast<const float4*>(E.addend + (int64_t)e_io * E.ld_add) + e_oq);
+        }
         // ---------------------------------------------------------------- (2) contraction P tile @ W_cat, k quarter per warp
         {
             float part[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
             constexpr int KQ = C::KSTEPS / 4;
 #pragma unroll
             for (int s = 0; s < KQ; s++) {
-                if (s == KQ / 2 && more) gather(0, 0);       // first node of the next tile: rows in flight over the rest
+                if (s == KQ / 2 && more) {                   // first node of the next tile: rows in flight over the rest
+                    pack_classes();
+                    gather(0, 0);
+                }
                 const int ks = kq * KQ + s;
                 uint32_t ah[4], al[4];
                 l1m_load_a(As, LDA, mt * 16, ks * 8, g, t, ah, al);
@@ -742,22 +787,36 @@ __global__ void __launch_bounds__(L1M_THREADS, 2) spline_l1_mma_kernel(
         }
         __syncthreads();
         // ---------------------------------------------------------------- (3) epilogue: BN / skip add / ReLU
-        if (tid < 4 * L1M_NODES) {
-            const int nl = tid >> 2, oq = tid & 3;
-            const int64_t iop = tile * L1M_NODES + nl;
-            if (iop < n) {
-                const int64_t io = perm ? (int64_t)perm[iop] : iop;
-                float4 v = *reinterpret_cast<const float4*>(Cs + nl * L1_LDC + 4 * oq);
+        if (e_io >= 0) {
+            float4 v = *reinterpret_cast<const float4*>(Cs + e_nl * L1_LDC + 4 * e_oq);
 #pragma unroll
-                for (int p = 1; p < 4; p++) {
-                    const float4 c = *reinterpret_cast<const float4*>(Cs + (p * L1M_NODES + nl) * L1_LDC + 4 * oq);
-                    v.x += c.x; v.y += c.y; v.z += c.z; v.w += c.w;
+            for (int p = 1; p < 4; p++) {
+                const float4 c = *reinterpret_cast<const float4*>(Cs + (p * L1M_NODES + e_nl) * L1_LDC + 4 * e_oq);
+                v.x += c.x; v.y += c.y; v.z += c.z; v.w += c.w;
+            }
+            const float4 sc = *reinterpret_cast<const float4*>(epc + 4 * e_oq);
+            const float4 sh = *reinterpret_cast<const float4*>(epc + 16 + 4 * e_oq);
+            float r[4] = {__fadd_rn(__fmul_rn(v.x, sc.x), sh.x), __fadd_rn(__fmul_rn(v.y, sc.y), sh.y),
+                          __fadd_rn(__fmul_rn(v.z, sc.z), sh.z), __fadd_rn(__fmul_rn(v.w, sc.w), sh.w)};
+            const float ad[4] = {e_add.x, e_add.y, e_add.z, e_add.w};
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                if (E.addend) r[b] = __fadd_rn(r[b], ad[b]);
+                if (E.relu) r[b] = fmaxf(r[b], 0.f);
+            }
+            *reinterpret_cast<float4*>(out + (int64_t)e_io * ldo + 4 * e_oq) = make_float4(r[0], r[1], r[2], r[3]);
+            if (has_skip) {
+                const float4 sv = *reinterpret_cast<const float4*>(Cs + (4 * L1M_NODES + e_nl) * L1_LDC + 4 * e_oq);
+                const float4 ssc = *reinterpret_cast<const float4*>(epc + 32 + 4 * e_oq);
+                const float4 ssh = *reinterpret_cast<const float4*>(epc + 48 + 4 * e_oq);
+                float q[4] = {__fadd_rn(__fmul_rn(sv.x, ssc.x), ssh.x), __fadd_rn(__fmul_rn(sv.y, ssc.y), ssh.y),
+                              __fadd_rn(__fmul_rn(sv.z, ssc.z), ssh.z), __fadd_rn(__fmul_rn(sv.w, ssc.w), ssh.w)};
+#pragma unroll
+                for (int b = 0; b < 4; b++) {
+                    if (ES.addend) q[b] = __fadd_rn(q[b], ES.addend[(int64_t)e_io * ES.ld_add + 4 * e_oq + b]);
+                    if (ES.relu) q[b] = fmaxf(q[b], 0.f);
                 }
-                *reinterpret_cast<float4*>(out + io * ldo + 4 * oq) = l1_epi(E, v, io, 4 * oq);
-                if (has_skip) {
-                    const float4 sv = *reinterpret_cast<const float4*>(Cs + (4 * L1M_NODES + nl) * L1_LDC + 4 * oq);
-                    *reinterpret_cast<float4*>(skip_out + io * ld_skip + 4 * oq) = l1_epi(ES, sv, io, 4 * oq);
-                }
+                *reinterpret_cast<float4*>(skip_out + (int64_t)e_io * ld_skip + 4 * e_oq) = make_float4(q[0], q[1], q[2], q[3]);
             }
         }
     }
@@ -792,6 +851,7 @@ extern "C" int evad_spline_conv_l1_mma(const int32_t* count, const int32_t* nbr,
     if (!count || !nbr || !nbr_cls || !x || !tapw || !Whi || !Wlo || !epi_h || !out) return EVAD_ERR_ARG;
     if (cin_pad != 16 && cin_pad != 20) return EVAD_ERR_UNSUPPORTED;
     if (n * 16 >= (1ll << 31) || n * (int64_t)ldx >= (1ll << 32)) return EVAD_ERR_ARG;   // 32-bit row offsets in the kernel
+    if (epi_h->addend && ((((uintptr_t)epi_h->addend) & 15) != 0 || epi_h->ld_add % 4 != 0)) return EVAD_ERR_ARG;
     if (ldx < cin_pad || ldx % 4 != 0 || ldo % 4 != 0 || ncls < 1 || ncls > 256) return EVAD_ERR_ARG;
     if ((((uintptr_t)x | (uintptr_t)tapw | (uintptr_t)Whi | (uintptr_t)Wlo | (uintptr_t)out | (uintptr_t)nbr |
           (uintptr_t)nbr_cls) & 15) != 0)
