@@ -377,7 +377,7 @@ def run_b200(a):
 
     cpu = None
     if not a.no_cpu_baseline and world == 1:
-        v, ms, cores, sample = cpu_reference_run(a, 2, 1)
+        v, ms, cores, sample = cpu_reference_run(a, 8, 1)        # ~13 s of CPU work at 100k events per window
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "ms_per_window": ms}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
