@@ -24,14 +24,8 @@ struct PoolGeom {
 };
 
 // torch_cluster grid_cluster, D = 4, start = 0: c_d = (int64)(p_d / size_d) in fp32
-__global__ void __launch_bounds__(256) pool_keys_kernel(const float* __restrict__ pos, int ld_pos,
-                                                        const int32_t* __restrict__ batch, int64_t n_cap,
-                                                        const int32_t* __restrict__ n_dev, PoolGeom G,
-                                                        uint32_t* __restrict__ keys, uint32_t* __restrict__ status) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_cap) return;
-    const int64_t n = n_dev ? min((int64_t)*n_dev, n_cap) : n_cap;
-    if (i >= n) { keys[i] = G.key_bound; return; }          // padding sorts to the end
+__device__ __forceinline__ uint32_t pool_voxel_key(const float* __restrict__ pos, int ld_pos, const int32_t* __restrict__ batch,
+                                                   int64_t i, const PoolGeom& G, uint32_t* __restrict__ status) {
     const long long cx = (long long)__fdiv_rn(pos[i * ld_pos], G.sx);
     const long long cy = (long long)__fdiv_rn(pos[i * ld_pos + 1], G.sy);
     const long long ct = (long long)__fdiv_rn(pos[i * ld_pos + 2], G.st);
@@ -41,7 +35,18 @@ __global__ void __launch_bounds__(256) pool_keys_kernel(const float* __restrict_
         atomicOr(status, EVAD_STATUS_CLUSTER_OOB);
         key = min(max(key, 0ll), (long long)G.key_bound - 1);
     }
-    keys[i] = (uint32_t)key;
+    return (uint32_t)key;
+}
+
+__global__ void __launch_bounds__(256) pool_keys_kernel(const float* __restrict__ pos, int ld_pos,
+                                                        const int32_t* __restrict__ batch, int64_t n_cap,
+                                                        const int32_t* __restrict__ n_dev, PoolGeom G,
+                                                        uint32_t* __restrict__ keys, uint32_t* __restrict__ status) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_cap) return;
+    const int64_t n = n_dev ? min((int64_t)*n_dev, n_cap) : n_cap;
+    if (i >= n) { keys[i] = G.key_bound; return; }          // padding sorts to the end
+    keys[i] = pool_voxel_key(pos, ld_pos, batch, i, G, status);
 }
 
 __global__ void __launch_bounds__(256) pool_flag_kernel(const uint32_t* __restrict__ skey, int64_t n_cap,
@@ -68,6 +73,93 @@ __global__ void __launch_bounds__(256) pool_relabel_kernel(const uint32_t* __res
     cluster[sidx[p]] = (int32_t)d;
     if (p == 0 || flag[p]) seg_start[d] = (int32_t)p;
     if (p == n_cap - 1 || skey[p + 1] >= key_bound) { seg_start[d + 1] = (int32_t)(p + 1); *n_out = (int32_t)(d + 1); }
+}
+
+// ------------------------------------------------------------------------------------------------ small inputs
+// Poolings 2-4 see a few thousand nodes: keys, stable sort, flag, scan and relabel (ten ~3 us launches above) run as ONE
+// CTA here, by counting in shared memory: voxel histogram -> block scan (segment starts, dense ids) -> placement ->
+// each segment put into ascending node order (segments are a handful of nodes: the children of one voxel).  Outputs are
+// identical to the general path: skey / sidx (sorted pairs, padding at the end), cluster, seg_start, n_out.
+#define PFS_THREADS 1024
+#define PFS_NMAX 4608
+#define PFS_KMAX 8192
+
+__global__ void __launch_bounds__(PFS_THREADS) pool_front_small_kernel(
+    const float* __restrict__ pos, int ld_pos, const int32_t* __restrict__ batch, int n_cap, const int32_t* __restrict__ n_dev,
+    PoolGeom G, uint32_t* __restrict__ skey, uint32_t* __restrict__ sidx, int32_t* __restrict__ cluster,
+    int32_t* __restrict__ seg_start, int32_t* __restrict__ n_out, uint32_t* __restrict__ status) {
+    extern __shared__ uint32_t pfs_smem[];
+    uint32_t* key = pfs_smem;                                // [PFS_NMAX]
+    uint32_t* sid = key + PFS_NMAX;                          // [PFS_NMAX] node ids in sorted order
+    uint32_t* cur = sid + PFS_NMAX;                          // [PFS_KMAX] counts, then placement cursors
+    uint32_t* beg = cur + PFS_KMAX;                          // [PFS_KMAX] segment starts
+    uint32_t* den = beg + PFS_KMAX;                          // [PFS_KMAX] dense ids
+    __shared__ uint32_t s_wc[32], s_wn[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = n_dev ? min(*n_dev, n_cap) : n_cap;
+    const int kb = (int)G.key_bound;
+    for (int b = tid; b < kb; b += PFS_THREADS) cur[b] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += PFS_THREADS) {
+        const uint32_t k = pool_voxel_key(pos, ld_pos, batch, i, G, status);
+        key[i] = k;
+        atomicAdd(&cur[k], 1u);
+    }
+    __syncthreads();
+    // block scan over the voxel bins: every thread owns a contiguous run of bins
+    const int per = (kb + PFS_THREADS - 1) / PFS_THREADS;
+    const int b0 = min(tid * per, kb), b1 = min(b0 + per, kb);
+    uint32_t csum = 0, nsum = 0;
+    for (int b = b0; b < b1; b++) { const uint32_t c = cur[b]; csum += c; nsum += c > 0; }
+    uint32_t ic = csum, in = nsum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t uc = __shfl_up_sync(0xffffffffu, ic, o), un = __shfl_up_sync(0xffffffffu, in, o);
+        if (lane >= o) { ic += uc; in += un; }
+    }
+    if (lane == 31) { s_wc[warp] = ic; s_wn[warp] = in; }
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t wc = s_wc[lane], wn = s_wn[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t uc = __shfl_up_sync(0xffffffffu, wc, o), un = __shfl_up_sync(0xffffffffu, wn, o);
+            if (lane >= o) { wc += uc; wn += un; }
+        }
+        s_wc[lane] = wc; s_wn[lane] = wn;                    // inclusive over warps
+    }
+    __syncthreads();
+    uint32_t ec = ic - csum + (warp ? s_wc[warp - 1] : 0u), en = in - nsum + (warp ? s_wn[warp - 1] : 0u);
+    const uint32_t total_n = s_wn[31];
+    for (int b = b0; b < b1; b++) {
+        const uint32_t c = cur[b];
+        beg[b] = ec; den[b] = en; cur[b] = ec;
+        if (c) seg_start[en] = (int32_t)ec;
+        ec += c; en += c > 0;
+    }
+    if (tid == 0) { *n_out = (int32_t)total_n; seg_start[total_n] = (int32_t)n; }
+    __syncthreads();
+    for (int i = tid; i < n; i += PFS_THREADS) sid[atomicAdd(&cur[key[i]], 1u)] = (uint32_t)i;
+    __syncthreads();
+    for (int b = tid; b < kb; b += PFS_THREADS) {            // ascending node ids inside every segment (= the stable sort)
+        const int s0 = (int)beg[b], s1 = (int)cur[b];
+        for (int a = s0 + 1; a < s1; a++) {
+            const uint32_t v = sid[a];
+            int q = a - 1;
+            while (q >= s0 && sid[q] > v) { sid[q + 1] = sid[q]; q--; }
+            sid[q + 1] = v;
+        }
+    }
+    __syncthreads();
+    for (int p = tid; p < n_cap; p += PFS_THREADS) {
+        if (p < n) {
+            const uint32_t i = sid[p], k = key[i];
+            skey[p] = k; sidx[p] = i;
+            cluster[i] = (int32_t)den[k];
+        } else {
+            skey[p] = G.key_bound; sidx[p] = (uint32_t)p;    // padding keeps its place, as in the stable sort
+        }
+    }
 }
 
 // c10::div_floor_floating (torch.div(..., rounding_mode='floor') on floats), used by round_to_pixel (pooling.py:47-49)
@@ -646,18 +738,33 @@ extern "C" int evad_voxel_pool(const evad_pool_params_t* p, int64_t n_cap, const
         if (want_edges) { cudaMemsetAsync(num_edges_out, 0, sizeof(int32_t), st); cudaMemsetAsync(rowptr_out, 0, sizeof(int32_t), st); }
         return EVAD_OK;
     }
-    pool_keys_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(pos, ld_pos, batch, n_cap, n_dev, G, w.k0, status);
-    EVAD_CHECK_LAUNCH();
-    int key_bits = 1;
-    while ((1ll << key_bits) <= kb) key_bits++;             // keys take values 0..kb (kb = padding)
     uint32_t *skey, *sidx;
-    EVAD_TRY(evad_sort_pairs_u32(w.k0, w.v0, w.k1, w.v1, 1, n_cap, key_bits, w.sort_tmp, &skey, &sidx, st));
-    pool_flag_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(skey, n_cap, G.key_bound, w.flag);
-    EVAD_CHECK_LAUNCH();
-    EVAD_TRY(evad_exclusive_scan_u32(w.flag, w.excl, n_cap, nullptr, w.scan_tmp, st));
-    pool_relabel_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(skey, sidx, w.flag, w.excl, n_cap, G.key_bound, cluster,
-                                                         w.seg_start, n_out);
-    EVAD_CHECK_LAUNCH();
+    if (n_cap <= PFS_NMAX && kb <= PFS_KMAX) {
+        const size_t fs_smem = (size_t)(2 * PFS_NMAX + 3 * PFS_KMAX) * sizeof(uint32_t);
+        static bool fs_attr = false;
+        if (!fs_attr) {
+            if (cudaFuncSetAttribute(pool_front_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs_smem) !=
+                cudaSuccess)
+                return EVAD_ERR_LAUNCH;
+            fs_attr = true;
+        }
+        skey = w.k1; sidx = w.v1;
+        pool_front_small_kernel<<<1, PFS_THREADS, fs_smem, st>>>(pos, ld_pos, batch, (int)n_cap, n_dev, G, skey, sidx, cluster,
+                                                                 w.seg_start, n_out, status);
+        EVAD_CHECK_LAUNCH();
+    } else {
+        pool_keys_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(pos, ld_pos, batch, n_cap, n_dev, G, w.k0, status);
+        EVAD_CHECK_LAUNCH();
+        int key_bits = 1;
+        while ((1ll << key_bits) <= kb) key_bits++;         // keys take values 0..kb (kb = padding)
+        EVAD_TRY(evad_sort_pairs_u32(w.k0, w.v0, w.k1, w.v1, 1, n_cap, key_bits, w.sort_tmp, &skey, &sidx, st));
+        pool_flag_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(skey, n_cap, G.key_bound, w.flag);
+        EVAD_CHECK_LAUNCH();
+        EVAD_TRY(evad_exclusive_scan_u32(w.flag, w.excl, n_cap, nullptr, w.scan_tmp, st));
+        pool_relabel_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(skey, sidx, w.flag, w.excl, n_cap, G.key_bound, cluster,
+                                                             w.seg_start, n_out);
+        EVAD_CHECK_LAUNCH();
+    }
     const int qf_h = p->feat ? p->feat_c / 4 : 0;
     const size_t prw_smem = (size_t)PRW_WARPS * (PRW_WIN * 4 * qf_h + 640) * sizeof(float);
     const bool quad_ok = cx % 4 == 0 && ldx % 4 == 0 && ldo % 4 == 0 && (((uintptr_t)x | (uintptr_t)x_out) & 15) == 0 &&
