@@ -125,7 +125,9 @@ def test_layer_fused(which):
 
 
 @pytest.mark.parametrize("B,n,level,aggr", [(1, 20_000, 0, "max"), (3, 9_000, 0, "max"), (1, 50_000, 1, "max"),
-                                            (2, 6_000, 3, "mean"), (1, 300, 2, "max")])
+                                            (2, 6_000, 3, "mean"), (1, 300, 2, "max"),
+                                            # <= 4608 nodes and <= 8192 voxel keys: the single-CTA front end of pool.cu
+                                            (1, 4_608, 0, "max"), (2, 2_000, 3, "mean"), (3, 1_500, 1, "max"), (1, 1, 0, "max")])
 def test_pooling(B, n, level, aggr):
     """Pooling.forward vs the oracle: cluster ids, coarse edge_index, batch bit-exact; pos bit-exact; x max exact."""
     from eventad_b200.data import Batch
