@@ -70,15 +70,19 @@ __global__ void __launch_bounds__(AG2_WARPS * 32) spline_agg2_kernel(const int32
                                                                      const int32_t* __restrict__ n_dev,
                                                                      const float* __restrict__ x, int ldx, int cin,
                                                                      EvadPseudo P, EvadSplineMode M, float* __restrict__ A,
-                                                                     int64_t lda, uint32_t* __restrict__ status) {
+                                                                     int64_t lda, uint32_t* __restrict__ status, int tsplit) {
+    // tsplit > 1 (small inputs, where one node's tap walk IS the kernel's latency): tsplit warps share a node, warp `sub`
+    // takes the taps sub, sub + tsplit, ...; every tap is still summed by one warp in ascending edge order (same bits)
     extern __shared__ __align__(16) float ag2_rows[];         // [AG2_WARPS][AG2_EDGES][ldx]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int ntap = M.ks * M.ks;
     const int qpr = ldx >> 2;                                 // 128-bit quads per row
     float* xs = ag2_rows + (size_t)warp * AG2_EDGES * ldx;
     const int64_t nn = n_dev ? min((int64_t)*n_dev, n) : n;
-    const int64_t stride = (int64_t)gridDim.x * AG2_WARPS;
-    for (int64_t i = (int64_t)blockIdx.x * AG2_WARPS + warp; i < nn; i += stride) {
+    const int64_t gw = (int64_t)blockIdx.x * AG2_WARPS + warp;
+    const int sub = (int)(gw % tsplit);
+    const int64_t stride = (int64_t)gridDim.x * AG2_WARPS / tsplit;
+    for (int64_t i = gw / tsplit; i < nn; i += stride) {
         const int r0 = rowptr[i], r1 = rowptr[i + 1];
         float* a = A + i * lda;
         bool first = true;
@@ -102,7 +106,7 @@ __global__ void __launch_bounds__(AG2_WARPS * 32) spline_agg2_kernel(const int32
                     reinterpret_cast<float4*>(xs)[idx] = __ldg(reinterpret_cast<const float4*>(x + (int64_t)jj * ldx) + q);
             }
             __syncwarp();
-            for (int tap = 0; tap < ntap; tap++) {
+            for (int tap = sub; tap < ntap; tap += tsplit) {
                 const float wt = k[0] == tap ? w[0] : (k[1] == tap ? w[1] : (k[2] == tap ? w[2] : w[3]));
                 const bool hit = k[0] == tap || k[1] == tap || k[2] == tap || k[3] == tap;
                 unsigned mask = __ballot_sync(0xffffffffu, hit);
@@ -139,11 +143,13 @@ __global__ void __launch_bounds__(AG2_WARPS * 32) spline_agg2_kernel(const int32
             first = false;
             __syncwarp();
         }
-        const float* xi = x + i * ldx;
+        if (sub == 0) {                                       // root slot: the node's own row
+            const float* xi = x + i * ldx;
 #pragma unroll
-        for (int u = 0; u < CPL; u++) {
-            const int c = lane + 32 * u;
-            if (c < cin) a[ntap * cin + c] = xi[c];
+            for (int u = 0; u < CPL; u++) {
+                const int c = lane + 32 * u;
+                if (c < cin) a[ntap * cin + c] = xi[c];
+            }
         }
     }
 }
@@ -160,10 +166,12 @@ static int launch_agg2(const int32_t* rowptr, const int32_t* src, int64_t n, con
             return EVAD_ERR_LAUNCH;
         attr_bytes = smem;
     }
-    const int64_t want = (n + AG2_WARPS - 1) / AG2_WARPS;
-    const int64_t cap = 148 * 4;
+    const int tsplit = n <= 2400 ? 4 : 1;                     // AG2_WARPS % tsplit == 0: a node's warps share a CTA
+    const int64_t want = (n * tsplit + AG2_WARPS - 1) / AG2_WARPS;
+    const int64_t cap = 148 * 4 * tsplit;
     const int grid = (int)(want < cap ? want : cap);
-    spline_agg2_kernel<CPL><<<grid, AG2_WARPS * 32, smem, st>>>(rowptr, src, n, n_dev, x, ldx, cin, P, M, A, lda, status);
+    spline_agg2_kernel<CPL><<<grid, AG2_WARPS * 32, smem, st>>>(rowptr, src, n, n_dev, x, ldx, cin, P, M, A, lda, status,
+                                                                tsplit);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }
