@@ -548,9 +548,14 @@ __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
     const uint32_t* __restrict__ sidx, const int32_t* __restrict__ seg_start, const int32_t* __restrict__ n_out,
     const int32_t* __restrict__ rowptr_in, int in_stride, int keep_self, const int32_t* __restrict__ src_in,
     const int32_t* __restrict__ cluster, uint32_t* __restrict__ deg, const uint32_t* __restrict__ rowptr_out, int32_t* __restrict__ src_out, int64_t e_cap,
-    int32_t* __restrict__ tmp, uint8_t* __restrict__ parked, uint32_t* __restrict__ status) {
+    int32_t* __restrict__ tmp, uint8_t* __restrict__ parked, uint32_t* __restrict__ status,
+    int32_t* __restrict__ rowptr_final, int32_t* __restrict__ num_edges) {
     const int c = blockIdx.x;
     const int nc = *n_out;
+    if (FILL && threadIdx.x == 0 && c <= nc) {               // the caller's int32 row pointers and edge count
+        rowptr_final[c] = (int32_t)rowptr_out[c];
+        if (c == nc) *num_edges = (int32_t)rowptr_out[c];
+    }
     if (c >= nc) {
         if (!FILL && c == nc) deg[c] = 0;
         return;
@@ -671,15 +676,6 @@ __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
     if (!FILL && threadIdx.x == 0) deg[c] = total;
 }
 
-__global__ void pool_finish_edges_kernel(const uint32_t* __restrict__ rowptr_u, const int32_t* __restrict__ n_out,
-                                         int64_t c_cap, int32_t* __restrict__ rowptr_out,
-                                         int32_t* __restrict__ num_edges) {
-    int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int nc = *n_out;
-    if (c <= nc && c <= c_cap) rowptr_out[c] = (int32_t)rowptr_u[c];
-    if (c == nc) *num_edges = (int32_t)rowptr_u[c];
-}
-
 // ------------------------------------------------------------------------------------------------ host side
 struct PoolWs {
     uint32_t *k0, *v0, *k1, *v1, *flag, *excl, *deg, *rowptr_u, *sort_tmp, *scan_tmp;
@@ -790,15 +786,12 @@ extern "C" int evad_voxel_pool(const evad_pool_params_t* p, int64_t n_cap, const
     if (want_edges) {
         pool_edges_kernel<false><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, p->ell_stride, p->self_loop, src_in,
                                                                              cluster, w.deg, nullptr, nullptr, e_cap,
-                                                                             w.row_tmp, w.parked, status);
+                                                                             w.row_tmp, w.parked, status, nullptr, nullptr);
         EVAD_CHECK_LAUNCH();
         EVAD_TRY(evad_exclusive_scan_u32(w.deg, w.rowptr_u, c_cap + 1, nullptr, w.scan_tmp, st));
         pool_edges_kernel<true><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, p->ell_stride, p->self_loop, src_in,
                                                                             cluster, w.deg, w.rowptr_u, src_out, e_cap,
-                                                                            w.row_tmp, w.parked, status);
-        EVAD_CHECK_LAUNCH();
-        pool_finish_edges_kernel<<<evad_cdiv(c_cap + 1, 256), 256, 0, st>>>(w.rowptr_u, n_out, c_cap, rowptr_out,
-                                                                          num_edges_out);
+                                                                            w.row_tmp, w.parked, status, rowptr_out, num_edges_out);
         EVAD_CHECK_LAUNCH();
     }
     return EVAD_OK;
