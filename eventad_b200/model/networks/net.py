@@ -260,11 +260,13 @@ class Net(torch.nn.Module):
             if k >= 2:
                 outs.append(dict(x=xo, pos=r["pos"], batch=r["batch"], rowptr=r["rowptr"], src=r["src"],
                                  num_edges=r["num_edges"], two_m=two_m_of(p.transform.max), k=k))
-        return dict(outs=outs, counts=counts, status=status)
+        # counts and status side by side, gathered as the last node of the enqueued work (inside a captured graph): the
+        # caller's single device->host read needs no launch of its own
+        return dict(outs=outs, counts=counts, status=status, readback=torch.cat([counts, status.view(-1)]))
 
     def finalize_fused(self, res):
         """One device->host read (counts + status), then tight views."""
-        c = torch.cat([res["counts"], res["status"].view(-1)]).cpu().tolist()
+        c = res["readback"].cpu().tolist()
         if c[12]:
             _lib.check_status(res["status"], "fused DAGR forward")
         datas = []
