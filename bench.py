@@ -110,7 +110,7 @@ def cpu_reference_run(a, steps, warmup):
     all host threads) on one window of `a.events` events per step.  Returns (Mevents/s, ms/step, cores, sample)."""
     from eventad_b200 import synthetic
     from oracle.dagr_net import net_forward
-    from tests.util import make_backbone, make_data, net_state_dict
+    from eventad_b200.synthetic import make_backbone, make_data, net_state_dict
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     model, args = make_backbone(seed=0, use_image=True)
@@ -184,7 +184,7 @@ def run_reference(a):
 # ------------------------------------------------------------------------------------------------ our arm
 def build_runner(dev):
     from eventad_b200.engine import EventBranchRunner
-    from tests.util import make_backbone
+    from eventad_b200.synthetic import make_backbone
     model, args = make_backbone(seed=0, use_image=True)
     model.cache_luts(320, 240, args.radius)
     return EventBranchRunner(model, dev), args

@@ -148,20 +148,44 @@ def stream():
 
 
 def check_status(status: torch.Tensor, what: str = ""):
-    """Reads the device status word (synchronises) and raises on any set bit."""
+    """Reads the device status word (synchronises) and raises on any set bit.  The word is cleared before raising, so
+    one bad batch does not poison the calls that follow (kernels only ever OR bits into it)."""
     s = int(status.item())
     if s:
+        status.zero_()
         msgs = [m for b, m in STATUS_BITS.items() if s & b]
         raise RuntimeError(f"eventad_b200: {what}: " + "; ".join(msgs))
 
 
 class Workspace:
-    """Grow-only scratch buffer per device (torch-owned memory; the library never allocates)."""
+    """Grow-only scratch buffer per device (torch-owned memory; the library never allocates).  A buffer handed out while
+    a CUDA graph was being captured is baked into that graph: it is kept alive in `pinned` and never handed to anyone
+    else's growth path (`Scratch` gives every captured graph its own Workspace objects in the first place)."""
 
     def __init__(self):
         self.buf = None
+        self.pinned = []
 
     def get(self, nbytes: int, device) -> torch.Tensor:
         if self.buf is None or self.buf.numel() < nbytes or self.buf.device != torch.device(device):
             self.buf = torch.empty(int(nbytes * 1.25) + 1024, dtype=torch.uint8, device=device)
+        if torch.cuda.is_available() and torch.cuda.is_current_stream_capturing() and \
+                not any(b is self.buf for b in self.pinned):
+            self.pinned.append(self.buf)                     # a replaced buffer stays alive as long as the graph may replay
         return self.buf
+
+
+class Scratch:
+    """Private scratch of one owner (e.g. one captured CUDA graph): the graph builder's workspace, the per-op workspaces
+    and the device status word.  engine.GraphedForward holds one, so that neither a later, larger eager call nor a
+    second captured graph on the same Net can free or share memory whose address a graph has baked in."""
+
+    def __init__(self):
+        self.graph_ws = Workspace()
+        self.ops_ws = {}
+        self._status = None
+
+    def status(self, device):
+        if self._status is None or self._status.device != torch.device(device):
+            self._status = torch.zeros(1, dtype=torch.int32, device=device)
+        return self._status

@@ -91,11 +91,13 @@ class GraphedForward:
         self.graph = None
         self.res = None
         self._ops = ops
+        from . import _lib
+        self.scratch = _lib.Scratch()                    # workspaces + status word owned by this captured graph
 
     def _enqueue(self):
         w, h, tw, b = self.meta
         f = [self._ops.to_channel_last(t) for t in self.feats] if self.feats is not None else None
-        return self.net.enqueue_fused(self.x, self.pos, self.batch, b, f, w, h, tw)
+        return self.net.enqueue_fused(self.x, self.pos, self.batch, b, f, w, h, tw, scratch=self.scratch)
 
     def load(self, data, feats):
         self.x.copy_(data.x.view(-1, 1), non_blocking=True)

@@ -3,10 +3,10 @@
 conv + folded BatchNorm + ReLU, and conv + BatchNorm + (Linear + BatchNorm skip) + ReLU, each one or two launches."""
 import torch
 
-from ... import ops
+from ... import _lib, ops
 from ..utils import shallow_copy
 from .components import BatchNormData, Linear
-from .spline_conv import MySplineConv, get_csr
+from .spline_conv import MySplineConv, get_csr, no_backward_guard
 
 
 def _fold(bn_data, conv_bias=None):
@@ -108,6 +108,7 @@ class Layer(torch.nn.Module):
             return self.conv_block2(data, data_skip)
         x = data.x.float()
         n = x.shape[0]
+        no_backward_guard(self, x)
         status = ops.new_status(x.device)
         if data.edge_index.numel() > 0:
             csr = get_csr(data)
@@ -117,5 +118,7 @@ class Layer(torch.nn.Module):
             rowptr = torch.zeros(n + 1, dtype=torch.int32, device=x.device)
             src = torch.zeros(1, dtype=torch.int32, device=x.device)
             pseudo = dict(edge_attr=torch.zeros((1, 2), device=x.device), eid=None)
-        data.x = self.run_fused(x, rowptr, src, n, None, pseudo, status)[:n]
+        out = self.run_fused(x, rowptr, src, n, None, pseudo, status)
+        _lib.check_status(status, "Layer.forward")
+        data.x = out[:n]
         return data

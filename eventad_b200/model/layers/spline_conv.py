@@ -34,6 +34,14 @@ class _PyGLinear(torch.nn.Module):
         return torch.nn.functional.linear(x, self.weight)
 
 
+def no_backward_guard(module, x):
+    """The kernels are forward-only (EventAD keeps DAGR frozen, /root/reference/models/EventAD.py:149-150).  Asking for
+    gradients through them would silently train nothing, so it is an error."""
+    if torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in module.parameters())):
+        raise RuntimeError("eventad_b200: the DAGR event-branch kernels have no backward; run them under torch.no_grad() "
+                           "or freeze the module (requires_grad_(False)) as EventADModel does")
+
+
 def get_csr(data):
     """dst-major CSR of data.edge_index, cached on the Data object (built by evad_coo_to_csr when missing)."""
     c = getattr(data, "_csr", None)
@@ -252,6 +260,7 @@ class MySplineConv(torch.nn.Module):
     def forward(self, data):
         x = data.x.float()
         n = x.shape[0]
+        no_backward_guard(self, x)
         status = ops.new_status(x.device)
         if data.edge_index.numel() > 0:
             csr = get_csr(data)
@@ -264,6 +273,8 @@ class MySplineConv(torch.nn.Module):
             pseudo = dict(edge_attr=torch.zeros((1, 2), device=x.device), eid=None)
         epi = dict(shift=self.bias.detach().float() if self.bias is not None else None)
         out, _ = self.run(x, rowptr, src, n, None, pseudo, epi, status)
+        from ... import _lib
+        _lib.check_status(status, "MySplineConv.forward")    # e.g. a LUT offset outside its table: raise, do not clamp silently
         data.x = out[:n]
         return data
 

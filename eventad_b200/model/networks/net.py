@@ -156,13 +156,20 @@ class Net(torch.nn.Module):
             image_feat, image_outputs = self.net(data.image)
         if hasattr(data, 'reset'):
             reset = data.reset
-        if self.fused and not self.training and reset:
+        if self.fused and not self.training and reset and self.fused_supported():
             output = self.forward_fused(data, image_feat)
         else:
             output = self.forward_modules(data, image_feat, reset)
         if self.use_image:
             return output[-self.num_scales:], (image_outputs[-self.num_scales:] if image_outputs is not None else None)
         return output[-self.num_scales:]
+
+    def fused_supported(self):
+        """The fused pipeline implements the configuration EventAD runs (pooling.py defaults).  Pooling options it does
+        not implement (`keep_temporal_ordering` edge filter pooling.py:69-72, `self_loop`, a pooling BatchNorm, no
+        transform) take the module-by-module path, which implements all of them."""
+        return all(not p.keep_temporal_ordering and not p.self_loop and p.bn is None and p.transform is not None
+                   for p in (self.pool1, self.pool2, self.pool3, self.pool4))
 
     def forward_modules(self, data, image_feat, reset=True):
         """Module-by-module composition, line by line net.py:113-197."""
@@ -195,16 +202,31 @@ class Net(torch.nn.Module):
         return [out3, out4]
 
     # ------------------------------------------------------------------------------------------------ fused
-    def enqueue_fused(self, x, pos, batch_i32, num_graphs, feats_nhwc, width, height, time_window):
+    def enqueue_fused(self, x, pos, batch_i32, num_graphs, feats_nhwc, width, height, time_window, scratch=None):
         """Enqueues the whole event branch; returns device tensors sized by host-known upper bounds plus `counts`
-        (int32[12]: n1,E1,n2,E2,n3,E3,n4,E4) and `status`.  No host synchronisation; capturable in a CUDA graph."""
-        dev = pos.device
-        n = pos.shape[0]
+        (int32[12]: n1,E1,n2,E2,n3,E3,n4,E4) and `status`.  No host synchronisation; capturable in a CUDA graph.
+        `scratch` (a _lib.Scratch): private workspaces and status word of the caller (one per captured graph)."""
         g = self.events_to_graph
         if g.graph_creators is None:
             g.init_graph_creator(Data(pos=pos, width=[width], height=[height], time_window=[time_window],
                                       _num_graphs=num_graphs))
         gc = g.graph_creators
+        if gc.device is None:
+            gc.device = pos.device
+            gc.initialize(pos.shape[0], pos.device)
+        if scratch is None:
+            return self._enqueue_fused(gc, x, pos, batch_i32, num_graphs, feats_nhwc, width, height, time_window)
+        saved = (gc._ws, gc._status, ops._SCRATCH)
+        gc._ws, gc._status, ops._SCRATCH = scratch.graph_ws, scratch.status(pos.device), scratch
+        try:
+            return self._enqueue_fused(gc, x, pos, batch_i32, num_graphs, feats_nhwc, width, height, time_window)
+        finally:
+            gc._ws, gc._status, ops._SCRATCH = saved
+
+    def _enqueue_fused(self, gc, x, pos, batch_i32, num_graphs, feats_nhwc, width, height, time_window):
+        dev = pos.device
+        n = pos.shape[0]
+        gc._status.zero_()                                   # the status word of THIS forward (kernels only OR bits in)
         gc.batch_size = max(gc.batch_size, num_graphs)
         gc.reset()
         pos_int = ops.denormalize_pos(pos, width, height, time_window)

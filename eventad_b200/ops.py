@@ -11,13 +11,17 @@ from . import _lib
 from ._lib import EpilogueT, PoolParamsT, PseudoT, SplineModeT, check, ptr, ptr_rows, stream
 
 _WS = {}
+_SCRATCH = None     # a _lib.Scratch while its owner (a captured CUDA graph) enqueues work: private workspaces
 
 
 def _ws(nbytes, device):
     key = (torch.device(device).index, torch.cuda.current_stream().cuda_stream)
-    w = _WS.get(key)
+    table = _SCRATCH.ops_ws if _SCRATCH is not None else _WS
+    if _SCRATCH is not None:
+        key = key[0]
+    w = table.get(key)
     if w is None:
-        w = _WS[key] = _lib.Workspace()
+        w = table[key] = _lib.Workspace()
     return w.get(nbytes, device)
 
 

@@ -18,12 +18,19 @@ import sys
 import sysconfig
 
 REF_SRC = "/root/reference/src/dagr/graph/ev_graph.cu"
+REF_ASY_SRC = "/root/reference/src/dagr/asynchronous/asy_tools/main.cu"     # pybind module `asy_tools` (setup.py:9-12)
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT_DIR = os.path.join(HERE, "_ref")
 OUT = os.path.join(OUT_DIR, "ev_graph_cuda.so")
+OUT_ASY = os.path.join(OUT_DIR, "asy_tools.so")
 
 
-def build(force: bool = False) -> str:
+def build_asy(force: bool = False) -> str:
+    """The reference's asy_tools extension (masked_lin, masked_lin_no_bias, masked_isdiff, masked_inplace_BN), unmodified."""
+    return build(force, REF_ASY_SRC, OUT_ASY, "asy_tools")
+
+
+def build(force: bool = False, REF_SRC: str = REF_SRC, OUT: str = OUT, name: str = "ev_graph_cuda") -> str:
     if not os.path.exists(REF_SRC):
         if os.path.exists(OUT):
             return OUT
@@ -39,7 +46,7 @@ def build(force: bool = False) -> str:
     torch_lib = os.path.join(os.path.dirname(torch.__file__), "lib")
     cmd = ["nvcc", "-shared", "-Xcompiler", "-fPIC", "-O2", "-std=c++17",
            "-gencode", "arch=compute_100a,code=sm_100a",
-           "-DTORCH_EXTENSION_NAME=ev_graph_cuda", "-DTORCH_API_INCLUDE_EXTENSION_H",
+           f"-DTORCH_EXTENSION_NAME={name}", "-DTORCH_API_INCLUDE_EXTENSION_H",
            f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}",
            "-w"]
     for i in inc:
@@ -54,3 +61,4 @@ def build(force: bool = False) -> str:
 
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv))
+    print(build_asy(force="--force" in sys.argv))

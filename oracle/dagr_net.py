@@ -46,7 +46,7 @@ def events_to_graph(pos, batch, num_graphs, radius, max_neighbors, width, height
 
 
 def net_forward(sd, args, x, pos, batch, num_graphs, image_feat, width, height, time_window=1000000,
-                use_lut=True, return_intermediate=False):
+                use_lut=True, return_intermediate=False, chunk_front_by_sample=False):
     """Event branch of Net.forward (net.py:106-197).  sd: state dict with keys relative to Net.
     x [N,1] polarity, pos [N,3] normalised, batch [N] int64, image_feat: list of 5 maps [B,C,h,w] or None.
     Returns [out3, out4] namespaces (x,pos,batch,edge_index,edge_attr)."""
@@ -56,19 +56,34 @@ def net_forward(sd, args, x, pos, batch, num_graphs, image_feat, width, height, 
     effective_radius = 2 * float(int(args.radius * width + 2) / width)
     inter = {}
 
-    edge_index = events_to_graph(pos, batch, num_graphs, args.radius, args.max_neighbors, width, height, time_window)
-    inter["edge_index0"] = edge_index
-    if use_image:
-        x = torch.cat((x, L.sample_features(pos, batch, image_feat[0], width, height)), dim=1)
-    if edge_index.shape[1] > 0:
-        edge_attr = ops.cartesian(pos, edge_index, effective_radius)
-    else:
-        edge_attr = torch.zeros((0, 3), dtype=x.dtype)
-    edge_attr = torch.clamp(edge_attr, min=0, max=1)
-    x = torch.cat((x, pos[:, :2]), dim=1)
-
     lut = L.lut_params_layer1(args.radius, width) if use_lut else None
-    x = L.layer(x, edge_index, edge_attr, sd, "conv_block1.", lut, height, width)
+
+    def front(x_, pos_, batch_, graph_batch, n_graphs):
+        """graph + CNN sampling + Cartesian + Layer 1 (net.py:113-124) on a set of whole samples."""
+        ei = events_to_graph(pos_, graph_batch, n_graphs, args.radius, args.max_neighbors, width, height, time_window)
+        if use_image:
+            x_ = torch.cat((x_, L.sample_features(pos_, batch_, image_feat[0], width, height)), dim=1)
+        ea = ops.cartesian(pos_, ei, effective_radius) if ei.shape[1] > 0 else torch.zeros((0, 3), dtype=x_.dtype)
+        ea = torch.clamp(ea, min=0, max=1)
+        x_ = torch.cat((x_, pos_[:, :2]), dim=1)
+        return ei, ea, L.layer(x_, ei, ea, sd, "conv_block1.", lut, height, width)
+
+    if chunk_front_by_sample and num_graphs > 1:
+        # Everything up to pool 1 is independent per sample (graph, sampling and convolution only see a sample's own
+        # events; sampling reads the sample's batch index, which is kept), so the samples are processed one at a time:
+        # same numbers, bounded memory at the 64 x 100k bench batch.
+        eis, xs, off = [], [], 0
+        for b in range(num_graphs):
+            m = batch == b
+            nb = int(m.sum())
+            ei, ea, xb = front(x[m], pos[m], batch[m], torch.zeros(nb, dtype=batch.dtype), 1)
+            eis.append(ei + off); xs.append(xb)           # the fine edge_attr is not read after layer 1
+            off += nb
+        assert bool((batch[1:] >= batch[:-1]).all()), "samples must be concatenated sample-major"
+        edge_index, edge_attr, x = torch.cat(eis, 1), torch.zeros((0, 3), dtype=x.dtype), torch.cat(xs, 0)
+    else:
+        edge_index, edge_attr, x = front(x, pos, batch, batch, num_graphs)
+    inter["edge_index0"] = edge_index
     inter["x_layer1"] = x
 
     pool_cart_max = [2 * effective_radius, max_vals[1], max_vals[2], max_vals[3]]
@@ -82,7 +97,8 @@ def net_forward(sd, args, x, pos, batch, num_graphs, image_feat, width, height, 
         voxel3 = poolings[k]
         if cur.x.shape[0] > 0:
             cur = L.pooling(cur.x, cur.pos, cur.batch, cur.edge_index, voxel3, width, height, args.batch_size,
-                            pool_cart_max[k], pool_aggr[k])
+                            pool_cart_max[k], pool_aggr[k],
+                            keep_temporal_ordering=getattr(args, "keep_temporal_ordering", False))
         inter[f"pool{k + 1}"] = cur
         lut = L.lut_params_from_pool(torch.cat([voxel3, torch.Tensor([1])]), pool_cart_max[k], height, width) \
             if use_lut else None

@@ -26,6 +26,28 @@ def build(force: bool = False) -> str:
     return _LIB_PATH
 
 
+_asy = None
+
+
+def asy_lib():
+    """oracle/asy_oracle.c (CPU restatement of the reference's asy_tools kernels)."""
+    global _asy
+    if _asy is None:
+        build()
+        path = os.path.join(_HERE, "_build", "libasy_oracle.so")
+        if not os.path.exists(path) or os.path.getmtime(path) < os.path.getmtime(os.path.join(_HERE, "asy_oracle.c")):
+            env = dict(os.environ)
+            env.pop("CC", None)
+            subprocess.check_call(["make", "-s", "-C", _HERE], env=env)
+        A = ctypes.CDLL(path)
+        p, i64, i, f = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_float
+        A.asyo_masked_isdiff.argtypes = [p, p, p, i64, i, f, f]
+        A.asyo_masked_inplace_bn.argtypes = [p, p, p, p, p, p, p, i64, i, f]
+        A.asyo_masked_lin.argtypes = [p, p, p, p, p, i64, i, i, i]
+        _asy = A
+    return _asy
+
+
 def lib():
     global _lib
     if _lib is None:

@@ -218,6 +218,83 @@ int64_t evgo_forward(evgo_t *g, const int32_t *batch, const int32_t *pos, int64_
     return E;
 }
 
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Kernel-level entry points with the pybind signatures of ev_graph.cu:279-283, on caller-owned CPU arrays.
+ * oracle/ref_py.py installs them as a CPU stand-in for the `ev_graph_cuda` module, so that the reference's OWN
+ * Python glue (graph/utils.py:6-23, graph/ev_graph.py:18-166) runs unmodified above them.
+ * ------------------------------------------------------------------------------------------------------------ */
+static void fifo_insert_q(int32_t *queue, int W, int H, int Q, int b, int y, int x, const int32_t *sorted_idx,
+                          int64_t offset, int counts) {
+    for (int q = Q - 1; q >= 0; q--) {                          /* ev_graph.cu:196-211 */
+        int64_t index = (int64_t)b * H * W * Q + (int64_t)q * H * W + (int64_t)y * W + x;
+        if (q >= counts) {
+            int64_t shifted = (int64_t)b * H * W * Q + (int64_t)(q - counts) * H * W + (int64_t)y * W + x;
+            queue[index] = queue[shifted];
+        } else {
+            queue[index] = sorted_idx[offset + counts - 1 - q];
+        }
+    }
+}
+
+/* insert_in_queue_cuda (ev_graph.cu:169-212, launcher :241-276): one "thread" per active pixel */
+void evgo_k_insert(int32_t *queue, int B, int Q, int H, int W, const int32_t *sorted_idx, const int32_t *unique_coords,
+                   const int32_t *cumsum_counts, int64_t n_runs) {
+    (void)B;
+    #pragma omp parallel for schedule(static)
+    for (int64_t r = 0; r < n_runs; r++) {
+        int32_t c = unique_coords[r];
+        int x = c % W;
+        int y = ((c - x) / W) % H;
+        int b = c / (W * H);
+        int64_t off = r > 0 ? cumsum_counts[r - 1] : 0;
+        int counts = (int)(cumsum_counts[r] - off);
+        fifo_insert_q(queue, W, H, Q, b, y, x, sorted_idx, off, counts);
+    }
+}
+
+/* insert_in_queue_single_cuda (ev_graph.cu:130-166): exactly one event, batch index forced to 0 */
+void evgo_k_insert_single(int32_t *queue, int Q, int H, int W, const int32_t *indices, const int32_t *events) {
+    fifo_insert_q(queue, W, H, Q, 0, events[1], events[0], indices, 0, 1);
+}
+
+/* fill_edges_cuda (ev_graph.cu:15-80, launcher :82-128): writes (src,dst) into slot e*K+num of edges[2][cap] */
+void evgo_k_fill_edges(const int32_t *batch, const int32_t *pos, const int32_t *all_ts, const int32_t *queue,
+                       const int32_t *indices, int64_t n, int Q, int H, int W, int max_nb, float radius,
+                       float delta_t_us, int64_t *edges, int64_t cap, int min_index) {
+    const int radius_int = (int)radius;
+    const int n_spiral = (2 * radius_int + 1) * (2 * radius_int + 1);
+    #pragma omp parallel for schedule(dynamic, 256)
+    for (int64_t e = 0; e < n; e++) {
+        int num = 0;
+        int64_t off = e * max_nb;
+        int b = batch[e], x = pos[3 * e], y = pos[3 * e + 1], ts = pos[3 * e + 2];
+        edges[off] = indices[e] - min_index;
+        edges[cap + off] = indices[e] - min_index;
+        num++;
+        spiral_t sp; spiral_init(&sp);
+        for (int i = 0; i < n_spiral; i++) {
+            if (num >= max_nb) break;
+            for (int q = 0; q < Q; q++) {
+                int xn = x + sp.x, yn = y + sp.y;
+                if (!(xn >= 0 && yn >= 0 && xn < W && yn < H)) break;
+                int64_t qi = (int64_t)xn + (int64_t)W * yn + (int64_t)H * W * q + (int64_t)H * W * Q * b;
+                int idx = queue[qi];
+                if (idx < min_index) break;
+                if (indices[e] > idx) {
+                    int32_t dt = ts - all_ts[idx - min_index];
+                    if ((float)dt > delta_t_us) continue;
+                    edges[off + num] = idx - min_index;
+                    edges[cap + off + num] = indices[e] - min_index;
+                    num++;
+                    if (num >= max_nb) break;
+                }
+            }
+            spiral_next(&sp);
+        }
+    }
+}
+
 /* first `count` spiral offsets, for tests of the ordering (spiral.h) */
 void evgo_spiral(int count, int32_t *dx, int32_t *dy) {
     spiral_t sp; spiral_init(&sp);

@@ -10,6 +10,7 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    config.addinivalue_line("markers", "slow: minutes of CPU oracle work at BASELINE.json's full sizes (still part of -m gpu)")
 
 
 def pytest_collection_modifyitems(config, items):
@@ -20,3 +21,11 @@ def pytest_collection_modifyitems(config, items):
     for item in items:
         if "gpu" in item.keywords:
             item.add_marker(skip)
+
+
+@pytest.fixture(autouse=True)
+def _inference_mode():
+    """The path is forward-only (DAGR is frozen in EventAD); the kernels refuse to run where autograd expects a backward."""
+    import torch
+    with torch.no_grad():
+        yield

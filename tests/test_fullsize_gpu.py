@@ -110,3 +110,28 @@ def test_bench_batch_window_independence():
             assert int(ma.sum()) == int(mb.sum())
             assert torch.equal(a.pos[ma], b.pos[mb])
             assert_close(a.x[ma], b.x[mb], what=f"window {w}")
+
+
+@pytest.mark.slow
+@pytest.mark.parametrize("dist", ["U", "C"])
+def test_bench_batch_matches_oracle(dist):
+    """The batch `bench.py` times (64 windows x 100k events, `synthetic.make_batch(100_000, 64, seed=1000*rank+s)`, rank 0,
+    s 0) through the whole fused branch against the CPU oracle on the same batch: out3 / out4 structure bit-exact,
+    features rtol 1e-4 / atol 1e-5.  The oracle walks the per-sample front end (graph, layer 1) one window at a time
+    (tests/test_oracle_cpu.py::test_chunked_front_equals_unchunked), ~2 s of CPU per window."""
+    from oracle.dagr_net import net_forward
+    B, n = 64, 100_000
+    model, args = make_backbone(seed=0, use_image=True)
+    model.cache_luts(W, H, args.radius)
+    sd = net_state_dict(model)
+    d = make_data(n, B, seed=0, dist=dist)
+    feats = synthetic.make_image_features(B, seed=0)
+    ref = net_forward(sd, args, d.x, d.pos, d.batch, B, feats, W, H, chunk_front_by_sample=True)
+    net = model.cuda().backbone
+    with torch.no_grad():
+        outs = net(make_data(n, B, seed=0, dist=dist, device="cuda"), image_feat=[f.cuda() for f in feats])[0]
+    for o, r, name in zip(outs, ref, ("out3", "out4")):
+        assert torch.equal(o.batch.cpu(), r.batch), name
+        assert torch.equal(o.edge_index.cpu(), r.edge_index), name
+        assert torch.equal(o.pos.cpu(), r.pos), name
+        assert_close(o.x, r.x, what=f"bench batch {dist} {name} x")

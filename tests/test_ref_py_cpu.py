@@ -1,0 +1,143 @@
+"""The torch-CPU oracle (oracle/dagr_layers.py, dagr_net.py) against THE REFERENCE'S OWN PYTHON.
+
+tests/golden/ref_py_*.npz are outputs of /root/reference/src/dagr executed unmodified on the CPU (oracle/ref_py.py;
+generator tests/golden/make_ref_py_golden.py).  Where the reference tree is mounted (the build container) the reference
+is also run live, and the stand-ins it runs on are cross-checked against the reference's independent restatements in
+src/dagr/asynchronous."""
+import glob
+import hashlib
+import importlib.util
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import dagr_ops, ref_py
+from oracle.dagr_net import net_forward
+from eventad_b200.synthetic import net_state_dict
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+spec = importlib.util.spec_from_file_location("make_ref_py_golden", os.path.join(HERE, "golden", "make_ref_py_golden.py"))
+gold = importlib.util.module_from_spec(spec)
+spec.loader.exec_module(gold)
+CASES = {c[0]: c for c in gold.CASES}
+needs_ref = pytest.mark.skipif(not ref_py.available(), reason="/root/reference is only mounted in the build container")
+
+
+def _oracle(case):
+    name, W, H, n, B, dist, mseed, dseed, use_image, luts, over = case
+    model, args, d, feats = gold.case_inputs(case)
+    sha = gold.sd_sha({k: v for k, v in model.state_dict().items()})
+    outs, inter = net_forward(net_state_dict(model), args, d.x, d.pos, d.batch, B, feats, W, H, use_lut=luts,
+                              return_intermediate=True)
+    return outs, inter, sha
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_oracle_matches_reference_python_golden(name):
+    z = np.load(os.path.join(HERE, "golden", f"ref_py_{name}.npz"))
+    outs, inter, sha = _oracle(CASES[name])
+    assert sha == str(z["sd_sha"]), "seeded weights differ from the ones the golden file was generated with"
+    e0 = inter["edge_index0"]
+    assert e0.shape[1] == int(z["n_edges0"])
+    assert hashlib.sha256(np.ascontiguousarray(e0.numpy().astype(np.int64)).tobytes()).hexdigest() == str(z["edges0_sha"])
+    stride = int(z["x1_stride"])
+    assert np.array_equal(inter["x_layer1"][::stride].numpy(), z["x1_sample"])            # same fp32 op order: exact
+    for k in range(1, 5):
+        p = inter[f"pool{k}"]
+        assert np.array_equal(p.pos.numpy(), z[f"pool{k}_pos"]), (name, k)
+        assert np.array_equal(p.batch.numpy(), z[f"pool{k}_batch"]), (name, k)
+        assert np.array_equal(p.edge_index.numpy(), z[f"pool{k}_edge_index"]), (name, k)
+        if f"pool{k}_x" in z:
+            assert np.array_equal(p.x.numpy(), z[f"pool{k}_x"]), (name, k)
+    for nm, o in zip(("out3", "out4"), outs):
+        assert np.array_equal(o.edge_index.numpy(), z[f"{nm}_edge_index"]), (name, nm)
+        assert np.array_equal(o.batch.numpy(), z[f"{nm}_batch"]), (name, nm)
+        assert np.array_equal(o.pos.numpy(), z[f"{nm}_pos"]), (name, nm)
+        assert np.array_equal(o.edge_attr.numpy(), z[f"{nm}_edge_attr"]), (name, nm)
+        np.testing.assert_allclose(o.x.numpy(), z[f"{nm}_x"], rtol=1e-6, atol=1e-7)
+
+
+@needs_ref
+@pytest.mark.parametrize("name", ["s_c2500_b3", "s_c3000_b2_kto", "s_c3000_b1_basis"])
+def test_reference_python_live_reproduces_golden(name):
+    """The committed fixtures are what the reference's text produces today (guards against a stale golden file)."""
+    case = CASES[name]
+    _, W, H, n, B, dist, mseed, dseed, use_image, luts, over = case
+    model, args, d, feats = gold.case_inputs(case)
+    ref = ref_py.build_dagr(args, H, W, {k: v.detach().clone() for k, v in model.state_dict().items()}, cache_luts=luts)
+    outs = ref_py.run_backbone(ref, d, feats)
+    z = np.load(os.path.join(HERE, "golden", f"ref_py_{name}.npz"))
+    for nm, o in zip(("out3", "out4"), outs):
+        assert np.array_equal(o.x.numpy(), z[f"{nm}_x"]) and np.array_equal(o.edge_index.numpy(), z[f"{nm}_edge_index"])
+
+
+@needs_ref
+def test_state_dict_loads_strictly_into_reference_net():
+    """`backbone.*` keys and shapes of our DAGR == the reference's Net: strict load, both directions."""
+    from eventad_b200.synthetic import make_backbone
+    model, args = make_backbone(seed=0, use_image=True, height=48, width=64)
+    ref = ref_py.build_dagr(args, 48, 64, None, cache_luts=False)
+    ours = {k: v for k, v in model.state_dict().items() if k.startswith("backbone.")}
+    theirs = {"backbone." + k: v for k, v in ref.backbone.state_dict().items()}
+    assert set(ours) == set(theirs)
+    assert all(ours[k].shape == theirs[k].shape and ours[k].dtype == theirs[k].dtype for k in ours)
+    model.backbone.load_state_dict(ref.backbone.state_dict(), strict=True)
+
+
+@needs_ref
+def test_standins_agree_with_reference_async_restatements():
+    """src/dagr/asynchronous restates T.Cartesian, the voxel index and the coarse-edge rule
+    independently of PyG / torch_cluster; the stand-ins must agree with those statements of intent."""
+    ref_py.install()
+    import dagr.asynchronous.cartesian as acart
+    import dagr.asynchronous.max_pool as amp
+    from dagr.model.layers.pooling import Pooling
+    import torch_geometric.transforms as T
+    g = torch.Generator().manual_seed(0)
+    pos = torch.rand((500, 3), generator=g)
+    ei = torch.randint(0, 500, (2, 4000), generator=g)
+    edge_attr = getattr(acart, "__edge_attr")
+    a_ref = edge_attr(pos, ei, True, 0.0625)
+    assert torch.equal(a_ref, dagr_ops.cartesian(pos, ei, 0.0625))
+    tr = T.Cartesian(norm=True, cat=False, max_value=0.0625)
+    assert torch.equal(amp.compute_attrs(tr, ei, pos), a_ref)
+    # voxel index: the async code computes x_v + grid_x * y_v from (pos / voxel).long(); grid_cluster's first two
+    # terms must be the same numbers (t < 1, batch 0 -> the remaining terms vanish)
+    vox = torch.tensor([1 / 56.0, 1 / 40.0, 1.0])
+    pool = Pooling(vox, width=320, height=240, batch_size=6, transform=tr)
+    pos_px = torch.stack([torch.randint(0, 320, (2000,), generator=g) / 320.0,
+                          torch.randint(0, 240, (2000,), generator=g) / 240.0,
+                          torch.rand(2000, generator=g) * 0.99], 1)
+    idx_async = getattr(amp, "__get_global_cluster_index")(pool, pos_px)
+    pos4 = torch.cat([pos_px, torch.zeros(2000, 1)], -1)
+    idx_gc = dagr_ops.grid_cluster(pos4, pool.voxel_size, pool.start, pool.end)
+    assert torch.equal(idx_async, idx_gc)
+    # coarse edges: remap, drop self loops, lexicographic unique
+    cl = torch.randint(0, 40, (500,), generator=g)
+    e_ref = amp.pool_edge(cl, ei, False)
+    e = cl[ei]
+    e = e[:, e[0] != e[1]].unique(dim=-1)
+    assert torch.equal(e_ref, e)
+
+
+@needs_ref
+def test_format_data_and_denormalize_reference_text():
+    """utils/buffers.py:33-44 and ev_tgn.py:11-16 executed from the reference tree vs the oracle's statements."""
+    ref_py.install()
+    from dagr.utils.buffers import format_data
+    from dagr.model.layers.ev_tgn import denormalize_pos
+    from eventad_b200 import synthetic
+    from eventad_b200.data import Batch
+    from oracle.dagr_net import denormalize_pos as oracle_denorm
+    raw = synthetic.make_batch(5000, 2, seed=9, dist="C")
+    d = Batch(x=torch.from_numpy(raw["x"]), pos=torch.from_numpy(raw["pos"]), batch=torch.from_numpy(raw["batch"]))
+    d.t = torch.from_numpy(raw["t"])
+    d.width, d.height, d.time_window = torch.tensor([320, 320]), torch.tensor([240, 240]), torch.tensor([1000000, 1000000])
+    f = format_data(d)
+    mine = synthetic.make_data(5000, 2, seed=9, dist="C")
+    assert torch.equal(f.pos, mine.pos) and torch.equal(f.x, mine.x)
+    pi = denormalize_pos(f)
+    assert torch.equal(pi, oracle_denorm(mine.pos, 320, 240, 1000000))
+    assert torch.equal(pi[:, :2].short(), torch.from_numpy(raw["pos"])) and torch.equal(pi[:, 2], torch.from_numpy(raw["t"]))

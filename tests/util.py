@@ -7,46 +7,7 @@ from eventad_b200.config import default_args
 from eventad_b200.data import Batch
 
 
-def randomize_bn(module, seed=0):
-    """BN running stats / affine away from identity so that eval BatchNorm is a real transform."""
-    g = torch.Generator().manual_seed(seed)
-    for m in module.modules():
-        if isinstance(m, torch.nn.BatchNorm1d):
-            m.running_mean.copy_(torch.randn(m.num_features, generator=g) * 0.1)
-            m.running_var.copy_(torch.rand(m.num_features, generator=g) + 0.5)
-            m.weight.data.copy_(torch.rand(m.num_features, generator=g) + 0.5)
-            m.bias.data.copy_(torch.randn(m.num_features, generator=g) * 0.1)
-
-
-def make_backbone(seed=0, use_image=True, height=240, width=320, **over):
-    from eventad_b200.model.networks.dagr import DAGR
-    torch.manual_seed(seed)
-    args = default_args(use_image=use_image, **over)
-    model = DAGR(args, height, width)
-    randomize_bn(model.backbone, seed)
-    model.eval()
-    return model, args
-
-
-def net_state_dict(model):
-    """state dict with keys relative to Net (what oracle/dagr_net.py reads), on the CPU."""
-    return {k[len("backbone."):]: v.detach().cpu().clone() for k, v in model.state_dict().items()
-            if k.startswith("backbone.") and not k.startswith("backbone.net.")}
-
-
-def make_data(n_events, batch_size=1, seed=0, dist="U", width=320, height=240, device="cpu"):
-    """Formatted input (after format_data): x [N,1] f32, pos [N,3] f32 normalised, batch int64."""
-    raw = synthetic.make_batch(n_events, batch_size, seed=seed, dist=dist, width=width, height=height)
-    pos = torch.from_numpy(raw["pos"].astype(np.float32))
-    t = torch.from_numpy(raw["t"].astype(np.float32)).view(-1, 1)
-    normalizer = torch.tensor([raw["width"], raw["height"], raw["time_window"]])
-    d = Batch(x=torch.from_numpy(raw["x"].astype(np.float32)), pos=torch.cat([pos, t], -1) / normalizer,
-              batch=torch.from_numpy(raw["batch"]))
-    d.num_graphs = batch_size
-    d.width = torch.tensor([width] * batch_size)
-    d.height = torch.tensor([height] * batch_size)
-    d.time_window = torch.tensor([raw["time_window"]] * batch_size)
-    return d.to(device) if device != "cpu" else d
+from eventad_b200.synthetic import make_backbone, make_data, net_state_dict, randomize_bn  # noqa: E402,F401
 
 
 def assert_close(a, b, rtol=1e-4, atol=1e-5, what=""):
