@@ -85,3 +85,41 @@ def test_ev_tgn_reset_false_after_fused_forward():
         p = (torch.tensor([320, 240, 1000000]) * dd.pos.cpu() + 1e-3).int().numpy()
         eo = o.forward(dd.batch.cpu().int().numpy(), p, delete_nodes=False)
     assert np.array_equal(out.edge_index.cpu().numpy(), eo)
+
+
+@pytest.mark.parametrize("dist", ["U", "C"])
+def test_streaming_at_baseline_config5_size(dist):
+    """BASELINE configs[4]: 320x240, 10^6 resident events (clustered: > Q = 128 events on single pixels, the FIFO cap is
+    live), then micro-batches of 1, 10, 10^2, 10^3, 10^4 events with delete_nodes=True (sliding window), bit-exact against
+    the C oracle AND against the unmodified reference kernels (oracle/_ref/ev_graph_cuda.so) on every micro-batch
+    (reference: ev_graph.py:75-103,121-136, ev_graph.cu:15-80,130-212)."""
+    from eventad_b200.graph.ev_graph import SlidingWindowGraph
+    from oracle.evg import OracleSlidingWindowGraph
+    from tests.util import RefGraph, load_ref_graph_module
+    W, H, N0 = 320, 240, 1_000_000
+    sizes = [1, 10, 100, 1000, 10_000, 1, 10, 100, 1000]
+    total = N0 + sum(sizes)
+    batch, pos = _mk(total, 1, W, H, dist=dist, seed=21)          # one time-sorted stream of `total` events
+    kw = dict(width=W, height=H, batch_size=1, max_num_neighbors=16, max_queue_size=128, radius=4, delta_t_us=10000)
+    g, o = SlidingWindowGraph(**kw), OracleSlidingWindowGraph(**kw)
+    m = load_ref_graph_module()
+    ref = RefGraph(m, W, H, 1, 16, 128, 4, 10000) if m is not None else None
+    cuts = np.cumsum([0, N0] + sizes)
+    if dist == "C":
+        px = pos[:N0, 0].astype(np.int64) + W * pos[:N0, 1].astype(np.int64)
+        assert np.bincount(px).max() > 128
+    for i, (a, b) in enumerate(zip(cuts[:-1], cuts[1:])):
+        bt, pt = torch.from_numpy(batch[a:b]).cuda(), torch.from_numpy(pos[a:b]).cuda()
+        n_delete = (b - a) if i > 0 else 0
+        r = g.forward(bt, pt, delete_nodes=True, return_node_counts=True)
+        ro = o.forward(batch[a:b], pos[a:b], delete_nodes=True, return_node_counts=True)
+        assert np.array_equal(r[0].cpu().numpy(), ro[0]), (dist, a, b)
+        if i > 0:
+            assert np.array_equal(r[1].cpu().numpy(), ro[1]), (dist, a, b)       # edges that left the window
+        assert r[2] == ro[2] and g.min_index == o.min_index and g.max_index == o.max_index
+        if ref is not None:
+            er = ref.forward(bt, pt)
+            assert torch.equal(er, r[0]), ("reference kernel", dist, a, b)
+            ref.delete_nodes(n_delete)
+    assert np.array_equal(g.edges.cpu().numpy(), o.edges)
+    assert m is not None, "oracle/_ref/ev_graph_cuda.so missing: the reference-kernel half of this test did not run"

@@ -70,3 +70,8 @@ class RefGraph:
         self.m.fill_edges_cuda(batch, pos, self.all_ts.contiguous(), self.queue, indices, self.K, self.r, self.dt,
                                edges, self.min_index)
         return edges[:, edges[1] >= 0]
+
+    def delete_nodes(self, n):
+        """SlidingWindowGraph.delete_nodes bookkeeping the kernels see (ev_graph.py:121-125)."""
+        self.all_ts = self.all_ts[n:]
+        self.min_index += n
