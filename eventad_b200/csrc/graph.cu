@@ -34,7 +34,7 @@ __global__ void __launch_bounds__(256) g_keys_kernel(const int32_t* __restrict__
 // cell_start[c] = first sorted position whose key >= c  (c = 0..ncells), plus sorted-order timestamps.
 __global__ void __launch_bounds__(256) g_cells_kernel(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ sidx,
                                                       const int32_t* __restrict__ pos, int64_t n, int64_t ncells,
-                                                      int32_t* __restrict__ cell_start, int2* __restrict__ rec,
+                                                      int32_t* __restrict__ cell_start, int32_t* __restrict__ st,
                                                       int32_t* __restrict__ cell_perm) {
     int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t <= ncells) {
@@ -47,150 +47,22 @@ __global__ void __launch_bounds__(256) g_cells_kernel(const uint32_t* __restrict
     }
     if (t < n) {
         uint32_t i = sidx[t];
-        rec[t] = make_int2((int)i, pos[3 * (int64_t)i + 2]);  // (event index, timestamp): one 64-bit load per candidate
+        st[t] = pos[3 * (int64_t)i + 2];
         if (cell_perm) cell_perm[t] = (int32_t)i;
     }
 }
 
-// Warp-cooperative spiral search: one warp per destination event, the (2r+1)^2 spiral cells spread over the LANES
-// (cell s = 32 * round + lane; 81 cells = 3 rounds) instead of over loop iterations of one thread.  Per round every lane
-// loads its cell's bucket bounds, applies the FIFO cap (newest Q entries of the pixel), walks its bucket newest-first
-// counting the candidates that pass the causal filter (index < own index; later events occupy FIFO slots but are
-// skipped, ev_graph.cu:64) and the time gate (`continue`, not `break`, ev_graph.cu:69); a warp prefix sum IN SPIRAL
-// ORDER (= lane order) assigns the output slots, lanes write until slot K, and the walk ends with the round in which the
-// running total reaches K -- the same edges in the same order as the serial walk of ev_graph.cu:49-78.
-// Events are taken in pixel-sorted order, 32 consecutive ones per warp, so the bucket bounds and candidate records of
-// neighbouring events are L1 hits; the 32 bucket lookups of a round are in flight together.
-#define GS_WARPS 8                    // warps per CTA; each warp owns 32 consecutive sorted events
-#define GS_MAXR 12                    // rounds supported: (2r+1)^2 <= 384 (r <= 9); larger radii take the serial kernel
-
-__global__ void __launch_bounds__(GS_WARPS * 32) g_search_warp_kernel(
-    const uint32_t* __restrict__ skey, const int2* __restrict__ rec, const int32_t* __restrict__ cell_start, int64_t n,
-    int H, int W, int radius, float delta_t, int Q, int K, int32_t* __restrict__ nbr /*[n][K]*/,
-    uint8_t* __restrict__ nbr_cls /*[n][K] or null*/, uint32_t* __restrict__ count /*[n]*/) {
-    // spiral walk of spiral.h:1-15 (layer starts at 1, leg 0), tabulated once per CTA
-    extern __shared__ int8_t g_spiral[];                      // [nsp] dx, then [nsp] dy
-    const int side = 2 * radius + 1;
-    const int nsp = side * side;
-    if (threadIdx.x == 0) {
-        int sx = 0, sy = 0, layer = 1, leg = 0;
-        for (int s = 0; s < nsp; s++) {
-            g_spiral[s] = (int8_t)sx;
-            g_spiral[nsp + s] = (int8_t)sy;
-            switch (leg) {
-            case 0: ++sx; if (sx == layer) ++leg; break;
-            case 1: ++sy; if (sy == layer) ++leg; break;
-            case 2: --sx; if (-sx == layer) ++leg; break;
-            default: --sy; if (-sy == layer) { leg = 0; ++layer; } break;
-            }
-        }
-    }
-    __syncthreads();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const unsigned lt = (1u << lane) - 1u;
-    const int rounds = (nsp + 31) >> 5;
-    const int WH = W * H;
-    const int64_t p0 = ((int64_t)blockIdx.x * GS_WARPS + warp) * 32;
-    if (p0 >= n) return;
-    // this warp's 32 events: lane l holds event p0 + l (one coalesced load each), broadcast per event below
-    const int64_t pl = p0 + lane;
-    const int my_c = pl < n ? (int)skey[pl] : 0;
-    const int2 my_r = pl < n ? rec[pl] : make_int2(0, 0);
-    const int nev = (int)min((int64_t)32, n - p0);
-    for (int e = 0; e < nev; e++) {
-        const int c = __shfl_sync(0xffffffffu, my_c, e);
-        const int i = __shfl_sync(0xffffffffu, my_r.x, e);
-        const int ti = __shfl_sync(0xffffffffu, my_r.y, e);
-        const int rem = c % WH;
-        const int y = rem / W, x = rem - y * W;
-        int32_t* out = nbr + (int64_t)i * K;
-        uint8_t* ocls = nbr_cls ? nbr_cls + (int64_t)i * K : nullptr;
-        if (lane == 0) {                                      // self edge first (ev_graph.cu:43-46)
-            out[0] = i;
-            if (ocls) ocls[0] = (uint8_t)(radius * side + radius);
-        }
-        int total = 1;
-        for (int rd = 0; rd < rounds && total < K; rd++) {
-            const int s = rd * 32 + lane;
-            int cnt = 0, lo = 0, hi = 0, v0 = 0, v1 = 0, sx = 0, sy = 0;
-            if (s < nsp) {
-                sx = g_spiral[s];
-                sy = g_spiral[nsp + s];
-                const int xn = x + sx, yn = y + sy;
-                if ((unsigned)xn < (unsigned)W && (unsigned)yn < (unsigned)H) {
-                    const int c2 = c + sy * W + sx;
-                    const int s0 = cell_start[c2], s1 = cell_start[c2 + 1];
-                    lo = max(s0, s1 - Q);                     // the FIFO holds the newest Q indices of the pixel
-                    hi = s1;
-                    if (hi - lo > 8) {                        // long bucket: first position in [lo, s1) with index >= i
-                        int a = lo, b = s1;
-                        while (a < b) {
-                            const int m = (a + b) >> 1;
-                            if (rec[m].x < i) a = m + 1; else b = m;
-                        }
-                        hi = a;
-                    }
-                    for (int q = hi - 1; q >= lo; q--) {      // newest first
-                        const int2 r = rec[q];
-                        if (r.x >= i) continue;               // later event (or the event itself): occupies a slot, skipped
-                        if ((float)(ti - r.y) > delta_t) continue;   // NOT break (ev_graph.cu:69)
-                        if (cnt == 0) v0 = r.x; else if (cnt == 1) v1 = r.x;
-                        if (++cnt >= K - 1) break;            // one bucket can fill at most K - 1 slots
-                    }
-                }
-            }
-            // exclusive prefix of cnt over the lanes = spiral order
-            const unsigned m1 = __ballot_sync(0xffffffffu, cnt > 0);
-            if (m1 == 0u) continue;
-            const unsigned mbig = __ballot_sync(0xffffffffu, cnt > 1);
-            int excl, sum;
-            if (mbig == 0u) {
-                excl = __popc(m1 & lt);
-                sum = __popc(m1);
-            } else {
-                int incl = cnt;
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const int v = __shfl_up_sync(0xffffffffu, incl, d);
-                    if (lane >= d) incl += v;
-                }
-                excl = incl - cnt;
-                sum = __shfl_sync(0xffffffffu, incl, 31);
-            }
-            int slot = total + excl;
-            if (cnt > 0 && slot < K) {
-                const uint8_t cl = (uint8_t)((sx + radius) * side + (sy + radius));
-                if (cnt <= 2) {
-                    out[slot] = v0;
-                    if (ocls) ocls[slot] = cl;
-                    if (cnt == 2 && slot + 1 < K) {
-                        out[slot + 1] = v1;
-                        if (ocls) ocls[slot + 1] = cl;
-                    }
-                } else {
-                    for (int q = hi - 1; q >= lo && slot < K; q--) {
-                        const int2 r = rec[q];
-                        if (r.x >= i || (float)(ti - r.y) > delta_t) continue;
-                        out[slot] = r.x;
-                        if (ocls) ocls[slot] = cl;
-                        slot++;
-                    }
-                }
-            }
-            total += sum;
-        }
-        if (lane == 0) count[i] = (uint32_t)min(total, K);
-    }
-}
-
-// one thread per event, in pixel-sorted order (radii beyond the warp kernel's round budget)
+// one thread per event, in pixel-sorted order
 __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __restrict__ skey,
-                                                             const int2* __restrict__ rec,
+                                                             const uint32_t* __restrict__ sidx,
+                                                             const int32_t* __restrict__ st,
                                                              const int32_t* __restrict__ cell_start, int64_t n, int H,
                                                              int W, int radius, float delta_t, int Q, int K,
                                                              int32_t* __restrict__ nbr /*[n][K]*/,
                                                              uint8_t* __restrict__ nbr_cls /*[n][K] or null*/,
                                                              uint32_t* __restrict__ count /*[n]*/) {
+    // spiral walk of spiral.h:1-15 (layer starts at 1, leg 0), tabulated once per CTA: the per-thread state machine cost
+    // more instructions per cell visit than the visit itself
     extern __shared__ int8_t g_spiral[];                      // [nsp] dx, then [nsp] dy
     const int nsp = (2 * radius + 1) * (2 * radius + 1);
     if (threadIdx.x == 0) {
@@ -209,10 +81,9 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
     __syncthreads();
     int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
-    const int2 me = rec[p];
-    const int i = me.x;
+    const int i = (int)sidx[p];
     const int c = (int)skey[p];
-    const int ti = me.y;
+    const int ti = st[p];
     const int rem = c % (W * H);
     const int y = rem / W, x = rem - y * W;
     int32_t* out = nbr + (int64_t)i * K;
@@ -227,14 +98,26 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
         if ((unsigned)xn < (unsigned)W && (unsigned)yn < (unsigned)H) {
             const int c2 = c + sy * W + sx;
             const int s0 = cell_start[c2], s1 = cell_start[c2 + 1];
-            const int lo = max(s0, s1 - Q);                   // the FIFO holds the newest Q indices of the pixel
-            for (int q = s1 - 1; q >= lo; q--) {              // newest first
-                const int2 r = rec[q];
-                if (r.x >= i) continue;                       // later events occupy FIFO slots but are skipped
-                if ((float)(ti - r.y) > delta_t) continue;    // NOT break (ev_graph.cu:69)
-                if (ocls) ocls[cnt] = (uint8_t)((sx + radius) * side + (sy + radius));
-                out[cnt++] = r.x;
-                if (cnt >= K) break;
+            if (s1 > s0) {
+                const int lo = max(s0, s1 - Q);               // the FIFO holds the newest Q indices of the pixel
+                int hi;
+                if (c2 == c) {
+                    hi = max((int)p, lo);                     // own pixel: everything before p is older
+                } else {                                      // first position in [lo,s1) with index >= i
+                    int a = lo, b = s1;
+                    while (a < b) {
+                        int m = (a + b) >> 1;
+                        if ((int)sidx[m] < i) a = m + 1; else b = m;
+                    }
+                    hi = a;
+                }
+                for (int q = hi - 1; q >= lo; q--) {          // newest first
+                    const int dt = ti - st[q];
+                    if ((float)dt > delta_t) continue;        // NOT break (ev_graph.cu:69)
+                    if (ocls) ocls[cnt] = (uint8_t)((sx + radius) * side + (sy + radius));
+                    out[cnt++] = (int)sidx[q];
+                    if (cnt >= K) break;
+                }
             }
         }
     }
@@ -269,15 +152,14 @@ __global__ void g_empty_kernel(int32_t* rowptr, int32_t* num_edges) { rowptr[0] 
 
 struct GraphWs {
     uint32_t *k0, *v0, *k1, *v1, *count, *rowptr_u, *sort_tmp, *scan_tmp;
-    int32_t *nbr, *cell_start;
-    int2* rec;
+    int32_t *st, *nbr, *cell_start;
     uint8_t* nbr_cls;
 };
 
 static size_t graph_ws_layout(EvadArena& a, int64_t n, int64_t ncells, int K, GraphWs* w) {
     w->k0 = a.take<uint32_t>(n); w->v0 = a.take<uint32_t>(n);
     w->k1 = a.take<uint32_t>(n); w->v1 = a.take<uint32_t>(n);
-    w->rec = a.take<int2>(n);
+    w->st = a.take<int32_t>(n);
     w->nbr = a.take<int32_t>(n * K);
     w->nbr_cls = a.take<uint8_t>(n * K);
     w->count = a.take<uint32_t>(n + 1);
@@ -306,15 +188,10 @@ static int graph_rows(const int32_t* batch, const int32_t* pos, int64_t n, int B
     uint32_t *skey, *sidx;
     EVAD_TRY(evad_sort_pairs_u32(w.k0, w.v0, w.k1, w.v1, 1, n, key_bits, w.sort_tmp, &skey, &sidx, st));
     const int64_t m = (ncells + 1 > n) ? ncells + 1 : n;
-    g_cells_kernel<<<evad_cdiv(m, 256), 256, 0, st>>>(skey, sidx, pos, n, ncells, cell_start, w.rec, cell_perm);
+    g_cells_kernel<<<evad_cdiv(m, 256), 256, 0, st>>>(skey, sidx, pos, n, ncells, cell_start, w.st, cell_perm);
     EVAD_CHECK_LAUNCH();
-    const int nsp = (2 * radius + 1) * (2 * radius + 1);
-    if (nsp <= 32 * GS_MAXR)
-        g_search_warp_kernel<<<evad_cdiv(n, 32 * GS_WARPS), 32 * GS_WARPS, 2 * nsp, st>>>(skey, w.rec, cell_start, n, H, W, radius,
-                                                                                       (float)delta_t_us, Q, K, nbr, nbr_cls, count);
-    else
-        g_search_kernel<<<evad_cdiv(n, G_THREADS), G_THREADS, 2 * nsp, st>>>(skey, w.rec, cell_start, n, H, W, radius,
-                                                                        (float)delta_t_us, Q, K, nbr, nbr_cls, count);
+    g_search_kernel<<<evad_cdiv(n, G_THREADS), G_THREADS, 2 * (2 * radius + 1) * (2 * radius + 1), st>>>(skey, sidx, w.st, cell_start, n, H, W, radius,
+                                                                  (float)delta_t_us, Q, K, nbr, nbr_cls, count);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }

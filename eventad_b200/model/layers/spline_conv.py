@@ -189,10 +189,14 @@ class MySplineConv(torch.nn.Module):
             W[15, :cin] = self.lin.weight.detach().float().cpu().t()
             whi, wlo = ops.split_tf32(W.view(16 * cin_pad, 16).to(dev))
             pack = dict(tapw=tapw.to(dev).contiguous(), whi=whi, wlo=wlo, shi=None, slo=None, cin_pad=cin_pad)
+            S = None
             if skip_weight is not None:
                 S = torch.zeros((cin_pad + 7) // 8 * 8, 16)
                 S[:cin] = skip_weight.detach().float().cpu().t()
                 pack["shi"], pack["slo"] = ops.split_tf32(S.to(dev))
+            p16 = ops.l1_pack16(W.view(16 * cin_pad, 16), S, cin_pad)        # fp16 operands of the tcgen05 contraction
+            pack.update(w16=p16["w16"].to(dev), inv_sw=p16["inv_sw"], inv_ss=p16["inv_ss"],
+                        s16=p16["s16"].to(dev) if p16["s16"] is not None else None)
         self._cache["l1"] = (key, pack)
         return pack
 

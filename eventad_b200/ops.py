@@ -307,6 +307,55 @@ def edge_class(rowptr, src, n, mode, pseudo, status):
 
 # EVAD_L1_MMA=0: keep the tap aggregation of layer 1 on the FFMA pipe (evad_spline_conv_l1) for A/B measurements
 USE_L1_MMA = os.environ.get("EVAD_L1_MMA", "1") != "0"
+# EVAD_L1_TC5=1: contraction of layer 1 on tcgen05 (csrc/spline_l1_tc5.cu) instead of mma.sync (A/B measurements)
+USE_L1_TC5 = os.environ.get("EVAD_L1_TC5", "0") == "1"   # measured slower than the mma.sync kernel (profiles/r02_summary.md): opt-in
+
+
+def l1_kmap(cin_pad):
+    """K index of the tcgen05 layer-1 contraction -> (slot, channel); the operand order of csrc/spline_l1_tc5.cu."""
+    nch = 5 if cin_pad > 16 else 4
+    k = torch.arange(nch * 64)
+    u, h, c = k >> 3, (k >> 2) & 1, k & 3
+    slot = (u >> 2) + 8 * h
+    ch = 4 * (u & 3) + c
+    q = k - 256
+    slot2 = (q >> 3) + 8 * ((q >> 1) & 1)
+    ch2 = 16 + 2 * ((q >> 2) & 1) + (q & 1)
+    hi = k >= 256
+    return torch.where(hi, slot2, slot), torch.where(hi, ch2, ch)
+
+
+def split_f16x2(w):
+    """w fp32 -> (w1, w2, inv_scale): w * 2^kw = w1 + w2 * 2^-11 with fp16 parts; the power-of-two scale puts max|w| in
+    [2^9, 2^10)."""
+    w = w.detach().float()
+    m = float(w.abs().max())
+    kw = 9 - math.floor(math.log2(m)) if m > 0 else 0
+    kw = max(min(kw, 100), -100)
+    ws = w * (2.0 ** kw)
+    w1 = ws.half()
+    w2 = ((ws - w1.float()) * 2048.0).half()
+    return w1, w2, 2.0 ** (-kw)
+
+
+def l1_pack16(W, S, cin_pad):
+    """fp16 operands of evad_spline_conv_l1_tc5.  W: [16 * cin_pad, 16] fp32 (row = slot * cin_pad + channel, slot 15 =
+    root weight); S: [>= cin_pad, 16] skip Linear weight^T (zero padded) or None."""
+    slot, ch = l1_kmap(cin_pad)
+    Wk = W.detach().float().cpu()[slot * cin_pad + ch]                    # [K, 16]
+    w1, w2, inv_sw = split_f16x2(Wk)
+    pack = dict(w16=torch.stack([w1.t(), w2.t()]).contiguous().view(torch.int16), inv_sw=inv_sw, s16=None, inv_ss=1.0)
+    if S is not None:
+        kk = torch.arange(192, 192 + 128)
+        valid = kk < slot.shape[0]
+        sl = torch.where(valid, slot[kk.clamp(max=slot.shape[0] - 1)], torch.full_like(kk, -1))
+        cc = ch[kk.clamp(max=slot.shape[0] - 1)]
+        Sk = torch.zeros(128, 16)
+        root = sl == 15
+        Sk[root] = S.detach().float().cpu()[cc[root]]
+        s1, s2, inv_ss = split_f16x2(Sk)
+        pack["s16"], pack["inv_ss"] = torch.stack([s1.t(), s2.t()]).contiguous().view(torch.int16), inv_ss
+    return pack
 
 
 def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None, perm=None, ell_stride=0):
@@ -318,6 +367,16 @@ def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None, perm=N
     skip_out = torch.empty((n, 16), dtype=torch.float32, device=x.device) if has_skip else None
     e = _epi_struct(**epi)
     se = _epi_struct(**skip_epi) if has_skip else None
+    if (USE_L1_MMA and USE_L1_TC5 and pack.get("w16") is not None and ell_stride == 16 and src.data_ptr() % 16 == 0 and
+            cls.data_ptr() % 16 == 0):
+        with _timed(f'spline_conv_l1_c{cin}'):
+            check(L.evad_spline_conv_l1_tc5(ptr(rowptr), ptr(src), ptr(cls), ptr(perm), n, ptr(x), x.stride(0), pack["cin_pad"],
+                                            ptr(pack["tapw"]), pack["tapw"].shape[0], ptr(pack["w16"]), float(pack["inv_sw"]),
+                                            ptr(pack["s16"]) if has_skip else None, float(pack["inv_ss"]),
+                                            ctypes.byref(e), ptr(out), out.stride(0), ctypes.byref(se) if has_skip else None,
+                                            ptr(skip_out), skip_out.stride(0) if has_skip else 0, stream()),
+                  "evad_spline_conv_l1_tc5")
+        return out, skip_out
     if (USE_L1_MMA and ell_stride == 16 and src.data_ptr() % 16 == 0 and
             cls.data_ptr() % 16 == 0):
         with _timed(f'spline_conv_l1_c{cin}'):

@@ -57,18 +57,23 @@ def _case(n, cin, with_skip, with_perm, seed, full_rows=False):
     pack = dict(tapw=tapw.to(dev), whi=whi, wlo=wlo, shi=None, slo=None, cin_pad=cin_pad)
     if with_skip:
         pack["shi"], pack["slo"] = ops.split_tf32(S.to(dev))
+    p16 = ops.l1_pack16(W.view(16 * cin_pad, 16), S if with_skip else None, cin_pad)   # operands of the tcgen05 contraction
+    pack.update(w16=p16["w16"].to(dev), inv_sw=p16["inv_sw"], inv_ss=p16["inv_ss"],
+                s16=p16["s16"].to(dev) if p16["s16"] is not None else None)
     epi = dict(scale=scale.to(dev), shift=shift.to(dev), relu=True)
     sepi = dict(scale=sscale.to(dev), shift=sshift.to(dev)) if with_skip else None
     args = (count.to(dev), nbr.to(dev).view(-1), cls.to(dev).view(-1), n, x.to(dev), cin, pack, epi, sepi)
     kw = dict(perm=perm.to(dev) if perm is not None else None, ell_stride=16)
     res = {}
-    for flag in (True, False):
-        old = ops.USE_L1_MMA
-        ops.USE_L1_MMA = flag
+    # "tc5": mma.sync aggregation + tcgen05 contraction (csrc/spline_l1_tc5.cu); True: both products on mma.sync;
+    # False: FFMA aggregation + mma.sync contraction
+    for flag, (use_mma, use_tc5) in (("tc5", (True, True)), (True, (True, False)), (False, (False, False))):
+        old = ops.USE_L1_MMA, ops.USE_L1_TC5
+        ops.USE_L1_MMA, ops.USE_L1_TC5 = use_mma, use_tc5
         try:
             res[flag] = ops.spline_conv_l1(*args, **kw)
         finally:
-            ops.USE_L1_MMA = old
+            ops.USE_L1_MMA, ops.USE_L1_TC5 = old
     torch.cuda.synchronize()
     for flag, (out, skip) in res.items():
         err = (out.double().cpu() - ref).abs()
@@ -80,8 +85,9 @@ def _case(n, cin, with_skip, with_perm, seed, full_rows=False):
             assert skip is None
     # the two variants sum the same 320 terms in different orders: north_star's rtol 1e-4 / atol 1e-5 plus the
     # cancellation term of the fp64 bar (the synthetic features here are far larger than real layer inputs)
-    diff = (res[True][0] - res[False][0]).abs().double().cpu()
-    assert bool((diff <= 1e-5 + 1e-4 * ref.abs() + 2e-6 * mag).all()), float(diff.max())
+    for other in (False, "tc5"):
+        diff = (res[True][0] - res[other][0]).abs().double().cpu()
+        assert bool((diff <= 1e-5 + 1e-4 * ref.abs() + 2e-6 * mag).all()), (other, float(diff.max()))
 
 
 @pytest.mark.parametrize("n,cin,with_skip,with_perm", [(1, 19, True, False), (31, 16, False, True), (33, 19, True, True),
