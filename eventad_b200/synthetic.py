@@ -125,3 +125,27 @@ def make_data(n_events, batch_size=1, seed=0, dist="U", width=W_DEFAULT, height=
     d.height = torch.tensor([height] * batch_size)
     d.time_window = torch.tensor([raw["time_window"]] * batch_size)
     return d.to(device) if device != "cpu" else d
+
+
+def make_boxes(batch_size, seed=0, n_boxes=8, width=W_DEFAULT, height=H_DEFAULT, drop=0.0, max_track=8):
+    """ROL-shaped box annotations for a batch of consecutive windows: per sample `n_boxes` boxes
+    [x, y, w, h, class, track_id] with w, h in [15, 80] px, track ids drawn from 1..max_track (each box kept with
+    probability 1 - drop, so tracks appear and disappear along the clip), for the current frame (`bbox`) and the previous
+    one (`bbox0`).  Returns dict(bbox [M,6] f32, bbox_batch [M] i64, bbox0, bbox0_batch)."""
+    import torch
+    rng = np.random.default_rng(seed)
+    out = {}
+    for key in ("bbox", "bbox0"):
+        rows, bidx = [], []
+        for b in range(batch_size):
+            ids = rng.permutation(max_track)[:n_boxes] + 1
+            for t in ids:
+                if rng.random() < drop:
+                    continue
+                w, h = rng.uniform(15, 80, 2) * (width / W_DEFAULT)   # 15..80 px at the 320-wide ROL sensor
+                x, y = rng.uniform(0, width - w), rng.uniform(0, height - h)
+                rows.append([x, y, w, h, float(rng.integers(0, 2)), float(t)])
+                bidx.append(b)
+        out[key] = torch.tensor(np.asarray(rows, np.float32).reshape(-1, 6))
+        out[key + "_batch"] = torch.tensor(np.asarray(bidx, np.int64))
+    return out

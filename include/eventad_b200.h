@@ -326,6 +326,18 @@ int evad_sample_concat(const float* x, int ldx, int cx, const float* pos, int ld
                        int64_t n_cap, const int32_t* n_dev, const float* feat, int feat_b, int feat_h, int feat_w,
                        int feat_c, float width, float height, int append_pos, float* out, int ldo, void* stream);
 
+/* ---- EventAD head input: per-bounding-box pooling of the out4 graph (csrc/bbox_pool.cu) ----
+ * Replaces the python loops of /root/reference/models/EventAD.py:382-397 and _process_bbox (:406-498): for every box
+ * [x, y, w, h, class, track_id] (pixels) of `bbox` (sample ids bbox_batch int64) the feature of the nodes of its sample
+ * that lie inside the box, weighted by the inverse distance to the box centre; without such nodes the mean of the 5
+ * closest nodes; written to batch_features[sample][frame][track_id][channels] (caller zero-fills; of several boxes with
+ * one (sample, track) the last wins, as in the reference's sequential loop).  width / height: fp32 [B].  node_batch int32
+ * [n_cap] with *n_dev valid rows (NULL: n_cap).  One launch per frame list (frame 1 = bbox, frame 0 = bbox0). */
+int evad_bbox_pool(const float* feat, int ldf, int channels, const float* pos, int ldp, const int32_t* node_batch,
+                   int64_t n_cap, const int32_t* n_dev, const float* bbox, int ldb, const int64_t* bbox_batch,
+                   int num_boxes, int frame, const float* width, const float* height, int n_frames, int max_boxes,
+                   float* batch_features, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
