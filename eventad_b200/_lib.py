@@ -114,6 +114,9 @@ def _declare(L):
     _sig(L, "evad_cartesian", c_i, [c_p, c_i, c_i, c_p, c_i64, c_i64, c_p, c_f, c_i, c_p, c_p])
     _sig(L, "evad_format_events", c_i, [c_p, c_p, c_p, c_p, c_i64, c_i, c_i, c_i, c_p, c_p, c_p, c_p])
     _sig(L, "evad_denormalize_pos", c_i, [c_p, c_i, c_i64, c_i, c_i, c_i, c_p, c_p])
+    _sig(L, "evad_asy_masked_lin", c_i, [c_p, c_i64, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_p])
+    _sig(L, "evad_asy_masked_bn", c_i, [c_p, c_i64, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_f, c_p])
+    _sig(L, "evad_asy_masked_isdiff", c_i, [c_p, c_i64, c_p, c_p, c_i, c_f, c_f, c_p])
     _sig(L, "evad_bbox_pool", c_i, [c_p, c_i, c_i, c_p, c_i, c_p, c_i64, c_p, c_p, c_i, c_p, c_i, c_i, c_p, c_p, c_i, c_i, c_p, c_p])
     _sig(L, "evad_sample_concat", c_i, [c_p, c_i, c_i, c_p, c_i, c_p, c_i64, c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_f,
                                         c_i, c_p, c_i, c_p])

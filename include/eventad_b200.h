@@ -338,6 +338,23 @@ int evad_bbox_pool(const float* feat, int ldf, int channels, const float* pos, i
                    int num_boxes, int frame, const float* width, const float* height, int n_frames, int max_boxes,
                    float* batch_features, void* stream);
 
+/* ---- asynchronous (incremental) layers: masked row updates (csrc/asy.cu) ----
+ * C-ABI counterparts of the reference's `asy_tools` pybind module (/root/reference/src/dagr/asynchronous/asy_tools/main.cu
+ * :239-244), bit-identical results:
+ *   evad_asy_masked_lin     masked_lin (:215-237) when bias != NULL, masked_lin_no_bias (:190-213) when NULL:
+ *                           x_out[idx] (+)= x_in[idx] @ weight^T (+ bias), weight [cout, cin] row-major, `add` keeps x_out
+ *   evad_asy_masked_bn      masked_inplace_BN (:69-95): eval BatchNorm of the selected rows of x into x_out
+ *   evad_asy_masked_isdiff  masked_isdiff (:97-125) without the host-side compaction: indices[k] stays where row
+ *                           indices[k] of x_a and x_b differ (|a - b| > atol + rtol * b), else becomes -1
+ * indices int64 [k] row numbers; x rows are dense [*, channels] fp32. */
+int evad_asy_masked_lin(const int64_t* indices, int64_t k, const float* x_in, float* x_out, const float* weight,
+                        const float* bias, int cin, int cout, int add, void* stream);
+int evad_asy_masked_bn(const int64_t* indices, int64_t k, const float* x, float* x_out, const float* running_mean,
+                       const float* running_var, const float* weight, const float* bias, int channels, float eps,
+                       void* stream);
+int evad_asy_masked_isdiff(int64_t* indices, int64_t k, const float* x_a, const float* x_b, int channels, float atol,
+                           float rtol, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
