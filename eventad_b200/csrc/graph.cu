@@ -34,7 +34,7 @@ __global__ void __launch_bounds__(256) g_keys_kernel(const int32_t* __restrict__
 // cell_start[c] = first sorted position whose key >= c  (c = 0..ncells), plus sorted-order timestamps.
 __global__ void __launch_bounds__(256) g_cells_kernel(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ sidx,
                                                       const int32_t* __restrict__ pos, int64_t n, int64_t ncells,
-                                                      int32_t* __restrict__ cell_start, int32_t* __restrict__ st,
+                                                      int32_t* __restrict__ cell_start, int2* __restrict__ rec,
                                                       int32_t* __restrict__ cell_perm) {
     int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t <= ncells) {
@@ -47,15 +47,14 @@ __global__ void __launch_bounds__(256) g_cells_kernel(const uint32_t* __restrict
     }
     if (t < n) {
         uint32_t i = sidx[t];
-        st[t] = pos[3 * (int64_t)i + 2];
+        rec[t] = make_int2((int)i, pos[3 * (int64_t)i + 2]);  // (event index, timestamp): one 64-bit load per candidate
         if (cell_perm) cell_perm[t] = (int32_t)i;
     }
 }
 
 // one thread per event, in pixel-sorted order
 __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __restrict__ skey,
-                                                             const uint32_t* __restrict__ sidx,
-                                                             const int32_t* __restrict__ st,
+                                                             const int2* __restrict__ rec,
                                                              const int32_t* __restrict__ cell_start, int64_t n, int H,
                                                              int W, int radius, float delta_t, int Q, int K,
                                                              int32_t* __restrict__ nbr /*[n][K]*/,
@@ -81,9 +80,10 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
     __syncthreads();
     int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
-    const int i = (int)sidx[p];
+    const int2 me = rec[p];
+    const int i = me.x;
     const int c = (int)skey[p];
-    const int ti = st[p];
+    const int ti = me.y;
     const int rem = c % (W * H);
     const int y = rem / W, x = rem - y * W;
     int32_t* out = nbr + (int64_t)i * K;
@@ -98,26 +98,23 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
         if ((unsigned)xn < (unsigned)W && (unsigned)yn < (unsigned)H) {
             const int c2 = c + sy * W + sx;
             const int s0 = cell_start[c2], s1 = cell_start[c2 + 1];
-            if (s1 > s0) {
-                const int lo = max(s0, s1 - Q);               // the FIFO holds the newest Q indices of the pixel
-                int hi;
-                if (c2 == c) {
-                    hi = max((int)p, lo);                     // own pixel: everything before p is older
-                } else {                                      // first position in [lo,s1) with index >= i
-                    int a = lo, b = s1;
-                    while (a < b) {
-                        int m = (a + b) >> 1;
-                        if ((int)sidx[m] < i) a = m + 1; else b = m;
-                    }
-                    hi = a;
+            const int lo = max(s0, s1 - Q);                   // the FIFO holds the newest Q indices of the pixel
+            int q = s1 - 1;
+            if (s1 - lo > 8) {                                // long bucket: skip the entries that are not older than i
+                int a = lo, b = s1;
+                while (a < b) {
+                    const int m = (a + b) >> 1;
+                    if (rec[m].x < i) a = m + 1; else b = m;
                 }
-                for (int q = hi - 1; q >= lo; q--) {          // newest first
-                    const int dt = ti - st[q];
-                    if ((float)dt > delta_t) continue;        // NOT break (ev_graph.cu:69)
-                    if (ocls) ocls[cnt] = (uint8_t)((sx + radius) * side + (sy + radius));
-                    out[cnt++] = (int)sidx[q];
-                    if (cnt >= K) break;
-                }
+                q = a - 1;
+            }
+            for (; q >= lo; q--) {                            // newest first
+                const int2 r = rec[q];
+                if (r.x >= i) continue;                       // later events occupy FIFO slots but are skipped
+                if ((float)(ti - r.y) > delta_t) continue;    // NOT break (ev_graph.cu:69)
+                if (ocls) ocls[cnt] = (uint8_t)((sx + radius) * side + (sy + radius));
+                out[cnt++] = r.x;
+                if (cnt >= K) break;
             }
         }
     }
@@ -152,14 +149,15 @@ __global__ void g_empty_kernel(int32_t* rowptr, int32_t* num_edges) { rowptr[0] 
 
 struct GraphWs {
     uint32_t *k0, *v0, *k1, *v1, *count, *rowptr_u, *sort_tmp, *scan_tmp;
-    int32_t *st, *nbr, *cell_start;
+    int32_t *nbr, *cell_start;
+    int2* rec;
     uint8_t* nbr_cls;
 };
 
 static size_t graph_ws_layout(EvadArena& a, int64_t n, int64_t ncells, int K, GraphWs* w) {
     w->k0 = a.take<uint32_t>(n); w->v0 = a.take<uint32_t>(n);
     w->k1 = a.take<uint32_t>(n); w->v1 = a.take<uint32_t>(n);
-    w->st = a.take<int32_t>(n);
+    w->rec = a.take<int2>(n);
     w->nbr = a.take<int32_t>(n * K);
     w->nbr_cls = a.take<uint8_t>(n * K);
     w->count = a.take<uint32_t>(n + 1);
@@ -188,9 +186,9 @@ static int graph_rows(const int32_t* batch, const int32_t* pos, int64_t n, int B
     uint32_t *skey, *sidx;
     EVAD_TRY(evad_sort_pairs_u32(w.k0, w.v0, w.k1, w.v1, 1, n, key_bits, w.sort_tmp, &skey, &sidx, st));
     const int64_t m = (ncells + 1 > n) ? ncells + 1 : n;
-    g_cells_kernel<<<evad_cdiv(m, 256), 256, 0, st>>>(skey, sidx, pos, n, ncells, cell_start, w.st, cell_perm);
+    g_cells_kernel<<<evad_cdiv(m, 256), 256, 0, st>>>(skey, sidx, pos, n, ncells, cell_start, w.rec, cell_perm);
     EVAD_CHECK_LAUNCH();
-    g_search_kernel<<<evad_cdiv(n, G_THREADS), G_THREADS, 2 * (2 * radius + 1) * (2 * radius + 1), st>>>(skey, sidx, w.st, cell_start, n, H, W, radius,
+    g_search_kernel<<<evad_cdiv(n, G_THREADS), G_THREADS, 2 * (2 * radius + 1) * (2 * radius + 1), st>>>(skey, w.rec, cell_start, n, H, W, radius,
                                                                   (float)delta_t_us, Q, K, nbr, nbr_cls, count);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;

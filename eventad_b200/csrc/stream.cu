@@ -128,6 +128,213 @@ __global__ void __launch_bounds__(128) st_search_kernel(const int32_t* __restric
     count[e] = (uint32_t)cnt;
 }
 
+// Warp-cooperative form of the search for micro-batches: one warp per new event, the (2r+1)^2 spiral cells spread over the
+// lanes (cell s = 32 * round + lane), so the 81 dependent ring look-ups of the serial walk become three rounds of 32
+// independent ones -- a micro-batch of 1..10^4 events is latency bound, not throughput bound (for the 6.4 M-event
+// reset-mode build the same layout was measured 2.9x SLOWER than thread-per-event, whose neighbouring threads coalesce;
+// profiles/r02_summary.md).  Per round: every lane walks its pixel's ring newest-first counting the entries that pass
+// the deleted-node stop (j < min_index: break, ev_graph.cu:61), the causal filter and the time gate (continue, :69); a
+// prefix sum over the lanes (= spiral order) assigns the output slots; lanes write until slot K.
+__device__ __forceinline__ void st_search_one(int e, int lane, const int32_t* __restrict__ batch,
+                                              const int32_t* __restrict__ pos, int base_index, int min_index, int B, int H,
+                                              int W, int radius, float delta_t, int Q, int K, const StreamView& S,
+                                              const int8_t* __restrict__ spiral, int32_t* __restrict__ out,
+                                              uint32_t* __restrict__ count_out) {
+    const int side = 2 * radius + 1, nsp = side * side;
+    const int rounds = (nsp + 31) >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    const int i = base_index + e;
+    const int x = pos[3 * (int64_t)e], y = pos[3 * (int64_t)e + 1], ti = pos[3 * (int64_t)e + 2];
+    const int b = min(max(batch[e], 0), B - 1);
+    if (lane == 0) out[0] = i - min_index;
+    int total = 1;
+    for (int rd = 0; rd < rounds && total < K; rd++) {
+        const int s = rd * 32 + lane;
+        int cnt = 0, tot = 0, depth = 0, v0 = 0, v1 = 0;
+        int64_t c2 = 0;
+        if (s < nsp) {
+            const int xn = x + spiral[s], yn = y + spiral[nsp + s];
+            if (xn >= 0 && yn >= 0 && xn < W && yn < H) {
+                c2 = xn + (int64_t)W * (yn + (int64_t)H * b);
+                tot = S.count[c2];
+                depth = min(tot, Q);
+                for (int q = 0; q < depth; q++) {             // q = 0 is the newest entry
+                    const int slot = (int)(((int64_t)tot - 1 - q) % Q);
+                    const int j = S.ring[c2 * Q + slot];
+                    if (j < min_index) break;                 // deleted node: stop this pixel
+                    if (i > j) {
+                        if ((float)(ti - S.tsr[c2 * Q + slot]) > delta_t) continue;
+                        if (cnt == 0) v0 = j; else if (cnt == 1) v1 = j;
+                        if (++cnt >= K - 1) break;
+                    }
+                }
+            }
+        }
+        const unsigned m1 = __ballot_sync(0xffffffffu, cnt > 0);
+        if (m1 == 0u) continue;
+        int incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += v;
+        }
+        int slot_out = total + incl - cnt;
+        const int sum = __shfl_sync(0xffffffffu, incl, 31);
+        if (cnt > 0 && slot_out < K) {
+            if (cnt <= 2) {
+                out[slot_out] = v0 - min_index;
+                if (cnt == 2 && slot_out + 1 < K) out[slot_out + 1] = v1 - min_index;
+            } else {
+                for (int q = 0; q < depth && slot_out < K; q++) {
+                    const int slot = (int)(((int64_t)tot - 1 - q) % Q);
+                    const int j = S.ring[c2 * Q + slot];
+                    if (j < min_index) break;
+                    if (i > j) {
+                        if ((float)(ti - S.tsr[c2 * Q + slot]) > delta_t) continue;
+                        out[slot_out++] = j - min_index;
+                    }
+                }
+            }
+        }
+        total += sum;
+    }
+    if (lane == 0) *count_out = (uint32_t)min(total, K);
+}
+
+__device__ __forceinline__ void st_spiral_table(int radius, int8_t* spiral) {
+    const int nsp = (2 * radius + 1) * (2 * radius + 1);
+    int sx = 0, sy = 0, layer = 1, leg = 0;
+    for (int s = 0; s < nsp; s++) {
+        spiral[s] = (int8_t)sx;
+        spiral[nsp + s] = (int8_t)sy;
+        switch (leg) {
+        case 0: ++sx; if (sx == layer) ++leg; break;
+        case 1: ++sy; if (sy == layer) ++leg; break;
+        case 2: --sx; if (-sx == layer) ++leg; break;
+        default: --sy; if (-sy == layer) { leg = 0; ++layer; } break;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) st_search_warp_kernel(const int32_t* __restrict__ batch, const int32_t* __restrict__ pos,
+                                                             int64_t n, int base_index, int min_index, int B, int H, int W,
+                                                             int radius, float delta_t, int Q, int K, StreamView S,
+                                                             int32_t* __restrict__ nbr, uint32_t* __restrict__ count) {
+    extern __shared__ int8_t st_spiral[];
+    if (threadIdx.x == 0) st_spiral_table(radius, st_spiral);
+    __syncthreads();
+    const int64_t e = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (e >= n) return;
+    st_search_one((int)e, threadIdx.x & 31, batch, pos, base_index, min_index, B, H, W, radius, delta_t, Q, K, S, st_spiral,
+                  nbr + e * K, count + e);
+}
+
+// The whole append for a micro-batch of at most ST_SMALL_MAX events in ONE launch of one CTA (a micro-batch is pure
+// latency: the multi-kernel path below is ~15 launches): keys -> stable sort in shared memory (bitonic on key << 32 |
+// position) -> ring insert + counter bump -> warp-cooperative search -> block scan -> CSR / edge_index + edge count.
+#define ST_SMALL_MAX 1024
+#define ST_SMALL_THREADS 1024
+#define ST_SMALL_ONE_CTA 96               // beyond this a single CTA's 32 warps serialise the searches: multi-kernel path
+
+__global__ void __launch_bounds__(ST_SMALL_THREADS) st_small_kernel(const int32_t* __restrict__ batch, const int32_t* __restrict__ pos,
+                                                                    int n, int base_index, int min_index, int B, int H, int W,
+                                                                    int radius, float delta_t, int Q, int K, int do_search,
+                                                                    StreamView S, int32_t* __restrict__ nbr_ws,
+                                                                    int32_t* __restrict__ rowptr, int32_t* __restrict__ src,
+                                                                    int32_t* __restrict__ num_edges, int64_t* __restrict__ edge_index,
+                                                                    int64_t stride, uint32_t* __restrict__ status) {
+    __shared__ unsigned long long skv[ST_SMALL_MAX];          // key << 32 | position in the micro-batch
+    __shared__ uint32_t scnt[ST_SMALL_MAX + 1];
+    __shared__ uint32_t swarp[32];
+    extern __shared__ int8_t st_spiral[];
+    const int tid = threadIdx.x;
+    int np2 = 1;
+    while (np2 < n) np2 <<= 1;
+    if (tid == 0) st_spiral_table(radius, st_spiral);
+    for (int t = tid; t < np2; t += ST_SMALL_THREADS) {
+        unsigned long long kv = ~0ull;
+        if (t < n) {
+            int b = n == 1 ? 0 : batch[t], x = pos[3 * t], y = pos[3 * t + 1];   // single event: b forced to 0 (ev_graph.cu:152)
+            if (x < 0 || y < 0 || x >= W || y >= H || b < 0 || b >= B) {
+                atomicOr(status, EVAD_STATUS_EVENT_OOB);
+                x = min(max(x, 0), W - 1); y = min(max(y, 0), H - 1); b = min(max(b, 0), B - 1);
+            }
+            kv = ((unsigned long long)(uint32_t)(x + W * (y + H * b)) << 32) | (uint32_t)t;
+        }
+        skv[t] = kv;
+    }
+    __syncthreads();
+    for (int k = 2; k <= np2; k <<= 1)                        // bitonic sort; unique keys, so the result is the stable order
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = tid; t < np2; t += ST_SMALL_THREADS) {
+                const int l = t ^ j;
+                if (l > t) {
+                    const unsigned long long a = skv[t], c = skv[l];
+                    const bool up = (t & k) == 0;
+                    if ((a > c) == up) { skv[t] = c; skv[l] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    // ring insert: position p of a run of c events at one pixel, r-th of the run (only the newest Q of a run survive)
+    for (int p = tid; p < n; p += ST_SMALL_THREADS) {
+        const uint32_t k = (uint32_t)(skv[p] >> 32), i = (uint32_t)skv[p];
+        int rs = p, re = p + 1;
+        while (rs > 0 && (uint32_t)(skv[rs - 1] >> 32) == k) rs--;
+        while (re < n && (uint32_t)(skv[re] >> 32) == k) re++;
+        const int c = re - rs, r = p - rs;
+        const int cnt = S.count[k];
+        if (r >= c - Q) {
+            const int slot = (int)(((int64_t)cnt + r) % Q);
+            S.ring[(int64_t)k * Q + slot] = base_index + (int)i;
+            S.tsr[(int64_t)k * Q + slot] = pos[3 * (int64_t)i + 2];
+        }
+        scnt[p] = (r == c - 1) ? (uint32_t)(cnt + c) : 0u;    // the last event of a run publishes the new counter
+    }
+    __syncthreads();
+    for (int p = tid; p < n; p += ST_SMALL_THREADS)
+        if (scnt[p]) S.count[(uint32_t)(skv[p] >> 32)] = (int32_t)scnt[p];
+    __threadfence_block();
+    __syncthreads();
+    if (!do_search) return;
+    // search: one warp per new event, in arrival order
+    for (int e = tid >> 5; e < n; e += ST_SMALL_THREADS / 32)
+        st_search_one(e, tid & 31, batch, pos, base_index, min_index, B, H, W, radius, delta_t, Q, K, S, st_spiral,
+                      nbr_ws + (int64_t)e * K, scnt + e);
+    __syncthreads();
+    // exclusive scan of the row lengths (n <= 1024: one element per thread)
+    const uint32_t mine = tid < n ? scnt[tid] : 0u;
+    uint32_t incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
+        if ((tid & 31) >= d) incl += v;
+    }
+    if ((tid & 31) == 31) swarp[tid >> 5] = incl;
+    __syncthreads();
+    if (tid < 32) {
+        uint32_t w = swarp[tid], wi = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, wi, d);
+            if (tid >= d) wi += v;
+        }
+        swarp[tid] = wi - w;
+    }
+    __syncthreads();
+    const uint32_t r0 = swarp[tid >> 5] + incl - mine;
+    if (tid < n) {
+        rowptr[tid] = (int32_t)r0;
+        if (tid == n - 1) { rowptr[n] = (int32_t)(r0 + mine); *num_edges = (int32_t)(r0 + mine); }
+        const int dst = base_index - min_index + tid;
+        for (uint32_t k = 0; k < mine; k++) {
+            const int32_t j = nbr_ws[(int64_t)tid * K + k];
+            src[r0 + k] = j;
+            if (edge_index) { edge_index[r0 + k] = j; edge_index[stride + r0 + k] = dst; }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) st_compact_kernel(const int32_t* __restrict__ nbr, const uint32_t* __restrict__ rowptr_u,
                                                          int64_t n, int K, int dst_base, int32_t* __restrict__ rowptr,
                                                          int32_t* __restrict__ src, int32_t* __restrict__ num_edges,
@@ -193,6 +400,14 @@ extern "C" int evad_stream_append(void* state, int B, int H, int W, int Q, const
     stream_ws_layout(a, n, K, &w);
     if (!a.ok) return EVAD_ERR_WORKSPACE;
     StreamView S = stream_view(state, cells, Q);
+    const int nsp = (2 * radius + 1) * (2 * radius + 1);
+    if (n <= ST_SMALL_ONE_CTA && radius <= 64) {              // micro-batch: the whole append in one launch
+        st_small_kernel<<<1, ST_SMALL_THREADS, 2 * nsp, st>>>(batch, pos, (int)n, base_index, min_index, B, H, W, radius,
+                                                              (float)delta_t_us, Q, K, do_search, S, w.nbr, rowptr, src,
+                                                              num_edges, edge_index, edge_index_stride, status);
+        EVAD_CHECK_LAUNCH();
+        return EVAD_OK;
+    }
     // insert_in_queue_single (one event) ignores `batch` and writes into sample 0 (ev_graph.cu:152)
     st_keys_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(batch, pos, n, B, H, W, n == 1 ? 1 : 0, w.k0, status);
     EVAD_CHECK_LAUNCH();
@@ -205,8 +420,12 @@ extern "C" int evad_stream_append(void* state, int B, int H, int W, int Q, const
     st_bump_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(skey, w.run_len, n, S);
     EVAD_CHECK_LAUNCH();
     if (!do_search) return EVAD_OK;
-    st_search_kernel<<<evad_cdiv(n, 128), 128, 0, st>>>(batch, pos, n, base_index, min_index, B, H, W, radius,
-                                                       (float)delta_t_us, Q, K, S, w.nbr, w.count);
+    if (n <= 200000 && radius <= 64)                          // latency-bound sizes: lanes over cells
+        st_search_warp_kernel<<<evad_cdiv(n, 8), 256, 2 * nsp, st>>>(batch, pos, n, base_index, min_index, B, H, W, radius,
+                                                                     (float)delta_t_us, Q, K, S, w.nbr, w.count);
+    else
+        st_search_kernel<<<evad_cdiv(n, 128), 128, 0, st>>>(batch, pos, n, base_index, min_index, B, H, W, radius,
+                                                           (float)delta_t_us, Q, K, S, w.nbr, w.count);
     EVAD_CHECK_LAUNCH();
     EVAD_TRY(evad_exclusive_scan_u32(w.count, w.rowptr_u, n, w.rowptr_u + n, w.scan_tmp, st));
     st_compact_kernel<<<evad_cdiv(n * K, 256), 256, 0, st>>>(w.nbr, w.rowptr_u, n, K, base_index - min_index, rowptr, src,

@@ -25,17 +25,63 @@ class AsyncGraph:
         self.batch_size = batch_size
         self.device = None
         self.edges = torch.zeros((2, 0), dtype=torch.long)
-        self.all_timestamps = torch.zeros((0,), dtype=torch.int32)
+        self._ts_buf, self._ts_lo, self._ts_hi = torch.zeros((0,), dtype=torch.int32), 0, 0
+        self._ts_pending, self._ts_npend = [], 0
         self.csr = None
         self._ws = _lib.Workspace()
         self._status = None
+        self._meta = None
         self._stream_state = None
         self._history = []          # (batch, pos, base_index) of reset-mode calls, replayed if streaming starts
+
+    # `all_timestamps` (ev_graph.py:75: torch.cat on every call, an O(resident) copy) is a window [lo, hi) of a buffer
+    # that grows geometrically: appending a micro-batch costs O(micro-batch), deleting the oldest nodes moves `lo`
+    # The kernels never read it (the ring carries the timestamps), so appended chunks are only queued and written into
+    # the buffer when somebody looks at the attribute.
+    @property
+    def all_timestamps(self):
+        self._ts_flush()
+        return self._ts_buf[self._ts_lo:self._ts_hi]
+
+    @all_timestamps.setter
+    def all_timestamps(self, t):
+        self._ts_buf, self._ts_lo, self._ts_hi, self._ts_pending, self._ts_npend = t, 0, t.shape[0], [], 0
+
+    @property
+    def num_resident(self):
+        """len(all_timestamps) without materialising it."""
+        return self._ts_hi - self._ts_lo + self._ts_npend
+
+    def _ts_append(self, t):
+        self._ts_pending.append(t)
+        self._ts_npend += t.shape[0]
+        if len(self._ts_pending) > 4096:
+            self._ts_flush()
+
+    def _ts_flush(self):
+        if not self._ts_pending:
+            return
+        new = torch.cat(self._ts_pending) if len(self._ts_pending) > 1 else self._ts_pending[0]
+        n = new.shape[0]
+        if self._ts_hi + n > self._ts_buf.shape[0]:
+            live = self._ts_hi - self._ts_lo
+            buf = torch.empty(max(2 * (live + n), 1 << 16), dtype=torch.int32, device=new.device)
+            buf[:live] = self._ts_buf[self._ts_lo:self._ts_hi]
+            self._ts_buf, self._ts_lo, self._ts_hi = buf, 0, live
+        self._ts_buf[self._ts_hi:self._ts_hi + n] = new
+        self._ts_hi += n
+        self._ts_pending, self._ts_npend = [], 0
+
+    def _ts_delete(self, n):
+        if self._ts_npend and self._ts_lo + n > self._ts_hi:
+            self._ts_flush()
+        self._ts_lo = min(self._ts_lo + n, self._ts_hi)
 
     def initialize(self, n_ev, device):
         self.edges = torch.zeros((2, 0), dtype=torch.long, device=device)
         self.all_timestamps = torch.zeros((0,), dtype=torch.int32, device=device)
-        self._status = torch.zeros(1, dtype=torch.int32, device=device)
+        self._meta = torch.zeros(2, dtype=torch.int32, device=device)   # [edge count of an append, status word]
+        self._status = self._meta[1:2]
 
     def reset(self):
         self.edges = torch.zeros((2, 0), dtype=torch.long, device=self.device)
@@ -132,7 +178,7 @@ class AsyncGraph:
         if self.max_index == 0 and self.min_index == 0 and self._stream_state is None:
             out = self.build_csr(batch, pos, want_edge_index=True)
             self._history = [(batch, pos, 0)]
-            self.all_timestamps = torch.cat([self.all_timestamps, pos[:, 2]])
+            self._ts_append(pos[:, 2])
             self.max_index += n_ev
             e = int(out["num_edges"].item())                    # the reference syncs here too (mask compaction)
             _lib.check_status(self._status, "graph build")
@@ -153,19 +199,22 @@ class SlidingWindowGraph(AsyncGraph):
 
     @property
     def init(self):
-        return len(self.all_timestamps) > 0
+        return self.num_resident > 0
 
     def delete_nodes(self, n_delete, delete_edges=True, return_edges=True):
-        self.all_timestamps = self.all_timestamps[n_delete:]
+        self._ts_delete(n_delete)
         self.min_index += n_delete
         if self._stream_state is not None:
             self._stream_state.delete(n_delete)
         deleted_edges = None
-        if delete_edges:
-            mask = (self.edges[0] < n_delete) | (self.edges[1] < n_delete)
-            deleted_edges = self.edges[:, mask].clone()
-            self.edges = self.edges[:, ~mask]
-        self.edges.add_(-n_delete)
+        if self.edges.shape[1] == 0:                          # nothing collected (collect_edges=False): no masks to evaluate
+            deleted_edges = self.edges if delete_edges else None
+        else:
+            if delete_edges:
+                mask = (self.edges[0] < n_delete) | (self.edges[1] < n_delete)
+                deleted_edges = self.edges[:, mask].clone()
+                self.edges = self.edges[:, ~mask]
+            self.edges.add_(-n_delete)
         if delete_edges and return_edges:
             return deleted_edges
 
@@ -176,7 +225,7 @@ class SlidingWindowGraph(AsyncGraph):
         if return_total_edges:
             total_edges = self.edges.clone()
         if return_node_counts:
-            tot_nodes = len(self.all_timestamps)
+            tot_nodes = self.num_resident
         ret = [edges]
         if delete_nodes:
             ret.append(self.delete_nodes(n_delete))

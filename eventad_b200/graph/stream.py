@@ -28,7 +28,7 @@ class StreamState:
         pos = pos.contiguous()
         rowptr = torch.empty(n + 1, dtype=torch.int32, device=dev) if do_search else None
         src = torch.empty(max(n * K, 1), dtype=torch.int32, device=dev) if do_search else None
-        num_edges = torch.empty(1, dtype=torch.int32, device=dev) if do_search else None
+        num_edges = graph._meta[0:1] if do_search else None      # next to the status word: one read-back for both
         ei = torch.empty((2, max(n * K, 1)), dtype=torch.int64, device=dev) if do_search else None
         ws = graph._ws.get(L.evad_stream_ws_bytes(n, K), dev)
         rc = L.evad_stream_append(_lib.ptr(self.buf), self.B, self.H, self.W, self.Q, _lib.ptr(batch), _lib.ptr(pos), n,
@@ -50,9 +50,10 @@ def append_events(graph, batch, pos):
     n_ev = batch.shape[0]
     base = graph.max_index
     rowptr, src, num_edges, ei = graph._stream_state.append(graph, batch, pos, base, do_search=True)
-    graph.all_timestamps = torch.cat([graph.all_timestamps, pos[:, 2]])
+    graph._ts_append(pos[:, 2])
     graph.max_index += n_ev
-    e = int(num_edges.item())
-    _lib.check_status(graph._status, "graph append")
-    graph.csr = (rowptr, src[:e], num_edges)
+    e, st = graph._meta.tolist()                              # the one host synchronisation of the call
+    if st:
+        _lib.check_status(graph._status, "graph append")
+    graph.csr = (rowptr, src[:e], num_edges.clone())
     return ei[:, :e]
