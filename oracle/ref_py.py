@@ -16,6 +16,7 @@ What the stand-ins are (the ONLY restated arithmetic; everything else is the ref
   torch_spline_conv.spline_basis / spline_weighting   -> oracle/dagr_ops.py   (library 1.2.2)  UNPINNED
   torch_cluster.grid_cluster                          -> oracle/dagr_ops.py   (library 1.6.3)    UNPINNED
   torch_scatter.scatter_max / scatter_sum             -> oracle/dagr_ops.py   (library 2.1.2)    UNPINNED
+      (with `out=` both continue IN PLACE and scatter_max returns the argmax: what dagr/asynchronous relies on)
   torch_geometric: SplineConv (parameters + propagate = gather / message / scatter-add), BatchNorm (.module =
       BatchNorm1d), T.Cartesian, pool_pos, _avg_pool_x, Data / Batch (attribute bags)  (2.6.1)  UNPINNED
   ev_graph_cuda.{fill_edges_cuda, insert_in_queue_cuda, insert_in_queue_single_cuda} on CPU tensors
@@ -99,6 +100,14 @@ def _pyg_modules():
             n = size[1] if size is not None else x_src.shape[0]
             return dagr_ops.scatter_sum(msg, edge_index[1], n)
 
+        def aggregate(self, inputs, index, ptr=None, dim_size=None):
+            """MessagePassing.aggregate with aggr='sum' (called directly by asynchronous/conv.py:14)."""
+            assert self.aggr in ("sum", "add")
+            return dagr_ops.scatter_sum(inputs, index, dim_size)
+
+    class GCNConv(torch.nn.Module):
+        """Only named in an isinstance test of asynchronous/__init__.py; never constructed by EventAD."""
+
     class BatchNorm(torch.nn.Module):
         """torch_geometric.nn.BatchNorm: wrapper whose `.module` is nn.BatchNorm1d."""
 
@@ -153,7 +162,7 @@ def _pyg_modules():
 
     tg = mod("torch_geometric")
     data = mod("torch_geometric.data", Data=Data, Batch=Batch)
-    nn_conv = mod("torch_geometric.nn.conv", SplineConv=SplineConv)
+    nn_conv = mod("torch_geometric.nn.conv", SplineConv=SplineConv, GCNConv=GCNConv)
     avg = mod("torch_geometric.nn.pool.avg_pool", _avg_pool_x=_avg_pool_x)
     pool = mod("torch_geometric.nn.pool.pool", pool_pos=pool_pos)
     nn_pool = mod("torch_geometric.nn.pool", avg_pool=avg, pool=pool)
@@ -244,11 +253,30 @@ def _asy_tools_module():
 
 def _misc_modules():
     def scatter_max(src, index, dim=0, out=None, dim_size=None):
+        """torch_scatter 2.1.2 scatter_max (csrc/cpu/scatter_cpu.cpp): values and argmax.  With `out` the reduction
+        continues from its contents IN PLACE and an entry is replaced only by a strictly greater value; argmax is the
+        FIRST source row that holds the maximum, src.size(0) where no row replaced the initial value (the CPU kernel's
+        order; the CUDA kernel's tie choice is a race).  Without `out`, untouched entries are 0."""
         assert dim == 0
-        return dagr_ops.scatter_max(src, index, dim_size), None
+        if out is None:
+            return dagr_ops.scatter_max(src, index, dim_size), None      # dense path: the argmax is never read
+        n_src = src.shape[0]
+        idx = index.view(-1, *([1] * (src.dim() - 1))).expand_as(src)
+        before = out.clone()
+        out.scatter_reduce_(0, idx, src, reduce="amax", include_self=True)
+        rows = torch.arange(n_src, device=src.device).view(-1, *([1] * (src.dim() - 1))).expand_as(src)
+        cand = torch.where(src == out.gather(0, idx), rows, torch.full_like(rows, n_src))
+        arg = torch.full(out.shape, n_src, dtype=torch.long, device=src.device)
+        arg.scatter_reduce_(0, idx, cand, reduce="amin", include_self=True)
+        arg[~(out > before)] = n_src
+        return out, arg
 
     def scatter_sum(src, index, dim=0, out=None, dim_size=None):
+        """torch_scatter 2.1.2 scatter_sum: with `out`, adds into it IN PLACE (the asynchronous layers rely on that)."""
         assert dim == 0
+        if out is not None:
+            idx = index.view(-1, *([1] * (src.dim() - 1))).expand_as(src)
+            return out.scatter_add_(0, idx, src)
         n = dim_size if dim_size is not None else (int(index.max()) + 1 if index.numel() else 0)
         return dagr_ops.scatter_sum(src, index, n)
 

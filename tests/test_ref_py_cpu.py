@@ -141,3 +141,42 @@ def test_format_data_and_denormalize_reference_text():
     pi = denormalize_pos(f)
     assert torch.equal(pi, oracle_denorm(mine.pos, 320, 240, 1000000))
     assert torch.equal(pi[:, :2].short(), torch.from_numpy(raw["pos"])) and torch.equal(pi[:, 2], torch.from_numpy(raw["t"]))
+
+
+@needs_ref
+def test_reference_asynchronous_model_runs_and_agrees_with_its_dense_forward():
+    """SURVEY 8 f-1 anchor: the reference's own `make_model_asynchronous` (asynchronous/__init__.py:39-110) over the
+    stand-ins -- N - 10 events with reset=True, then 10 events with reset=False -- against its dense forward on all N,
+    within the 1e-3 bar of the reference's checker (asynchronous/evaluate_flops.py:141-143).  The dense model holds one
+    more voxel: the window's last event has t == 1.0 and lands in a voxel of its own in the 3-D grid_cluster
+    (SURVEY A.7-2), which the asynchronous pooling's 2-D cell index (max_pool.py:245-252) does not reproduce."""
+    import copy
+    from eventad_b200 import synthetic
+    W, H, n = 64, 48, 3000
+    model, args = synthetic.make_backbone(seed=0, use_image=False, height=H, width=W)
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    d = synthetic.make_data(n, 1, seed=3, dist="U", width=W, height=H)
+    ref = ref_py.build_dagr(args, H, W, sd, cache_luts=True)
+    dense = ref_py.run_backbone(ref, copy.copy(d), None)
+    from dagr.asynchronous import make_model_asynchronous, make_model_synchronous
+
+    def part(a, b):
+        p = copy.copy(d)
+        p.x, p.pos, p.batch = d.x[a:b].clone(), d.pos[a:b].clone(), d.batch[a:b].clone()
+        return p
+
+    net = make_model_asynchronous(ref.backbone)
+    try:
+        with torch.no_grad():
+            net(part(0, n - 10), reset=True)
+            inc = net(part(n - 10, n), reset=False)
+    finally:
+        make_model_synchronous(ref.backbone)
+    scale = torch.tensor([W, H])
+    for a, b in zip(dense, inc):
+        ka = [tuple(r) for r in (a.pos[:, :2] * scale).round().int().tolist()]
+        kb = [tuple(r) for r in (b.pos[:, :2] * scale).round().int().tolist()]
+        assert len(set(ka)) == len(ka) and set(kb) <= set(ka) and len(ka) - len(kb) <= 1
+        row = {k: i for i, k in enumerate(ka)}
+        sel = torch.tensor([row[k] for k in kb])
+        assert float((a.x[sel] - b.x).abs().max()) < 1e-3
