@@ -13,7 +13,8 @@ LIB_PATH = os.path.join(_HERE, "libeventad_b200.so")
 _lib = None
 
 ERRORS = {-1: "EVAD_ERR_ARG (bad argument)", -2: "EVAD_ERR_WORKSPACE (workspace too small)",
-          -3: "EVAD_ERR_LAUNCH (CUDA launch failed)", -4: "EVAD_ERR_UNSUPPORTED"}
+          -3: "EVAD_ERR_LAUNCH (CUDA launch failed)", -4: "EVAD_ERR_UNSUPPORTED",
+          -5: "EVAD_ERR_STATIC_LIMIT (size beyond the static-scratch entry point's maximum)"}
 STATUS_BITS = {1: "event outside the sensor / batch range", 2: "LUT offset outside its table",
                4: "voxel id outside the cluster table", 8: "coarse edge buffer overflow"}
 
@@ -68,6 +69,10 @@ def _declare(L):
     _sig(L, "evad_launch_count", ctypes.c_longlong, [])
     _sig(L, "evad_scan_ws_bytes", c_sz, [c_i64])
     _sig(L, "evad_exclusive_scan", c_i, [c_p, c_p, c_i64, c_p, c_p, c_sz, c_p])
+    _sig(L, "evad_exclusive_scan_static", c_i, [c_p, c_p, c_i64, c_p, c_p])
+    _sig(L, "evad_exclusive_scan_static_max_n", c_i64, [])
+    _sig(L, "evad_exclusive_scan_static_bytes", c_sz, [])
+    _sig(L, "evad_no_alloc_last_error", ctypes.c_char_p, [])
     _sig(L, "evad_sort_ws_bytes", c_sz, [c_i64])
     _sig(L, "evad_sort_pairs", c_i, [c_p, c_p, c_p, c_p, c_i64, c_i, c_p, c_sz, c_p])
     _sig(L, "evad_graph_ws_bytes", c_sz, [c_i64, c_i, c_i, c_i, c_i])

@@ -29,6 +29,7 @@ extern "C" {
 #define EVAD_ERR_WORKSPACE (-2) /* workspace too small */
 #define EVAD_ERR_LAUNCH (-3)    /* cudaGetLastError() after a launch */
 #define EVAD_ERR_UNSUPPORTED (-4)
+#define EVAD_ERR_STATIC_LIMIT (-5) /* size beyond the maximum of an entry point that works in static device scratch */
 
 /* bits of the device status word */
 #define EVAD_STATUS_EVENT_OOB 1u     /* event outside [0,W)x[0,H) or batch outside [0,B)           */
@@ -48,6 +49,18 @@ long long evad_launch_count(void);
 size_t evad_scan_ws_bytes(int64_t n);
 int evad_exclusive_scan(const uint32_t* in, uint32_t* out, int64_t n, uint32_t* total, void* ws, size_t ws_bytes,
                         void* stream);
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  evad_exclusive_scan without a
+ * workspace argument: the tile-sum scratch is a file-scope `static __device__` array of 33,024 bytes
+ * (csrc/no_alloc.cu; every GPU that loads the library holds it until exit), so n is limited to
+ * evad_exclusive_scan_static_max_n() = 16,777,216 values; larger n returns EVAD_ERR_STATIC_LIMIT and
+ * evad_no_alloc_last_error() says why.  Calls no cudaMalloc / cudaFree / allocating routine.  All calls on a device
+ * share the scratch: calls ordered on one stream are safe, calls that overlap on the GPU race.  in may alias out;
+ * total may be NULL. */
+int evad_exclusive_scan_static(const uint32_t* in, uint32_t* out, int64_t n, uint32_t* total, void* stream);
+int64_t evad_exclusive_scan_static_max_n(void);
+size_t evad_exclusive_scan_static_bytes(void);
+const char* evad_no_alloc_last_error(void);
 size_t evad_sort_ws_bytes(int64_t n);
 /* stable sort of (key,val) pairs on the low key_bits bits; keys_in/vals_in are clobbered; vals_in may be NULL
  * (values = 0..n-1).  Result in keys_out/vals_out. */
