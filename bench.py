@@ -238,7 +238,7 @@ def run_reference(a):
                     "this is the CPU restatement in oracle/ (kind=port), timed with all host threads inside one window "
                     f"per step; --steps / --warmup are honoured up to {REF_STEP_CAP} / {REF_WARMUP_CAP} (1.6 s of CPU "
                     "work per step), the `steps` / `warmup` keys say what ran"}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 
@@ -653,13 +653,32 @@ def run_b200(a):
                     "format_data kernel + graph replay + D2H; stage_ms/roofline: plain stream launches with CUDA events",
             "ms_per_window": ms_total / a.steps / B, "strong_scaling": strong, "sweep": sweep, "graph_stage": graph_stage,
             "streaming": streaming, "full_model": full_model}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+def _json_only_stdout():
+    """Everything a library writes to fd 1 during the run (NCCL's version banner, warnings of C extensions) goes to
+    stderr; the one JSON line is written to the real stdout by `emit`."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
+_REAL_STDOUT = None
+
+
 def main():
     a = parse()
+    _json_only_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:

@@ -148,8 +148,9 @@ __global__ void __launch_bounds__(256) cartesian_kernel(const float* __restrict_
     const int64_t ne = num_edges ? min((int64_t)*num_edges, e_cap) : e_cap;
     if (e >= ne) return;
     const int64_t j = row[e], i = col[e];
+    const float inv = __fdiv_rn(1.0f, two_m);      // tensor / Python scalar on CUDA = multiply by the fp32 reciprocal
     for (int d = 0; d < dims; d++) {
-        float a = __fadd_rn(__fdiv_rn(__fsub_rn(pos[j * ld_pos + d], pos[i * ld_pos + d]), two_m), 0.5f);
+        float a = __fadd_rn(__fmul_rn(__fsub_rn(pos[j * ld_pos + d], pos[i * ld_pos + d]), inv), 0.5f);
         if (clamp01) a = fminf(fmaxf(a, 0.f), 1.f);
         out[e * dims + d] = a;
     }

@@ -22,8 +22,11 @@ __device__ __forceinline__ void evad_pseudo(const EvadPseudo& P, int e, int j, i
     } else {
         const float dx = __fsub_rn(P.pos[(int64_t)j * P.ld_pos], P.pos[(int64_t)i * P.ld_pos]);
         const float dy = __fsub_rn(P.pos[(int64_t)j * P.ld_pos + 1], P.pos[(int64_t)i * P.ld_pos + 1]);
-        a0 = __fadd_rn(__fdiv_rn(dx, P.two_m), 0.5f);
-        a1 = __fadd_rn(__fdiv_rn(dy, P.two_m), 0.5f);
+        // torch on CUDA divides a tensor by a Python scalar as a multiplication with the fp32 reciprocal
+        // (BinaryDivTrueKernel.cu, is_cpu_scalar branch): T.Cartesian's `cart / (2 * max_value)` as the reference runs it
+        const float inv = __fdiv_rn(1.0f, P.two_m);
+        a0 = __fadd_rn(__fmul_rn(dx, inv), 0.5f);
+        a1 = __fadd_rn(__fmul_rn(dy, inv), 0.5f);
         if (P.clamp01) {
             a0 = fminf(fmaxf(a0, 0.f), 1.f);
             a1 = fminf(fmaxf(a1, 0.f), 1.f);

@@ -283,7 +283,7 @@ def offset_class_is_lut_class(mode, two_m, clamp01, width, height):
         valid = (pj_idx >= 0) & (pj_idx < ext)
         pi = pix.float() / torch.tensor(float(ext))
         pj = pj_idx.clamp(0, ext - 1).float() / torch.tensor(float(ext))
-        a = (pj - pi[:, None]) / tm + torch.tensor(0.5)
+        a = (pj - pi[:, None]) * (torch.tensor(1.0) / tm) + torch.tensor(0.5)     # CUDA: multiply by the reciprocal
         if clamp01:
             a = a.clamp(0, 1)
         idx = (a * torch.tensor(coef, dtype=torch.float32) + torch.tensor(off, dtype=torch.float32) +

@@ -62,8 +62,15 @@ def cartesian(pos: torch.Tensor, edge_index: torch.Tensor, max_value):
     row, col = edge_index[0], edge_index[1]
     cart = pos[row] - pos[col]
     if cart.numel() > 0:
-        cart = cart / (2 * max_value) + 0.5
+        cart = cart * cuda_scalar_reciprocal(2 * max_value) + 0.5
     return cart
+
+
+def cuda_scalar_reciprocal(scalar):
+    """`tensor / python_scalar` as torch evaluates it ON CUDA, where the reference runs: the scalar is converted to fp32,
+    its reciprocal is taken in fp32 and the tensor is MULTIPLIED by it (ATen/native/cuda/BinaryDivTrueKernel.cu,
+    `iter.is_cpu_scalar(2)` branch); differs from the CPU's true division by up to 1 ulp."""
+    return torch.tensor(1.0, dtype=torch.float32) / torch.tensor(float(scalar), dtype=torch.float32)
 
 
 # ---------------------------------------------------------------------------------------------

@@ -133,7 +133,7 @@ def _pyg_modules():
             cart = cart.view(-1, 1) if cart.dim() == 1 else cart
             if self.norm and cart.numel() > 0:
                 max_value = cart.abs().max() if self.max is None else self.max
-                cart = cart / (2 * max_value) + 0.5
+                cart = cart * dagr_ops.cuda_scalar_reciprocal(2 * max_value) + 0.5    # the division as CUDA does it
             if pseudo is not None and self.cat:
                 pseudo = pseudo.view(-1, 1) if pseudo.dim() == 1 else pseudo
                 data.edge_attr = torch.cat([pseudo, cart.type_as(pseudo)], dim=-1)
