@@ -16,7 +16,8 @@ ERRORS = {-1: "EVAD_ERR_ARG (bad argument)", -2: "EVAD_ERR_WORKSPACE (workspace 
           -3: "EVAD_ERR_LAUNCH (CUDA launch failed)", -4: "EVAD_ERR_UNSUPPORTED",
           -5: "EVAD_ERR_STATIC_LIMIT (size beyond the static-scratch entry point's maximum)"}
 STATUS_BITS = {1: "event outside the sensor / batch range", 2: "LUT offset outside its table",
-               4: "voxel id outside the cluster table", 8: "coarse edge buffer overflow"}
+               4: "voxel id outside the cluster table", 8: "coarse edge buffer overflow",
+               16: "feature value with |v| >= 2048 in the fp16-pair layer-1 kernel (set EVAD_L1_H16=0)"}
 
 c_p = ctypes.c_void_p
 c_i = ctypes.c_int
@@ -100,6 +101,9 @@ def _declare(L):
                                              c_p, c_i, P(EpilogueT), c_p, c_i, c_p])
     _sig(L, "evad_spline_conv_l1_tc5", c_i, [c_p, c_p, c_p, c_p, c_i64, c_p, c_i, c_i, c_p, c_i, c_p, c_f, c_p, c_f, P(EpilogueT),
                                              c_p, c_i, P(EpilogueT), c_p, c_i, c_p])
+    _sig(L, "evad_split_h2", c_i, [c_p, c_p, c_i64, c_p, c_p])
+    _sig(L, "evad_spline_conv_l1_h16", c_i, [c_p, c_p, c_p, c_p, c_i64, c_p, c_i, c_i, c_p, c_i, c_p, c_p, c_p, c_p, P(EpilogueT),
+                                             c_p, c_i, c_i, P(EpilogueT), c_p, c_i, c_p, c_p])
     _sig(L, "evad_spline_tap_lists", c_i, [c_p, c_p, c_i64, c_p, P(PseudoT), P(SplineModeT), c_p, c_p, c_p, c_p])
     _sig(L, "evad_spline_conv64_fused_ws_bytes", c_sz, [c_i64, c_i])
     _sig(L, "evad_spline_conv64_fused", c_i, [c_p, c_p, c_p, c_i, c_i64, c_p, c_i, c_i, c_p, c_p, c_i64, P(EpilogueT),

@@ -90,13 +90,17 @@ class Layer(torch.nn.Module):
         if USE_FUSED and b1.conv.out_channels == 64 and b2.conv.out_channels == 64 and n_cap >= FUSED_MIN_ROWS and sm[2]:
             # both convolutions see the same graph and pseudo-coordinates: one tap-sorted entry list serves both
             lists = ops.spline_tap_lists(rowptr, src, n_cap, n_dev, src.shape[0], b1.conv.mode(), pseudo, status)
+        # fp16-pair layer-1 kernel: the first convolution hands its output to the second one as h2 words (ops.split_h2)
+        mid_h2 = bool(relu and cls is not None and n_dev is None and ops.l1_h16_ok(src, cls, ell_stride) and
+                      b1.conv.small_ok() and b2.conv.small_ok() and b1.conv.l1_pack(b2.lin.mlp.weight) is not None and
+                      b2.conv.l1_pack() is not None)
         y, skip = b1.conv.run(x, rowptr, src, n_cap, n_dev, pseudo, dict(scale=s1, shift=h1, relu=relu), status, lists=lists,
                               skip_weight=b2.lin.mlp.weight, skip_epi=dict(scale=ss, shift=hs), cls=cls, perm=perm,
-                              ell_stride=ell_stride)
+                              ell_stride=ell_stride, out_h2=mid_h2)
         if not relu:
             y = b1.activation(y)
         out, _ = b2.conv.run(y, rowptr, src, n_cap, n_dev, pseudo, dict(scale=s2, shift=h2, addend=skip, relu=relu), status, lists=lists,
-                             cls=cls, perm=perm, ell_stride=ell_stride)
+                             cls=cls, perm=perm, ell_stride=ell_stride, x_h2=mid_h2)
         if not relu:
             out = b2.activation(out)
         return out

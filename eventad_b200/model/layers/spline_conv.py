@@ -207,7 +207,7 @@ class MySplineConv(torch.nn.Module):
 
     # ---- kernels ---------------------------------------------------------------------------------------------
     def run(self, x, rowptr, src, n_cap, n_dev, pseudo, epi, status, skip_weight=None, skip_epi=None, cls=None,
-            perm=None, ell_stride=0, lists=None):
+            perm=None, ell_stride=0, lists=None, x_h2=False, out_h2=False):
         """x [n_cap, >=Cin] float32 -> epi(conv(x)) [n_cap, Cout] (+ skip_epi(x @ skip_weight^T) when requested)."""
         cin = self.in_channels
         if self.small_ok() and n_dev is None:
@@ -223,7 +223,8 @@ class MySplineConv(torch.nn.Module):
                     assert ell_stride == 0
                     cls = ops.edge_class(rowptr, src, n_cap, self.mode(), pseudo, status)
                 return ops.spline_conv_l1(rowptr, src, cls, n_cap, x, cin, pack, epi, skip_epi, perm=perm,
-                                          ell_stride=ell_stride)
+                                          ell_stride=ell_stride, x_h2=x_h2, out_h2=out_h2, status=status)
+            assert not x_h2 and not out_h2
             assert ell_stride == 0, "fixed-stride rows are only read by the layer-1 tensor-core kernel"
             return ops.spline_conv_small(rowptr, src, n_cap, x, cin, self.small_lut(skip_weight), self.mode(), pseudo, epi,
                                          status, skip_epi)

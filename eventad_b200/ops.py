@@ -311,6 +311,20 @@ USE_L1_MMA = os.environ.get("EVAD_L1_MMA", "1") != "0"
 USE_L1_TC5 = os.environ.get("EVAD_L1_TC5", "0") == "1"   # measured slower than the mma.sync kernel (profiles/r02_summary.md): opt-in
 
 
+# EVAD_L1_H16=0: keep layer 1 on the 3xTF32 mma.sync kernel (evad_spline_conv_l1_mma) instead of the fp16-pair kernel
+USE_L1_H16 = os.environ.get("EVAD_L1_H16", "1") != "0"
+
+
+def split_h2(x, status=None):
+    """fp32 rows -> "h2 words" (fp16 leading part | fp16 remainder * 2048, include/eventad_b200.h): the operand format of
+    evad_spline_conv_l1_h16.  Returned with dtype float32 (same bytes); |x| >= 2048 raises EVAD_STATUS_H16_RANGE."""
+    assert x.is_contiguous() and x.numel() % 4 == 0
+    out = torch.empty_like(x)
+    with _timed('split_h2'):
+        check(_lib.lib().evad_split_h2(ptr(x), ptr(out), x.numel(), ptr(status), stream()), "evad_split_h2")
+    return out
+
+
 def l1_kmap(cin_pad):
     """K index of the tcgen05 layer-1 contraction -> (slot, channel); the operand order of csrc/spline_l1_tc5.cu."""
     nch = 5 if cin_pad > 16 else 4
@@ -358,15 +372,36 @@ def l1_pack16(W, S, cin_pad):
     return pack
 
 
-def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None, perm=None, ell_stride=0):
+def l1_h16_ok(src, cls, ell_stride):
+    """True when spline_conv_l1 will take the fp16-pair kernel (fixed-stride rows of 16, aligned)."""
+    return (USE_L1_MMA and USE_L1_H16 and not USE_L1_TC5 and ell_stride == 16 and cls is not None and
+            src.data_ptr() % 16 == 0 and cls.data_ptr() % 16 == 0)
+
+
+def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None, perm=None, ell_stride=0, x_h2=False,
+                   out_h2=False, status=None):
     """Tap aggregation + tensor-core contraction, cout = 16.  pack = dict(tapw, whi, wlo, shi, slo, cin_pad).
-    ell_stride > 0: fixed-stride rows (graph build_rows): rowptr = row lengths [n], src / cls rows at i * ell_stride."""
+    ell_stride > 0: fixed-stride rows (graph build_rows): rowptr = row lengths [n], src / cls rows at i * ell_stride.
+    x_h2 / out_h2 (fp16-pair kernel only, `l1_h16_ok`): x already holds h2 words / the output is wanted as h2 words."""
     L = _lib.lib()
     out = torch.empty((n, 16), dtype=torch.float32, device=x.device)
     has_skip = skip_epi is not None and pack.get("shi") is not None
     skip_out = torch.empty((n, 16), dtype=torch.float32, device=x.device) if has_skip else None
     e = _epi_struct(**epi)
     se = _epi_struct(**skip_epi) if has_skip else None
+    if l1_h16_ok(src, cls, ell_stride):
+        if not x_h2:
+            x = split_h2(x.contiguous(), status)
+        with _timed(f'spline_conv_l1_c{cin}'):
+            check(L.evad_spline_conv_l1_h16(ptr(rowptr), ptr(src), ptr(cls), ptr(perm), n, ptr(x), x.stride(0), pack["cin_pad"],
+                                            ptr(pack["tapw"]), pack["tapw"].shape[0], ptr(pack["whi"]), ptr(pack["wlo"]),
+                                            ptr(pack["shi"]) if has_skip else None, ptr(pack["slo"]) if has_skip else None,
+                                            ctypes.byref(e), ptr(out), out.stride(0), int(out_h2),
+                                            ctypes.byref(se) if has_skip else None, ptr(skip_out),
+                                            skip_out.stride(0) if has_skip else 0, ptr(status), stream()),
+                  "evad_spline_conv_l1_h16")
+        return out, skip_out
+    assert not x_h2 and not out_h2, "h2 words are only understood by evad_spline_conv_l1_h16"
     if (USE_L1_MMA and USE_L1_TC5 and pack.get("w16") is not None and ell_stride == 16 and src.data_ptr() % 16 == 0 and
             cls.data_ptr() % 16 == 0):
         with _timed(f'spline_conv_l1_c{cin}'):

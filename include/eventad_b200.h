@@ -36,6 +36,7 @@ extern "C" {
 #define EVAD_STATUS_LUT_OOB 2u       /* LUT offset outside [-r, r] (reference would index out of range) */
 #define EVAD_STATUS_CLUSTER_OOB 4u   /* voxel id outside the cluster table (t >= 2.0 or pos outside [0,1)) */
 #define EVAD_STATUS_EDGE_OVERFLOW 8u /* coarse edge buffer too small */
+#define EVAD_STATUS_H16_RANGE 16u    /* a value with |v| >= 2048 met the fp16-pair ("h2") operand format of evad_spline_conv_l1_h16 */
 
 int evad_version(void);
 /* returns the SM architecture the library was compiled for (100) */
@@ -233,6 +234,20 @@ int evad_spline_conv_l1_tc5(const int32_t* count, const int32_t* nbr, const uint
                             const uint16_t* w16, float inv_sw, const uint16_t* s16, float inv_ss,
                             const evad_epilogue_t* epi_h, float* out, int ldo, const evad_epilogue_t* skip_epi_h,
                             float* skip_out, int ld_skip, void* stream);
+
+/* Layer-1 block as evad_spline_conv_l1_mma (same reference lines: spline_conv.py:39-47,72-76, conv.py:23-28,47-56), with
+ * both tensor-core products on fp16 operand pairs (mma.sync m16n8k16, csrc/spline_l1_h16.cu): half the HMMA per node.
+ * x_h2: node features as "h2 words" (low half = rn16(v), high half = rn16((v - hi) * 2048); |v| < 2048), produced by
+ * evad_split_h2 from fp32 rows or by this entry point itself when out_h2 != 0 (the layer's second convolution gathers the
+ * first one's output).  Weights as for evad_spline_conv_l1_mma (the TF32 pair; their sum is re-split in the kernel).
+ * status: device word, EVAD_STATUS_H16_RANGE is raised when an h2 output leaves the range (may be NULL). */
+int evad_split_h2(const float* in, uint32_t* out, int64_t n_words, uint32_t* status, void* stream);
+int evad_spline_conv_l1_h16(const int32_t* count, const int32_t* nbr, const uint8_t* nbr_cls, const int32_t* perm,
+                            int64_t n, const uint32_t* x_h2, int ldx, int cin_pad, const float* tapw, int ncls,
+                            const float* Whi, const float* Wlo, const float* Shi, const float* Slo,
+                            const evad_epilogue_t* epi_h, float* out, int ldo, int out_h2,
+                            const evad_epilogue_t* skip_epi_h, float* skip_out, int ld_skip, uint32_t* status,
+                            void* stream);
 
 /* The same contraction on the tensor cores for N = 64 (csrc/gemm_tc.cu): every product is split into TF32 parts
  * (a_hi + a_lo)(w_hi + w_lo) and accumulated in fp32 as a_lo*w_hi + a_hi*w_lo + a_hi*w_hi, so the result keeps fp32

@@ -65,16 +65,29 @@ def _case(n, cin, with_skip, with_perm, seed, full_rows=False):
     args = (count.to(dev), nbr.to(dev).view(-1), cls.to(dev).view(-1), n, x.to(dev), cin, pack, epi, sepi)
     kw = dict(perm=perm.to(dev) if perm is not None else None, ell_stride=16)
     res = {}
-    # "tc5": mma.sync aggregation + tcgen05 contraction (csrc/spline_l1_tc5.cu); True: both products on mma.sync;
-    # False: FFMA aggregation + mma.sync contraction
-    for flag, (use_mma, use_tc5) in (("tc5", (True, True)), (True, (True, False)), (False, (False, False))):
-        old = ops.USE_L1_MMA, ops.USE_L1_TC5
-        ops.USE_L1_MMA, ops.USE_L1_TC5 = use_mma, use_tc5
+    # "h16": both products as fp16-pair mma.sync m16n8k16 (csrc/spline_l1_h16.cu, the default); "h16w": the same with
+    # input and output as h2 words (how the two convolutions of the layer are chained); "tc5": mma.sync aggregation +
+    # tcgen05 contraction (csrc/spline_l1_tc5.cu); True: both products as 3xTF32 mma.sync; False: FFMA aggregation
+    status = ops.new_status(dev)
+    for flag, (use_mma, use_tc5, use_h16) in (("h16", (True, False, True)), ("h16w", (True, False, True)),
+                                              ("tc5", (True, True, False)), (True, (True, False, False)),
+                                              (False, (False, False, False))):
+        old = ops.USE_L1_MMA, ops.USE_L1_TC5, ops.USE_L1_H16
+        ops.USE_L1_MMA, ops.USE_L1_TC5, ops.USE_L1_H16 = use_mma, use_tc5, use_h16
         try:
-            res[flag] = ops.spline_conv_l1(*args, **kw)
+            if flag == "h16w":
+                a2 = list(args)
+                a2[4] = ops.split_h2(args[4], status)
+                o, sk = ops.spline_conv_l1(*a2, **kw, x_h2=True, out_h2=True, status=status)
+                h = o.view(torch.int32)
+                lo16, hi16 = (h & 0xffff).to(torch.int16).view(torch.float16), (h >> 16).to(torch.int16).view(torch.float16)
+                res[flag] = (lo16.float() + hi16.float() / 2048.0, sk)
+            else:
+                res[flag] = ops.spline_conv_l1(*args, **kw, status=status)
         finally:
-            ops.USE_L1_MMA, ops.USE_L1_TC5 = old
+            ops.USE_L1_MMA, ops.USE_L1_TC5, ops.USE_L1_H16 = old
     torch.cuda.synchronize()
+    assert int(status.item()) == 0
     for flag, (out, skip) in res.items():
         err = (out.double().cpu() - ref).abs()
         assert bool((err <= 2e-6 + 2e-5 * ref.abs() + 1e-6 * mag).all()), (flag, float(err.max()), float((err / mag).max()))
@@ -85,7 +98,7 @@ def _case(n, cin, with_skip, with_perm, seed, full_rows=False):
             assert skip is None
     # the two variants sum the same 320 terms in different orders: north_star's rtol 1e-4 / atol 1e-5 plus the
     # cancellation term of the fp64 bar (the synthetic features here are far larger than real layer inputs)
-    for other in (False, "tc5"):
+    for other in (False, "tc5", "h16", "h16w"):
         diff = (res[True][0] - res[other][0]).abs().double().cpu()
         assert bool((diff <= 1e-5 + 1e-4 * ref.abs() + 2e-6 * mag).all()), (other, float(diff.max()))
 
@@ -125,3 +138,15 @@ def test_l1_mma_rejects_what_it_cannot_read():
     assert call(nbr[1:], 16) != 0          # rows not 16-byte aligned
     assert call(nbr, 24) != 0              # channel width without a kernel
     torch.cuda.synchronize()
+
+
+def test_l1_h16_raises_the_range_bit():
+    """|x| >= 2048 does not fit the fp16-pair operand format: evad_split_h2 raises EVAD_STATUS_H16_RANGE."""
+    from eventad_b200 import ops
+    status = ops.new_status("cuda")
+    x = torch.zeros(8, 16, device="cuda")
+    ops.split_h2(x, status)
+    assert int(status.item()) == 0
+    x[3, 5] = -3000.0
+    ops.split_h2(x, status)
+    assert int(status.item()) == 16
