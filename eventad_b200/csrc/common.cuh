@@ -1,5 +1,6 @@
 // eventad_b200/csrc/common.cuh -- shared helpers for the sm_100a kernels (no torch headers anywhere in csrc/).
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stddef.h>
@@ -57,6 +58,14 @@ int evad_sort_pairs_u32(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, 
 // deterministic split-K reduce + epilogue for [m, 64] outputs (gemm_tc.cu): out = epi(sum_y partial[y][m][64])
 int evad_gemm64_reduce(const float* partial, int splits, int64_t m, const int32_t* m_dev, const evad_epilogue_t* E,
                        float* out, int ldo, cudaStream_t st);
+
+// "h2 word" of an fp32 value (operand format of csrc/spline_l1_h16.cu): low half = rn16(v), high half = rn16((v - hi) * 2048)
+#define EVAD_H2_RANGE 2048.f
+__device__ __forceinline__ uint32_t evad_h2_split(float v) {
+    const __half h = __float2half_rn(v);
+    const __half l = __float2half_rn(__fmul_rn(__fsub_rn(v, __half2float(h)), 2048.f));
+    return (uint32_t)__half_as_ushort(h) | ((uint32_t)__half_as_ushort(l) << 16);
+}
 
 __device__ __forceinline__ unsigned evad_lanemask_lt() {
     unsigned m;

@@ -231,12 +231,14 @@ __global__ void __launch_bounds__(256) sample_concat_quad_kernel(const float* __
 // Layer-1 shape (one polarity channel + 16 sampled channels + position, rows of 20 floats): one thread per node builds
 // the whole row in registers -- taps resolved once per node instead of once per channel quad, and the row leaves as five
 // 128-bit stores instead of twenty 32-bit ones.
-template <int CX, int C, int LDO>
+// H2: the row leaves as "h2 words" (evad_h2_split), the input format of evad_spline_conv_l1_h16.
+template <int CX, int C, int LDO, bool H2>
 __global__ void __launch_bounds__(256) sample_concat_row_kernel(const float* __restrict__ x, int ldx,
                                                                 const float* __restrict__ pos, int ld_pos,
                                                                 const int32_t* __restrict__ batch, int64_t n_cap,
                                                                 const int32_t* __restrict__ n_dev, PoolSample S,
-                                                                int append_pos, float* __restrict__ out) {
+                                                                int append_pos, float* __restrict__ out,
+                                                                uint32_t* __restrict__ status) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t n = n_dev ? min((int64_t)*n_dev, n_cap) : n_cap;
     if (i >= n) return;
@@ -263,6 +265,18 @@ __global__ void __launch_bounds__(256) sample_concat_row_kernel(const float* __r
         }
     }
     if (append_pos) { row[CX + C] = px; row[CX + C + 1] = py; }
+    if (H2) {
+        bool ok = true;
+#pragma unroll
+        for (int c = 0; c < LDO; c++) ok = ok && fabsf(row[c]) < EVAD_H2_RANGE;
+        if (!ok && status) atomicOr(status, EVAD_STATUS_H16_RANGE);
+        uint4* o = reinterpret_cast<uint4*>(out + i * LDO);
+#pragma unroll
+        for (int c = 0; c < LDO / 4; c++)
+            o[c] = make_uint4(evad_h2_split(row[4 * c]), evad_h2_split(row[4 * c + 1]), evad_h2_split(row[4 * c + 2]),
+                              evad_h2_split(row[4 * c + 3]));
+        return;
+    }
     float4* o = reinterpret_cast<float4*>(out + i * LDO);
 #pragma unroll
     for (int c = 0; c < LDO / 4; c++) o[c] = make_float4(row[4 * c], row[4 * c + 1], row[4 * c + 2], row[4 * c + 3]);
@@ -278,8 +292,8 @@ extern "C" int evad_sample_concat(const float* x, int ldx, int cx, const float* 
     if (n_cap == 0) return EVAD_OK;
     PoolSample S{feat, feat_b, feat_h, feat_w, feat_c, width, height};
     if (feat && cx == 1 && feat_c == 16 && ldo == 20 && (((uintptr_t)feat | (uintptr_t)out) & 15) == 0) {
-        sample_concat_row_kernel<1, 16, 20><<<evad_cdiv(n_cap, 256), 256, 0, (cudaStream_t)stream>>>(
-            x, ldx, pos, ld_pos, batch, n_cap, n_dev, S, append_pos, out);
+        sample_concat_row_kernel<1, 16, 20, false><<<evad_cdiv(n_cap, 256), 256, 0, (cudaStream_t)stream>>>(
+            x, ldx, pos, ld_pos, batch, n_cap, n_dev, S, append_pos, out, nullptr);
         EVAD_CHECK_LAUNCH();
         return EVAD_OK;
     }
@@ -293,6 +307,24 @@ extern "C" int evad_sample_concat(const float* x, int ldx, int cx, const float* 
     sample_concat_kernel<<<evad_cdiv(n_cap * ldo, 256), 256, 0, (cudaStream_t)stream>>>(x, ldx, cx, pos, ld_pos, batch,
                                                                                       n_cap, n_dev, S, append_pos, out,
                                                                                       ldo);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
+// the layer-1 row shape of evad_sample_concat (one polarity channel + 16 sampled channels + position, rows of 20) with the
+// row written as h2 words for evad_spline_conv_l1_h16; EVAD_ERR_UNSUPPORTED for any other shape (caller: evad_sample_concat
+// + evad_split_h2)
+extern "C" int evad_sample_concat_h2(const float* x, int ldx, int cx, const float* pos, int ld_pos, const int32_t* batch,
+                                     int64_t n_cap, const int32_t* n_dev, const float* feat, int feat_b, int feat_h,
+                                     int feat_w, int feat_c, float width, float height, int append_pos, uint32_t* out,
+                                     int ldo, uint32_t* status, void* stream) {
+    if (!pos || !out || n_cap < 0 || cx < 0 || (cx > 0 && !x) || (feat && !batch)) return EVAD_ERR_ARG;
+    if (!(feat && cx == 1 && feat_c == 16 && ldo == 20 && (((uintptr_t)feat | (uintptr_t)out) & 15) == 0))
+        return EVAD_ERR_UNSUPPORTED;
+    if (n_cap == 0) return EVAD_OK;
+    PoolSample S{feat, feat_b, feat_h, feat_w, feat_c, width, height};
+    sample_concat_row_kernel<1, 16, 20, true><<<evad_cdiv(n_cap, 256), 256, 0, (cudaStream_t)stream>>>(
+        x, ldx, pos, ld_pos, batch, n_cap, n_dev, S, append_pos, reinterpret_cast<float*>(out), status);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }

@@ -32,7 +32,7 @@
 #define L1H_TW_LD 24                  // words per class row of the tap table: 8 x (hi pair, lo pair) + pad
 #define L1H_LDC 20                    // C tile row stride (floats)
 #define L1H_AUX 128                   // words: node ids of the tile [2 parities][32] + epilogue scale / shift [4][16]
-#define L1H_RANGE 2048.f              // |v| bound of an h2 word (P sums 16 of them: < 32768 < 65504)
+#define L1H_RANGE EVAD_H2_RANGE        // |v| bound of an h2 word (P sums 16 of them: < 32768 < 65504)
 
 template <int CP>
 struct L1HCfg {
@@ -59,15 +59,11 @@ struct L1HCfg {
 
 struct L1HHead {                      // what a lane keeps of one node's row: id, length, its 4 sources and their classes
     int i, deg;
-    int s[4];
-    uint32_t c;                       // class bytes of row positions t, t+4, t+8, t+12
+    uint32_t s[4];                    // sources of row positions t, t+4, t+8, t+12, clamped to valid rows
+    uint32_t c;                       // their class bytes; positions beyond the row length hold the all-zero class
 };
 
-__device__ __forceinline__ uint32_t l1h_split(float v) {     // fp32 -> h2 word
-    const __half h = __float2half_rn(v);
-    const __half l = __float2half_rn(__fmul_rn(__fsub_rn(v, __half2float(h)), 2048.f));
-    return (uint32_t)__half_as_ushort(h) | ((uint32_t)__half_as_ushort(l) << 16);
-}
+__device__ __forceinline__ uint32_t l1h_split(float v) { return evad_h2_split(v); }
 __device__ __forceinline__ float l1h_join(uint32_t w) {      // h2 word -> fp32
     return __fmaf_rn(__half2float(__ushort_as_half((unsigned short)(w >> 16))), 1.f / 2048.f,
                      __half2float(__ushort_as_half((unsigned short)(w & 0xffffu))));
@@ -183,12 +179,16 @@ __global__ void __launch_bounds__(L1H_THREADS, 2) spline_l1_h16_kernel(
 
     const int mt = warp & 1, kq = warp >> 1;                 // contraction role: m16 tile, k quarter
     const int64_t ntiles = (n + L1H_NODES - 1) / L1H_NODES;
-    const uint32_t tw_zero = (uint32_t)ncls;
-    const uint32_t* xg = x + 2 * g;                          // lane bases of the row gathers (offsets fit 32 bits)
-    const uint32_t* xg16 = x + 16 + g;
-    const uint32_t* xt = x + 4 * t;
-    const uint32_t uldx = (uint32_t)ldx;
+    const uint32_t zero4 = (uint32_t)ncls * 0x01010101u;     // four copies of the all-zero class
+    const uint32_t nmax = (uint32_t)(n - 1);
+    // lane bases of the row gathers; an address is base + row * (4 ldx) as ONE 32 x 32 + 64 bit multiply-add
+    const char* xg = reinterpret_cast<const char*>(x + 2 * g);
+    const char* xg16 = reinterpret_cast<const char*>(x + 16 + g);
+    const char* xt = reinterpret_cast<const char*>(x + 4 * t);
+    const char* xt16 = reinterpret_cast<const char*>(x + 16 + 2 * t);
+    const uint32_t ldxb = 4u * (uint32_t)ldx;
 
+    const uint32_t* twg = tw + 2 * g;
     L1HHead hd[4];
     uint4 craw[4];
     int inext[4];
@@ -208,11 +208,12 @@ __global__ void __launch_bounds__(L1H_THREADS, 2) spline_l1_h16_kernel(
             hd[k].deg = 0;
             craw[k] = make_uint4(0, 0, 0, 0);
 #pragma unroll
-            for (int j = 0; j < 4; j++) hd[k].s[j] = 0;
+            for (int j = 0; j < 4; j++) hd[k].s[j] = 0u;
             if (i >= 0) {
-                hd[k].deg = count[i];
+                hd[k].deg = __ldg(count + i);
                 craw[k] = __ldg(reinterpret_cast<const uint4*>(cls) + i);
-                const int32_t* srow = src + ((uint32_t)i * 16u + (uint32_t)t);
+                const uint32_t* srow = reinterpret_cast<const uint32_t*>(
+                    reinterpret_cast<const char*>(src + t) + (uint64_t)(uint32_t)i * 64u);
 #pragma unroll
                 for (int j = 0; j < 4; j++) hd[k].s[j] = __ldg(srow + 4 * j);
             }
@@ -220,29 +221,34 @@ __global__ void __launch_bounds__(L1H_THREADS, 2) spline_l1_h16_kernel(
     };
     auto pack_classes = [&]() {
 #pragma unroll
-        for (int k = 0; k < 4; k++)
-            hd[k].c = __byte_perm(__byte_perm(craw[k].x, craw[k].y, t | ((4 + t) << 4)),
-                                  __byte_perm(craw[k].z, craw[k].w, t | ((4 + t) << 4)), 0x5410);
+        for (int k = 0; k < 4; k++) {
+            const uint32_t c = __byte_perm(__byte_perm(craw[k].x, craw[k].y, t | ((4 + t) << 4)),
+                                           __byte_perm(craw[k].z, craw[k].w, t | ((4 + t) << 4)), 0x5410);
+            // positions t + 4j < deg  <=>  j < nv; slots beyond the row hold garbage: all-zero class, any valid source row
+            const int nv = min(4, (hd[k].deg - t + 3) >> 2);
+            const uint32_t live = __funnelshift_rc(0xffffffffu, 0u, 32 - 8 * nv);
+            hd[k].c = (c & live) | (zero4 & ~live);
+#pragma unroll
+            for (int j = 0; j < 4; j++) hd[k].s[j] = min(hd[k].s[j], nmax);
+        }
     };
     uint2 xa[2][4];                                          // [buffer][row position j]: h2 words of channels 2g, 2g+1
     uint32_t xb[2][4];                                       // channel 16 + g (Cin 20)
     uint4 xr[2];                                             // the node's own row (lanes g == 7): channels 4t..4t+3
     uint2 xr2[2];                                            //   and 16+2t, 17+2t
     auto gather = [&](int k, int buf) {
-        const int i = hd[k].i < 0 ? 0 : hd[k].i;
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            const int sj = (4 * j + t) < hd[k].deg ? hd[k].s[j] : i;   // empty slots read the node's own (valid) row
-            const uint32_t off = (uint32_t)sj * uldx;
+            const uint64_t off = (uint64_t)hd[k].s[j] * ldxb;
             xa[buf][j] = __ldg(reinterpret_cast<const uint2*>(xg + off));
-            if (CP > 16) xb[buf][j] = g < 4 ? __ldg(xg16 + off) : 0u;
+            if (CP > 16) xb[buf][j] = g < 4 ? __ldg(reinterpret_cast<const uint32_t*>(xg16 + off)) : 0u;
         }
         xr[buf] = make_uint4(0u, 0u, 0u, 0u);
         xr2[buf] = make_uint2(0u, 0u);
         if (g == 7 && hd[k].i >= 0) {
-            const uint32_t off = (uint32_t)i * uldx;
+            const uint64_t off = (uint64_t)(uint32_t)hd[k].i * ldxb;
             xr[buf] = __ldg(reinterpret_cast<const uint4*>(xt + off));
-            if (CP > 16 && t < 2) xr2[buf] = __ldg(reinterpret_cast<const uint2*>(x + off + 16 + 2 * t));
+            if (CP > 16 && t < 2) xr2[buf] = __ldg(reinterpret_cast<const uint2*>(xt16 + off));
         }
     };
     load_ids(blockIdx.x);
@@ -269,10 +275,9 @@ __global__ void __launch_bounds__(L1H_THREADS, 2) spline_l1_h16_kernel(
             uint32_t ah[4], al[4];
 #pragma unroll
             for (int p = 0; p < 2; p++) {
-                const uint32_t c0 = (8 * p + t) < hd[k].deg ? ((hd[k].c >> (16 * p)) & 0xffu) : tw_zero;
-                const uint32_t c1 = (8 * p + 4 + t) < hd[k].deg ? ((hd[k].c >> (16 * p + 8)) & 0xffu) : tw_zero;
-                const uint2 r0 = *reinterpret_cast<const uint2*>(tw + c0 * L1H_TW_LD + 2 * g);
-                const uint2 r1 = *reinterpret_cast<const uint2*>(tw + c1 * L1H_TW_LD + 2 * g);
+                const uint32_t c0 = (hd[k].c >> (16 * p)) & 0xffu, c1 = (hd[k].c >> (16 * p + 8)) & 0xffu;
+                const uint2 r0 = *reinterpret_cast<const uint2*>(twg + c0 * L1H_TW_LD);
+                const uint2 r1 = *reinterpret_cast<const uint2*>(twg + c1 * L1H_TW_LD);
                 ah[2 * p] = L1H_LO(r0.x, r1.x);              // slot g,     positions j = 2p, 2p+1
                 ah[2 * p + 1] = L1H_HI(r0.x, r1.x);          // slot g + 8
                 al[2 * p] = L1H_LO(r0.y, r1.y);
@@ -479,7 +484,7 @@ extern "C" int evad_spline_conv_l1_h16(const int32_t* count, const int32_t* nbr,
     if (cin_pad != 16 && cin_pad != 20) return EVAD_ERR_UNSUPPORTED;
     if (n * 16 >= (1ll << 31) || n * (int64_t)ldx >= (1ll << 32)) return EVAD_ERR_ARG;   // 32-bit row offsets in the kernel
     if (epi_h->addend && ((((uintptr_t)epi_h->addend) & 15) != 0 || epi_h->ld_add % 4 != 0)) return EVAD_ERR_ARG;
-    if (ldx < cin_pad || ldx % 4 != 0 || ldo % 4 != 0 || ncls < 1 || ncls > 256) return EVAD_ERR_ARG;
+    if (ldx < cin_pad || ldx % 4 != 0 || ldo % 4 != 0 || ncls < 1 || ncls > 255) return EVAD_ERR_ARG;   // class ncls = the all-zero row, one byte
     if ((((uintptr_t)x_h2 | (uintptr_t)tapw | (uintptr_t)Whi | (uintptr_t)Wlo | (uintptr_t)out | (uintptr_t)nbr |
           (uintptr_t)nbr_cls) & 15) != 0)
         return EVAD_ERR_ARG;

@@ -70,7 +70,15 @@ class Layer(torch.nn.Module):
         self.conv_block2 = ConvBlockWithSkip(out_channels, out_channels, in_channels, args=args)
 
     # fused eval path on raw tensors (used by Layer.forward and by the fused Net.forward)
-    def run_fused(self, x, rowptr, src, n_cap, n_dev, pseudo, status, perm=None, cls=None, ell_stride=0):
+    def h16_chain_ok(self, src, cls, ell_stride, n_dev=None):
+        """True when both convolutions of the layer run on evad_spline_conv_l1_h16, so that features can travel between
+        them (and into the first one: run_fused(x_h2=True)) as h2 words."""
+        b1, b2 = self.conv_block1, self.conv_block2
+        return bool(b1.activation is torch.nn.functional.relu and cls is not None and n_dev is None and
+                    ops.l1_h16_ok(src, cls, ell_stride) and b1.conv.small_ok() and b2.conv.small_ok() and
+                    b1.conv.l1_pack(b2.lin.mlp.weight) is not None and b2.conv.l1_pack() is not None)
+
+    def run_fused(self, x, rowptr, src, n_cap, n_dev, pseudo, status, perm=None, cls=None, ell_stride=0, x_h2=False):
         b1, b2 = self.conv_block1, self.conv_block2
         relu = b1.activation is torch.nn.functional.relu
         s1, h1 = _fold(b1.norm, b1.conv.bias)
@@ -91,12 +99,11 @@ class Layer(torch.nn.Module):
             # both convolutions see the same graph and pseudo-coordinates: one tap-sorted entry list serves both
             lists = ops.spline_tap_lists(rowptr, src, n_cap, n_dev, src.shape[0], b1.conv.mode(), pseudo, status)
         # fp16-pair layer-1 kernel: the first convolution hands its output to the second one as h2 words (ops.split_h2)
-        mid_h2 = bool(relu and cls is not None and n_dev is None and ops.l1_h16_ok(src, cls, ell_stride) and
-                      b1.conv.small_ok() and b2.conv.small_ok() and b1.conv.l1_pack(b2.lin.mlp.weight) is not None and
-                      b2.conv.l1_pack() is not None)
+        mid_h2 = self.h16_chain_ok(src, cls, ell_stride, n_dev)
+        assert mid_h2 or not x_h2
         y, skip = b1.conv.run(x, rowptr, src, n_cap, n_dev, pseudo, dict(scale=s1, shift=h1, relu=relu), status, lists=lists,
                               skip_weight=b2.lin.mlp.weight, skip_epi=dict(scale=ss, shift=hs), cls=cls, perm=perm,
-                              ell_stride=ell_stride, out_h2=mid_h2)
+                              ell_stride=ell_stride, x_h2=x_h2, out_h2=mid_h2)
         if not relu:
             y = b1.activation(y)
         out, _ = b2.conv.run(y, rowptr, src, n_cap, n_dev, pseudo, dict(scale=s2, shift=h2, addend=skip, relu=relu), status, lists=lists,

@@ -254,11 +254,17 @@ class Net(torch.nn.Module):
             rowptr, src, ell, cls1 = graph["rowptr"], graph["src"], 0, None
         gc.max_index, gc.all_timestamps, gc._history = n, pos_int[:, 2], [(batch_i32, pos_int, 0)]   # AsyncGraph bookkeeping
         status = gc._status
-        x0 = ops.sample_concat(x, pos, batch_i32, f[0], width, height, append_pos=True, ldo=(cin1 + 3) // 4 * 4)
+        x0 = None
+        if cls1 is not None and cin1 == 19 and self.conv_block1.h16_chain_ok(src, cls1, ell):
+            # fp16-pair layer-1 kernel: x0 is produced as h2 words (ops.split_h2) by the sampling kernel itself
+            x0 = ops.sample_concat_h2(x, pos, batch_i32, f[0], width, height, status)
+        x0_h2 = x0 is not None
+        if x0 is None:
+            x0 = ops.sample_concat(x, pos, batch_i32, f[0], width, height, append_pos=True, ldo=(cin1 + 3) // 4 * 4)
         # layer 1 walks the nodes in pixel order: neighbouring destinations share their sources, so the row gathers
         # of a tile hit L1 instead of L2
         xk = self.conv_block1.run_fused(x0, rowptr, src, n, None, pseudo, status, perm=graph["cell_perm"], cls=cls1,
-                                        ell_stride=ell)
+                                        ell_stride=ell, x_h2=x0_h2)
         counts = torch.zeros(12, dtype=torch.int32, device=dev)
         pools = [self.pool1, self.pool2, self.pool3, self.pool4]
         layers = [self.layer2, self.layer3, self.layer4, self.layer5]

@@ -167,6 +167,23 @@ def sample_concat(x, pos, batch_i32, feat_nhwc, width, height, append_pos=False,
     return out
 
 
+def sample_concat_h2(x, pos, batch_i32, feat_nhwc, width, height, status):
+    """sample_concat for the layer-1 row shape ([polarity | 16 sampled channels | pos_xy | 0], rows of 20) written as h2
+    words (split_h2 fused into the producer); None when the shape is another one."""
+    if (x is None or feat_nhwc is None or x.shape[1] != 1 or feat_nhwc.shape[3] != 16 or pos.shape[0] == 0 or
+            feat_nhwc.data_ptr() % 16 != 0):
+        return None
+    n = pos.shape[0]
+    out = torch.empty((n, 20), dtype=torch.float32, device=pos.device)
+    x, pos = x.contiguous(), pos.contiguous()
+    fb, fh, fw, fc = feat_nhwc.shape
+    with _timed('sample_concat'):
+        check(_lib.lib().evad_sample_concat_h2(ptr(x), x.stride(0), 1, ptr(pos), pos.stride(0), ptr(batch_i32), n, None,
+                                               ptr(feat_nhwc), fb, fh, fw, fc, float(width), float(height), 1, ptr(out), 20,
+                                               ptr(status), stream()), "evad_sample_concat_h2")
+    return out
+
+
 # --------------------------------------------------------------------------------------------------- spline tables
 def spline_mode_basis(kernel_size: int):
     return dict(use_lut=0, ks=int(kernel_size), nx=0, ny=0, r=(0.0, 0.0, 0.0, 0.0), tab_k=None, tab_w=None)

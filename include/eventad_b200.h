@@ -353,6 +353,12 @@ int evad_denormalize_pos(const float* pos, int ld_pos, int64_t n, int width, int
 int evad_sample_concat(const float* x, int ldx, int cx, const float* pos, int ld_pos, const int32_t* batch,
                        int64_t n_cap, const int32_t* n_dev, const float* feat, int feat_b, int feat_h, int feat_w,
                        int feat_c, float width, float height, int append_pos, float* out, int ldo, void* stream);
+/* the same rows for the layer-1 shape (cx 1, feat_c 16, ldo 20) written as h2 words, the input of
+ * evad_spline_conv_l1_h16 (no separate evad_split_h2 pass); EVAD_ERR_UNSUPPORTED for other shapes. */
+int evad_sample_concat_h2(const float* x, int ldx, int cx, const float* pos, int ld_pos, const int32_t* batch,
+                          int64_t n_cap, const int32_t* n_dev, const float* feat, int feat_b, int feat_h, int feat_w,
+                          int feat_c, float width, float height, int append_pos, uint32_t* out, int ldo,
+                          uint32_t* status, void* stream);
 
 /* ---- EventAD head input: per-bounding-box pooling of the out4 graph (csrc/bbox_pool.cu) ----
  * Replaces the python loops of /root/reference/models/EventAD.py:382-397 and _process_bbox (:406-498): for every box
