@@ -6,20 +6,21 @@
 //   layers/conv.py:23-28,47-56 (eval BatchNorm, activation, skip Linear + BatchNorm).
 //
 // Same re-association as spline_l1_mma_kernel:  out_i = W_cat^T P_i,  P_i[slot] = sum_e tapw[class_e][slot] * x_src(e)
-// (15 tap slots + the node's own row as slot 15).  What changes (profiles/r01g_summary.md: that kernel is bound by the
-// L1 data pipe, 72 shared + 27 global wavefronts per node, and runs 33 legacy HMMA per node):
+// (15 tap slots + the node's own row as slot 15).  What changes against the mma.sync kernels:
 //   * the [tile x 16*Cin] @ [16*Cin x 16] contraction leaves mma.sync: a 128-node P tile is written ONCE to shared
 //     memory in the K-major SWIZZLE_128B operand layout and contracted by tcgen05.mma (M 128, N 16, K 16 per
 //     instruction) issued by one thread; the weights sit in shared memory behind UMMA descriptors for the life of the
-//     persistent CTA.  No weight-fragment or A-fragment LDS, no partial-sum tiles, 15 fewer HMMA per node.
-//   * fp32 accuracy without an 8-byte operand: every P row is block-scaled by a power of two (row maximum -> [2^13, 2^14))
-//     and split into two fp16 parts, P * s = p1 + p2 * 2^-11 (22 significant bits, the same for the weights,
-//     W * s_w = w1 + w2 * 2^-11, split once on the host), so the operand stays at 4 bytes per element = 160 KB per tile
-//     and three kind::f16 products (p1 w1 | p1 w2 + p2 w1) give 2^-22 relative accuracy; the leading product is
-//     accumulated in 64-column K chunks in separate TMEM accumulators that are added in fp32 registers (the tensor core
-//     truncates when it accumulates).
-//   * epilogue from tensor memory (tcgen05.ld, one row per thread): un-scale, BatchNorm, skip add, ReLU, 64-byte row store.
-// The per-node tap aggregation (gathers + 3xTF32 mma.sync m16n8k8, one warp per node) is spline_l1_mma_kernel's.
+//     persistent CTA.  No weight-fragment or A-fragment LDS, no partial-sum tiles.
+//   * fp32 accuracy without an 8-byte operand: P is split into two fp16 parts, P = p1 + p2 * 2^-11 (22 significant bits;
+//     the weights the same, W * s_w = w1 + w2 * 2^-11, split and block-scaled once on the host), so the operand stays at
+//     4 bytes per element = 160 KB per tile and three kind::f16 products (p1 w1 | p1 w2 + p2 w1) give 2^-22 relative
+//     accuracy; the leading product is accumulated in 64-column K chunks in separate TMEM accumulators that are added
+//     in fp32 registers (the tensor core truncates when it accumulates).
+//   * epilogue from tensor memory (tcgen05.ld, one row per thread): BatchNorm, skip add, ReLU, 64-byte row store.
+// The per-node tap aggregation is spline_l1_h16_kernel's (csrc/spline_l1_h16.cu): features arrive as h2 words, 9 / 6
+// mma.sync m16n8k16 per node, two accumulators (hi x hi | hi x lo + lo x hi) that are merged while P is split.
+// Measured (profiles/r02_summary.md): equal to spline_l1_h16_kernel at Cin 16, 30 % slower at Cin 20: opt-in
+// (EVAD_L1_TC5=1).
 #include <cuda_fp16.h>
 
 #include "spline_common.cuh"
@@ -30,7 +31,7 @@
 #define L1T_WARPS 16                  // producer warps (aggregation, operand conversion, epilogue)
 #define L1T_THREADS (32 * L1T_WARPS)
 #define L1T_SLOTS 16
-#define L1T_TW_LD 36                  // floats per class row of the tap table: 8 x (hi g, hi g+8, lo g, lo g+8) + pad
+#define L1T_TW_LD 24                  // words per class row of the tap table: 8 x (hi pair, lo pair) of (slot g, slot g+8) + pad
 #define L1T_CHUNK 16384               // bytes of one K chunk of the P tile: 128 rows x 64 halves
 #define L1T_WCHUNK 8192               // bytes of one K chunk of the weight operand: 64 rows [w2 | w1 | s1 | s2] x 64 halves
 #define L1T_ACC_COLS 256              // per K chunk ch < 3: 32 columns [p1 w2 | p1 w1]; ch 3, 4: 64 [p1 w2 | p1 w1 | p1 s1 | p1 s2];
@@ -48,18 +49,18 @@ struct L1TCfg {
     static constexpr int P_BYTES = 2 * NCH * L1T_CHUNK;      // p1 chunks, then p2 chunks
     static constexpr int W_BYTES = NCH * L1T_WCHUNK;         // per K chunk 64 operand rows: w2, w1, s1, s2 (16 each)
     static size_t smem_bytes(int ncls) {
-        return 1024 + (size_t)P_BYTES + W_BYTES + (size_t)(ncls + 1) * L1T_TW_LD * 4 + 4 * L1T_ROWS * 4 * 2 + 64 * 4 + 64;
+        return 1024 + (size_t)P_BYTES + W_BYTES + (size_t)(ncls + 1) * L1T_TW_LD * 4 + 4 * L1T_ROWS * 4 + 64 * 4 + 64;
     }
 };
 
 struct L1THead {                      // what a lane keeps of one node's row: id, length, its 4 sources and their classes
     int i, deg;
-    int s[4];
-    uint32_t c;                       // class bytes of row positions t, t+4, t+8, t+12
+    uint32_t s[4];                    // sources of row positions t, t+4, t+8, t+12, clamped to valid rows
+    uint32_t c;                       // their class bytes; positions beyond the row length hold the all-zero class
 };
 
 __device__ __forceinline__ void l1t_mma_sync(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+    asm("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
         : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
@@ -78,14 +79,17 @@ __device__ __forceinline__ void l1t_ldtm4(uint32_t taddr, uint32_t (&r)[4]) {
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr) : "memory");
 }
 
-// two fp32 values (already block-scaled) -> packed fp16 leading parts and packed fp16 remainders * 2^11
-__device__ __forceinline__ void l1t_split2(float a, float b, uint32_t* h1, uint32_t* h2) {
-    const __half2 p1 = __floats2half2_rn(a, b);
+// two fp32 values v + e * 2^-11 (the two accumulators of the aggregation) -> packed fp16 leading parts and packed fp16
+// remainders * 2^11
+__device__ __forceinline__ void l1t_split2(float v0, float e0, float v1, float e1, uint32_t* h1, uint32_t* h2) {
+    const __half2 p1 = __floats2half2_rn(v0, v1);
     const float2 f1 = __half22float2(p1);
-    const __half2 p2 = __floats2half2_rn(__fmul_rn(__fsub_rn(a, f1.x), 2048.f), __fmul_rn(__fsub_rn(b, f1.y), 2048.f));
+    const __half2 p2 = __floats2half2_rn(__fmaf_rn(__fsub_rn(v0, f1.x), 2048.f, e0), __fmaf_rn(__fsub_rn(v1, f1.y), 2048.f, e1));
     *h1 = *reinterpret_cast<const uint32_t*>(&p1);
     *h2 = *reinterpret_cast<const uint32_t*>(&p2);
 }
+#define L1T_LO(a, b) __byte_perm((a), (b), 0x5410)            // (low half of a, low half of b)
+#define L1T_HI(a, b) __byte_perm((a), (b), 0x7632)            // (high half of a, high half of b)
 
 // Operand layout (K index of the contraction -> (slot, channel)), chosen so that a lane's D fragments of the aggregation
 // are one 128-bit store per part:
@@ -104,9 +108,10 @@ __device__ __forceinline__ void l1t_split2(float a, float b, uint32_t* h1, uint3
 template <int CP>
 __global__ void __launch_bounds__(L1T_THREADS, 1) spline_l1_tc5_kernel(
     const int32_t* __restrict__ count, const int32_t* __restrict__ src, const uint8_t* __restrict__ cls,
-    const int32_t* __restrict__ perm, int64_t n, const float* __restrict__ x, int ldx, const float* __restrict__ tapw,
+    const int32_t* __restrict__ perm, int64_t n, const uint32_t* __restrict__ x, int ldx, const float* __restrict__ tapw,
     int ncls, const uint16_t* __restrict__ W16, float inv_sw, const uint16_t* __restrict__ S16, float inv_ss,
-    evad_epilogue_t E, float* __restrict__ out, int ldo, evad_epilogue_t ES, float* __restrict__ skip_out, int ld_skip) {
+    evad_epilogue_t E, float* __restrict__ out, int ldo, int out_h2, evad_epilogue_t ES, float* __restrict__ skip_out,
+    int ld_skip, uint32_t* __restrict__ status) {
     using C = L1TCfg<CP>;
     constexpr int NT = C::NT, NCH = C::NCH;
     extern __shared__ uint8_t l1t_smem[];
@@ -120,10 +125,9 @@ __global__ void __launch_bounds__(L1T_THREADS, 1) spline_l1_tc5_kernel(
     uint8_t* p_g = l1t_smem + (p_base - t5_smem(l1t_smem));
     const uint32_t w_base = p_base + C::P_BYTES;
     uint8_t* w_g = p_g + C::P_BYTES;
-    float* tw = reinterpret_cast<float*>(w_g + C::W_BYTES);
+    uint32_t* tw = reinterpret_cast<uint32_t*>(w_g + C::W_BYTES);
     int* ids = reinterpret_cast<int*>(tw + (ncls + 1) * L1T_TW_LD);    // [4 tiles in flight][128] node ids of the tile rows
-    float* rsc = reinterpret_cast<float*>(ids + 4 * L1T_ROWS);         // [4][128] row un-scale factors
-    float* epc = rsc + 4 * L1T_ROWS;                                   // epilogue scale / shift [4][16]
+    float* epc = reinterpret_cast<float*>(ids + 4 * L1T_ROWS);         // epilogue scale / shift [4][16]
 
     // ---------------------------------------------------------------- one-time staging
     if (tid == 0) {
@@ -157,18 +161,16 @@ __global__ void __launch_bounds__(L1T_THREADS, 1) spline_l1_tc5_kernel(
         }
         *reinterpret_cast<uint4*>(w_g + ch * L1T_WCHUNK + orow * 128 + ((u ^ (orow & 7)) << 4)) = v;
     }
-    // tap table, pre-split into TF32 parts: row c, unit k (16 bytes) = hi[k], hi[k + 8], lo[k], lo[k + 8]; row ncls = zeros
+    // tap table as h2 words: row c, lane group g: word 2g = (hi[c][g], hi[c][g+8]), word 2g+1 = (lo[c][g], lo[c][g+8]);
+    // row ncls = zeros
     for (int idx = tid; idx < (ncls + 1) * 8; idx += L1T_THREADS) {
         const int r = idx >> 3, k = idx & 7;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        uint32_t a = 0u, b = 0u;
         if (r < ncls) {
-            const float a = __ldg(tapw + r * L1T_SLOTS + k), b = __ldg(tapw + r * L1T_SLOTS + k + 8);
-            v.x = __uint_as_float(__float_as_uint(a) & 0xffffe000u);
-            v.y = __uint_as_float(__float_as_uint(b) & 0xffffe000u);
-            v.z = __fsub_rn(a, v.x);
-            v.w = __fsub_rn(b, v.y);
+            a = evad_h2_split(__ldg(tapw + r * L1T_SLOTS + k));
+            b = evad_h2_split(__ldg(tapw + r * L1T_SLOTS + k + 8));
         }
-        *reinterpret_cast<float4*>(tw + r * L1T_TW_LD + 4 * k) = v;
+        *reinterpret_cast<uint2*>(tw + r * L1T_TW_LD + 2 * k) = make_uint2(L1T_LO(a, b), L1T_HI(a, b));
     }
     for (int idx = tid; idx < C::P_BYTES / 16; idx += L1T_THREADS)     // rows of a partial last tile read as zeros
         reinterpret_cast<uint4*>(p_g)[idx] = make_uint4(0, 0, 0, 0);
@@ -192,11 +194,15 @@ __global__ void __launch_bounds__(L1T_THREADS, 1) spline_l1_tc5_kernel(
         // the tile's tcgen05.mma once every warp has arrived on the "tile stored" named barrier -- the other warps only
         // arrive and go on (epilogue of the previous tile, next tile's aggregation): nobody waits for the slowest warp
         // except the issuer of that one tile, and the issuing cost rotates over the warps.
-        const uint32_t tw_zero = (uint32_t)ncls;
-        const float* xg = x + 2 * g;                         // lane bases of the row gathers (offsets fit 32 bits)
-        const float* xg16 = x + 16 + g;
-        const float* xt = x + 4 * t;
-        const uint32_t uldx = (uint32_t)ldx;
+        const uint32_t zero4 = (uint32_t)ncls * 0x01010101u; // four copies of the all-zero class
+        const uint32_t nmax = (uint32_t)(n - 1);
+        // lane bases of the row gathers; an address is base + row * (4 ldx) as one 32 x 32 + 64 bit multiply-add
+        const char* xg = reinterpret_cast<const char*>(x + 2 * g);
+        const char* xg16 = reinterpret_cast<const char*>(x + 16 + g);
+        const char* xt = reinterpret_cast<const char*>(x + 4 * t);
+        const char* xt16 = reinterpret_cast<const char*>(x + 16 + 2 * t);
+        const uint32_t ldxb = 4u * (uint32_t)ldx;
+        const uint32_t* twg = tw + 2 * g;
         L1THead hd[4];
         uint4 craw[4];
         int inext[4];
@@ -214,38 +220,43 @@ __global__ void __launch_bounds__(L1T_THREADS, 1) spline_l1_tc5_kernel(
             hd[k].deg = 0;
             craw[k] = make_uint4(0, 0, 0, 0);
 #pragma unroll
-            for (int j = 0; j < 4; j++) hd[k].s[j] = 0;
+            for (int j = 0; j < 4; j++) hd[k].s[j] = 0u;
             if (i >= 0) {
-                hd[k].deg = count[i];
+                hd[k].deg = __ldg(count + i);
                 craw[k] = __ldg(reinterpret_cast<const uint4*>(cls) + i);
-                const int32_t* srow = src + ((uint32_t)i * 16u + (uint32_t)t);
+                const uint32_t* srow = reinterpret_cast<const uint32_t*>(
+                    reinterpret_cast<const char*>(src + t) + (uint64_t)(uint32_t)i * 64u);
 #pragma unroll
                 for (int j = 0; j < 4; j++) hd[k].s[j] = __ldg(srow + 4 * j);
             }
         };
         auto pack_class = [&](int k) {
-            hd[k].c = __byte_perm(__byte_perm(craw[k].x, craw[k].y, t | ((4 + t) << 4)),
-                                  __byte_perm(craw[k].z, craw[k].w, t | ((4 + t) << 4)), 0x5410);
+            const uint32_t c = __byte_perm(__byte_perm(craw[k].x, craw[k].y, t | ((4 + t) << 4)),
+                                           __byte_perm(craw[k].z, craw[k].w, t | ((4 + t) << 4)), 0x5410);
+            // positions t + 4j < deg  <=>  j < nv; slots beyond the row hold garbage: all-zero class, any valid source row
+            const int nv = min(4, (hd[k].deg - t + 3) >> 2);
+            const uint32_t live = __funnelshift_rc(0xffffffffu, 0u, 32 - 8 * nv);
+            hd[k].c = (c & live) | (zero4 & ~live);
+#pragma unroll
+            for (int j = 0; j < 4; j++) hd[k].s[j] = min(hd[k].s[j], nmax);
         };
-        float2 xa[2][4];                                     // [buffer][row position j]: channels 2g, 2g+1
-        float xb[2][4];                                      // channel 16 + g (Cin 20)
-        float4 xr[2];                                        // the node's own row (lanes g == 7): channels 4t..4t+3
-        float2 xr2[2];                                       //   and 16+2t, 17+2t
+        uint2 xa[2][4];                                      // [buffer][row position j]: h2 words of channels 2g, 2g+1
+        uint32_t xb[2][4];                                   // channel 16 + g (Cin 20)
+        uint4 xr[2];                                         // the node's own row (lanes g == 7): channels 4t..4t+3
+        uint2 xr2[2];                                        //   and 16+2t, 17+2t
         auto gather = [&](int k, int buf) {
-            const int i = hd[k].i < 0 ? 0 : hd[k].i;
 #pragma unroll
             for (int j = 0; j < 4; j++) {
-                const int sj = (4 * j + t) < hd[k].deg ? hd[k].s[j] : i;   // empty slots read the node's own (valid) row
-                const uint32_t off = (uint32_t)sj * uldx;
-                xa[buf][j] = __ldg(reinterpret_cast<const float2*>(xg + off));
-                if (CP > 16) xb[buf][j] = g < 4 ? __ldg(xg16 + off) : 0.f;
+                const uint64_t off = (uint64_t)hd[k].s[j] * ldxb;
+                xa[buf][j] = __ldg(reinterpret_cast<const uint2*>(xg + off));
+                if (CP > 16) xb[buf][j] = g < 4 ? __ldg(reinterpret_cast<const uint32_t*>(xg16 + off)) : 0u;
             }
-            xr[buf] = make_float4(0.f, 0.f, 0.f, 0.f);
-            xr2[buf] = make_float2(0.f, 0.f);
+            xr[buf] = make_uint4(0u, 0u, 0u, 0u);
+            xr2[buf] = make_uint2(0u, 0u);
             if (g == 7 && hd[k].i >= 0) {
-                const uint32_t off = (uint32_t)i * uldx;
-                xr[buf] = __ldg(reinterpret_cast<const float4*>(xt + off));
-                if (CP > 16 && t < 2) xr2[buf] = __ldg(reinterpret_cast<const float2*>(x + off + 16 + 2 * t));
+                const uint64_t off = (uint64_t)(uint32_t)hd[k].i * ldxb;
+                xr[buf] = __ldg(reinterpret_cast<const uint4*>(xt + off));
+                if (CP > 16 && t < 2) xr2[buf] = __ldg(reinterpret_cast<const uint2*>(xt16 + off));
             }
         };
         // Epilogue of UMMA tile number `tn` of this CTA (accumulator buffer tn & 1, ids / rsc slot tn & 3): every producer
@@ -256,7 +267,6 @@ __global__ void __launch_bounds__(L1T_THREADS, 1) spline_l1_tc5_kernel(
             const int quarter = warp & 3, cq = warp >> 2;
             const int r = quarter * 32 + lane;
             const int io = ids[(tn & 3) * L1T_ROWS + r];
-            const float rs = rsc[(tn & 3) * L1T_ROWS + r];
             const uint32_t ta = tmem + (uint32_t)((tn & 1) * L1T_ACC_COLS + 4 * cq) + ((uint32_t)(quarter * 32) << 16);
             float4 ad = make_float4(0.f, 0.f, 0.f, 0.f);
             if (io >= 0 && E.addend) ad = __ldg(reinterpret_cast<const float4*>(E.addend + (int64_t)io * E.ld_add) + cq);
@@ -291,7 +301,7 @@ __global__ void __launch_bounds__(L1T_THREADS, 1) spline_l1_tc5_kernel(
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             if (io < 0) return;
-            const float um = rs * inv_sw;
+            const float um = inv_sw;
             const float adv[4] = {ad.x, ad.y, ad.z, ad.w};
             float rr[4];
 #pragma unroll
@@ -302,9 +312,17 @@ __global__ void __launch_bounds__(L1T_THREADS, 1) spline_l1_tc5_kernel(
                 if (E.addend) rr[b] = __fadd_rn(rr[b], adv[b]);
                 if (E.relu) rr[b] = fmaxf(rr[b], 0.f);
             }
-            *reinterpret_cast<float4*>(out + (int64_t)io * ldo + 4 * cq) = make_float4(rr[0], rr[1], rr[2], rr[3]);
+            if (out_h2) {                                    // the next convolution of the layer gathers h2 words
+                if (!(fabsf(rr[0]) < EVAD_H2_RANGE && fabsf(rr[1]) < EVAD_H2_RANGE && fabsf(rr[2]) < EVAD_H2_RANGE &&
+                      fabsf(rr[3]) < EVAD_H2_RANGE) && status)
+                    atomicOr(status, EVAD_STATUS_H16_RANGE);
+                *reinterpret_cast<uint4*>(out + (int64_t)io * ldo + 4 * cq) =
+                    make_uint4(evad_h2_split(rr[0]), evad_h2_split(rr[1]), evad_h2_split(rr[2]), evad_h2_split(rr[3]));
+            } else {
+                *reinterpret_cast<float4*>(out + (int64_t)io * ldo + 4 * cq) = make_float4(rr[0], rr[1], rr[2], rr[3]);
+            }
             if (has_skip) {
-                const float us = rs * inv_ss;
+                const float us = inv_ss;
 #pragma unroll
                 for (int b = 0; b < 4; b++) {
                     const int j = 4 * cq + b;
@@ -345,69 +363,54 @@ __global__ void __launch_bounds__(L1T_THREADS, 1) spline_l1_tc5_kernel(
                     pack_class(k + 1);
                     gather(k + 1, buf ^ 1);
                 }
-                float d[NT][4];
+                // MMA k slots (2t, 2t+1, 2t+8, 2t+9) of a lane = its row positions t, t+4, t+8, t+12 (j = 0..3)
+                uint32_t ah[4], al[4];
+#pragma unroll
+                for (int p = 0; p < 2; p++) {
+                    const uint32_t c0 = (hd[k].c >> (16 * p)) & 0xffu, c1 = (hd[k].c >> (16 * p + 8)) & 0xffu;
+                    const uint2 r0 = *reinterpret_cast<const uint2*>(twg + c0 * L1T_TW_LD);
+                    const uint2 r1 = *reinterpret_cast<const uint2*>(twg + c1 * L1T_TW_LD);
+                    ah[2 * p] = L1T_LO(r0.x, r1.x);          // slot g,     positions j = 2p, 2p+1
+                    ah[2 * p + 1] = L1T_HI(r0.x, r1.x);      // slot g + 8
+                    al[2 * p] = L1T_LO(r0.y, r1.y);
+                    al[2 * p + 1] = L1T_HI(r0.y, r1.y);
+                }
+                float d1[NT][4], d2[NT][4];                  // hi x hi | hi x lo + lo x hi (weight 2^-11)
 #pragma unroll
                 for (int nt = 0; nt < NT; nt++)
 #pragma unroll
-                    for (int b = 0; b < 4; b++) d[nt][b] = 0.f;
+                    for (int b = 0; b < 4; b++) d1[nt][b] = 0.f, d2[nt][b] = 0.f;
+                uint32_t bh[NT][2], bl[NT][2];
 #pragma unroll
-                for (int ks = 0; ks < 2; ks++) {
-                    uint32_t ah[4], al[4];
+                for (int nt = 0; nt < NT; nt++)
 #pragma unroll
-                    for (int h = 0; h < 2; h++) {
-                        const int j = 2 * ks + h;
-                        const uint32_t c = (4 * j + t) < hd[k].deg ? ((hd[k].c >> (8 * j)) & 0xffu) : tw_zero;
-                        const float4 w = *reinterpret_cast<const float4*>(tw + c * L1T_TW_LD + 4 * g);
-                        ah[2 * h] = __float_as_uint(w.x);
-                        ah[2 * h + 1] = __float_as_uint(w.y);
-                        al[2 * h] = __float_as_uint(w.z);
-                        al[2 * h + 1] = __float_as_uint(w.w);
+                    for (int p = 0; p < 2; p++) {
+                        const uint32_t w0 = nt == 0 ? xa[buf][2 * p].x : nt == 1 ? xa[buf][2 * p].y : xb[buf][2 * p];
+                        const uint32_t w1 = nt == 0 ? xa[buf][2 * p + 1].x : nt == 1 ? xa[buf][2 * p + 1].y : xb[buf][2 * p + 1];
+                        bh[nt][p] = L1T_LO(w0, w1);
+                        bl[nt][p] = L1T_HI(w0, w1);
                     }
-                    uint32_t bh[NT][2], bl[NT][2];
 #pragma unroll
-                    for (int nt = 0; nt < NT; nt++)
+                for (int nt = 0; nt < NT; nt++) l1t_mma_sync(d1[nt], ah, bh[nt][0], bh[nt][1]);
 #pragma unroll
-                        for (int h = 0; h < 2; h++) {
-                            const int j = 2 * ks + h;
-                            const float v = nt == 0 ? xa[buf][j].x : nt == 1 ? xa[buf][j].y : xb[buf][j];
-                            bh[nt][h] = __float_as_uint(v) & 0xffffe000u;
-                            bl[nt][h] = __float_as_uint(__fsub_rn(v, __uint_as_float(bh[nt][h])));
-                        }
+                for (int nt = 0; nt < NT; nt++) l1t_mma_sync(d2[nt], ah, bl[nt][0], bl[nt][1]);
 #pragma unroll
-                    for (int nt = 0; nt < NT; nt++) l1t_mma_sync(d[nt], al, bh[nt][0], bh[nt][1]);
-#pragma unroll
-                    for (int nt = 0; nt < NT; nt++) l1t_mma_sync(d[nt], ah, bl[nt][0], bl[nt][1]);
-#pragma unroll
-                    for (int nt = 0; nt < NT; nt++) l1t_mma_sync(d[nt], ah, bh[nt][0], bh[nt][1]);
-                }
-                // lane (g, t): slot g and slot g + 8 of channels 4t..4t+3 (and 16+2t, 17+2t for t < 2); slot 15 = own row
-                float v[8] = {d[0][0], d[1][0], d[0][1], d[1][1], d[0][2], d[1][2], d[0][3], d[1][3]};
-                if (g == 7) { v[4] = xr[buf].x; v[5] = xr[buf].y; v[6] = xr[buf].z; v[7] = xr[buf].w; }
-                float u[4] = {0.f, 0.f, 0.f, 0.f};
-                if (CP > 16) {
-                    u[0] = d[NT - 1][0]; u[1] = d[NT - 1][1]; u[2] = d[NT - 1][2]; u[3] = d[NT - 1][3];
-                    if (g == 7) { u[2] = xr2[buf].x; u[3] = xr2[buf].y; }
-                    if (t >= 2) { u[0] = u[1] = u[2] = u[3] = 0.f; }   // D columns 4..7 of the third tile are padding
-                }
+                for (int nt = 0; nt < NT; nt++) l1t_mma_sync(d2[nt], al, bh[nt][0], bh[nt][1]);
                 // the row head of this position in the NEXT sub-tile (its node id arrived a sub-tile ago): in flight
                 // until that sub-tile's aggregation, three to four nodes from now
                 load_head(k);
-                // block scale of the row: maximum magnitude -> [2^13, 2^14) (exact power of two, undone in the epilogue)
-                float m = fmaxf(fmaxf(fmaxf(fabsf(v[0]), fabsf(v[1])), fmaxf(fabsf(v[2]), fabsf(v[3]))),
-                                fmaxf(fmaxf(fabsf(v[4]), fabsf(v[5])), fmaxf(fabsf(v[6]), fabsf(v[7]))));
-                if (CP > 16) m = fmaxf(m, fmaxf(fmaxf(fabsf(u[0]), fabsf(u[1])), fmaxf(fabsf(u[2]), fabsf(u[3]))));
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-                int ex = (int)(__float_as_uint(m) >> 23);
-                ex = min(max(ex, 20), 240);
-                const float sc = __uint_as_float((uint32_t)(267 - ex) << 23);          // 2^(140 - ex)
+                // lane (g, t): slot g and slot g + 8 of channels 4t..4t+3 (and 16+2t, 17+2t for t < 2); slot 15 = own row,
+                // already h2 words.  fp16 pairs without a block scale: |P| < 16 * 2048 fits, small values keep 2^-36 absolute
                 const int r = sub * L1T_SUB + warp * 4 + k;                             // row of the tile
-                if (lane == 0) rsc[(tn & 3) * L1T_ROWS + r] = __uint_as_float((uint32_t)(ex - 13) << 23);   // 2^(ex - 140)
                 uint4 h1, h2;
-                l1t_split2(__fmul_rn(v[0], sc), __fmul_rn(v[1], sc), &h1.x, &h2.x);
-                l1t_split2(__fmul_rn(v[2], sc), __fmul_rn(v[3], sc), &h1.y, &h2.y);
-                l1t_split2(__fmul_rn(v[4], sc), __fmul_rn(v[5], sc), &h1.z, &h2.z);
-                l1t_split2(__fmul_rn(v[6], sc), __fmul_rn(v[7], sc), &h1.w, &h2.w);
+                l1t_split2(d1[0][0], d2[0][0], d1[1][0], d2[1][0], &h1.x, &h2.x);
+                l1t_split2(d1[0][1], d2[0][1], d1[1][1], d2[1][1], &h1.y, &h2.y);
+                l1t_split2(d1[0][2], d2[0][2], d1[1][2], d2[1][2], &h1.z, &h2.z);
+                l1t_split2(d1[0][3], d2[0][3], d1[1][3], d2[1][3], &h1.w, &h2.w);
+                if (g == 7) {
+                    h1.z = L1T_LO(xr[buf].x, xr[buf].y); h1.w = L1T_LO(xr[buf].z, xr[buf].w);
+                    h2.z = L1T_HI(xr[buf].x, xr[buf].y); h2.w = L1T_HI(xr[buf].z, xr[buf].w);
+                }
                 // the P tile is free once the MMAs of the previous UMMA tile have completed (first store of a tile only)
                 if (k == 0 && sub == 0 && tn > 0)
                     t5_mbar_wait(t5_smem(&s_bar[(tn - 1) & 1]), (uint32_t)(((tn - 1) >> 1) & 1));
@@ -419,8 +422,12 @@ __global__ void __launch_bounds__(L1T_THREADS, 1) spline_l1_tc5_kernel(
                 }
                 if (CP > 16 && t < 2) {
                     uint2 e1, e2;
-                    l1t_split2(__fmul_rn(u[0], sc), __fmul_rn(u[1], sc), &e1.x, &e2.x);
-                    l1t_split2(__fmul_rn(u[2], sc), __fmul_rn(u[3], sc), &e1.y, &e2.y);
+                    l1t_split2(d1[NT - 1][0], d2[NT - 1][0], d1[NT - 1][1], d2[NT - 1][1], &e1.x, &e2.x);
+                    l1t_split2(d1[NT - 1][2], d2[NT - 1][2], d1[NT - 1][3], d2[NT - 1][3], &e1.y, &e2.y);
+                    if (g == 7) {
+                        e1.y = L1T_LO(xr2[buf].x, xr2[buf].y);
+                        e2.y = L1T_HI(xr2[buf].x, xr2[buf].y);
+                    }
                     uint8_t* dst = p_g + 4 * L1T_CHUNK + r * 128 + ((g ^ (r & 7)) << 4) + t * 8;
                     *reinterpret_cast<uint2*>(dst) = e1;
                     *reinterpret_cast<uint2*>(dst + NCH * L1T_CHUNK) = e2;
@@ -483,9 +490,9 @@ __global__ void __launch_bounds__(L1T_THREADS, 1) spline_l1_tc5_kernel(
 
 template <int CP>
 static int launch_l1_tc5(const int32_t* count, const int32_t* src, const uint8_t* cls, const int32_t* perm, int64_t n,
-                         const float* x, int ldx, const float* tapw, int ncls, const uint16_t* W16, float inv_sw,
-                         const uint16_t* S16, float inv_ss, const evad_epilogue_t& E, float* out, int ldo,
-                         const evad_epilogue_t& ES, float* skip_out, int ld_skip, cudaStream_t st) {
+                         const uint32_t* x, int ldx, const float* tapw, int ncls, const uint16_t* W16, float inv_sw,
+                         const uint16_t* S16, float inv_ss, const evad_epilogue_t& E, float* out, int ldo, int out_h2,
+                         const evad_epilogue_t& ES, float* skip_out, int ld_skip, uint32_t* status, cudaStream_t st) {
     const size_t smem = L1TCfg<CP>::smem_bytes(ncls);
     if (smem > 227 * 1024) return EVAD_ERR_UNSUPPORTED;
     static size_t attr_bytes = 0;
@@ -497,21 +504,22 @@ static int launch_l1_tc5(const int32_t* count, const int32_t* src, const uint8_t
     const int64_t ntiles = (n + L1T_ROWS - 1) / L1T_ROWS;
     const int grid = (int)(ntiles < 148 ? ntiles : 148);     // persistent: one CTA per SM
     spline_l1_tc5_kernel<CP><<<grid, L1T_THREADS, smem, st>>>(count, src, cls, perm, n, x, ldx, tapw, ncls, W16, inv_sw, S16,
-                                                               inv_ss, E, out, ldo, ES, skip_out, ld_skip);
+                                                               inv_ss, E, out, ldo, out_h2, ES, skip_out, ld_skip, status);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }
 
 extern "C" int evad_spline_conv_l1_tc5(const int32_t* count, const int32_t* nbr, const uint8_t* nbr_cls, const int32_t* perm,
-                                       int64_t n, const float* x, int ldx, int cin_pad, const float* tapw, int ncls,
+                                       int64_t n, const uint32_t* x, int ldx, int cin_pad, const float* tapw, int ncls,
                                        const uint16_t* w16, float inv_sw, const uint16_t* s16, float inv_ss,
-                                       const evad_epilogue_t* epi_h, float* out, int ldo,
-                                       const evad_epilogue_t* skip_epi_h, float* skip_out, int ld_skip, void* stream) {
+                                       const evad_epilogue_t* epi_h, float* out, int ldo, int out_h2,
+                                       const evad_epilogue_t* skip_epi_h, float* skip_out, int ld_skip, uint32_t* status,
+                                       void* stream) {
     if (!count || !nbr || !nbr_cls || !x || !tapw || !w16 || !epi_h || !out) return EVAD_ERR_ARG;
     if (cin_pad != 16 && cin_pad != 20) return EVAD_ERR_UNSUPPORTED;
     if (n * 16 >= (1ll << 31) || n * (int64_t)ldx >= (1ll << 32)) return EVAD_ERR_ARG;   // 32-bit row offsets in the kernel
     if (epi_h->addend && ((((uintptr_t)epi_h->addend) & 15) != 0 || epi_h->ld_add % 4 != 0)) return EVAD_ERR_ARG;
-    if (ldx < cin_pad || ldx % 4 != 0 || ldo % 4 != 0 || ncls < 1 || ncls > 256) return EVAD_ERR_ARG;
+    if (ldx < cin_pad || ldx % 4 != 0 || ldo % 4 != 0 || ncls < 1 || ncls > 255) return EVAD_ERR_ARG;
     if ((((uintptr_t)x | (uintptr_t)tapw | (uintptr_t)w16 | (uintptr_t)out | (uintptr_t)nbr | (uintptr_t)nbr_cls) & 15) != 0)
         return EVAD_ERR_ARG;
     const bool has_skip = s16 && skip_epi_h && skip_out;
@@ -521,7 +529,7 @@ extern "C" int evad_spline_conv_l1_tc5(const int32_t* count, const int32_t* nbr,
     cudaStream_t st = (cudaStream_t)stream;
     if (cin_pad == 20)
         return launch_l1_tc5<20>(count, nbr, nbr_cls, perm, n, x, ldx, tapw, ncls, w16, inv_sw, has_skip ? s16 : nullptr,
-                                 inv_ss, *epi_h, out, ldo, es, skip_out, ld_skip, st);
+                                 inv_ss, *epi_h, out, ldo, out_h2, es, skip_out, ld_skip, status, st);
     return launch_l1_tc5<16>(count, nbr, nbr_cls, perm, n, x, ldx, tapw, ncls, w16, inv_sw, has_skip ? s16 : nullptr, inv_ss,
-                             *epi_h, out, ldo, es, skip_out, ld_skip, st);
+                             *epi_h, out, ldo, out_h2, es, skip_out, ld_skip, status, st);
 }

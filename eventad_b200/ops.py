@@ -324,8 +324,9 @@ def edge_class(rowptr, src, n, mode, pseudo, status):
 
 # EVAD_L1_MMA=0: keep the tap aggregation of layer 1 on the FFMA pipe (evad_spline_conv_l1) for A/B measurements
 USE_L1_MMA = os.environ.get("EVAD_L1_MMA", "1") != "0"
-# EVAD_L1_TC5=1: contraction of layer 1 on tcgen05 (csrc/spline_l1_tc5.cu) instead of mma.sync (A/B measurements)
-USE_L1_TC5 = os.environ.get("EVAD_L1_TC5", "0") == "1"   # measured slower than the mma.sync kernel (profiles/r02_summary.md): opt-in
+# EVAD_L1_TC5=1: with the fp16-pair kernel (EVAD_L1_H16), contraction of layer 1 on tcgen05 (csrc/spline_l1_tc5.cu)
+# instead of mma.sync (A/B measurements)
+USE_L1_TC5 = os.environ.get("EVAD_L1_TC5", "0") == "1"
 
 
 # EVAD_L1_H16=0: keep layer 1 on the 3xTF32 mma.sync kernel (evad_spline_conv_l1_mma) instead of the fp16-pair kernel
@@ -391,7 +392,7 @@ def l1_pack16(W, S, cin_pad):
 
 def l1_h16_ok(src, cls, ell_stride):
     """True when spline_conv_l1 will take the fp16-pair kernel (fixed-stride rows of 16, aligned)."""
-    return (USE_L1_MMA and USE_L1_H16 and not USE_L1_TC5 and ell_stride == 16 and cls is not None and
+    return (USE_L1_MMA and USE_L1_H16 and ell_stride == 16 and cls is not None and
             src.data_ptr() % 16 == 0 and cls.data_ptr() % 16 == 0)
 
 
@@ -409,6 +410,16 @@ def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None, perm=N
     if l1_h16_ok(src, cls, ell_stride):
         if not x_h2:
             x = split_h2(x.contiguous(), status)
+        if USE_L1_TC5 and pack.get("w16") is not None:
+            with _timed(f'spline_conv_l1_c{cin}'):
+                check(L.evad_spline_conv_l1_tc5(ptr(rowptr), ptr(src), ptr(cls), ptr(perm), n, ptr(x), x.stride(0), pack["cin_pad"],
+                                                ptr(pack["tapw"]), pack["tapw"].shape[0], ptr(pack["w16"]), float(pack["inv_sw"]),
+                                                ptr(pack["s16"]) if has_skip else None, float(pack["inv_ss"]),
+                                                ctypes.byref(e), ptr(out), out.stride(0), int(out_h2),
+                                                ctypes.byref(se) if has_skip else None, ptr(skip_out),
+                                                skip_out.stride(0) if has_skip else 0, ptr(status), stream()),
+                      "evad_spline_conv_l1_tc5")
+            return out, skip_out
         with _timed(f'spline_conv_l1_c{cin}'):
             check(L.evad_spline_conv_l1_h16(ptr(rowptr), ptr(src), ptr(cls), ptr(perm), n, ptr(x), x.stride(0), pack["cin_pad"],
                                             ptr(pack["tapw"]), pack["tapw"].shape[0], ptr(pack["whi"]), ptr(pack["wlo"]),
@@ -419,16 +430,6 @@ def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None, perm=N
                   "evad_spline_conv_l1_h16")
         return out, skip_out
     assert not x_h2 and not out_h2, "h2 words are only understood by evad_spline_conv_l1_h16"
-    if (USE_L1_MMA and USE_L1_TC5 and pack.get("w16") is not None and ell_stride == 16 and src.data_ptr() % 16 == 0 and
-            cls.data_ptr() % 16 == 0):
-        with _timed(f'spline_conv_l1_c{cin}'):
-            check(L.evad_spline_conv_l1_tc5(ptr(rowptr), ptr(src), ptr(cls), ptr(perm), n, ptr(x), x.stride(0), pack["cin_pad"],
-                                            ptr(pack["tapw"]), pack["tapw"].shape[0], ptr(pack["w16"]), float(pack["inv_sw"]),
-                                            ptr(pack["s16"]) if has_skip else None, float(pack["inv_ss"]),
-                                            ctypes.byref(e), ptr(out), out.stride(0), ctypes.byref(se) if has_skip else None,
-                                            ptr(skip_out), skip_out.stride(0) if has_skip else 0, stream()),
-                  "evad_spline_conv_l1_tc5")
-        return out, skip_out
     if (USE_L1_MMA and ell_stride == 16 and src.data_ptr() % 16 == 0 and
             cls.data_ptr() % 16 == 0):
         with _timed(f'spline_conv_l1_c{cin}'):

@@ -221,19 +221,21 @@ int evad_spline_conv_l1_mma(const int32_t* count, const int32_t* nbr, const uint
                             const evad_epilogue_t* epi_h, float* out, int ldo, const evad_epilogue_t* skip_epi_h,
                             float* skip_out, int ld_skip, void* stream);
 
-/* The same layer with the weight contraction on the 5th-generation tensor cores (csrc/spline_l1_tc5.cu): the per-node tap
- * aggregation is evad_spline_conv_l1_mma's; the [128 nodes x 16*cin_pad] P tile is block-scaled per row (power of two),
- * split into two fp16 parts (22 significant bits) in the K-major SWIZZLE_128B operand layout and contracted by
- * tcgen05.mma kind::f16 (M 128, N 16) into tensor memory; epilogue (un-scale, BatchNorm, skip add, ReLU) from
- * tcgen05.ld.  w16 = [2 parts][16 output rows][K] fp16 (K = 256, or 320 for cin_pad 20, in the kernel's operand order:
- * MySplineConv.l1_pack), W * 2^kw = w1 + w2 * 2^-11 with inv_sw = 2^-kw; s16 = [2][16][128] fp16, the skip Linear weight
- * at the K positions of the root slot (or NULL), inv_ss its un-scale.  Replaces spline_conv.py:39-47,72-76 +
- * conv.py:23-28,47-56 like evad_spline_conv_l1; result within rtol 1e-4 / atol 1e-5. */
+/* The same layer with the weight contraction on the 5th-generation tensor cores (csrc/spline_l1_tc5.cu): x_h2 are h2
+ * words (see evad_spline_conv_l1_h16 below), the per-node tap aggregation is that kernel's (mma.sync m16n8k16 on fp16
+ * pairs); the [128 nodes x 16*cin_pad] P tile is written as two fp16 parts (22 significant bits) in the K-major
+ * SWIZZLE_128B operand layout and contracted by tcgen05.mma kind::f16 (M 128, N 16) into tensor memory; epilogue
+ * (BatchNorm, skip add, ReLU; h2 words when out_h2) from tcgen05.ld.  w16 = [2 parts][16 output rows][K] fp16 (K = 256,
+ * or 320 for cin_pad 20, in the kernel's operand order: MySplineConv.l1_pack), W * 2^kw = w1 + w2 * 2^-11 with
+ * inv_sw = 2^-kw; s16 = [2][16][128] fp16, the skip Linear weight at the K positions of the root slot (or NULL), inv_ss
+ * its un-scale.  Replaces spline_conv.py:39-47,72-76 + conv.py:23-28,47-56 like evad_spline_conv_l1; result within
+ * rtol 1e-4 / atol 1e-5. */
 int evad_spline_conv_l1_tc5(const int32_t* count, const int32_t* nbr, const uint8_t* nbr_cls, const int32_t* perm,
-                            int64_t n, const float* x, int ldx, int cin_pad, const float* tapw, int ncls,
+                            int64_t n, const uint32_t* x_h2, int ldx, int cin_pad, const float* tapw, int ncls,
                             const uint16_t* w16, float inv_sw, const uint16_t* s16, float inv_ss,
-                            const evad_epilogue_t* epi_h, float* out, int ldo, const evad_epilogue_t* skip_epi_h,
-                            float* skip_out, int ld_skip, void* stream);
+                            const evad_epilogue_t* epi_h, float* out, int ldo, int out_h2,
+                            const evad_epilogue_t* skip_epi_h, float* skip_out, int ld_skip, uint32_t* status,
+                            void* stream);
 
 /* Layer-1 block as evad_spline_conv_l1_mma (same reference lines: spline_conv.py:39-47,72-76, conv.py:23-28,47-56), with
  * both tensor-core products on fp16 operand pairs (mma.sync m16n8k16, csrc/spline_l1_h16.cu): half the HMMA per node.

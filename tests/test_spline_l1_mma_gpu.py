@@ -66,11 +66,11 @@ def _case(n, cin, with_skip, with_perm, seed, full_rows=False):
     kw = dict(perm=perm.to(dev) if perm is not None else None, ell_stride=16)
     res = {}
     # "h16": both products as fp16-pair mma.sync m16n8k16 (csrc/spline_l1_h16.cu, the default); "h16w": the same with
-    # input and output as h2 words (how the two convolutions of the layer are chained); "tc5": mma.sync aggregation +
+    # input and output as h2 words (how the two convolutions of the layer are chained); "tc5": the same aggregation +
     # tcgen05 contraction (csrc/spline_l1_tc5.cu); True: both products as 3xTF32 mma.sync; False: FFMA aggregation
     status = ops.new_status(dev)
     for flag, (use_mma, use_tc5, use_h16) in (("h16", (True, False, True)), ("h16w", (True, False, True)),
-                                              ("tc5", (True, True, False)), (True, (True, False, False)),
+                                              ("tc5", (True, True, True)), (True, (True, False, False)),
                                               (False, (False, False, False))):
         old = ops.USE_L1_MMA, ops.USE_L1_TC5, ops.USE_L1_H16
         ops.USE_L1_MMA, ops.USE_L1_TC5, ops.USE_L1_H16 = use_mma, use_tc5, use_h16
