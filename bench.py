@@ -379,6 +379,36 @@ def leg_full_model(dev, world, rank, windows=100, B=6, events=100_000):
            "what": "EventADModel.forward(data, labels, testing=True): ResNet-50 (cuDNN, channels_last, random weights) + fused "
                    "event branch + evad_bbox_pool + batched GRU head; 'FPS' as utils/fps.py:58-59 counts it = boxes of frame t "
                    "and t-1 per second"}
+    # ---- the CNN branch (HookModule.forward) eager vs captured in a CUDA graph (fp32 / bf16 autocast)
+    try:
+        from eventad_b200.engine import GraphedImageBranch
+        hook = ead.dagr_model.backbone.net
+        branch = {}
+        for bsz in (1, B):
+            img = torch.rand((bsz, 3, 240, 320), device=dev).contiguous(memory_format=torch.channels_last)
+            g32 = GraphedImageBranch(hook, bsz, 240, 320, device=dev).capture()
+            g16 = GraphedImageBranch(hook, bsz, 240, 320, device=dev, dtype=torch.bfloat16).capture()
+
+            def p50(fn, iters=30):
+                ts = []
+                with torch.no_grad():
+                    for i in range(iters + 5):
+                        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        a0.record()
+                        fn()
+                        a1.record()
+                        torch.cuda.synchronize()
+                        if i >= 5:
+                            ts.append(a0.elapsed_time(a1))
+                return float(np.median(ts))
+            branch[f"B{bsz}"] = {"eager_ms": p50(lambda: hook(img)), "cuda_graph_ms": p50(lambda: g32(img)),
+                                 "cuda_graph_bf16_ms": p50(lambda: g16(img))}
+        branch["what"] = ("HookModule.forward (ResNet-50 trunk + 1x1 feature convolutions, cuDNN, channels_last): p50 of "
+                          "the eager hooked forward vs engine.GraphedImageBranch (one CUDA-graph replay incl. the image "
+                          "copy-in), fp32 and bf16 autocast")
+        res["image_branch"] = branch
+    except Exception as ex:                                       # report, do not hide
+        res["image_branch"] = {"error": repr(ex)[:200]}
     # ---- BASELINE configs[3]: training step, DAGR frozen, flat-bucket gradient all-reduce over NCCL when world > 1
     opt = train.make_optimizer(ead)
     timers = {}

@@ -139,6 +139,61 @@ class GraphedForward:
         return self.net.finalize_fused(self.res) if finalize else self.res
 
 
+class GraphedImageBranch:
+    """the CNN branch (`HookModule.forward`, net_img.py:122-135: torchvision ResNet-50 trunk with forward
+    hooks + the 1x1 `feature_dconv` convolutions) captured once in a CUDA graph for a fixed image batch, weights and
+    activations channels-last (cuDNN's tensor-core layout; the event branch consumes channel-last maps in place), fp32 by
+    default, bf16 autocast on request.  The `output_dconv` convolutions feed the detection head only, which EventAD never
+    runs: they are skipped unless want_outputs.  The returned maps are static buffers of the graph -- hand them to
+    GraphedForward(static_feats=True) and the CNN branch writes where the event branch reads, without a copy.
+
+    Kernels are cuDNN's (north_star keeps the ResNet branch a library call); what is ours is the capture: at B = 1 the
+    eager hooked forward costs ~160 launches of host time, several times the event branch's whole 0.78 ms."""
+
+    def __init__(self, hook_module, batch, height, width, device="cuda", dtype=None, want_outputs=False):
+        self.hook = hook_module.to(device).eval().to(memory_format=torch.channels_last)
+        self.dtype, self.want_outputs = dtype, bool(want_outputs)
+        self.image = torch.zeros((int(batch), 3, int(height), int(width)), device=device).contiguous(
+            memory_format=torch.channels_last)
+        self.graph, self.features, self.outputs = None, None, None
+
+    def _run(self):
+        h = self.hook
+        h.features, h.outputs = [], []
+        with torch.autocast("cuda", dtype=self.dtype, enabled=self.dtype is not None):
+            h.module(self.image)
+            feats = [dconv(f) for f, dconv in zip(h.features, h.feature_dconv)] if len(h.feature_dconv) > 0 else h.features
+            outs = h.outputs
+            if self.want_outputs and len(h.output_dconv) > 0:
+                outs = [dconv(o) for o, dconv in zip(h.outputs, h.output_dconv)]
+        # fp32 channel-last maps: what evad_sample_concat / evad_voxel_pool read
+        feats = [f.float().contiguous(memory_format=torch.channels_last) for f in feats]
+        return feats, ([o.float() for o in outs] if self.want_outputs else [])
+
+    @torch.no_grad()
+    def capture(self):
+        side = torch.cuda.Stream(device=self.image.device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):                           # cuDNN algorithm selection, workspaces
+                self._run()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.features, self.outputs = self._run()
+        return self
+
+    @torch.no_grad()
+    def __call__(self, image):
+        """image [B, 3, H, W] (any memory format) -> (features, outputs) as HookModule.forward; static buffers."""
+        if self.graph is None:
+            self.capture()
+        self.image.copy_(image, non_blocking=True)
+        self.graph.replay()
+        return self.features, self.outputs
+
+
 class StreamedRunner:
     """End-to-end serving loop for a fixed (events, windows) shape: raw host events of step i+1 are uploaded on a copy
     stream into one of two device staging slots while step i computes; `evad_format_events` (format_data,

@@ -285,29 +285,26 @@ class MySplineConv(torch.nn.Module):
 
 
 def to_dense(self, x, pos, pooling, batch=None, batch_size=None):
-    """spline_conv.py:80-106 (head only; not on the EventAD path, kept for API completeness)."""
-    if hasattr(self, "batch_size"):
-        B = self.batch_size
-    elif batch_size is not None:
+    """Nodes of a pooled graph -> dense map [B, C, H, W] (spline_conv.py:80-106; head only, not on the EventAD path).
+    Same state as the reference: `self.batch_size` is fixed by the first call (argument, else 1 without `batch`, else
+    batch.max() + 1) and `self.dense` is allocated once, zeroed per call and returned (sliced to B samples)."""
+    if not hasattr(self, "batch_size"):
+        if batch_size is None:
+            if batch is None:
+                batch = x.new_zeros(len(x), dtype=torch.long)
+            batch_size = 1 if batch.numel() == 0 or batch is None else int(batch.max().item()) + 1
         self.batch_size = batch_size
-        B = batch_size
-    elif batch is None:
-        batch = torch.zeros(size=(len(x),), dtype=torch.long, device=x.device)
-        B = 1
-        self.batch_size = B
-    else:
-        B = batch.max().item() + 1
-        self.batch_size = B
+    B = self.batch_size
+    cell = pooling[:2]
     if not hasattr(self, "dense"):
-        W, H = (1 / pooling[:2] + 1e-3).long()
-        C = x.shape[-1]
-        self.dense = torch.zeros(size=(B, C, H, W), dtype=x.dtype, device=x.device)
-    est_x, est_y = (pos[:, :2] / pooling[:2]).t().long()
+        grid_w, grid_h = (1 / cell + 1e-3).long()
+        self.dense = x.new_zeros((B, x.shape[-1], int(grid_h), int(grid_w)))
+    col, row = (pos[:, :2] / cell).t().long()
     self.dense = self.dense.detach()
     self.dense.zero_()
-    dense = self.dense[:B] if B < self.dense.shape[0] else self.dense
-    dense[batch.long(), :, est_y, est_x] = x
-    return dense
+    view = self.dense[:B] if B < self.dense.shape[0] else self.dense
+    view[batch.long(), :, row, col] = x
+    return view
 
 
 class SplineConvToDense(MySplineConv):

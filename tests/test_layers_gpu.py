@@ -216,3 +216,44 @@ def test_spiral_offset_class_equals_lut_class(dist, B):
                          dict(pos=d.pos.contiguous(), two_m=two_m, clamp01=True), status)
     assert int(status.item()) == 0
     assert torch.equal(out["edge_cls"][:e], ref[:e])
+
+
+def test_spline_conv_to_dense():
+    """SplineConvToDense.forward (spline_conv.py:80-118): the convolution, then every node written into the dense
+    [B, C, H, W] map at (pos / pooling).long(); against the oracle convolution scattered independently (numpy loop)."""
+    import numpy as np
+    from eventad_b200.data import Data
+    from eventad_b200.model.layers.spline_conv import SplineConvToDense
+    from oracle import dagr_layers, dagr_ops
+    model, args = make_backbone(use_image=False)
+    B, Wc, Hc = 2, 10, 8                                        # a pooled graph: one node per occupied cell of a 10 x 8 grid
+    g = torch.Generator().manual_seed(5)
+    cells = torch.stack([torch.randperm(Wc * Hc, generator=g)[:40] for _ in range(B)])
+    batch = torch.arange(B).repeat_interleave(40)
+    cx, cy = (cells % Wc).flatten(), (cells // Wc).flatten()
+    pooling = torch.tensor([1.0 / Wc, 1.0 / Hc, 1.0])
+    pos = torch.stack([(cx + 0.5) / Wc, (cy + 0.5) / Hc, torch.rand(B * 40, generator=g)], 1)
+    n = pos.shape[0]
+    src, dst = torch.randint(0, 40, (2, 300), generator=g)
+    off = (torch.arange(300) % B) * 40
+    ei = torch.stack([src + off, dst + off])
+    attr = dagr_ops.cartesian(pos, ei, 1.0).clamp(0, 1)
+    torch.manual_seed(1)
+    conv = SplineConvToDense(12, 8, args)
+    x = torch.randn(n, 12, generator=g)
+    sd = {"c." + k: v.detach() for k, v in conv.state_dict().items()}
+    ref = dagr_layers.spline_conv(x, ei, attr, sd, "c.", None).numpy()
+    want = np.zeros((B, 8, Hc, Wc), dtype=np.float32)
+    for i in range(n):
+        want[int(batch[i]), :, int(cy[i]), int(cx[i])] = ref[i]
+    d = Data(x=x.cuda(), edge_index=ei.cuda(), edge_attr=attr.cuda(), pos=pos.cuda(), batch=batch.cuda())
+    d.pooling = pooling.cuda()
+    dense = conv.cuda()(d)
+    assert tuple(dense.shape) == (B, 8, Hc, Wc)
+    assert_close(dense.cpu(), torch.from_numpy(want), what="SplineConvToDense")
+    # second call reuses (and clears) the cached map, as the reference does
+    d2 = Data(x=x[:40].cuda(), edge_index=ei[:, ei[0] < 40][:, :50].cuda(), edge_attr=attr[ei[0] < 40][:50].cuda(),
+              pos=pos[:40].cuda(), batch=batch[:40].cuda())
+    d2.pooling = pooling.cuda()
+    dense2 = conv(d2)
+    assert float(dense2[1].abs().max()) == 0.0 and float(dense2[0].abs().max()) > 0.0

@@ -127,3 +127,36 @@ def test_streamed_runner_matches_infer():
         for o, r in zip(host, ref):
             for key in ("x", "pos", "batch"):
                 assert torch.equal(o[key], r[key]), key
+
+
+def test_graphed_image_branch_matches_hooked_forward():
+    """engine.GraphedImageBranch (HookModule.forward captured in a CUDA graph, channels-last) against the
+    eager hooked forward (net_img.py:122-135) on new images: fp32 within cuDNN's algorithm-choice noise, bf16 autocast
+    within 5e-2 of the map's scale; and the whole DAGR forward fed by its static maps equals the eager one's."""
+    from eventad_b200.engine import GraphedImageBranch
+    model, args = make_backbone(seed=2, use_image=True)
+    model.cache_luts(320, 240, args.radius)
+    model = model.cuda()
+    hook = model.backbone.net
+    gib = GraphedImageBranch(hook, 2, 240, 320).capture()
+    gib16 = GraphedImageBranch(hook, 2, 240, 320, dtype=torch.bfloat16).capture()
+    for seed in (1, 2):
+        img = torch.rand((2, 3, 240, 320), device="cuda", generator=torch.Generator("cuda").manual_seed(seed))
+        with torch.no_grad():
+            want, _ = hook(img)
+        got, outs = gib(img)
+        assert outs == [] and len(got) == len(want) == 5
+        for a, b in zip(got, want):
+            assert a.shape == b.shape and a.is_contiguous(memory_format=torch.channels_last)
+            scale = float(b.abs().max())
+            assert float((a - b).abs().max()) <= 1e-4 * scale + 1e-5
+        for a, b in zip(gib16(img)[0], want):
+            assert float((a - b).abs().max()) <= 5e-2 * float(b.abs().max())
+    d = make_data(8000, 2, seed=3, device="cuda")
+    feats, _ = gib(img)
+    with torch.no_grad():
+        ref = model.backbone(make_data(8000, 2, seed=3, device="cuda"), image_feat=[f.clone() for f in want])[0]
+        out = model.backbone(d, image_feat=feats)[0]
+    for o, r in zip(out, ref):
+        assert torch.equal(o.batch, r.batch) and torch.equal(o.pos, r.pos)
+        assert_close(o.x, r.x, what="event branch on graphed CNN maps")

@@ -180,3 +180,22 @@ def test_reference_asynchronous_model_runs_and_agrees_with_its_dense_forward():
         row = {k: i for i, k in enumerate(ka)}
         sel = torch.tensor([row[k] for k in kb])
         assert float((a.x[sel] - b.x).abs().max()) < 1e-3
+
+
+@needs_ref
+def test_to_dense_equals_reference_text():
+    """`to_dense` (spline_conv.py:80-106) of the mirror against the reference's own function on the same CPU tensors."""
+    import types
+    ref_py.install()
+    from dagr.model.layers import spline_conv as ref_sc
+    from eventad_b200.model.layers import spline_conv as our_sc
+    g = torch.Generator().manual_seed(0)
+    n, B = 50, 3
+    x = torch.randn(n, 6, generator=g)
+    pos = torch.rand(n, 3, generator=g) * 0.999
+    batch = torch.randint(0, B, (n,), generator=g)
+    pooling = torch.tensor([1 / 20, 1 / 15, 1.0])
+    for kw in (dict(batch=batch), dict(batch=batch, batch_size=4), dict(batch=None)):
+        a = ref_sc.to_dense(types.SimpleNamespace(), x, pos, pooling, **kw)
+        b = our_sc.to_dense(types.SimpleNamespace(), x, pos, pooling, **kw)
+        assert a.shape == b.shape and torch.equal(a, b), kw
