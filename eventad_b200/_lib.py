@@ -102,7 +102,8 @@ def _declare(L):
     _sig(L, "evad_spline_conv_l1_tc5", c_i, [c_p, c_p, c_p, c_p, c_i64, c_p, c_i, c_i, c_p, c_i, c_p, c_f, c_p, c_f, P(EpilogueT),
                                              c_p, c_i, c_i, P(EpilogueT), c_p, c_i, c_p, c_p])
     _sig(L, "evad_split_h2", c_i, [c_p, c_p, c_i64, c_p, c_p])
-    _sig(L, "evad_spline_conv_l1_h16", c_i, [c_p, c_p, c_p, c_p, c_i64, c_p, c_i, c_i, c_p, c_i, c_p, c_p, c_p, c_p, P(EpilogueT),
+    _sig(L, "evad_stream_rows", c_i, [c_p, c_p, c_i64, c_i, c_i, c_p, c_i, c_i, c_p, c_p, c_p, c_p, c_p])
+    _sig(L, "evad_spline_conv_l1_h16", c_i, [c_p, c_p, c_p, c_p, c_i64, c_i64, c_p, c_i, c_i, c_p, c_i, c_p, c_p, c_p, c_p, P(EpilogueT),
                                              c_p, c_i, c_i, P(EpilogueT), c_p, c_i, c_p, c_p])
     _sig(L, "evad_spline_tap_lists", c_i, [c_p, c_p, c_i64, c_p, P(PseudoT), P(SplineModeT), c_p, c_p, c_p, c_p])
     _sig(L, "evad_spline_conv64_fused_ws_bytes", c_sz, [c_i64, c_i])

@@ -112,8 +112,8 @@ extern "C" int evad_split_h2(const float* in, uint32_t* out, int64_t n_words, ui
 template <int CP>
 __global__ void __launch_bounds__(L1H_THREADS, 2) spline_l1_h16_kernel(
     const int32_t* __restrict__ count, const int32_t* __restrict__ src, const uint8_t* __restrict__ cls,
-    const int32_t* __restrict__ perm, int64_t n, const uint32_t* __restrict__ x, int ldx, const float* __restrict__ tapw,
-    int ncls, const float* __restrict__ Whi, const float* __restrict__ Wlo, const float* __restrict__ Shi,
+    const int32_t* __restrict__ perm, int64_t n, int64_t n_rows, const uint32_t* __restrict__ x, int ldx,
+    const float* __restrict__ tapw, int ncls, const float* __restrict__ Whi, const float* __restrict__ Wlo, const float* __restrict__ Shi,
     const float* __restrict__ Slo, evad_epilogue_t E, float* __restrict__ out, int ldo, int out_h2, evad_epilogue_t ES,
     float* __restrict__ skip_out, int ld_skip, uint32_t* __restrict__ status) {
     using C = L1HCfg<CP>;
@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(L1H_THREADS, 2) spline_l1_h16_kernel(
     const int mt = warp & 1, kq = warp >> 1;                 // contraction role: m16 tile, k quarter
     const int64_t ntiles = (n + L1H_NODES - 1) / L1H_NODES;
     const uint32_t zero4 = (uint32_t)ncls * 0x01010101u;     // four copies of the all-zero class
-    const uint32_t nmax = (uint32_t)(n - 1);
+    const uint32_t nmax = (uint32_t)(n_rows - 1);
     // lane bases of the row gathers; an address is base + row * (4 ldx) as ONE 32 x 32 + 64 bit multiply-add
     const char* xg = reinterpret_cast<const char*>(x + 2 * g);
     const char* xg16 = reinterpret_cast<const char*>(x + 16 + g);
@@ -455,7 +455,7 @@ __global__ void __launch_bounds__(L1H_THREADS, 2) spline_l1_h16_kernel(
 
 template <int CP>
 static int launch_l1_h16(const int32_t* count, const int32_t* src, const uint8_t* cls, const int32_t* perm, int64_t n,
-                         const uint32_t* x, int ldx, const float* tapw, int ncls, const float* Whi, const float* Wlo,
+                         int64_t n_rows, const uint32_t* x, int ldx, const float* tapw, int ncls, const float* Whi, const float* Wlo,
                          const float* Shi, const float* Slo, const evad_epilogue_t& E, float* out, int ldo, int out_h2,
                          const evad_epilogue_t& ES, float* skip_out, int ld_skip, uint32_t* status, cudaStream_t st) {
     const size_t smem = L1HCfg<CP>::smem_bytes(ncls);
@@ -468,21 +468,21 @@ static int launch_l1_h16(const int32_t* count, const int32_t* src, const uint8_t
     }
     const int64_t ntiles = (n + L1H_NODES - 1) / L1H_NODES;
     const int grid = (int)(ntiles < 2 * 148 ? ntiles : 2 * 148);
-    spline_l1_h16_kernel<CP><<<grid, L1H_THREADS, smem, st>>>(count, src, cls, perm, n, x, ldx, tapw, ncls, Whi, Wlo, Shi, Slo,
+    spline_l1_h16_kernel<CP><<<grid, L1H_THREADS, smem, st>>>(count, src, cls, perm, n, n_rows, x, ldx, tapw, ncls, Whi, Wlo, Shi, Slo,
                                                                E, out, ldo, out_h2, ES, skip_out, ld_skip, status);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }
 
 extern "C" int evad_spline_conv_l1_h16(const int32_t* count, const int32_t* nbr, const uint8_t* nbr_cls, const int32_t* perm,
-                                       int64_t n, const uint32_t* x_h2, int ldx, int cin_pad, const float* tapw, int ncls,
-                                       const float* Whi, const float* Wlo, const float* Shi, const float* Slo,
+                                       int64_t n, int64_t n_rows, const uint32_t* x_h2, int ldx, int cin_pad,
+                                       const float* tapw, int ncls, const float* Whi, const float* Wlo, const float* Shi, const float* Slo,
                                        const evad_epilogue_t* epi_h, float* out, int ldo, int out_h2,
                                        const evad_epilogue_t* skip_epi_h, float* skip_out, int ld_skip, uint32_t* status,
                                        void* stream) {
     if (!count || !nbr || !nbr_cls || !x_h2 || !tapw || !Whi || !Wlo || !epi_h || !out) return EVAD_ERR_ARG;
     if (cin_pad != 16 && cin_pad != 20) return EVAD_ERR_UNSUPPORTED;
-    if (n * 16 >= (1ll << 31) || n * (int64_t)ldx >= (1ll << 32)) return EVAD_ERR_ARG;   // 32-bit row offsets in the kernel
+    if (n_rows < n || n_rows * 16 >= (1ll << 31) || n_rows * (int64_t)ldx >= (1ll << 32)) return EVAD_ERR_ARG;
     if (epi_h->addend && ((((uintptr_t)epi_h->addend) & 15) != 0 || epi_h->ld_add % 4 != 0)) return EVAD_ERR_ARG;
     if (ldx < cin_pad || ldx % 4 != 0 || ldo % 4 != 0 || ncls < 1 || ncls > 255) return EVAD_ERR_ARG;   // class ncls = the all-zero row, one byte
     if ((((uintptr_t)x_h2 | (uintptr_t)tapw | (uintptr_t)Whi | (uintptr_t)Wlo | (uintptr_t)out | (uintptr_t)nbr |
@@ -495,8 +495,8 @@ extern "C" int evad_spline_conv_l1_h16(const int32_t* count, const int32_t* nbr,
     const evad_epilogue_t es = has_skip ? *skip_epi_h : *epi_h;
     cudaStream_t st = (cudaStream_t)stream;
     if (cin_pad == 20)
-        return launch_l1_h16<20>(count, nbr, nbr_cls, perm, n, x_h2, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
+        return launch_l1_h16<20>(count, nbr, nbr_cls, perm, n, n_rows, x_h2, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
                                  has_skip ? Slo : nullptr, *epi_h, out, ldo, out_h2, es, skip_out, ld_skip, status, st);
-    return launch_l1_h16<16>(count, nbr, nbr_cls, perm, n, x_h2, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
+    return launch_l1_h16<16>(count, nbr, nbr_cls, perm, n, n_rows, x_h2, ldx, tapw, ncls, Whi, Wlo, has_skip ? Shi : nullptr,
                              has_skip ? Slo : nullptr, *epi_h, out, ldo, out_h2, es, skip_out, ld_skip, status, st);
 }

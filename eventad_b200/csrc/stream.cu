@@ -433,3 +433,48 @@ extern "C" int evad_stream_append(void* state, int B, int H, int W, int Q, const
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }
+
+// ------------------------------------------------------------------------------------------------ rows of appended events
+// Incremental layer updates (reference: the asynchronous convolution recomputes new nodes from their
+// in-edges, src/dagr/asynchronous/conv.py:110-127,183-193): the CSR rows evad_stream_append returns for the n new events
+// are written into the GLOBAL fixed-stride row arrays nbr[N][K] / count[N] / nbr_cls[N][K] at node ids base_index + p,
+// the layout evad_spline_conv_l1_h16 and evad_voxel_pool read (ell_stride = K).  The class byte of an edge is its pixel
+// offset (dx + r) * (2r + 1) + (dy + r), as evad_graph_build_rows writes it; unused slots hold the node itself and 255.
+__global__ void __launch_bounds__(256) st_rows_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ src,
+                                                      int64_t n, int base_index, int min_index, const int32_t* __restrict__ pos,
+                                                      int radius, int K, int32_t* __restrict__ nbr, int32_t* __restrict__ count,
+                                                      uint8_t* __restrict__ nbr_cls, uint32_t* __restrict__ status) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t p = t / K;
+    const int s = (int)(t - p * K);
+    if (p >= n) return;
+    const int i = base_index + (int)p;
+    const int r0 = rowptr[p], deg = min(rowptr[p + 1] - r0, K);
+    if (s == 0) count[i] = deg;
+    int j = i;
+    uint32_t c = 255u;
+    if (s < deg) {
+        j = src[r0 + s] + min_index;
+        const int dx = pos[3 * (int64_t)j] - pos[3 * (int64_t)i], dy = pos[3 * (int64_t)j + 1] - pos[3 * (int64_t)i + 1];
+        if (abs(dx) > radius || abs(dy) > radius) {
+            atomicOr(status, EVAD_STATUS_LUT_OOB);
+        } else {
+            c = (uint32_t)((dx + radius) * (2 * radius + 1) + (dy + radius));
+        }
+    }
+    nbr[(int64_t)i * K + s] = j;
+    nbr_cls[(int64_t)i * K + s] = (uint8_t)c;
+}
+
+extern "C" int evad_stream_rows(const int32_t* rowptr, const int32_t* src, int64_t n_new, int base_index, int min_index,
+                                const int32_t* pos_int, int radius, int max_neighbors, int32_t* nbr, int32_t* count,
+                                uint8_t* nbr_cls, uint32_t* status, void* stream) {
+    if (!rowptr || !src || !pos_int || !nbr || !count || !nbr_cls || !status || n_new < 0 || max_neighbors < 1)
+        return EVAD_ERR_ARG;
+    if ((2 * radius + 1) * (2 * radius + 1) > 255) return EVAD_ERR_UNSUPPORTED;
+    if (n_new == 0) return EVAD_OK;
+    st_rows_kernel<<<evad_cdiv(n_new * max_neighbors, 256), 256, 0, (cudaStream_t)stream>>>(
+        rowptr, src, n_new, base_index, min_index, pos_int, radius, max_neighbors, nbr, count, nbr_cls, status);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}

@@ -265,10 +265,16 @@ class Net(torch.nn.Module):
         # of a tile hit L1 instead of L2
         xk = self.conv_block1.run_fused(x0, rowptr, src, n, None, pseudo, status, perm=graph["cell_perm"], cls=cls1,
                                         ell_stride=ell, x_h2=x0_h2)
+        cur = dict(x=xk, pos=pos, batch=batch_i32, rowptr=rowptr, src=src, n_cap=n, n_dev=None, e_cap=src.shape[0], ell=ell)
+        return self._enqueue_tail(cur, f, num_graphs, width, height, status)
+
+    def _enqueue_tail(self, cur, f, num_graphs, width, height, status):
+        """pool1 .. layer5 on the layer-1 output `cur` (net.py:129-187); also the dense tail of the incremental update
+        (asynchronous/incremental.py), where `cur` holds all resident nodes and only its newest rows were recomputed."""
+        dev = cur["x"].device
         counts = torch.zeros(12, dtype=torch.int32, device=dev)
         pools = [self.pool1, self.pool2, self.pool3, self.pool4]
         layers = [self.layer2, self.layer3, self.layer4, self.layer5]
-        cur = dict(x=xk, pos=pos, batch=batch_i32, rowptr=rowptr, src=src, n_cap=n, n_dev=None, e_cap=src.shape[0], ell=ell)
         outs = []
         for k in range(4):
             p = pools[k]

@@ -421,7 +421,7 @@ def spline_conv_l1(rowptr, src, cls, n, x, cin, pack, epi, skip_epi=None, perm=N
                       "evad_spline_conv_l1_tc5")
             return out, skip_out
         with _timed(f'spline_conv_l1_c{cin}'):
-            check(L.evad_spline_conv_l1_h16(ptr(rowptr), ptr(src), ptr(cls), ptr(perm), n, ptr(x), x.stride(0), pack["cin_pad"],
+            check(L.evad_spline_conv_l1_h16(ptr(rowptr), ptr(src), ptr(cls), ptr(perm), n, n, ptr(x), x.stride(0), pack["cin_pad"],
                                             ptr(pack["tapw"]), pack["tapw"].shape[0], ptr(pack["whi"]), ptr(pack["wlo"]),
                                             ptr(pack["shi"]) if has_skip else None, ptr(pack["slo"]) if has_skip else None,
                                             ctypes.byref(e), ptr(out), out.stride(0), int(out_h2),

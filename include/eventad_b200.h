@@ -124,6 +124,15 @@ int evad_stream_append(void* state, int batch_size, int height, int width, int m
                        int32_t* num_edges, int64_t* edge_index, int64_t edge_index_stride, uint32_t* status, void* ws,
                        size_t ws_bytes, void* stream);
 
+/* Incremental layer updates (src/dagr/asynchronous/conv.py:110-127,183-193: new nodes are recomputed from
+ * their in-edges): the CSR rows evad_stream_append returned for n_new events (rowptr[n_new+1], src relative to
+ * min_index) are written into GLOBAL fixed-stride rows nbr[N][K] / count[N] / nbr_cls[N][K] at node ids
+ * base_index + p, the layout evad_spline_conv_l1_h16 and evad_voxel_pool read; pos_int = [N][3] pixel / microsecond
+ * coordinates of all resident events.  Class byte = (dx + r)(2r + 1) + (dy + r) like evad_graph_build_rows. */
+int evad_stream_rows(const int32_t* rowptr, const int32_t* src, int64_t n_new, int base_index, int min_index,
+                     const int32_t* pos_int, int radius, int max_neighbors, int32_t* nbr, int32_t* count,
+                     uint8_t* nbr_cls, uint32_t* status, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------------
  * SplineConv message passing.
  * Replaces MySplineConv.forward/_forward/message_lut/init_lut (src/dagr/model/layers/spline_conv.py:16-78), PyG
@@ -242,10 +251,12 @@ int evad_spline_conv_l1_tc5(const int32_t* count, const int32_t* nbr, const uint
  * x_h2: node features as "h2 words" (low half = rn16(v), high half = rn16((v - hi) * 2048); |v| < 2048), produced by
  * evad_split_h2 from fp32 rows or by this entry point itself when out_h2 != 0 (the layer's second convolution gathers the
  * first one's output).  Weights as for evad_spline_conv_l1_mma (the TF32 pair; their sum is re-split in the kernel).
- * status: device word, EVAD_STATUS_H16_RANGE is raised when an h2 output leaves the range (may be NULL). */
+ * status: device word, EVAD_STATUS_H16_RANGE is raised when an h2 output leaves the range (may be NULL).
+ * n nodes are computed (ids perm[0..n), or 0..n-1 without perm); n_rows >= n is the row count of x_h2 / the row arrays
+ * (incremental updates compute a few new nodes of a larger resident graph: n << n_rows). */
 int evad_split_h2(const float* in, uint32_t* out, int64_t n_words, uint32_t* status, void* stream);
 int evad_spline_conv_l1_h16(const int32_t* count, const int32_t* nbr, const uint8_t* nbr_cls, const int32_t* perm,
-                            int64_t n, const uint32_t* x_h2, int ldx, int cin_pad, const float* tapw, int ncls,
+                            int64_t n, int64_t n_rows, const uint32_t* x_h2, int ldx, int cin_pad, const float* tapw, int ncls,
                             const float* Whi, const float* Wlo, const float* Shi, const float* Slo,
                             const evad_epilogue_t* epi_h, float* out, int ldo, int out_h2,
                             const evad_epilogue_t* skip_epi_h, float* skip_out, int ld_skip, uint32_t* status,

@@ -1,0 +1,70 @@
+"""Incremental forward of the event branch (eventad_b200/asynchronous/incremental.py): a window is started
+with `reset(first events)` and fed micro-batches with `update(new events)`; after every call the outputs must be the
+dense fused forward's on ALL events seen so far.  The reference's checker for its asynchronous layers compares dense and
+incremental activations within 1e-3 (asynchronous/evaluate_flops.py:141-143); here the two paths run the same kernels on
+the same rows, so the bar is bit-exact: node sets, positions, edges and features."""
+import copy
+
+import pytest
+import torch
+
+from eventad_b200 import synthetic
+from eventad_b200.synthetic import make_backbone, make_data
+
+pytestmark = pytest.mark.gpu
+
+
+def _part(d, a, b):
+    from eventad_b200.data import Batch
+    p = Batch(x=d.x[a:b].clone(), pos=d.pos[a:b].clone(), batch=d.batch[a:b].clone())
+    p.num_graphs, p.width, p.height, p.time_window = d.num_graphs, d.width, d.height, d.time_window
+    return p
+
+
+def _same(got, want, what):
+    assert len(got) == len(want) == 2
+    for o, r in zip(got, want):
+        assert torch.equal(o.batch, r.batch), what
+        assert torch.equal(o.pos, r.pos), what
+        assert torch.equal(o.edge_index, r.edge_index), what
+        assert torch.equal(o.x, r.x), (what, float((o.x - r.x).abs().max()))
+
+
+@pytest.mark.parametrize("dist,n0,steps", [("U", 20_000, (1, 1, 10, 100, 1000, 3, 5000)),
+                                           ("C", 5_000, (7, 64, 96, 97, 2000, 1)),
+                                           ("U", 1, (1, 2, 500))])
+def test_incremental_updates_equal_dense_forward(dist, n0, steps):
+    from eventad_b200.asynchronous.incremental import IncrementalBackbone
+    model, args = make_backbone(seed=3, use_image=True)
+    model.cache_luts(320, 240, args.radius)
+    net = model.cuda().backbone
+    dense_net = copy.deepcopy(net)                       # its own graph creator: the dense passes must not touch the stream
+    feats = [f.cuda() for f in synthetic.make_image_features(1, seed=6)]
+    total = n0 + sum(steps)
+    d = make_data(total, 1, seed=11, dist=dist, device="cuda")
+    inc = IncrementalBackbone(net, capacity=total, feats=feats)
+    with torch.no_grad():
+        _same(inc.reset(_part(d, 0, n0)), dense_net(_part(d, 0, n0), image_feat=feats)[0], "reset")
+        done = n0
+        for k, m in enumerate(steps):
+            got = inc.update(_part(d, done, done + m))
+            done += m
+            _same(got, dense_net(_part(d, 0, done), image_feat=feats)[0], f"update {k} (+{m})")
+    assert inc.n == total
+
+
+def test_incremental_reset_starts_a_new_window_and_capacity_is_checked():
+    from eventad_b200.asynchronous.incremental import IncrementalBackbone
+    model, args = make_backbone(seed=1, use_image=True)
+    model.cache_luts(320, 240, args.radius)
+    net = model.cuda().backbone
+    dense_net = copy.deepcopy(net)
+    feats = [f.cuda() for f in synthetic.make_image_features(1, seed=2)]
+    inc = IncrementalBackbone(net, capacity=4000, feats=feats)
+    with torch.no_grad():
+        for seed in (1, 2):
+            d = make_data(3000, 1, seed=seed, dist="C", device="cuda")
+            inc.reset(_part(d, 0, 2000))
+            _same(inc.update(_part(d, 2000, 3000)), dense_net(_part(d, 0, 3000), image_feat=feats)[0], f"window {seed}")
+        with pytest.raises(RuntimeError, match="capacity"):
+            inc.update(_part(d, 0, 1500))
