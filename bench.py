@@ -331,10 +331,64 @@ def leg_streaming(a, dev, iters=200):
                            delta_t_us=10000)
     g.forward(batch[:n0], pos[:n0], delete_nodes=False, collect_edges=False)
     res = time_stream(lambda b, p: g.forward(b, p, delete_nodes=True, collect_edges=False), batch, pos, n0, iters)
-    return {"resident_events": n0, "iters": iters - 5, "distribution": a.dist, "latency": res,
-            "what": "graph stage of the asynchronous mode (append + search of the new events + delete_nodes), CUDA events "
-                    "around every SlidingWindowGraph.forward call incl. its edge-count read-back; the layer stack of a "
-                    "streamed window is the dense branch (`latency` key) -- incremental layer updates are not built"}
+    out = {"resident_events": n0, "iters": iters - 5, "distribution": a.dist, "latency": res,
+           "what": "graph stage of the asynchronous mode (append + search of the new events + delete_nodes), CUDA events "
+                   "around every SlidingWindowGraph.forward call incl. its edge-count read-back"}
+    del g
+    try:
+        out["incremental_forward"] = leg_incremental(a, dev)
+    except Exception as ex:                                       # report, do not hide
+        out["incremental_forward"] = {"error": repr(ex)[:300]}
+    return out
+
+
+def leg_incremental(a, dev, n0=1_000_000, iters=25):
+    """the WHOLE event branch per micro-batch on n0 resident events of one window (B = 1): graph append +
+    layer 1 on the new nodes + dense tail (asynchronous/incremental.py), against the dense fused forward of the same
+    n0 events.  Outputs are bit-identical to the dense forward's (tests/test_incremental_gpu.py)."""
+    from eventad_b200 import synthetic
+    from eventad_b200.asynchronous.incremental import IncrementalBackbone
+    from eventad_b200.data import Batch
+    model, args = synthetic.make_backbone(seed=0, use_image=True)
+    model.cache_luts(320, 240, args.radius)
+    net = model.to(dev).backbone
+    feats = [f.to(dev) for f in synthetic.make_image_features(1, seed=0)]
+    extra = sum(s * (iters + 3) for s in STREAM_SIZES)
+    d = synthetic.make_data(n0 + extra, 1, seed=42, dist=a.dist, device=dev)
+
+    def part(lo, hi):
+        p = Batch(x=d.x[lo:hi], pos=d.pos[lo:hi], batch=d.batch[lo:hi])
+        p.num_graphs, p.width, p.height, p.time_window = 1, d.width, d.height, d.time_window
+        return p
+    inc = IncrementalBackbone(net, capacity=n0 + extra, feats=feats)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    dense = []
+    with torch.no_grad():
+        for i in range(6):
+            e0, e1 = ev(), ev()
+            e0.record()
+            inc.reset(part(0, n0))
+            e1.record()
+            torch.cuda.synchronize()
+            if i:
+                dense.append(e0.elapsed_time(e1))
+        lat, done = {}, n0
+        for sz in STREAM_SIZES:
+            ts = []
+            for i in range(iters + 3):
+                e0, e1 = ev(), ev()
+                e0.record()
+                inc.update(part(done, done + sz))
+                e1.record()
+                torch.cuda.synchronize()
+                done += sz
+                if i >= 3:
+                    ts.append(e0.elapsed_time(e1))
+            lat[str(sz)] = {"p50_ms": float(np.median(ts)), "p90_ms": float(np.percentile(ts, 90))}
+    return {"resident_events": n0, "iters": iters, "dense_forward_ms_p50": float(np.median(dense)), "latency": lat,
+            "what": "IncrementalBackbone.update(micro-batch) -> out3 / out4 of ALL resident events, CUDA events around the "
+                    "call incl. its two host read-backs; dense_forward = IncrementalBackbone.reset(all n0 events) = graph "
+                    "build + layer 1 on every node + the same tail"}
 
 
 def leg_full_model(dev, world, rank, windows=100, B=6, events=100_000):

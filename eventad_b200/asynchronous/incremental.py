@@ -14,8 +14,9 @@ hence not its layer-1 output.  The incremental update is therefore exact, not a 
   x0        evad_sample_concat_h2 on the new events only
   layer 1   evad_spline_conv_l1_h16 over perm = the new node ids (two launches: conv + skip, conv + residual)
   pool1 ..  the dense tail (Net._enqueue_tail: evad_voxel_pool over all resident nodes, then 2 240 voxels per window
-  layer5    through layers 2-5): its cost is independent of the micro-batch and small next to graph + layer 1,
-            which are 60 % of a dense forward and are what grows with the resident events.
+  layer5    through layers 2-5), captured once in a CUDA graph over the full-capacity buffers (the resident count is a
+            device cell): its cost is independent of the micro-batch and small next to graph + layer 1, which are
+            60 % of a dense forward and are what grows with the resident events.
 
 Results equal the dense fused forward on the accumulated events BIT FOR BIT (same kernels, same rows, same per-node
 arithmetic; tests/test_incremental_gpu.py), which is stronger than the reference checker's 1e-3.  Not built: an
@@ -23,12 +24,16 @@ incremental voxel pooling with cached arg-max (the tail recomputes pool 1 from t
 inside a window (SlidingWindowGraph.delete_nodes): `update` is append-only until the next `reset`.
 """
 import ctypes
+import os
 
 import torch
 
 from .. import _lib, ops
 from ..graph import stream as gstream
 from ..model.layers.conv import _fold
+
+
+USE_TAIL_GRAPH = os.environ.get("EVAD_INCR_GRAPH", "1") != "0"   # 0: the dense tail as plain launches (debugging)
 
 
 class IncrementalBackbone:
@@ -55,6 +60,11 @@ class IncrementalBackbone:
         self.skip = torch.zeros((c, 16), dtype=torch.float32, device=dev)
         self.xk = torch.zeros((c, 16), dtype=torch.float32, device=dev)      # layer-1 output
         self._packs = None
+        # the dense tail is captured once in a CUDA graph over the full-capacity buffers; the number of resident events
+        # is a device cell (every kernel of the tail takes its row count from device memory)
+        self._n_dev = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._scratch = _lib.Scratch()
+        self._tail_graph, self._tail_res = None, None
 
     # ------------------------------------------------------------------------------------------------ pieces
     def _graph_creator(self):
@@ -101,13 +111,41 @@ class IncrementalBackbone:
                 ctypes.byref(pk["e2"]), ptr(self.xk), 16, 0, None, None, 0, ptr(status), _lib.stream()),
                 "evad_spline_conv_l1_h16 (incremental, conv 2)")
 
+    def _enqueue_tail(self):
+        w, h, tw, b = self.meta
+        cur = dict(x=self.xk, pos=self.pos, batch=self.batch, rowptr=self.count, src=self.nbr.view(-1), n_cap=self.cap,
+                   n_dev=self._n_dev, e_cap=self.cap * 16, ell=16)
+        saved = ops._SCRATCH
+        ops._SCRATCH = self._scratch
+        try:
+            status = self._scratch.status(self.pos.device)
+            status.zero_()
+            return self.net._enqueue_tail(cur, self.feats, b, w, h, status)
+        finally:
+            ops._SCRATCH = saved
+
     def _tail(self):
         w, h, tw, b = self.meta
-        N = self.n
-        cur = dict(x=self.xk[:N], pos=self.pos[:N], batch=self.batch[:N], rowptr=self.count[:N], src=self.nbr.view(-1),
-                   n_cap=N, n_dev=None, e_cap=N * 16, ell=16)
-        res = self.net._enqueue_tail(cur, self.feats, b, w, h, self._gc._status)
-        outs = self.net.finalize_fused(res)
+        self._n_dev.fill_(self.n)
+        if not USE_TAIL_GRAPH:
+            res = self._enqueue_tail()
+            return self._finish(self.net.finalize_fused(res))
+        if self._tail_graph is None:
+            side = torch.cuda.Stream(device=self.dev)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(2):                           # warm-up: workspaces, folded BN, function attributes
+                    self._enqueue_tail()
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            self._tail_graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._tail_graph):
+                self._tail_res = self._enqueue_tail()
+        self._tail_graph.replay()
+        return self._finish(self.net.finalize_fused(self._tail_res))
+
+    def _finish(self, outs):
+        w, h, tw, b = self.meta
         for o in outs:
             o.width, o.height = torch.tensor([w] * b), torch.tensor([h] * b)
         return outs

@@ -2,7 +2,10 @@
 with `reset(first events)` and fed micro-batches with `update(new events)`; after every call the outputs must be the
 dense fused forward's on ALL events seen so far.  The reference's checker for its asynchronous layers compares dense and
 incremental activations within 1e-3 (asynchronous/evaluate_flops.py:141-143); here the two paths run the same kernels on
-the same rows, so the bar is bit-exact: node sets, positions, edges and features."""
+the same rows, so the bar is bit-exact for node sets, positions and edges, and for the features too whenever both paths
+plan their kernels on the same size bounds (capacity >= the 4 480 voxel keys of a window: the pooled layers pick GEMM
+variants / split-K plans from upper bounds, and a different plan sums in a different order); north_star's rtol 1e-4 /
+atol 1e-5 otherwise."""
 import copy
 
 import pytest
@@ -10,6 +13,7 @@ import torch
 
 from eventad_b200 import synthetic
 from eventad_b200.synthetic import make_backbone, make_data
+from tests.util import assert_close
 
 pytestmark = pytest.mark.gpu
 
@@ -21,18 +25,21 @@ def _part(d, a, b):
     return p
 
 
-def _same(got, want, what):
+def _same(got, want, what, exact=True):
     assert len(got) == len(want) == 2
     for o, r in zip(got, want):
         assert torch.equal(o.batch, r.batch), what
         assert torch.equal(o.pos, r.pos), what
         assert torch.equal(o.edge_index, r.edge_index), what
-        assert torch.equal(o.x, r.x), (what, float((o.x - r.x).abs().max()))
+        if exact:
+            assert torch.equal(o.x, r.x), (what, float((o.x - r.x).abs().max()))
+        else:
+            assert_close(o.x, r.x, what=what)
 
 
 @pytest.mark.parametrize("dist,n0,steps", [("U", 20_000, (1, 1, 10, 100, 1000, 3, 5000)),
                                            ("C", 5_000, (7, 64, 96, 97, 2000, 1)),
-                                           ("U", 1, (1, 2, 500))])
+                                           ("U", 4_700, (1, 2, 500))])
 def test_incremental_updates_equal_dense_forward(dist, n0, steps):
     from eventad_b200.asynchronous.incremental import IncrementalBackbone
     model, args = make_backbone(seed=3, use_image=True)
@@ -64,7 +71,26 @@ def test_incremental_reset_starts_a_new_window_and_capacity_is_checked():
     with torch.no_grad():
         for seed in (1, 2):
             d = make_data(3000, 1, seed=seed, dist="C", device="cuda")
-            inc.reset(_part(d, 0, 2000))
-            _same(inc.update(_part(d, 2000, 3000)), dense_net(_part(d, 0, 3000), image_feat=feats)[0], f"window {seed}")
+            _same(inc.reset(_part(d, 0, 2000)), dense_net(_part(d, 0, 2000), image_feat=feats)[0], f"window {seed} reset", exact=False)
+            _same(inc.update(_part(d, 2000, 3000)), dense_net(_part(d, 0, 3000), image_feat=feats)[0], f"window {seed}", exact=False)
         with pytest.raises(RuntimeError, match="capacity"):
             inc.update(_part(d, 0, 1500))
+
+
+def test_incremental_from_a_single_event():
+    """A window that starts with one event (EV_TGN's insert_in_queue_single path) and grows by 1, 2, 500."""
+    from eventad_b200.asynchronous.incremental import IncrementalBackbone
+    model, args = make_backbone(seed=3, use_image=True)
+    model.cache_luts(320, 240, args.radius)
+    net = model.cuda().backbone
+    dense_net = copy.deepcopy(net)
+    feats = [f.cuda() for f in synthetic.make_image_features(1, seed=6)]
+    d = make_data(504, 1, seed=11, dist="U", device="cuda")
+    inc = IncrementalBackbone(net, capacity=504, feats=feats)
+    with torch.no_grad():
+        _same(inc.reset(_part(d, 0, 1)), dense_net(_part(d, 0, 1), image_feat=feats)[0], "reset", exact=False)
+        done = 1
+        for m in (1, 2, 500):
+            got = inc.update(_part(d, done, done + m))
+            done += m
+            _same(got, dense_net(_part(d, 0, done), image_feat=feats)[0], f"+{m}", exact=False)
