@@ -646,24 +646,26 @@ def run_b200(a):
     # index (4 B) read, conv output 64 B + skip output 64 B written; per edge the source index (4 B) and the offset-class
     # byte (1 B); gathered rows counted once
     dom_bytes = Ntot * (80 + 4 + 4 + 64 + 64) + 5 * E
-    # DRAM bytes of the same launch from the committed `ncu --set full` capture (profiles/r01g_spline_l1_mma_full_raw.csv:
-    # dram__bytes_read.sum 134.5 MB + dram__bytes_write.sum 74.4 MB at 8 x 100k uniform events), scaled per event
-    ncu_traffic = 208.9e6 / 800000.0 * Ntot if a.dist == "U" else None
+    # DRAM bytes of the same launch from the committed `ncu --set full` capture of THIS kernel (profiles/
+    # r02n_l1_h16_full_raw.csv, round 2: dram__bytes_read.sum 134.54 MB + dram__bytes_write.sum 75.21 MB for
+    # spline_l1_h16_kernel<20> at 8 x 100k uniform events), scaled per event; null for other distributions / kernels
+    from eventad_b200 import ops as _ops
+    h16 = _ops.USE_L1_MMA and _ops.USE_L1_H16 and not _ops.USE_L1_TC5
+    ncu_traffic = 209.75e6 / 800000.0 * Ntot if (a.dist == "U" and h16) else None
     roofline = None
     if dom_ms:
         ach = dom_bytes / (dom_ms * 1e-3) / 1e9
-        from eventad_b200 import ops as _ops
-        kname = ("spline_l1_mma_kernel<20> (conv_block1.conv_block1: 19->16 LUT conv + BN + ReLU + skip Linear/BN; per-node "
-                 "tap aggregation and the weight contraction both as 3xTF32 mma.sync products, one launch)") if _ops.USE_L1_MMA else \
-                ("spline_l1_kernel<20> (conv_block1.conv_block1: 19->16 LUT conv + BN + ReLU + skip Linear/BN; "
-                 "register tap aggregation + 3xTF32 mma contraction, one launch)")
+        kname = ("spline_l1_h16_kernel<20> (conv_block1.conv_block1: 19->16 LUT conv + BN + ReLU + skip Linear/BN; per-node tap "
+                 "aggregation and the weight contraction both as fp16-pair mma.sync m16n8k16 products, one launch)") if h16 else \
+                ("layer-1 kernel selected by EVAD_L1_H16 / EVAD_L1_MMA / EVAD_L1_TC5 (not the default)")
         roofline = {"bound": "hbm", "kernel": kname,
                     "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": ncu_traffic,
+                    "traffic_source": "profiles/r02n_l1_h16_full_raw.csv (ncu --set full, round 2), scaled per event",
                     "peak_source": peak_kind, "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": dom_ms,
                     "share_of_step": dom_ms / ms_plain_step,
-                    "note": "ncu: DRAM 4.3 % of peak, L1 data pipe (LSU wavefronts: row gathers + shared-memory fragment "
-                            "traffic) 75 %, tensor pipe 42 %, issue slots 53 % -- bound by the L1 data pipe and by latency at "
-                            "16 warps per SM, not by HBM; see profiles/r01g_summary.md"}
+                    "note": "ncu: DRAM traffic = the algorithmic bytes (6 % of the HBM peak); the kernel is bound on chip: L1 "
+                            "data-pipe LSU wavefronts 83 % (shared-memory fragments + row gathers), issue slots 50 %, 16 warps "
+                            "per SM at 128 registers, top stall long_scoreboard; see profiles/r02_summary.md"}
     n1 = 2240.0 * B                                              # pool-1 nodes (upper bound without the t==T extras)
     path_bytes = 1200 * Ntot + 108 * E + 1100 * n1                # SURVEY.md 8(d) module-boundary model
     path_ach = path_bytes / (ms_total / a.steps * 1e-3) / 1e9
