@@ -62,10 +62,18 @@ __global__ void __launch_bounds__(AG_THREADS) spline_agg_kernel(const int32_t* _
 // straight to A (no shared accumulators, no zero fill / copy-out pass).  Per tap the contributions are added in
 // ascending edge order with separate fp32 multiply and add, exactly like spline_agg_kernel, so both give the same bits.
 #define AG2_WARPS 8
+#define AG2_WARPS_H2 4                // H2: a warp also owns a ring of AH2_RING floats through which its rows leave
+#define AH2_RING 512                  // floats; >= 256 (flush threshold) + cin + 64 (root slot + K tail)
 #define AG2_EDGES 16
 
-template <int CPL>
-__global__ void __launch_bounds__(AG2_WARPS * 32) spline_agg2_kernel(const int32_t* __restrict__ rowptr,
+// H2 (evad_spline_aggregate_h2): A is not a row-major fp32 matrix but the operand image of evad_gemm64_h2 -- per
+// (128-row tile, 64-column K chunk) one 32 KB block [leading fp16 parts 16 KB | fp16 remainders x 2048 16 KB], each a
+// 128 x 128-byte tile in the SWIZZLE_128B K-major layout of a UMMA operand (16-byte unit u of row r at (u ^ (r & 7))),
+// so that the GEMM fetches a block with ONE bulk copy and hands it to tcgen05.mma without touching it.  `lda` is then
+// the number of K chunks per row tile; columns K .. 64 * lda - 1 of valid rows are written as zeros.
+#define AH2_BLOCK 32768
+template <int CPL, bool H2>
+__global__ void __launch_bounds__((H2 ? AG2_WARPS_H2 : AG2_WARPS) * 32) spline_agg2_kernel(const int32_t* __restrict__ rowptr,
                                                                      const int32_t* __restrict__ src, int64_t n,
                                                                      const int32_t* __restrict__ n_dev,
                                                                      const float* __restrict__ x, int ldx, int cin,
@@ -73,18 +81,61 @@ __global__ void __launch_bounds__(AG2_WARPS * 32) spline_agg2_kernel(const int32
                                                                      int64_t lda, uint32_t* __restrict__ status, int tsplit) {
     // tsplit > 1 (small inputs, where one node's tap walk IS the kernel's latency): tsplit warps share a node, warp `sub`
     // takes the taps sub, sub + tsplit, ...; every tap is still summed by one warp in ascending edge order (same bits)
-    extern __shared__ __align__(16) float ag2_rows[];         // [AG2_WARPS][AG2_EDGES][ldx]
+    extern __shared__ __align__(16) float ag2_rows[];         // [WARPS][AG2_EDGES][ldx] (+ H2: [WARPS][AH2_RING])
+    constexpr int WARPS = H2 ? AG2_WARPS_H2 : AG2_WARPS;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int ntap = M.ks * M.ks;
     const int qpr = ldx >> 2;                                 // 128-bit quads per row
     float* xs = ag2_rows + (size_t)warp * AG2_EDGES * ldx;
+    // H2: tap rows go through a small fp32 ring in shared memory (column k at k mod AH2_RING) and leave as 16-byte units
+    // (8 columns) of leading parts / remainders as soon as >= 256 columns are complete: all lanes store, and the ring is
+    // small enough to keep the occupancy of the fp32 variant.  Rows with more than AG2_EDGES edges add their later
+    // chunks to the image by read-modify-write of the same units.
+    float* ring = H2 ? ag2_rows + (size_t)WARPS * AG2_EDGES * ldx + (size_t)warp * AH2_RING : nullptr;
+    bool h2_ok = true;
+    auto ring_flush = [&](int64_t i, int lo, int hi, bool accum) {   // columns [lo, hi), both multiples of 8
+        __syncwarp();
+        const int r = (int)(i & 127);
+        uint8_t* tile = reinterpret_cast<uint8_t*>(A) + (i >> 7) * lda * AH2_BLOCK + r * 128;
+        for (int unit = (lo >> 3) + lane; unit < (hi >> 3); unit += 32) {
+            const float* rp = ring + ((8 * unit) & (AH2_RING - 1));
+            const float4 v0 = *reinterpret_cast<const float4*>(rp), v1 = *reinterpret_cast<const float4*>(rp + 4);
+            float v[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+            uint8_t* dst = tile + (int64_t)(unit >> 3) * AH2_BLOCK + (((unit & 7) ^ (r & 7)) << 4);
+            if (accum) {
+                const uint4 ph = *reinterpret_cast<const uint4*>(dst), pl = *reinterpret_cast<const uint4*>(dst + AH2_BLOCK / 2);
+                const uint32_t hw[4] = {ph.x, ph.y, ph.z, ph.w}, lw[4] = {pl.x, pl.y, pl.z, pl.w};
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const float2 fh = __half22float2(*reinterpret_cast<const __half2*>(&hw[q]));
+                    const float2 fl = __half22float2(*reinterpret_cast<const __half2*>(&lw[q]));
+                    v[2 * q] = __fadd_rn(__fmaf_rn(fl.x, 1.f / 2048.f, fh.x), v[2 * q]);
+                    v[2 * q + 1] = __fadd_rn(__fmaf_rn(fl.y, 1.f / 2048.f, fh.y), v[2 * q + 1]);
+                }
+            }
+            uint32_t hi2[4], lo2[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                h2_ok = h2_ok && fabsf(v[2 * q]) < 32768.f && fabsf(v[2 * q + 1]) < 32768.f;
+                const __half2 h = __floats2half2_rn(v[2 * q], v[2 * q + 1]);
+                const float2 f = __half22float2(h);
+                const __half2 l = __floats2half2_rn(__fmul_rn(__fsub_rn(v[2 * q], f.x), 2048.f),
+                                                    __fmul_rn(__fsub_rn(v[2 * q + 1], f.y), 2048.f));
+                hi2[q] = *reinterpret_cast<const uint32_t*>(&h);
+                lo2[q] = *reinterpret_cast<const uint32_t*>(&l);
+            }
+            *reinterpret_cast<uint4*>(dst) = make_uint4(hi2[0], hi2[1], hi2[2], hi2[3]);
+            *reinterpret_cast<uint4*>(dst + AH2_BLOCK / 2) = make_uint4(lo2[0], lo2[1], lo2[2], lo2[3]);
+        }
+        __syncwarp();
+    };
     const int64_t nn = n_dev ? min((int64_t)*n_dev, n) : n;
-    const int64_t gw = (int64_t)blockIdx.x * AG2_WARPS + warp;
+    const int64_t gw = (int64_t)blockIdx.x * WARPS + warp;
     const int sub = (int)(gw % tsplit);
-    const int64_t stride = (int64_t)gridDim.x * AG2_WARPS / tsplit;
+    const int64_t stride = (int64_t)gridDim.x * WARPS / tsplit;
     for (int64_t i = gw / tsplit; i < nn; i += stride) {
         const int r0 = rowptr[i], r1 = rowptr[i + 1];
-        float* a = A + i * lda;
+        float* a = H2 ? A : A + i * lda;
         bool first = true;
         for (int e0 = r0; e0 < r1 || first; e0 += AG2_EDGES) {
             const int cnt = max(0, min(AG2_EDGES, r1 - e0));
@@ -106,6 +157,7 @@ __global__ void __launch_bounds__(AG2_WARPS * 32) spline_agg2_kernel(const int32
                     reinterpret_cast<float4*>(xs)[idx] = __ldg(reinterpret_cast<const float4*>(x + (int64_t)jj * ldx) + q);
             }
             __syncwarp();
+            int flushed = 0;                                  // H2: columns [0, flushed) of this chunk's pass have left the ring
             for (int tap = sub; tap < ntap; tap += tsplit) {
                 const float wt = k[0] == tap ? w[0] : (k[1] == tap ? w[1] : (k[2] == tap ? w[2] : w[3]));
                 const bool hit = k[0] == tap || k[1] == tap || k[2] == tap || k[3] == tap;
@@ -126,7 +178,18 @@ __global__ void __launch_bounds__(AG2_WARPS * 32) spline_agg2_kernel(const int32
                     }
                 }
                 float* at = a + tap * cin;
-                if (first) {
+                if (H2) {
+#pragma unroll
+                    for (int u = 0; u < CPL; u++) {
+                        const int c = lane + 32 * u;
+                        if (c < cin) ring[(tap * cin + c) & (AH2_RING - 1)] = acc[u];
+                    }
+                    const int end8 = ((tap + 1) * cin) & ~7;
+                    if (end8 - flushed >= 256) {
+                        ring_flush(i, flushed, end8, !first);
+                        flushed = end8;
+                    }
+                } else if (first) {
 #pragma unroll
                     for (int u = 0; u < CPL; u++) {
                         const int c = lane + 32 * u;
@@ -140,10 +203,29 @@ __global__ void __launch_bounds__(AG2_WARPS * 32) spline_agg2_kernel(const int32
                     }
                 }
             }
+            if (H2) {
+                // end of the pass over the taps: the first chunk appends the root slot (the node's own row) and the
+                // zero K tail; later chunks add nothing there (zeros up to the unit boundary)
+                int end = ntap * cin;
+                if (first) {
+                    const float* xi = x + i * ldx;
+#pragma unroll
+                    for (int u = 0; u < CPL; u++) {
+                        const int c = lane + 32 * u;
+                        if (c < cin) ring[(end + c) & (AH2_RING - 1)] = xi[c];
+                    }
+                    for (int k2 = end + cin + lane; k2 < 64 * (int)lda; k2 += 32) ring[k2 & (AH2_RING - 1)] = 0.f;
+                    end = 64 * (int)lda;
+                } else {
+                    for (int k2 = end + lane; k2 < ((end + 7) & ~7); k2 += 32) ring[k2 & (AH2_RING - 1)] = 0.f;
+                    end = (end + 7) & ~7;
+                }
+                ring_flush(i, flushed, end, !first);
+            }
             first = false;
             __syncwarp();
         }
-        if (sub == 0) {                                       // root slot: the node's own row
+        if (sub == 0 && !H2) {                                // root slot: the node's own row
             const float* xi = x + i * ldx;
 #pragma unroll
             for (int u = 0; u < CPL; u++) {
@@ -152,26 +234,29 @@ __global__ void __launch_bounds__(AG2_WARPS * 32) spline_agg2_kernel(const int32
             }
         }
     }
+    if (H2 && !h2_ok) atomicOr(status, EVAD_STATUS_H16_RANGE);
 }
 
-template <int CPL>
+template <int CPL, bool H2 = false>
 static int launch_agg2(const int32_t* rowptr, const int32_t* src, int64_t n, const int32_t* n_dev, const float* x, int ldx,
                        int cin, const evad_pseudo_t& P, const evad_spline_mode_t& M, float* A, int64_t lda,
                        uint32_t* status, cudaStream_t st) {
-    const size_t smem = (size_t)AG2_WARPS * AG2_EDGES * ldx * sizeof(float);
+    constexpr int WARPS = H2 ? AG2_WARPS_H2 : AG2_WARPS;
+    const size_t smem = (size_t)WARPS * (AG2_EDGES * ldx + (H2 ? AH2_RING : 0)) * sizeof(float);
+    if (smem > 200 * 1024) return EVAD_ERR_UNSUPPORTED;
     static size_t attr_bytes = 0;
     if (smem > attr_bytes) {
-        if (cudaFuncSetAttribute(spline_agg2_kernel<CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
+        if (cudaFuncSetAttribute(spline_agg2_kernel<CPL, H2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
             cudaSuccess)
             return EVAD_ERR_LAUNCH;
         attr_bytes = smem;
     }
-    const int tsplit = n <= 2400 ? 4 : 1;                     // AG2_WARPS % tsplit == 0: a node's warps share a CTA
-    const int64_t want = (n * tsplit + AG2_WARPS - 1) / AG2_WARPS;
-    const int64_t cap = 148 * 4 * tsplit;
+    const int tsplit = (n <= 2400 && !H2) ? 4 : 1;            // AG2_WARPS % tsplit == 0: a node's warps share a CTA
+    const int64_t want = (n * tsplit + WARPS - 1) / WARPS;
+    const int64_t cap = 148 * (H2 ? 7 : 4) * tsplit;
     const int grid = (int)(want < cap ? want : cap);
-    spline_agg2_kernel<CPL><<<grid, AG2_WARPS * 32, smem, st>>>(rowptr, src, n, n_dev, x, ldx, cin, P, M, A, lda, status,
-                                                                tsplit);
+    spline_agg2_kernel<CPL, H2><<<grid, WARPS * 32, smem, st>>>(rowptr, src, n, n_dev, x, ldx, cin, P, M, A, lda, status,
+                                                                    tsplit);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }
@@ -211,6 +296,37 @@ extern "C" int evad_spline_aggregate(const int32_t* rowptr, const int32_t* src, 
                                                                       *mode_h, A, lda, status);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
+}
+
+// The same aggregation written as the operand image of evad_gemm64_h2 (see AH2_BLOCK above).  A_h2: evad_gemm64_h2_a_bytes
+// (n, K) bytes, K = (ks*ks + 1) * cin.  Values must satisfy |v| < 32768 (EVAD_STATUS_H16_RANGE otherwise).
+extern "C" size_t evad_gemm64_h2_a_bytes(int64_t m, int k) {
+    if (m <= 0 || k < 1) return 256;
+    return (size_t)((m + 127) / 128) * (size_t)((k + 63) / 64) * AH2_BLOCK;
+}
+
+extern "C" int evad_spline_aggregate_h2(const int32_t* rowptr, const int32_t* src, int64_t n, const int32_t* n_dev,
+                                        const float* x, int ldx, int cin, const evad_pseudo_t* pseudo_h,
+                                        const evad_spline_mode_t* mode_h, void* A_h2, uint32_t* status, void* stream) {
+    if (!rowptr || !src || !x || !pseudo_h || !mode_h || !A_h2 || !status || cin < 1) return EVAD_ERR_ARG;
+    if (mode_h->use_lut && (!mode_h->tab_k || !mode_h->tab_w)) return EVAD_ERR_ARG;
+    if (((uintptr_t)A_h2 & 1023) != 0) return EVAD_ERR_ARG;   // blocks are 1024-byte aligned swizzle atoms
+    if (n <= 0) return EVAD_OK;
+    const int ntap = mode_h->ks * mode_h->ks;
+    const int64_t kchunks = ((int64_t)(ntap + 1) * cin + 63) / 64;
+    if (!(ldx % 4 == 0 && ((uintptr_t)x & 15) == 0 && cin <= 160 &&
+          (size_t)AG2_WARPS_H2 * (AG2_EDGES * ldx + AH2_RING) * 4 <= 200 * 1024 && cin + 320 <= AH2_RING))
+        return EVAD_ERR_UNSUPPORTED;
+    const int cpl = (cin + 31) / 32;
+    cudaStream_t st = (cudaStream_t)stream;
+    float* A = reinterpret_cast<float*>(A_h2);
+    switch (cpl) {
+    case 1: return launch_agg2<1, true>(rowptr, src, n, n_dev, x, ldx, cin, *pseudo_h, *mode_h, A, kchunks, status, st);
+    case 2: return launch_agg2<2, true>(rowptr, src, n, n_dev, x, ldx, cin, *pseudo_h, *mode_h, A, kchunks, status, st);
+    case 3: return launch_agg2<3, true>(rowptr, src, n, n_dev, x, ldx, cin, *pseudo_h, *mode_h, A, kchunks, status, st);
+    case 4: return launch_agg2<4, true>(rowptr, src, n, n_dev, x, ldx, cin, *pseudo_h, *mode_h, A, kchunks, status, st);
+    default: return launch_agg2<5, true>(rowptr, src, n, n_dev, x, ldx, cin, *pseudo_h, *mode_h, A, kchunks, status, st);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ step 2

@@ -141,6 +141,17 @@ class MySplineConv(torch.nn.Module):
             c = self._cache["wcat_t"] = (key, ops.transpose_pad_weight(self.wcat()))
         return c[1]
 
+    def wcat_h2(self):
+        """wcat() as the weight image of evad_gemm64_h2 (fp16 pairs, tiled + swizzled per 64-row K chunk)."""
+        key = self._versions()
+        c = self._cache.get("wcat_h2")
+        if c is None or c[0] != key:
+            img = ops.pack_weight_h2(self.wcat()).to(self.weight.device)
+            buf = ops._aligned_bytes(img.numel() * 2, self.weight.device)
+            buf.view(torch.int16).copy_(img)
+            c = self._cache["wcat_h2"] = (key, buf)
+        return c[1]
+
     def fused_pack(self, ldx):
         """(Wt_hi, Wt_lo, cp) of evad_spline_conv64_fused for inputs with row stride ldx."""
         key = self._versions() + (int(ldx),)
@@ -236,6 +247,15 @@ class MySplineConv(torch.nn.Module):
                 lists = ops.spline_tap_lists(rowptr, src, n_cap, n_dev, src.shape[0], self.mode(), pseudo, status)
             out = ops.spline_conv64_fused(lists, x, n_cap, n_dev, self.fused_pack(x.stride(0)), epi)
             A = None
+        elif (ops.USE_GEMM_H2 and USE_TC5 and self.out_channels == 64 and n_cap >= TC5_MIN_ROWS and cin <= 160 and
+              x.stride(0) % 4 == 0 and x.data_ptr() % 16 == 0 and
+              4 * (16 * x.stride(0) + 512) * 4 <= 200 * 1024):
+            # large pooled layers: the aggregated operand is written as fp16 pairs in the UMMA operand image and the
+            # contraction is a bulk-copy -> tcgen05 pipeline (csrc/gemm_h2.cu); nothing re-formats it in between
+            A = None
+            Ah = ops.spline_aggregate_h2(rowptr, src, n_cap, n_dev, x, cin, self.mode(), pseudo, status)
+            out = ops.gemm64_h2(Ah, self.wcat_h2(), n_cap, n_dev, epi, k=(self.K + 1) * cin)
+            fused = True                                     # `out` is final
         else:
             A = ops.spline_aggregate(rowptr, src, n_cap, n_dev, x, cin, self.mode(), pseudo, status)
         tc = self.out_channels == 64 and A is not None and A.stride(0) % 4 == 0

@@ -463,6 +463,64 @@ def spline_aggregate(rowptr, src, n_cap, n_dev, x, cin, mode, pseudo, status):
     return A
 
 
+# EVAD_GEMM_H2=0: pooled layers back on the fp32 operand + cp.async tcgen05 kernel (evad_gemm64_tc5)
+USE_GEMM_H2 = os.environ.get("EVAD_GEMM_H2", "1") != "0"
+
+
+def _aligned_bytes(nbytes, device, align=1024):
+    """uint8 buffer whose data pointer is `align`-byte aligned (SWIZZLE_128B operand tiles are 1024-byte atoms)."""
+    buf = torch.empty(int(nbytes) + align, dtype=torch.uint8, device=device)
+    off = (-buf.data_ptr()) % align
+    return buf[off:off + int(nbytes)]
+
+
+def spline_aggregate_h2(rowptr, src, n_cap, n_dev, x, cin, mode, pseudo, status):
+    """spline_aggregate written as the operand image of gemm64_h2: fp16 pairs, tiled and swizzled per (128 rows, 64
+    columns) block (csrc/spline_general.cu: AH2_BLOCK).  Returns the byte buffer."""
+    L = _lib.lib()
+    k = (mode["ks"] ** 2 + 1) * cin
+    A = _aligned_bytes(L.evad_gemm64_h2_a_bytes(max(n_cap, 1), k), x.device)
+    m = _mode_struct(mode)
+    p = _pseudo_struct(**pseudo)
+    with _timed('spline_aggregate'):
+        check(L.evad_spline_aggregate_h2(ptr(rowptr), ptr(src), n_cap, ptr(n_dev), ptr(x), x.stride(0), cin, ctypes.byref(p),
+                                         ctypes.byref(m), ptr(A), ptr(status), stream()), "evad_spline_aggregate_h2")
+    return A
+
+
+def pack_weight_h2(W):
+    """W [K, 64] fp32 -> the weight image of gemm64_h2: per 64-row K chunk 16 KB = [w1 | w2] (W = w1 + w2 * 2^-11 in fp16),
+    each a 64 x 128-byte tile (row = output channel, K-major) with 16-byte units swizzled by (row & 7)."""
+    W = W.detach().float().cpu()
+    K = W.shape[0]
+    assert W.shape[1] == 64
+    kc = (K + 63) // 64
+    Wp = torch.zeros((kc * 64, 64), dtype=torch.float32)
+    Wp[:K] = W
+    w1 = Wp.half()
+    w2 = ((Wp - w1.float()) * 2048.0).half()
+    t = torch.stack([w.view(kc, 64, 64).permute(0, 2, 1) for w in (w1, w2)], dim=1).contiguous()   # [kc, part, n, kk]
+    n, kk = torch.arange(64)[:, None], torch.arange(64)[None, :]
+    dst = (((kk >> 3) ^ (n & 7)) << 3) + (kk & 7)                                                  # position inside row n
+    out = torch.empty_like(t)
+    out.scatter_(3, dst.expand(kc, 2, 64, 64).contiguous(), t)
+    return out.view(torch.int16).reshape(-1)
+
+
+def gemm64_h2(A_h2, W_h2, m_cap, m_dev, epi, k, out=None):
+    """out = epi(A @ W) for the operand images of spline_aggregate_h2 / pack_weight_h2 (cp.async.bulk -> tcgen05.mma
+    kind::f16 -> TMEM drain, warp-specialised; csrc/gemm_h2.cu)."""
+    L = _lib.lib()
+    if out is None:
+        out = torch.empty((max(m_cap, 1), 64), dtype=torch.float32, device=A_h2.device)
+    e = _epi_struct(**epi)
+    ws = _ws(L.evad_gemm64_h2_ws_bytes(m_cap, k), A_h2.device)
+    with _timed('gemm_epilogue'):
+        check(L.evad_gemm64_h2(ptr(A_h2), ptr(W_h2), m_cap, ptr(m_dev), k, ctypes.byref(e), ptr(out), out.stride(0), ptr(ws),
+                               ws.numel(), stream()), "evad_gemm64_h2")
+    return out
+
+
 def gemm_epilogue(A, W, m_cap, m_dev, epi, out=None, k=None):
     """out = epi(A[:, :k] @ W) ; W [k, n] row-major."""
     L = _lib.lib()

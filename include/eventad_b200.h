@@ -281,6 +281,23 @@ size_t evad_gemm64_tc5_ws_bytes(int64_t m, int k);
 int evad_gemm64_tc5(const float* A, int64_t lda, const float* Wt, int64_t ldw, int64_t m, const int32_t* m_dev, int k,
                     const evad_epilogue_t* epi_h, float* out, int ldo, void* ws, size_t ws_bytes, void* stream);
 
+/* Pooled-layer contraction on fp16 operand pairs fed by bulk copies (csrc/gemm_h2.cu; replaces the same reference lines
+ * as evad_gemm64_tc5: spline_conv.py:39-47,64-78 + conv.py:23-28,47-56).  evad_spline_aggregate_h2 = evad_spline_aggregate
+ * with A written as the operand image: per (128-row tile, 64-column K chunk) one 32 KB block [a1 | a2], v = a1 + a2 *
+ * 2^-11 in fp16, each a 128 x 128-byte tile in the SWIZZLE_128B K-major layout (16-byte unit u of row r stored at
+ * u ^ (r & 7)); |v| < 32768 or EVAD_STATUS_H16_RANGE.  W_h2: per K chunk 16 KB [w1 | w2], 64 rows (output channels) x
+ * 128 bytes, same swizzle (eventad_b200/ops.py: pack_weight_h2).  Both buffers 1024-byte aligned.  evad_gemm64_h2:
+ * out[m, 64] = epi(A @ W), one cp.async.bulk pair per stage -> tcgen05.mma kind::f16 -> TMEM drain, split-K over the SMs
+ * with the deterministic reduce of evad_gemm64_tc (ws: evad_gemm64_h2_ws_bytes). */
+size_t evad_gemm64_h2_a_bytes(int64_t m, int k);
+size_t evad_gemm64_h2_w_bytes(int k);
+size_t evad_gemm64_h2_ws_bytes(int64_t m, int k);
+int evad_spline_aggregate_h2(const int32_t* rowptr, const int32_t* src, int64_t n, const int32_t* n_dev, const float* x,
+                             int ldx, int cin, const evad_pseudo_t* pseudo_h, const evad_spline_mode_t* mode_h,
+                             void* A_h2, uint32_t* status, void* stream);
+int evad_gemm64_h2(const void* A_h2, const void* W_h2, int64_t m, const int32_t* m_dev, int k,
+                   const evad_epilogue_t* epi_h, float* out, int ldo, void* ws, size_t ws_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------------
  * SplineConv with Cout = 64 as one kernel (csrc/spline_tc5.cu): per-tap aggregation in registers feeding tcgen05.mma
  * (kind::tf32, 3xTF32, TMEM accumulator) -- evad_spline_aggregate + evad_gemm64_tc5 without the [n, 26*Cin] operand in HBM.

@@ -43,8 +43,9 @@ def test_sample_features(B):
         assert_close(got, ref, rtol=1e-5, atol=1e-6, what="sample_features")
 
 
-def _conv_case(cin, cout, mode, n=3000, seed=0):
-    """One MySplineConv on a real event graph; mode in {'lut', 'basis'}."""
+def _conv_case(cin, cout, mode, n=3000, seed=0, pad4=False):
+    """One MySplineConv on a real event graph; mode in {'lut', 'basis'}.  pad4: the GPU input rows are zero-padded to a
+    multiple of four floats, the row shape the fused forward hands to the pooled layers."""
     from types import SimpleNamespace
     from eventad_b200.data import Data
     from eventad_b200.model.layers.spline_conv import MySplineConv
@@ -64,7 +65,10 @@ def _conv_case(cin, cout, mode, n=3000, seed=0):
     conv = conv.cuda()
     if mode == "lut":
         conv.init_lut(height=240, width=320, **{k: lut[k] for k in ("rx", "Mx")})
-    data = Data(x=x.cuda(), edge_index=ei.cuda(), edge_attr=attr.cuda(), pos=d.pos.cuda())
+    xg = x.cuda()
+    if pad4 and cin % 4:
+        xg = torch.nn.functional.pad(xg, (0, 4 - cin % 4))
+    data = Data(x=xg, edge_index=ei.cuda(), edge_attr=attr.cuda(), pos=d.pos.cuda())
     out = conv(data).x
     assert_close(out, ref, what=f"MySplineConv {cin}->{cout} {mode}")
 
@@ -257,3 +261,23 @@ def test_spline_conv_to_dense():
     d2.pooling = pooling.cuda()
     dense2 = conv(d2)
     assert float(dense2[1].abs().max()) == 0.0 and float(dense2[0].abs().max()) > 0.0
+
+
+@pytest.mark.parametrize("cin,mode", [(82, "lut"), (64, "basis"), (130, "lut"), (18, "lut")])
+def test_spline_conv_large_rows_h2_gemm(cin, mode):
+    """>= 8 192 rows: the aggregated operand is written as fp16 pairs in the UMMA operand image (evad_spline_aggregate_h2)
+    and contracted by the bulk-copy / tcgen05 pipeline (evad_gemm64_h2); K = 26 * cin with and without a K tail, and
+    against the fp32-operand tcgen05 kernel (EVAD_GEMM_H2=0) on the same inputs."""
+    from eventad_b200 import ops
+    assert ops.USE_GEMM_H2
+    calls = []
+    real = ops.gemm64_h2
+    ops.gemm64_h2 = lambda *a, **k: (calls.append(1), real(*a, **k))[1]
+    try:
+        _conv_case(cin, 64, mode, n=20_000, seed=cin % 2, pad4=True)
+        assert calls == [1], "the h2 path did not run"
+        ops.USE_GEMM_H2 = False
+        _conv_case(cin, 64, mode, n=20_000, seed=cin % 2, pad4=True)
+        assert calls == [1]
+    finally:
+        ops.USE_GEMM_H2, ops.gemm64_h2 = True, real
