@@ -339,7 +339,48 @@ def leg_streaming(a, dev, iters=200):
         out["incremental_forward"] = leg_incremental(a, dev)
     except Exception as ex:                                       # report, do not hide
         out["incremental_forward"] = {"error": repr(ex)[:300]}
+    try:
+        out["ingest"] = leg_ingest(dev)
+    except Exception as ex:                                       # report, do not hide
+        out["ingest"] = {"error": repr(ex)[:300]}
     return out
+
+
+def leg_ingest(dev, iters=30):
+    """cutting one 50 ms / ~100k-event window out of a device-resident recording (EventStore.load_events =
+    _load_events of dsec_utils.py:80-120) and the down-sampling filter (downsample_events.py:91-122) on 1M events."""
+    from eventad_b200 import ingest
+    rng = np.random.default_rng(5)
+    n, span = 4_000_000, 2_000_000
+    t = np.sort(rng.integers(0, span, n)).astype(np.int64)
+    x, y, p = rng.integers(0, 640, n), rng.integers(0, 480, n), rng.integers(0, 2, n)
+    store = ingest.EventStore(x=x, y=y, p=p, t=t, t_offset=0, device=dev)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    ts, cnt = [], 0
+    for i in range(iters + 3):
+        e0, e1 = ev(), ev()
+        e0.record()
+        (xy, tt, pp), tq = store.load_events(100_000 + 50_000 * (i % 30), num_us=50_000, height=430, time_window=50_000)
+        e1.record()
+        torch.cuda.synchronize()
+        cnt = xy.shape[0]
+        if i >= 3:
+            ts.append(e0.elapsed_time(e1))
+    evs = dict(x=store.x[:1_000_000], y=store.y[:1_000_000], t=store.t[:1_000_000], p=2 * store.p[:1_000_000] - 1)
+    td = []
+    for i in range(8):
+        e0, e1 = ev(), ev()
+        e0.record()
+        out, cm = ingest.downsample_events(evs, 480, 640, 240, 320)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 2:
+            td.append(e0.elapsed_time(e1))
+    return {"resident_events": n, "window_events": cnt, "load_events_p50_ms": float(np.median(ts)),
+            "downsample_1M_events_p50_ms": float(np.median(td)), "downsample_survivors": int(out["t"].shape[0]),
+            "what": "EventStore.load_events (ms_to_idx lookup on the host, flag + scan + scatter on the device, survivor "
+                    "count read back) and downsample_events (stable sort by coarse cell + per-cell walk + compaction) on "
+                    "device-resident arrays; CUDA events around the calls"}
 
 
 def leg_incremental(a, dev, n0=1_000_000, iters=25):

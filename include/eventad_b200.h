@@ -390,6 +390,26 @@ int evad_sample_concat_h2(const float* x, int ldx, int cx, const float* pos, int
                           int feat_c, float width, float height, int append_pos, uint32_t* out, int ldo,
                           uint32_t* status, void* stream);
 
+/* ---- Event ingest on the device (csrc/ingest.cu) ----
+ * A recording's arrays (int32 x, y, t in microseconds relative to t_offset and ascending; int8 p) stay in HBM.
+ * evad_ingest_ms_to_idx: create_ms_to_idx (/root/reference/scripts/downsample_events.py:36-42): ms_to_idx[m] = number of
+ *   events with t / 1000 < m, m < n_ms (= t[n-1] / 1000 + 1).
+ * evad_ingest_slice: the array half of _load_events (/root/reference/src/dagr/data/dsec_utils.py:80-120) for events
+ *   [idx0, idx0 + cnt): xy int16 [.,2], t = time_window - tq + t_ev (int32 [.,1]), p = 2 p - 1 (int8 [.,1]), kept where
+ *   t > 0 and y < height (height < 0: no crop), order preserved; *n_out = survivors (device).
+ * evad_ingest_downsample: downsample_events + _filter_events_resize (downsample_events.py:91-122): the per-cell
+ *   integrate-and-fire filter (float32 cells, float64 expression) over a stable sort by coarse cell; change_map
+ *   [out_h, out_w] is read and updated; survivors in original order with x / fx, y / fy. */
+int evad_ingest_ms_to_idx(const int32_t* t_us, int64_t n, int64_t n_ms, int64_t* ms_to_idx, void* stream);
+size_t evad_ingest_slice_ws_bytes(int64_t cnt);
+int evad_ingest_slice(const int32_t* x, const int32_t* y, const int32_t* t, const int8_t* p, int64_t idx0, int64_t cnt,
+                      int64_t tq, int64_t time_window, int height, int16_t* xy_out, int32_t* t_out, int8_t* p_out,
+                      int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
+size_t evad_ingest_downsample_ws_bytes(int64_t n);
+int evad_ingest_downsample(const int32_t* x, const int32_t* y, const int32_t* t, const int8_t* p, int64_t n, int fx, int fy,
+                           int out_w, int out_h, float* change_map, int32_t* x_out, int32_t* y_out, int32_t* t_out,
+                           int8_t* p_out, int32_t* n_out, uint32_t* status, void* ws, size_t ws_bytes, void* stream);
+
 /* ---- EventAD head input: per-bounding-box pooling of the out4 graph (csrc/bbox_pool.cu) ----
  * Replaces the python loops of /root/reference/models/EventAD.py:382-397 and _process_bbox (:406-498): for every box
  * [x, y, w, h, class, track_id] (pixels) of `bbox` (sample ids bbox_batch int64) the feature of the nodes of its sample
