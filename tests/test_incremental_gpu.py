@@ -94,3 +94,44 @@ def test_incremental_from_a_single_event():
             got = inc.update(_part(d, done, done + m))
             done += m
             _same(got, dense_net(_part(d, 0, done), image_feat=feats)[0], f"+{m}", exact=False)
+
+
+@pytest.mark.parametrize("name", ["u", "c"])
+def test_incremental_update_matches_reference_asynchronous_model(name):
+    """tests/golden/ref_async_*.npz hold what the REFERENCE'S OWN asynchronous model (`make_model_asynchronous`, executed
+    unmodified on the CPU; generator tests/golden/make_ref_async_golden.py) returns after reset(n0 events) + one update of
+    m events.  IncrementalBackbone must give the same voxels (by position) and features within the reference checker's
+    1e-3 (evaluate_flops.py:141-143).  The window's last event (t == 1.0) is never streamed: the reference's two modes
+    disagree on its voxel (see the generator)."""
+    import importlib.util
+    import os
+    import numpy as np
+    from eventad_b200.asynchronous.incremental import IncrementalBackbone
+    here = os.path.dirname(os.path.abspath(__file__))
+    spec = importlib.util.spec_from_file_location("make_ref_async_golden", os.path.join(here, "golden", "make_ref_async_golden.py"))
+    gold = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gold)
+    case = [c for c in gold.CASES if c[0] == name][0]
+    _, mseed, dseed, dist, n0, steps = case
+    model, args, d, feats = gold.case_inputs(case)
+    z = np.load(os.path.join(here, "golden", f"ref_async_{name}.npz"))
+    model.cache_luts(gold.W, gold.H, args.radius)
+    net = model.cuda().backbone
+    for k in ("x", "pos", "batch"):
+        setattr(d, k, getattr(d, k).cuda())
+    feats = [f.cuda() for f in feats]
+    scale = torch.tensor([gold.W, gold.H])
+    with torch.no_grad():
+        for s, m in enumerate(steps):
+            inc = IncrementalBackbone(net, capacity=n0 + max(steps), feats=feats, width=gold.W, height=gold.H)
+            inc.reset(_part(d, 0, n0))
+            outs = inc.update(_part(d, n0, n0 + m))
+            for lvl, o in zip((3, 4), outs):
+                rp, rx = torch.from_numpy(z[f"s{s}_out{lvl}_pos"]), torch.from_numpy(z[f"s{s}_out{lvl}_x"])
+                ours = {tuple(r): i for i, r in enumerate((o.pos[:, :2].cpu() * scale).round().int().tolist())}
+                keys = [tuple(r) for r in (rp[:, :2] * scale).round().int().tolist()]
+                assert len(set(keys)) == len(keys) and all(k in ours for k in keys), (name, s, lvl)
+                assert len(ours) == len(keys), (name, s, lvl, len(ours), len(keys))
+                sel = torch.tensor([ours[k] for k in keys])
+                err = float((o.x.cpu()[sel] - rx).abs().max())
+                assert err < 1e-3, (name, s, lvl, err)
