@@ -110,6 +110,14 @@ def _declare(L):
     _sig(L, "evad_spline_conv64_fused", c_i, [c_p, c_p, c_p, c_i, c_i64, c_p, c_i, c_i, c_p, c_p, c_i64, P(EpilogueT),
                                               c_p, c_i, c_p, c_sz, c_p])
     _sig(L, "evad_split_tf32", c_i, [c_p, c_i64, c_p, c_p, c_p])
+    _sig(L, "evad_pool_inc_state_bytes", c_sz, [P(PoolParamsT), c_i])
+    _sig(L, "evad_pool_inc_reset", c_i, [c_p, P(PoolParamsT), c_i, c_p])
+    _sig(L, "evad_pool_inc_update_ws_bytes", c_sz, [c_i64])
+    _sig(L, "evad_pool_inc_update", c_i, [c_p, P(PoolParamsT), c_i64, c_i64, c_p, c_i, c_p, c_p, c_i, c_i, c_p, c_p, c_p, c_p,
+                                          c_p, c_sz, c_p])
+    _sig(L, "evad_pool_inc_emit_ws_bytes", c_sz, [P(PoolParamsT), c_i64])
+    _sig(L, "evad_pool_inc_emit", c_i, [c_p, P(PoolParamsT), c_i, c_i64, c_i64, c_p, c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p,
+                                        c_p, c_sz, c_p])
     _sig(L, "evad_ingest_ms_to_idx", c_i, [c_p, c_i64, c_i64, c_p, c_p])
     _sig(L, "evad_ingest_slice_ws_bytes", c_sz, [c_i64])
     _sig(L, "evad_ingest_slice", c_i, [c_p, c_p, c_p, c_p, c_i64, c_i64, c_i64, c_i64, c_i, c_p, c_p, c_p, c_p, c_p, c_sz, c_p])

@@ -13,15 +13,18 @@ hence not its layer-1 output.  The incremental update is therefore exact, not a 
   rows      evad_stream_rows     ... written into the resident fixed-stride rows nbr / count / nbr_cls at the new ids
   x0        evad_sample_concat_h2 on the new events only
   layer 1   evad_spline_conv_l1_h16 over perm = the new node ids (two launches: conv + skip, conv + residual)
-  pool1 ..  the dense tail (Net._enqueue_tail: evad_voxel_pool over all resident nodes, then 2 240 voxels per window
-  layer5    through layers 2-5), captured once in a CUDA graph over the full-capacity buffers (the resident count is a
-            device cell): its cost is independent of the micro-batch and small next to graph + layer 1, which are
-            60 % of a dense forward and are what grows with the resident events.
+  pool 1    evad_pool_inc_update folds the new nodes and their in-edges into per-voxel state (running maxima of
+            [layer-1 output | sampled CNN map], serial position sums, counts, one bitmap row of coarse in-edges per
+            voxel); evad_pool_inc_emit writes the pooled graph of everything seen so far, bit-identical to
+            evad_voxel_pool over all resident nodes (max is order independent; appended nodes have the highest ids, so
+            the position sums are continued in the dense kernel's order)
+  layer2 .. the dense tail (Net._enqueue_tail) on the 2 240 voxels per window, captured once in a CUDA graph together
+  layer5    with the emit step: its cost is independent of the micro-batch and of the number of resident events.
 
 Results equal the dense fused forward on the accumulated events BIT FOR BIT (same kernels, same rows, same per-node
-arithmetic; tests/test_incremental_gpu.py), which is stronger than the reference checker's 1e-3.  Not built: an
-incremental voxel pooling with cached arg-max (the tail recomputes pool 1 from the resident layer-1 rows), node deletion
-inside a window (SlidingWindowGraph.delete_nodes): `update` is append-only until the next `reset`.
+arithmetic; tests/test_incremental_gpu.py), which is stronger than the reference checker's 1e-3.  Not built: node deletion
+inside a window (SlidingWindowGraph.delete_nodes; it would need the arg-max bookkeeping of max_pool.py): `update` is
+append-only until the next `reset`.  EVAD_INCR_POOL=0 keeps pool 1 in the dense tail (evad_voxel_pool over all nodes).
 """
 import ctypes
 import os
@@ -34,6 +37,7 @@ from ..model.layers.conv import _fold
 
 
 USE_TAIL_GRAPH = os.environ.get("EVAD_INCR_GRAPH", "1") != "0"   # 0: the dense tail as plain launches (debugging)
+USE_INC_POOL = os.environ.get("EVAD_INCR_POOL", "1") != "0"      # 0: pool 1 recomputed over all resident nodes by the tail
 
 
 class IncrementalBackbone:
@@ -65,6 +69,12 @@ class IncrementalBackbone:
         self._n_dev = torch.zeros(1, dtype=torch.int32, device=dev)
         self._scratch = _lib.Scratch()
         self._tail_graph, self._tail_res = None, None
+        self._pool = None
+        if USE_INC_POOL:
+            p = net.pool1
+            P = ops.pool_params(p._vs, p._nv, self.meta[3], p._inv_wh, p.aggr, self.meta[0], self.meta[1], self.feats[1],
+                                append_pos=True, ell_stride=16)
+            self._pool = ops.PoolIncState(P, 16, c, dev)
 
     # ------------------------------------------------------------------------------------------------ pieces
     def _graph_creator(self):
@@ -120,7 +130,8 @@ class IncrementalBackbone:
         try:
             status = self._scratch.status(self.pos.device)
             status.zero_()
-            return self.net._enqueue_tail(cur, self.feats, b, w, h, status)
+            return self.net._enqueue_tail(cur, self.feats, b, w, h, status,
+                                          pool1=self._pool.emit if self._pool is not None else None)
         finally:
             ops._SCRATCH = saved
 
@@ -187,6 +198,9 @@ class IncrementalBackbone:
         self.cls[:n] = graph["nbr_cls"].view(n, 16)
         gc.max_index, gc.all_timestamps, gc._history = n, pi[:, 2], [(bi.clone(), pi, 0)]
         self._layer1(graph["cell_perm"], n)
+        if self._pool is not None:
+            self._pool.reset()
+            self._pool.update(0, n, self.pos, self.batch, self.xk, self.count, self.nbr, gc._status)
         return self._tail()
 
     @torch.no_grad()
@@ -205,4 +219,6 @@ class IncrementalBackbone:
                                                _lib.ptr(gc._status), _lib.stream()), "evad_stream_rows")
         perm = torch.arange(n0, n0 + n, dtype=torch.int32, device=self.dev)
         self._layer1(perm, n)
+        if self._pool is not None:
+            self._pool.update(n0, n, self.pos, self.batch, self.xk, self.count, self.nbr, gc._status)
         return self._tail()

@@ -796,3 +796,337 @@ extern "C" int evad_voxel_pool(const evad_pool_params_t* p, int64_t n_cap, const
     }
     return EVAD_OK;
 }
+
+// ================================================================================================================
+// Incremental voxel pooling (reference: src/dagr/asynchronous/max_pool.py:123-243 keeps, per voxel, the
+// maximum with its arg-max and the homogeneous position sums, and updates the voxels that receive nodes).
+//
+// State per voxel KEY (dense key space, key_bound entries; caller-owned memory): running maximum of
+// [x | sampled CNN map] (max is order independent: exact), serial position sums and member count (appended nodes have
+// the highest ids, so "old sum + new members in ascending id" IS the dense kernel's ascending-node order: bit-identical),
+// and one bitmap row of coarse in-edges (key of the source voxel).  evad_pool_inc_update folds appended nodes and their
+// in-edges into the state; evad_pool_inc_emit writes the pooled graph exactly as evad_voxel_pool would for all nodes
+// seen so far (dense ids = rank of the key among the occupied keys, sources ascending).  Max aggregation, no coarse
+// self loops, fixed-stride fine rows.
+struct PincState {
+    float* vmax;      // [kb][ctot]
+    float* vsum;      // [kb][3]
+    int32_t* vcnt;    // [kb]
+    int32_t* vbatch;  // [kb]
+    uint32_t* adj;    // [kb][kw]
+    int kw;
+};
+
+static size_t pinc_layout(void* state, long long kb, int ctot, PincState* s) {
+    EvadArena a(state, (size_t)1 << 62);
+    s->kw = (int)((kb + 31) / 32);
+    s->vmax = a.take<float>((size_t)kb * ctot);
+    s->vsum = a.take<float>((size_t)kb * 3);
+    s->vcnt = a.take<int32_t>((size_t)kb);
+    s->vbatch = a.take<int32_t>((size_t)kb);
+    s->adj = a.take<uint32_t>((size_t)kb * s->kw);
+    return a.off;
+}
+
+__global__ void __launch_bounds__(256) pinc_reset_kernel(float* __restrict__ vmax, int64_t n_max, uint32_t* __restrict__ rest,
+                                                         int64_t n_rest) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_max) vmax[i] = -INFINITY;
+    if (i < n_rest) rest[i] = 0u;
+}
+
+__global__ void __launch_bounds__(256) pinc_keys_kernel(const float* __restrict__ pos, int ld_pos,
+                                                        const int32_t* __restrict__ batch, int64_t n0, int64_t n_new,
+                                                        PoolGeom G, uint32_t* __restrict__ nodekey, uint32_t* __restrict__ keys,
+                                                        uint32_t* __restrict__ status) {
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_new) return;
+    const uint32_t k = pool_voxel_key(pos, ld_pos, batch, n0 + p, G, status);
+    nodekey[n0 + p] = k;
+    keys[p] = k;
+}
+
+// one thread per run of equal keys in the (stably) sorted new nodes: serial position sums in ascending node order
+__global__ void __launch_bounds__(128) pinc_pos_kernel(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ sidx,
+                                                       int64_t n0, int64_t n_new, const float* __restrict__ pos, int ld_pos,
+                                                       const int32_t* __restrict__ batch, PincState S) {
+    const int64_t q0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q0 >= n_new) return;
+    const uint32_t key = skey[q0];
+    if (q0 > 0 && skey[q0 - 1] == key) return;
+    float sx = S.vsum[3 * (int64_t)key], sy = S.vsum[3 * (int64_t)key + 1], st = S.vsum[3 * (int64_t)key + 2];
+    int cnt = S.vcnt[key], last = 0;
+    for (int64_t q = q0; q < n_new && skey[q] == key; q++) {
+        const int64_t i = n0 + sidx[q];
+        sx = __fadd_rn(sx, pos[i * ld_pos]);
+        sy = __fadd_rn(sy, pos[i * ld_pos + 1]);
+        st = __fadd_rn(st, pos[i * ld_pos + 2]);
+        cnt++;
+        last = batch[i];
+    }
+    S.vsum[3 * (int64_t)key] = sx; S.vsum[3 * (int64_t)key + 1] = sy; S.vsum[3 * (int64_t)key + 2] = st;
+    S.vcnt[key] = cnt;
+    S.vbatch[key] = last;
+}
+
+__device__ __forceinline__ void pinc_atomic_max(float* addr, float v) {
+    if (v >= 0.f) atomicMax(reinterpret_cast<int*>(addr), __float_as_int(v));
+    else atomicMin(reinterpret_cast<unsigned int*>(addr), __float_as_uint(v));
+}
+
+// one thread per (new node, channel quad): the node's [x | sampled map] quad folded into its voxel's running maximum
+__global__ void __launch_bounds__(256) pinc_feat_kernel(const uint32_t* __restrict__ nodekey, int64_t n0, int64_t n_new,
+                                                        const float* __restrict__ pos, int ld_pos,
+                                                        const int32_t* __restrict__ batch, const float* __restrict__ x,
+                                                        int ldx, int cx, PoolSample Sm, PincState S, int ctot) {
+    const int qx = cx >> 2, qf = Sm.feat ? (Sm.C >> 2) : 0, qt = qx + qf;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t p = t / qt;
+    const int q = (int)(t - p * qt);
+    if (p >= n_new) return;
+    const int64_t i = n0 + p;
+    float4 v;
+    if (q < qx) {
+        v = __ldg(reinterpret_cast<const float4*>(x + i * ldx) + q);
+    } else {
+        int tap[8];
+        float wgt[8];
+        sample_taps(Sm, pos[i * ld_pos], pos[i * ld_pos + 1], (float)batch[i], tap, wgt);
+        v = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4* f4 = reinterpret_cast<const float4*>(Sm.feat);
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            if (tap[k] < 0 || wgt[k] == 0.f) continue;
+            const float4 f = __ldg(f4 + (int64_t)tap[k] * qf + (q - qx));
+            v.x = fmaf(f.x, wgt[k], v.x); v.y = fmaf(f.y, wgt[k], v.y);
+            v.z = fmaf(f.z, wgt[k], v.z); v.w = fmaf(f.w, wgt[k], v.w);
+        }
+    }
+    float* dst = S.vmax + (int64_t)nodekey[i] * ctot + 4 * q;
+    pinc_atomic_max(dst, v.x); pinc_atomic_max(dst + 1, v.y); pinc_atomic_max(dst + 2, v.z); pinc_atomic_max(dst + 3, v.w);
+}
+
+// one thread per slot of a new node's fixed-stride row: coarse in-edge (voxel of the source -> voxel of the node)
+__global__ void __launch_bounds__(256) pinc_adj_kernel(const uint32_t* __restrict__ nodekey, int64_t n0, int64_t n_new,
+                                                       const int32_t* __restrict__ count, const int32_t* __restrict__ nbr,
+                                                       int K, PincState S) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t p = t / K;
+    const int s = (int)(t - p * K);
+    if (p >= n_new) return;
+    const int64_t i = n0 + p;
+    if (s >= count[i]) return;
+    const uint32_t kd = nodekey[i], ks = nodekey[nbr[i * K + s]];
+    if (ks != kd) atomicOr(S.adj + (int64_t)kd * S.kw + (ks >> 5), 1u << (ks & 31));
+}
+
+// ---- emit: the pooled graph of everything folded in so far
+__global__ void __launch_bounds__(256) pinc_flag_kernel(const int32_t* __restrict__ vcnt, int64_t kb, uint32_t* __restrict__ flag) {
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < kb) flag[k] = vcnt[k] > 0 ? 1u : 0u;
+}
+
+// one warp per occupied key: node row [max | pos_x pos_y | 0], position (mean + round_to_pixel), batch, in-degree
+__global__ void __launch_bounds__(256) pinc_emit_nodes_kernel(PincState S, int64_t kb, int ctot, const uint32_t* __restrict__ flag,
+                                                              const uint32_t* __restrict__ rank, int64_t c_cap, float inv_w,
+                                                              float inv_h, int append_pos, float* __restrict__ x_out, int ldo,
+                                                              float* __restrict__ pos_out, int32_t* __restrict__ batch_out,
+                                                              uint32_t* __restrict__ deg, uint32_t* __restrict__ status) {
+    const int lane = threadIdx.x & 31;
+    const int64_t key = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (key >= kb || !flag[key]) return;
+    const int64_t c = rank[key];
+    if (c >= c_cap) {
+        if (lane == 0) atomicOr(status, EVAD_STATUS_CLUSTER_OOB);
+        return;
+    }
+    const float cntf = fmaxf((float)S.vcnt[key], 1.f);
+    float mx = __fdiv_rn(S.vsum[3 * key], cntf), my = __fdiv_rn(S.vsum[3 * key + 1], cntf);
+    const float mt = __fdiv_rn(S.vsum[3 * key + 2], cntf);
+    mx = __fmul_rn(div_floor_f(__fadd_rn(mx, 1e-5f), inv_w), inv_w);
+    my = __fmul_rn(div_floor_f(__fadd_rn(my, 1e-5f), inv_h), inv_h);
+    if (lane == 0) {
+        pos_out[c * 3] = mx; pos_out[c * 3 + 1] = my; pos_out[c * 3 + 2] = mt;
+        batch_out[c] = S.vbatch[key];
+    }
+    float* o = x_out + c * ldo;
+    const float* v = S.vmax + key * ctot;
+    for (int ch = lane; ch < ldo; ch += 32) {
+        float val = 0.f;
+        if (ch < ctot) val = v[ch];
+        else if (append_pos && ch < ctot + 2) val = ch == ctot ? mx : my;
+        o[ch] = val;
+    }
+    uint32_t d = 0;
+    const uint32_t* row = S.adj + key * S.kw;
+    for (int w = lane; w < S.kw; w += 32) d += __popc(row[w]);
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) d += __shfl_xor_sync(0xffffffffu, d, s);
+    if (lane == 0) deg[c] = d;
+}
+
+// one warp per occupied key: the set bits of its row, ascending, as dense source ids
+__global__ void __launch_bounds__(256) pinc_emit_edges_kernel(PincState S, int64_t kb, const uint32_t* __restrict__ flag,
+                                                              const uint32_t* __restrict__ rank, int64_t c_cap,
+                                                              const uint32_t* __restrict__ rowptr_u, int64_t e_cap,
+                                                              int32_t* __restrict__ rowptr_out, int32_t* __restrict__ src_out,
+                                                              int32_t* __restrict__ num_edges_out, const int32_t* __restrict__ n_out,
+                                                              uint32_t* __restrict__ status) {
+    const int lane = threadIdx.x & 31;
+    const int64_t key = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (key == 0 && lane == 0) {
+        const int n = min((int64_t)*n_out, c_cap);
+        const uint32_t tot = rowptr_u[n];
+        if ((int64_t)tot > e_cap) atomicOr(status, EVAD_STATUS_EDGE_OVERFLOW);
+        *num_edges_out = (int32_t)min((int64_t)tot, e_cap);
+        rowptr_out[n] = (int32_t)tot;
+    }
+    if (key >= kb || !flag[key]) return;
+    const int64_t c = rank[key];
+    if (c >= c_cap) return;
+    uint32_t base = rowptr_u[c];
+    if (lane == 0) rowptr_out[c] = (int32_t)base;
+    const uint32_t* row = S.adj + key * S.kw;
+    for (int w0 = 0; w0 < S.kw; w0 += 32) {
+        const int w = w0 + lane;
+        uint32_t bits = w < S.kw ? row[w] : 0u;
+        const uint32_t cntw = __popc(bits);
+        uint32_t inc = cntw;                                  // inclusive prefix over the lanes
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, s);
+            if (lane >= s) inc += t;
+        }
+        uint32_t o = base + inc - cntw;
+        while (bits) {
+            const int b = __ffs(bits) - 1;
+            bits &= bits - 1;
+            if ((int64_t)o < e_cap) src_out[o] = (int32_t)rank[(int64_t)w * 32 + b];
+            o++;
+        }
+        base += __shfl_sync(0xffffffffu, inc, 31);
+    }
+}
+
+static int pinc_check(const evad_pool_params_t* p, int cx, long long* kb, int* ctot) {
+    if (!p || cx < 0 || cx % 4 != 0 || p->batch_size < 1) return EVAD_ERR_ARG;
+    if (p->aggr_mean || p->self_loop || p->ell_stride < 1) return EVAD_ERR_UNSUPPORTED;   // max pooling over fixed-stride rows
+    if (p->feat && (p->feat_c % 4 != 0 || ((uintptr_t)p->feat & 15) != 0)) return EVAD_ERR_UNSUPPORTED;
+    *kb = (long long)p->nvx * p->nvy * p->nvt * ((long long)p->batch_size + 1);
+    if (*kb >= (1ll << 24)) return EVAD_ERR_UNSUPPORTED;      // the coarse adjacency is a dense bitmap: kb^2 / 8 bytes
+    *ctot = cx + (p->feat ? p->feat_c : 0);
+    return EVAD_OK;
+}
+
+extern "C" size_t evad_pool_inc_state_bytes(const evad_pool_params_t* p, int cx) {
+    long long kb;
+    int ctot;
+    if (pinc_check(p, cx, &kb, &ctot) != EVAD_OK) return 0;
+    PincState s;
+    return pinc_layout(nullptr, kb, ctot, &s) + 256;
+}
+
+extern "C" int evad_pool_inc_reset(void* state, const evad_pool_params_t* p, int cx, void* stream) {
+    long long kb;
+    int ctot;
+    EVAD_TRY(pinc_check(p, cx, &kb, &ctot));
+    if (!state || ((uintptr_t)state & 255) != 0) return EVAD_ERR_ARG;
+    PincState s;
+    const size_t total = pinc_layout(state, kb, ctot, &s);
+    const int64_t n_max = kb * ctot;
+    uint32_t* rest = reinterpret_cast<uint32_t*>(s.vsum);
+    const int64_t n_rest = (int64_t)((reinterpret_cast<char*>(state) + total) - reinterpret_cast<char*>(rest)) / 4;
+    const int64_t n = n_max > n_rest ? n_max : n_rest;
+    pinc_reset_kernel<<<evad_cdiv(n, 256), 256, 0, (cudaStream_t)stream>>>(s.vmax, n_max, rest, n_rest);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
+extern "C" size_t evad_pool_inc_update_ws_bytes(int64_t n_new) {
+    const size_t n = (size_t)(n_new > 0 ? n_new : 1);
+    return evad_align(n * 4) * 4 + evad_align(evad_sort_tmp_elems(n_new) * 4) + 256;
+}
+
+// folds the nodes n0 .. n0 + n_new - 1 (positions, batch, features x [., ldx] with cx channels, fixed-stride rows
+// count / nbr of K = p->ell_stride) into the state; node_key [>= n0 + n_new] is the caller's per-node key array
+extern "C" int evad_pool_inc_update(void* state, const evad_pool_params_t* p, int64_t n0, int64_t n_new, const float* pos,
+                                    int ld_pos, const int32_t* batch, const float* x, int ldx, int cx, const int32_t* count,
+                                    const int32_t* nbr, uint32_t* node_key, uint32_t* status, void* ws, size_t ws_bytes,
+                                    void* stream) {
+    long long kb;
+    int ctot;
+    EVAD_TRY(pinc_check(p, cx, &kb, &ctot));
+    if (!state || !pos || !batch || !x || !count || !nbr || !node_key || !status || !ws || n0 < 0 || n_new < 0 || ld_pos < 3 ||
+        ldx % 4 != 0 || ((uintptr_t)x & 15) != 0)
+        return EVAD_ERR_ARG;
+    if (ws_bytes < evad_pool_inc_update_ws_bytes(n_new)) return EVAD_ERR_WORKSPACE;
+    if (n_new == 0) return EVAD_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    PincState s;
+    pinc_layout(state, kb, ctot, &s);
+    EvadArena a(ws, ws_bytes);
+    uint32_t* k0 = a.take<uint32_t>(n_new);
+    uint32_t* v0 = a.take<uint32_t>(n_new);
+    uint32_t* k1 = a.take<uint32_t>(n_new);
+    uint32_t* v1 = a.take<uint32_t>(n_new);
+    uint32_t* sort_tmp = a.take<uint32_t>(evad_sort_tmp_elems(n_new));
+    if (!a.ok) return EVAD_ERR_WORKSPACE;
+    PoolGeom G{p->size_x, p->size_y, p->size_t, p->nvx, p->nvy, p->nvt, (uint32_t)kb};
+    PoolSample S{p->feat, p->feat_b, p->feat_h, p->feat_w, p->feat_c, p->width, p->height};
+    pinc_keys_kernel<<<evad_cdiv(n_new, 256), 256, 0, st>>>(pos, ld_pos, batch, n0, n_new, G, node_key, k0, status);
+    EVAD_CHECK_LAUNCH();
+    int key_bits = 1;
+    while ((1ll << key_bits) < kb) key_bits++;
+    uint32_t *skey, *sidx;
+    EVAD_TRY(evad_sort_pairs_u32(k0, v0, k1, v1, 1, n_new, key_bits, sort_tmp, &skey, &sidx, st));
+    pinc_pos_kernel<<<evad_cdiv(n_new, 128), 128, 0, st>>>(skey, sidx, n0, n_new, pos, ld_pos, batch, s);
+    EVAD_CHECK_LAUNCH();
+    const int qt = ctot / 4;
+    pinc_feat_kernel<<<evad_cdiv(n_new * qt, 256), 256, 0, st>>>(node_key, n0, n_new, pos, ld_pos, batch, x, ldx, cx, S, s, ctot);
+    EVAD_CHECK_LAUNCH();
+    pinc_adj_kernel<<<evad_cdiv(n_new * p->ell_stride, 256), 256, 0, st>>>(node_key, n0, n_new, count, nbr, p->ell_stride, s);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}
+
+extern "C" size_t evad_pool_inc_emit_ws_bytes(const evad_pool_params_t* p, int64_t c_cap) {
+    long long kb = (long long)p->nvx * p->nvy * p->nvt * ((long long)p->batch_size + 1);
+    return evad_align((size_t)kb * 4) * 2 + evad_align((size_t)(c_cap + 2) * 4) * 2 +
+           evad_align(evad_scan_tmp_elems(kb > c_cap + 1 ? kb : c_cap + 1) * 4) + 256;
+}
+
+// writes the pooled graph of all folded nodes in the layout of evad_voxel_pool (same argument meaning)
+extern "C" int evad_pool_inc_emit(void* state, const evad_pool_params_t* p, int cx, int64_t c_cap, int64_t e_cap,
+                                  int32_t* n_out, float* x_out, int ldo, float* pos_out, int32_t* batch_out,
+                                  int32_t* rowptr_out, int32_t* src_out, int32_t* num_edges_out, uint32_t* status, void* ws,
+                                  size_t ws_bytes, void* stream) {
+    long long kb;
+    int ctot;
+    EVAD_TRY(pinc_check(p, cx, &kb, &ctot));
+    if (!state || !n_out || !x_out || !pos_out || !batch_out || !rowptr_out || !src_out || !num_edges_out || !status || !ws ||
+        c_cap < 1 || e_cap < 1 || ldo < ctot + (p->append_pos ? 2 : 0))
+        return EVAD_ERR_ARG;
+    if (ws_bytes < evad_pool_inc_emit_ws_bytes(p, c_cap)) return EVAD_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    PincState s;
+    pinc_layout(state, kb, ctot, &s);
+    EvadArena a(ws, ws_bytes);
+    uint32_t* flag = a.take<uint32_t>(kb);
+    uint32_t* rank = a.take<uint32_t>(kb);
+    uint32_t* deg = a.take<uint32_t>(c_cap + 2);
+    uint32_t* rowptr_u = a.take<uint32_t>(c_cap + 2);
+    uint32_t* scan_tmp = a.take<uint32_t>(evad_scan_tmp_elems(kb > c_cap + 1 ? kb : c_cap + 1));
+    if (!a.ok) return EVAD_ERR_WORKSPACE;
+    pinc_flag_kernel<<<evad_cdiv(kb, 256), 256, 0, st>>>(s.vcnt, kb, flag);
+    EVAD_CHECK_LAUNCH();
+    EVAD_TRY(evad_exclusive_scan_u32(flag, rank, kb, reinterpret_cast<uint32_t*>(n_out), scan_tmp, st));
+    if (cudaMemsetAsync(deg, 0, (size_t)(c_cap + 2) * 4, st) != cudaSuccess) return EVAD_ERR_LAUNCH;
+    pinc_emit_nodes_kernel<<<evad_cdiv(kb * 32, 256), 256, 0, st>>>(s, kb, ctot, flag, rank, c_cap, p->inv_w, p->inv_h,
+                                                                    p->append_pos, x_out, ldo, pos_out, batch_out, deg, status);
+    EVAD_CHECK_LAUNCH();
+    EVAD_TRY(evad_exclusive_scan_u32(deg, rowptr_u, c_cap + 1, nullptr, scan_tmp, st));
+    pinc_emit_edges_kernel<<<evad_cdiv(kb * 32, 256), 256, 0, st>>>(s, kb, flag, rank, c_cap, rowptr_u, e_cap, rowptr_out,
+                                                                    src_out, num_edges_out, n_out, status);
+    EVAD_CHECK_LAUNCH();
+    return EVAD_OK;
+}

@@ -268,9 +268,11 @@ class Net(torch.nn.Module):
         cur = dict(x=xk, pos=pos, batch=batch_i32, rowptr=rowptr, src=src, n_cap=n, n_dev=None, e_cap=src.shape[0], ell=ell)
         return self._enqueue_tail(cur, f, num_graphs, width, height, status)
 
-    def _enqueue_tail(self, cur, f, num_graphs, width, height, status):
+    def _enqueue_tail(self, cur, f, num_graphs, width, height, status, pool1=None):
         """pool1 .. layer5 on the layer-1 output `cur` (net.py:129-187); also the dense tail of the incremental update
-        (asynchronous/incremental.py), where `cur` holds all resident nodes and only its newest rows were recomputed."""
+        (asynchronous/incremental.py), where `cur` holds all resident nodes and only its newest rows were recomputed.
+        pool1: optional callable(c_cap, e_cap, ldo, n_out, num_edges, status) that yields the first pooling's result in
+        ops.voxel_pool's format (the incremental pooling state emits it instead of re-pooling all nodes)."""
         dev = cur["x"].device
         counts = torch.zeros(12, dtype=torch.int32, device=dev)
         pools = [self.pool1, self.pool2, self.pool3, self.pool4]
@@ -282,11 +284,14 @@ class Net(torch.nn.Module):
             c_cap = max(1, min(cur["n_cap"], key_bound))
             e_cap = max(1, min(cur["e_cap"], c_cap * 64))
             cin_next = layers[k].in_channel
-            r = ops.voxel_pool(cur["x"], cur["pos"], cur["batch"], cur["rowptr"], cur["src"], cur["n_cap"], cur["n_dev"],
-                               p._vs, p._nv, num_graphs, p._inv_wh, p.aggr, width, height, f[k + 1], append_pos=True,
-                               ldo=(cin_next + 3) // 4 * 4, c_cap=c_cap, e_cap=e_cap, status=status,
-                               n_out=counts[2 * k:2 * k + 1], num_edges=counts[2 * k + 1:2 * k + 2],
-                               ell_stride=cur.get("ell", 0))
+            if k == 0 and pool1 is not None:
+                r = pool1(c_cap, e_cap, (cin_next + 3) // 4 * 4, counts[0:1], counts[1:2], status)
+            else:
+                r = ops.voxel_pool(cur["x"], cur["pos"], cur["batch"], cur["rowptr"], cur["src"], cur["n_cap"], cur["n_dev"],
+                                   p._vs, p._nv, num_graphs, p._inv_wh, p.aggr, width, height, f[k + 1], append_pos=True,
+                                   ldo=(cin_next + 3) // 4 * 4, c_cap=c_cap, e_cap=e_cap, status=status,
+                                   n_out=counts[2 * k:2 * k + 1], num_edges=counts[2 * k + 1:2 * k + 2],
+                                   ell_stride=cur.get("ell", 0))
             pseudo = dict(pos=r["pos"], two_m=two_m_of(p.transform.max), clamp01=False)
             xo = layers[k].run_fused(r["x"], r["rowptr"], r["src"], c_cap, r["n_out"], pseudo, status)
             cur = dict(x=xo, pos=r["pos"], batch=r["batch"], rowptr=r["rowptr"], src=r["src"], n_cap=c_cap,

@@ -632,6 +632,60 @@ def pool_geometry(voxel_size4: torch.Tensor, end4: torch.Tensor):
     return [int(v) for v in nv[:3]]
 
 
+def pool_params(voxel_size, nv, batch_size, inv_wh, aggr, width, height, feat_nhwc=None, append_pos=False, ell_stride=0,
+                self_loop=False):
+    """evad_pool_params_t of a Pooling layer (the struct keeps `feat_nhwc` alive only through the caller)."""
+    fb, fh, fw, fc = (feat_nhwc.shape if feat_nhwc is not None else (0, 0, 0, 0))
+    return PoolParamsT(size_x=float(voxel_size[0]), size_y=float(voxel_size[1]), size_t=float(voxel_size[2]), nvx=nv[0],
+                       nvy=nv[1], nvt=nv[2], batch_size=int(batch_size), inv_w=float(inv_wh[0]), inv_h=float(inv_wh[1]),
+                       aggr_mean=int(aggr == "mean"), append_pos=int(append_pos), feat=ptr(feat_nhwc), feat_b=fb, feat_h=fh,
+                       feat_w=fw, feat_c=fc, width=float(width), height=float(height), ell_stride=int(ell_stride),
+                       self_loop=int(bool(self_loop)))
+
+
+class PoolIncState:
+    """Incremental voxel pooling state (csrc/pool.cu: evad_pool_inc_*): per-voxel maxima, position sums, counts and coarse
+    adjacency of everything folded in since `reset`."""
+
+    def __init__(self, P, cx, capacity, device):
+        L = _lib.lib()
+        self.P, self.cx = P, int(cx)
+        nbytes = L.evad_pool_inc_state_bytes(ctypes.byref(P), self.cx)
+        if nbytes == 0:
+            raise RuntimeError("eventad_b200: this Pooling configuration has no incremental kernel (max aggregation, "
+                               "no self loops, fixed-stride rows, < 2^24 voxel keys)")
+        self.buf = _aligned_bytes(nbytes, device, 256)
+        self.node_key = torch.zeros(max(int(capacity), 1), dtype=torch.int32, device=device)
+
+    def reset(self):
+        check(_lib.lib().evad_pool_inc_reset(ptr(self.buf), ctypes.byref(self.P), self.cx, stream()), "evad_pool_inc_reset")
+
+    def update(self, n0, n_new, pos, batch_i32, x, count, nbr, status):
+        L = _lib.lib()
+        ws = _ws(L.evad_pool_inc_update_ws_bytes(n_new), pos.device)
+        with _timed('pool_inc_update'):
+            check(L.evad_pool_inc_update(ptr(self.buf), ctypes.byref(self.P), int(n0), int(n_new), ptr(pos), pos.stride(0),
+                                         ptr(batch_i32), ptr(x), x.stride(0), self.cx, ptr(count), ptr(nbr), ptr(self.node_key),
+                                         ptr(status), ptr(ws), ws.numel(), stream()), "evad_pool_inc_update")
+
+    def emit(self, c_cap, e_cap, ldo, n_out, num_edges, status):
+        """The pooled graph of all folded nodes, in voxel_pool's return format."""
+        L = _lib.lib()
+        dev = self.buf.device
+        x_out = torch.empty((c_cap, ldo), dtype=torch.float32, device=dev)
+        pos_out = torch.empty((c_cap, 3), dtype=torch.float32, device=dev)
+        batch_out = torch.empty(c_cap, dtype=torch.int32, device=dev)
+        rowptr_out = torch.empty(c_cap + 1, dtype=torch.int32, device=dev)
+        src_out = torch.empty(e_cap, dtype=torch.int32, device=dev)
+        ws = _ws(L.evad_pool_inc_emit_ws_bytes(ctypes.byref(self.P), c_cap), dev)
+        with _timed('voxel_pool'):
+            check(L.evad_pool_inc_emit(ptr(self.buf), ctypes.byref(self.P), self.cx, c_cap, e_cap, ptr(n_out), ptr(x_out), ldo,
+                                       ptr(pos_out), ptr(batch_out), ptr(rowptr_out), ptr(src_out), ptr(num_edges), ptr(status),
+                                       ptr(ws), ws.numel(), stream()), "evad_pool_inc_emit")
+        return dict(cluster=None, n_out=n_out, x=x_out, pos=pos_out, batch=batch_out, rowptr=rowptr_out, src=src_out,
+                    num_edges=num_edges, c_cap=c_cap, e_cap=e_cap, status=status)
+
+
 def voxel_pool(x, pos, batch_i32, rowptr, src, n_cap, n_dev, voxel_size, nv, batch_size, inv_wh, aggr, width, height,
                feat_nhwc=None, append_pos=False, ldo=None, c_cap=None, e_cap=None, status=None, n_out=None,
                num_edges=None, ell_stride=0, self_loop=False):

@@ -354,6 +354,24 @@ int evad_voxel_pool(const evad_pool_params_t* params_h, int64_t n_cap, const int
 /* ------------------------------------------------------------------------------------------------------------
  * Format glue.
  * ---------------------------------------------------------------------------------------------------------- */
+/* Incremental voxel pooling (src/dagr/asynchronous/max_pool.py:123-243 keeps per-voxel maxima / position
+ * sums and updates the voxels that receive nodes).  `state` (evad_pool_inc_state_bytes, 256-byte aligned, caller-owned)
+ * holds per voxel key the running maximum of [x | sampled CNN map], serial position sums, member count and one bitmap
+ * row of coarse in-edges.  evad_pool_inc_update folds the appended nodes n0 .. n0 + n_new - 1 (ids ascending with time)
+ * and their fixed-stride rows count / nbr (K = params->ell_stride) in; node_key[>= n0 + n_new] is the caller's per-node
+ * key array.  evad_pool_inc_emit writes the pooled graph of all folded nodes in evad_voxel_pool's output layout:
+ * bit-identical to evad_voxel_pool over the same nodes.  Max aggregation, no coarse self loops. */
+size_t evad_pool_inc_state_bytes(const evad_pool_params_t* params_h, int cx);
+int evad_pool_inc_reset(void* state, const evad_pool_params_t* params_h, int cx, void* stream);
+size_t evad_pool_inc_update_ws_bytes(int64_t n_new);
+int evad_pool_inc_update(void* state, const evad_pool_params_t* params_h, int64_t n0, int64_t n_new, const float* pos,
+                         int ld_pos, const int32_t* batch, const float* x, int ldx, int cx, const int32_t* count,
+                         const int32_t* nbr, uint32_t* node_key, uint32_t* status, void* ws, size_t ws_bytes, void* stream);
+size_t evad_pool_inc_emit_ws_bytes(const evad_pool_params_t* params_h, int64_t c_cap);
+int evad_pool_inc_emit(void* state, const evad_pool_params_t* params_h, int cx, int64_t c_cap, int64_t e_cap, int32_t* n_out,
+                       float* x_out, int ldo, float* pos_out, int32_t* batch_out, int32_t* rowptr_out, int32_t* src_out,
+                       int32_t* num_edges_out, uint32_t* status, void* ws, size_t ws_bytes, void* stream);
+
 /* edge_index int64 [2][stride] in any order -> dst-major CSR (stable: slots of a row keep the original edge order,
  * i.e. the order in which PyG's scatter-add visits them); eid[slot] = original edge id. */
 size_t evad_coo_to_csr_ws_bytes(int64_t num_edges);
