@@ -13,12 +13,13 @@
 // The search runs one thread per event in pixel-sorted order, so the 81 cell lookups of neighbouring threads hit
 // the same L1 lines; candidate lists (index, timestamp) are contiguous per pixel row.
 #include "common.cuh"
+#include <stdlib.h>
 
 #define G_THREADS 128
 
 __global__ void __launch_bounds__(256) g_keys_kernel(const int32_t* __restrict__ batch, const int32_t* __restrict__ pos,
                                                      int64_t n, int B, int H, int W, uint32_t* __restrict__ keys,
-                                                     uint32_t* __restrict__ status) {
+                                                     uint32_t* __restrict__ status, uint32_t* __restrict__ long_bucket) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     int b = batch[i], x = pos[3 * i], y = pos[3 * i + 1];
@@ -29,13 +30,15 @@ __global__ void __launch_bounds__(256) g_keys_kernel(const int32_t* __restrict__
         b = min(max(b, 0), B - 1);
     }
     keys[i] = (uint32_t)(x + W * (y + H * b));
+    if (i == 0 && long_bucket) *long_bucket = 0u;             // raised by g_cells_kernel, read by the search kernels
 }
 
 // cell_start[c] = first sorted position whose key >= c  (c = 0..ncells), plus sorted-order timestamps.
 __global__ void __launch_bounds__(256) g_cells_kernel(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ sidx,
                                                       const int32_t* __restrict__ pos, int64_t n, int64_t ncells,
                                                       int32_t* __restrict__ cell_start, int2* __restrict__ rec,
-                                                      int32_t* __restrict__ cell_perm) {
+                                                      int32_t* __restrict__ cell_perm, int Q,
+                                                      uint32_t* __restrict__ long_bucket) {
     int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t <= ncells) {
         int64_t lo = 0, hi = n;                               // lower_bound(skey, t)
@@ -49,6 +52,8 @@ __global__ void __launch_bounds__(256) g_cells_kernel(const uint32_t* __restrict
         uint32_t i = sidx[t];
         rec[t] = make_int2((int)i, pos[3 * (int64_t)i + 2]);  // (event index, timestamp): one 64-bit load per candidate
         if (cell_perm) cell_perm[t] = (int32_t)i;
+        // a pixel holding more than Q events: its FIFO has dropped the oldest ones, which only the per-cell walk models
+        if (long_bucket && t + Q < n && skey[t] == skey[t + Q]) *long_bucket = 1u;
     }
 }
 
@@ -59,7 +64,9 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
                                                              int W, int radius, float delta_t, int Q, int K,
                                                              int32_t* __restrict__ nbr /*[n][K]*/,
                                                              uint8_t* __restrict__ nbr_cls /*[n][K] or null*/,
-                                                             uint32_t* __restrict__ count /*[n]*/) {
+                                                             uint32_t* __restrict__ count /*[n]*/,
+                                                             const uint32_t* __restrict__ long_bucket, int run_if) {
+    if (long_bucket && (int)(*long_bucket != 0u) != run_if) return;   // the row-span kernel below has taken this call
     // spiral walk of spiral.h:1-15 (layer starts at 1, leg 0), tabulated once per CTA: the per-thread state machine cost
     // more instructions per cell visit than the visit itself
     extern __shared__ int8_t g_spiral[];                      // [nsp] dx, then [nsp] dy
@@ -121,6 +128,186 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
     count[i] = (uint32_t)cnt;
 }
 
+// The same search when no pixel holds more than Q events (`long_bucket` == 0: every bucket IS its whole FIFO), Q <= 255,
+// |delta_t| < 2^24 (the float time gate is then the integer test dt <= delta_t) and radius <= 7.  In pixel-sorted order the
+// (2r+1) pixels of one image row are ONE contiguous span of `rec`, so a thread reads 2r+1 spans (two cell_start loads per
+// row) instead of (2r+1)^2 buckets of a different length in every lane:
+//   pass 1  admissible entries (older than i, inside the time gate) of each row as a bit mask over the 32 entries from
+//           the span's (even) start, read two per 128-bit load;
+//   count   per admissible entry: spiral position of its pixel -> one byte counter per position in shared memory;
+//   prefix  counters -> first output slot of each position (four positions per 32-bit word);
+//   place   per admissible entry, newest first inside a pixel: slot = counter++, written straight into the row.
+// Entries beyond the 32 of a mask (dense scenes) are tested one by one in `count` and `place` (tails before masks: they
+// are the newer ones of their pixel).  The result is the list the per-cell walk above produces (spiral position, then
+// newest first); nothing is sorted.
+__device__ __forceinline__ uint32_t gsr_lds8(uint32_t a) { uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a) : "memory"); return v; }
+__device__ __forceinline__ uint32_t gsr_lds16(uint32_t a) { uint32_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a) : "memory"); return v; }
+__device__ __forceinline__ uint32_t gsr_lds32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory"); return v; }
+__device__ __forceinline__ void gsr_sts8(uint32_t a, uint32_t v) { asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void gsr_sts32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+
+struct GsrTable {
+    uint16_t off_of[225];        // [(dy+R)*(2R+1) + dx+R] -> byte offset of the pixel's counter: (s >> 2) * 4 * G_THREADS + (s & 3)
+};
+
+template <int R>
+__global__ void __launch_bounds__(G_THREADS) g_search_rows_kernel(const uint32_t* __restrict__ skey,
+                                                                  const int2* __restrict__ rec,
+                                                                  const int32_t* __restrict__ cell_start, int64_t n,
+                                                                  int H, int W, int delta_t, int K,
+                                                                  int32_t* __restrict__ nbr, uint8_t* __restrict__ nbr_cls,
+                                                                  uint32_t* __restrict__ count,
+                                                                  const uint32_t* __restrict__ long_bucket,
+                                                                  const __grid_constant__ GsrTable T) {
+    if (*long_bucket != 0u) return;
+    constexpr int ROWS = 2 * R + 1, NSP = ROWS * ROWS, NW = (NSP + 3) / 4;
+    __shared__ __align__(16) uint32_t s_slot[NW * G_THREADS];              // [NW][thread]: 4 position counters per word
+    __shared__ uint16_t s_off_of[NSP];
+    // shared-space addresses behind an opaque move: ptxas otherwise rebuilds them (S2R CgaCtaId + 2 more) at every use
+    uint32_t slot_a = (uint32_t)__cvta_generic_to_shared(s_slot) + threadIdx.x * 4;   // this thread's counter column
+    uint32_t off_a = (uint32_t)__cvta_generic_to_shared(s_off_of);
+    asm volatile("mov.u32 %0, %0;" : "+r"(slot_a));
+    asm volatile("mov.u32 %0, %0;" : "+r"(off_a));
+    for (int t = threadIdx.x; t < NSP; t += G_THREADS) s_off_of[t] = T.off_of[t];
+#pragma unroll
+    for (int w = 0; w < NW; w++) gsr_sts32(slot_a + w * (4 * G_THREADS), 0u);
+    __syncthreads();
+    int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const int2 me = rec[p];
+    const int i = me.x, ti = me.y;
+    const int c = (int)skey[p];
+    const int rem = c % (W * H);
+    const int y = rem / W, x = rem - y * W;
+    const int xl = max(x - R, 0) - x, xh = min(x + R, W - 1) - x;          // clipped dx range
+    const int KM = K - 1;
+    const int4* rec2 = reinterpret_cast<const int4*>(rec);                 // entries (2k, 2k + 1)
+    int ra[ROWS];                                                          // even start of the row's mask
+    uint32_t mask[ROWS];
+    bool tails = false;
+    // ---- pass 1
+#pragma unroll
+    for (int j = 0; j < ROWS; j++) {
+        const int dy = j - R;
+        ra[j] = 0;
+        mask[j] = 0u;
+        if ((unsigned)(y + dy) >= (unsigned)H) continue;
+        const int rowc = c + dy * W;
+        const int a = cell_start[rowc + xl], b = cell_start[rowc + xh + 1];
+        const int a2 = a & ~1, len = min(b - a2, 32);
+        ra[j] = a2;
+        tails |= b - a2 > 32;
+        uint32_t m = 0u;
+        int done = 0;
+#pragma unroll 2
+        for (int q2 = a2 >> 1; done < len; q2++, done += 2) {              // the entry past an odd end is masked off below
+            const int4 v = rec2[q2];
+            m = __funnelshift_r(m, (v.x < i && ti - v.y <= delta_t) ? 1u : 0u, 1);
+            m = __funnelshift_r(m, (v.z < i && ti - v.w <= delta_t) ? 1u : 0u, 1);
+        }
+        m = done ? m >> (32 - done) : 0u;                                  // bit k <-> entry a2 + k
+        if (a & 1) m &= ~1u;
+        if (len < 32) m &= (1u << max(len, 0)) - 1u;
+        mask[j] = m;
+    }
+    auto admissible = [&](int q) { const int2 r = rec[q]; return r.x < i && ti - r.y <= delta_t; };   // ev_graph.cu:63, 69
+    // ---- count
+    if (tails) {
+        for (int j = 0; j < ROWS; j++) {
+            if ((unsigned)(y + j - R) >= (unsigned)H) continue;
+            const int rowc = c + (j - R) * W;
+            const int prow = j * ROWS + R - rowc;
+            const int b = cell_start[rowc + xh + 1];
+            for (int q = (cell_start[rowc + xl] & ~1) + 32; q < b; q++)
+                if (admissible(q)) {
+                    const uint32_t h = slot_a + gsr_lds16(off_a + 2 * (prow + (int)skey[q]));
+                    gsr_sts8(h, gsr_lds8(h) + 1);                          // <= Q <= 255
+                }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < ROWS; j++) {
+        const int prow = j * ROWS + R - (c + (j - R) * W);
+#pragma unroll 1
+        for (uint32_t m = mask[j]; m; m &= m - 1) {
+            const uint32_t h = slot_a + gsr_lds16(off_a + 2 * (prow + (int)skey[ra[j] + __ffs((int)m) - 1]));
+            gsr_sts8(h, gsr_lds8(h) + 1);
+        }
+    }
+    // ---- prefix: byte k of a word becomes the first slot of its position; everything saturates at 31 >= KM
+    uint32_t run = 0u;
+#pragma unroll
+    for (int w = 0; w < NW; w++) {
+        const uint32_t v = __vminu4(gsr_lds32(slot_a + w * (4 * G_THREADS)), 0x1f1f1f1fu);
+        const uint32_t incl = v * 0x01010101u;                             // bytes <= 124
+        gsr_sts32(slot_a + w * (4 * G_THREADS), (incl << 8) + run * 0x01010101u);   // bytes <= 124 + 31
+        run = min(run + (incl >> 24), 31u);
+    }
+    const int m_out = min((int)run, KM);
+    int32_t* out = nbr + (int64_t)i * K;
+    uint8_t* ocls = nbr_cls ? nbr_cls + (int64_t)i * K : nullptr;
+    out[0] = i;                                                            // self edge first (ev_graph.cu:43-46)
+    if (ocls) ocls[0] = (uint8_t)(R * ROWS + R);
+    count[i] = (uint32_t)(m_out + 1);
+    // ---- place, newest first inside every pixel
+    auto place = [&](int q, int j, int prow) {
+        const int cell = prow + (int)skey[q];                              // j * ROWS + dx + R
+        const uint32_t h = slot_a + gsr_lds16(off_a + 2 * cell);
+        const int slot = (int)gsr_lds8(h);
+        if (slot < KM) {
+            gsr_sts8(h, (uint32_t)slot + 1);
+            out[1 + slot] = rec[q].x;
+            if (ocls) ocls[1 + slot] = (uint8_t)((cell - j * ROWS) * ROWS + j);   // (dx + R) * (2R + 1) + dy + R
+        }
+    };
+    if (tails) {
+        for (int j = 0; j < ROWS; j++) {
+            if ((unsigned)(y + j - R) >= (unsigned)H) continue;
+            const int rowc = c + (j - R) * W;
+            const int prow = j * ROWS + R - rowc;
+            const int lo = (cell_start[rowc + xl] & ~1) + 32;
+            for (int q = cell_start[rowc + xh + 1] - 1; q >= lo; q--)
+                if (admissible(q)) place(q, j, prow);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < ROWS; j++) {
+        const int prow = j * ROWS + R - (c + (j - R) * W);
+#pragma unroll 1
+        for (uint32_t m = mask[j]; m; ) {
+            const int bit = 31 - __clz((int)m);
+            m &= ~(1u << bit);
+            place(ra[j] + bit, j, prow);
+        }
+    }
+}
+
+// off_of table of the spiral walk of spiral.h:1-15 (layer starts at 1, leg 0) for one radius
+static GsrTable gsr_table(int R) {
+    GsrTable T;
+    const int side = 2 * R + 1;
+    int sx = 0, sy = 0, layer = 1, leg = 0;
+    for (int s = 0; s < side * side; s++) {
+        T.off_of[(sy + R) * side + sx + R] = (uint16_t)((s >> 2) * 4 * G_THREADS + (s & 3));
+        switch (leg) {
+        case 0: ++sx; if (sx == layer) ++leg; break;
+        case 1: ++sy; if (sy == layer) ++leg; break;
+        case 2: --sx; if (-sx == layer) ++leg; break;
+        default: --sy; if (-sy == layer) { leg = 0; ++layer; } break;
+        }
+    }
+    return T;
+}
+
+template <int R>
+static void g_search_rows_launch(const uint32_t* skey, const int2* rec, const int32_t* cell_start, int64_t n, int H, int W,
+                                 int delta_t, int K, int32_t* nbr, uint8_t* nbr_cls, uint32_t* count,
+                                 const uint32_t* long_bucket, cudaStream_t st) {
+    static const GsrTable T = gsr_table(R);
+    g_search_rows_kernel<R><<<evad_cdiv(n, G_THREADS), G_THREADS, 0, st>>>(skey, rec, cell_start, n, H, W, delta_t, K, nbr,
+                                                                         nbr_cls, count, long_bucket, T);
+}
+
 // scatter the per-event neighbour slots into the compact CSR (+ optional int64 edge_index rows)
 __global__ void __launch_bounds__(256) g_compact_kernel(const int32_t* __restrict__ nbr, const uint32_t* __restrict__ rowptr_u,
                                                         int64_t n, int K, int32_t* __restrict__ rowptr,
@@ -152,6 +339,7 @@ struct GraphWs {
     int32_t *nbr, *cell_start;
     int2* rec;
     uint8_t* nbr_cls;
+    uint32_t* long_bucket;
 };
 
 static size_t graph_ws_layout(EvadArena& a, int64_t n, int64_t ncells, int K, GraphWs* w) {
@@ -165,6 +353,7 @@ static size_t graph_ws_layout(EvadArena& a, int64_t n, int64_t ncells, int K, Gr
     w->cell_start = a.take<int32_t>(ncells + 2);
     w->sort_tmp = a.take<uint32_t>(evad_sort_tmp_elems(n));
     w->scan_tmp = a.take<uint32_t>(evad_scan_tmp_elems(n + 1));
+    w->long_bucket = a.take<uint32_t>(1);
     return a.off;
 }
 
@@ -179,17 +368,32 @@ static int graph_rows(const int32_t* batch, const int32_t* pos, int64_t n, int B
                       int Q, int K, const GraphWs& w, int32_t* cell_start, int32_t* cell_perm, int32_t* nbr,
                       uint8_t* nbr_cls, uint32_t* count, uint32_t* status, cudaStream_t st) {
     const int64_t ncells = (int64_t)B * H * W;
-    g_keys_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(batch, pos, n, B, H, W, w.k0, status);
+    // the row-span search covers: radius 1..7, K >= 2, Q <= 255, |delta_t| < 2^24; otherwise (or when a pixel
+    // holds more than Q events, found on the device) the per-cell walk runs.  EVAD_GRAPH_ROWSPAN=0 forces the walk.
+    static const bool rowspan_on = [] { const char* e = getenv("EVAD_GRAPH_ROWSPAN"); return !(e && e[0] == '0'); }();
+    const int nsp = (2 * radius + 1) * (2 * radius + 1);
+    const bool rowspan = rowspan_on && radius >= 1 && radius <= 7 && K >= 2 && Q <= 255 && delta_t_us > -(1 << 24) &&
+                         delta_t_us < (1 << 24);
+    uint32_t* long_bucket = rowspan ? w.long_bucket : nullptr;
+    g_keys_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(batch, pos, n, B, H, W, w.k0, status, long_bucket);
     EVAD_CHECK_LAUNCH();
     int key_bits = 1;
     while ((1ll << key_bits) < ncells) key_bits++;
     uint32_t *skey, *sidx;
     EVAD_TRY(evad_sort_pairs_u32(w.k0, w.v0, w.k1, w.v1, 1, n, key_bits, w.sort_tmp, &skey, &sidx, st));
     const int64_t m = (ncells + 1 > n) ? ncells + 1 : n;
-    g_cells_kernel<<<evad_cdiv(m, 256), 256, 0, st>>>(skey, sidx, pos, n, ncells, cell_start, w.rec, cell_perm);
+    g_cells_kernel<<<evad_cdiv(m, 256), 256, 0, st>>>(skey, sidx, pos, n, ncells, cell_start, w.rec, cell_perm, Q, long_bucket);
     EVAD_CHECK_LAUNCH();
-    g_search_kernel<<<evad_cdiv(n, G_THREADS), G_THREADS, 2 * (2 * radius + 1) * (2 * radius + 1), st>>>(skey, w.rec, cell_start, n, H, W, radius,
-                                                                  (float)delta_t_us, Q, K, nbr, nbr_cls, count);
+    if (rowspan) {
+        switch (radius) {
+#define GSR_CASE(RR) case RR: g_search_rows_launch<RR>(skey, w.rec, cell_start, n, H, W, delta_t_us, K, nbr, nbr_cls, count, long_bucket, st); break;
+        GSR_CASE(1) GSR_CASE(2) GSR_CASE(3) GSR_CASE(4) GSR_CASE(5) GSR_CASE(6) GSR_CASE(7)
+#undef GSR_CASE
+        }
+        EVAD_CHECK_LAUNCH();
+    }
+    g_search_kernel<<<evad_cdiv(n, G_THREADS), G_THREADS, 2 * nsp, st>>>(skey, w.rec, cell_start, n, H, W, radius,
+                                                                    (float)delta_t_us, Q, K, nbr, nbr_cls, count, long_bucket, 1);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }

@@ -106,3 +106,33 @@ def test_fixed_stride_rows_equal_the_compacted_graph(n, B, dist):
     assert np.array_equal(rows["nbr"].cpu().numpy()[:N][mask], csr["src"].cpu().numpy()[:E])
     assert np.array_equal(rows["nbr_cls"].cpu().numpy()[:N][mask], csr["edge_cls"].cpu().numpy()[:E])
     assert torch.equal(rows["cell_perm"][:N], csr["cell_perm"][:N])
+
+
+@pytest.mark.parametrize("W,H,n,K,Q,r,dt", [(12, 9, 4000, 16, 128, 4, 10_000), (12, 9, 4000, 16, 128, 4, 300),
+                                             (20, 16, 9000, 32, 64, 5, 2000), (7, 5, 600, 2, 128, 3, 10_000),
+                                             (16, 16, 6000, 9, 48, 2, 1500), (30, 20, 5000, 16, 128, 7, 3000),
+                                             (30, 20, 5000, 12, 128, 6, 3000), (9, 9, 700, 16, 200, 1, 10_000),
+                                             (40, 30, 3000, 16, 128, 4, 0)])
+def test_row_span_search_saturated_lists(W, H, n, K, Q, r, dt):
+    """Tens of events per pixel but never more than Q (g_search_rows_kernel takes the call): the K-1 list overflows on most
+    events, so what is kept and in which order is the spiral-position / newest-first rule; offset classes are recomputed
+    from the coordinates of both ends."""
+    from eventad_b200.graph.ev_graph import SlidingWindowGraph
+    rng = np.random.default_rng(W * H + K)
+    x, y = rng.integers(0, W, n), rng.integers(0, H, n)
+    assert np.bincount(y * W + x).max() <= Q
+    t = np.sort(rng.integers(0, 20_000, n)) // 3 * 3
+    pos = np.stack([x, y, t], 1).astype(np.int32)
+    batch = np.zeros(n, np.int32)
+    e, eo, _ = _run_both(batch, pos, W, H, 1, K=K, Q=Q, r=r, dt=dt)
+    assert np.array_equal(e.cpu().numpy(), eo)
+    g = SlidingWindowGraph(width=W, height=H, batch_size=1, max_num_neighbors=K, max_queue_size=Q, radius=r, delta_t_us=dt)
+    g.reset()
+    rows = g.build_rows(torch.from_numpy(batch).cuda(), torch.from_numpy(pos).cuda(), want_cls=True)
+    cnt = rows["count"].cpu().numpy()[:n]
+    mask = np.arange(K)[None, :] < cnt[:, None]
+    nbr = rows["nbr"].cpu().numpy()[:n].reshape(n, K)
+    assert np.array_equal(nbr[mask].astype(np.int64), eo[0])
+    dst = np.repeat(np.arange(n), cnt)
+    want = (x[eo[0]] - x[dst] + r) * (2 * r + 1) + (y[eo[0]] - y[dst] + r)
+    assert np.array_equal(rows["nbr_cls"].cpu().numpy()[:n].reshape(n, K)[mask].astype(np.int64), want)
