@@ -14,6 +14,7 @@
 // the same L1 lines; candidate lists (index, timestamp) are contiguous per pixel row.
 #include "common.cuh"
 #include <stdlib.h>
+#include <string.h>
 
 #define G_THREADS 128
 
@@ -38,7 +39,7 @@ __global__ void __launch_bounds__(256) g_cells_kernel(const uint32_t* __restrict
                                                       const int32_t* __restrict__ pos, int64_t n, int64_t ncells,
                                                       int32_t* __restrict__ cell_start, int2* __restrict__ rec,
                                                       int32_t* __restrict__ cell_perm, int Q,
-                                                      uint32_t* __restrict__ long_bucket) {
+                                                      uint32_t* __restrict__ long_bucket, int W, int xs) {
     int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t <= ncells) {
         int64_t lo = 0, hi = n;                               // lower_bound(skey, t)
@@ -50,7 +51,9 @@ __global__ void __launch_bounds__(256) g_cells_kernel(const uint32_t* __restrict
     }
     if (t < n) {
         uint32_t i = sidx[t];
-        rec[t] = make_int2((int)i, pos[3 * (int64_t)i + 2]);  // (event index, timestamp): one 64-bit load per candidate
+        // (event index, timestamp): one 64-bit load per candidate.  xs = 5: the index sits above the low 5 bits of the
+        // pixel column (order and `<` on the word are those of the index), read by g_search_rows_kernel
+        rec[t] = make_int2((int)((i << xs) | (xs ? (skey[t] % (uint32_t)W) & 31u : 0u)), pos[3 * (int64_t)i + 2]);
         if (cell_perm) cell_perm[t] = (int32_t)i;
         // a pixel holding more than Q events: its FIFO has dropped the oldest ones, which only the per-cell walk models
         if (long_bucket && t + Q < n && skey[t] == skey[t + Q]) *long_bucket = 1u;
@@ -65,7 +68,7 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
                                                              int32_t* __restrict__ nbr /*[n][K]*/,
                                                              uint8_t* __restrict__ nbr_cls /*[n][K] or null*/,
                                                              uint32_t* __restrict__ count /*[n]*/,
-                                                             const uint32_t* __restrict__ long_bucket, int run_if) {
+                                                             const uint32_t* __restrict__ long_bucket, int run_if, int xs) {
     if (long_bucket && (int)(*long_bucket != 0u) != run_if) return;   // the row-span kernel below has taken this call
     // spiral walk of spiral.h:1-15 (layer starts at 1, leg 0), tabulated once per CTA: the per-thread state machine cost
     // more instructions per cell visit than the visit itself
@@ -88,7 +91,7 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
     int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     const int2 me = rec[p];
-    const int i = me.x;
+    const int i = me.x >> xs;
     const int c = (int)skey[p];
     const int ti = me.y;
     const int rem = c % (W * H);
@@ -111,12 +114,13 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
                 int a = lo, b = s1;
                 while (a < b) {
                     const int m = (a + b) >> 1;
-                    if (rec[m].x < i) a = m + 1; else b = m;
+                    if ((rec[m].x >> xs) < i) a = m + 1; else b = m;
                 }
                 q = a - 1;
             }
             for (; q >= lo; q--) {                            // newest first
-                const int2 r = rec[q];
+                int2 r = rec[q];
+                r.x >>= xs;
                 if (r.x >= i) continue;                       // later events occupy FIFO slots but are skipped
                 if ((float)(ti - r.y) > delta_t) continue;    // NOT break (ev_graph.cu:69)
                 if (ocls) ocls[cnt] = (uint8_t)((sx + radius) * side + (sy + radius));
@@ -134,7 +138,9 @@ __global__ void __launch_bounds__(G_THREADS) g_search_kernel(const uint32_t* __r
 // row) instead of (2r+1)^2 buckets of a different length in every lane:
 //   pass 1  admissible entries (older than i, inside the time gate) of each row as a bit mask over the 32 entries from
 //           the span's (even) start, read two per 128-bit load;
-//   count   per admissible entry: spiral position of its pixel -> one byte counter per position in shared memory;
+//   count   per admissible entry: spiral position of its pixel (from the 5 column bits packed under the index in the
+//           entry's first word and a per-row table in the kernel parameters) -> one byte counter per position in shared
+//           memory;
 //   prefix  counters -> first output slot of each position (four positions per 32-bit word);
 //   place   per admissible entry, newest first inside a pixel: slot = counter++, written straight into the row.
 // Entries beyond the 32 of a mask (dense scenes) are tested one by one in `count` and `place` (tails before masks: they
@@ -147,53 +153,49 @@ __device__ __forceinline__ void gsr_sts8(uint32_t a, uint32_t v) { asm volatile(
 __device__ __forceinline__ void gsr_sts32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 
 struct GsrTable {
-    uint16_t off_of[225];        // [(dy+R)*(2R+1) + dx+R] -> byte offset of the pixel's counter: (s >> 2) * 4 * G_THREADS + (s & 3)
+    unsigned long long lo[15], hi[15];   // row j = dy + R: spiral position of dx + R = 0..7 (lo) / 8..14 (hi), one byte each
 };
 
 template <int R>
-__global__ void __launch_bounds__(G_THREADS) g_search_rows_kernel(const uint32_t* __restrict__ skey,
-                                                                  const int2* __restrict__ rec,
-                                                                  const int32_t* __restrict__ cell_start, int64_t n,
-                                                                  int H, int W, int delta_t, int K,
-                                                                  int32_t* __restrict__ nbr, uint8_t* __restrict__ nbr_cls,
-                                                                  uint32_t* __restrict__ count,
-                                                                  const uint32_t* __restrict__ long_bucket,
-                                                                  const __grid_constant__ GsrTable T) {
+__global__ void __launch_bounds__(G_THREADS, R <= 4 ? 10 : 4) g_search_rows_kernel(
+    const uint32_t* __restrict__ skey, const int2* __restrict__ rec /* .x = index << 5 | column & 31 */,
+    const int32_t* __restrict__ cell_start, int64_t n, int H, int W, int delta_t, int K, int32_t* __restrict__ nbr,
+    uint8_t* __restrict__ nbr_cls, uint32_t* __restrict__ count, const uint32_t* __restrict__ long_bucket,
+    const __grid_constant__ GsrTable T) {
     if (*long_bucket != 0u) return;
     constexpr int ROWS = 2 * R + 1, NSP = ROWS * ROWS, NW = (NSP + 3) / 4;
     __shared__ __align__(16) uint32_t s_slot[NW * G_THREADS];              // [NW][thread]: 4 position counters per word
-    __shared__ uint16_t s_off_of[NSP];
-    // shared-space addresses behind an opaque move: ptxas otherwise rebuilds them (S2R CgaCtaId + 2 more) at every use
+    // shared-space address behind an opaque move: ptxas otherwise rebuilds it (S2R CgaCtaId + 2 more) at every use
     uint32_t slot_a = (uint32_t)__cvta_generic_to_shared(s_slot) + threadIdx.x * 4;   // this thread's counter column
-    uint32_t off_a = (uint32_t)__cvta_generic_to_shared(s_off_of);
     asm volatile("mov.u32 %0, %0;" : "+r"(slot_a));
-    asm volatile("mov.u32 %0, %0;" : "+r"(off_a));
-    for (int t = threadIdx.x; t < NSP; t += G_THREADS) s_off_of[t] = T.off_of[t];
 #pragma unroll
     for (int w = 0; w < NW; w++) gsr_sts32(slot_a + w * (4 * G_THREADS), 0u);
-    __syncthreads();
     int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     const int2 me = rec[p];
-    const int i = me.x, ti = me.y;
+    const int iw = me.x & ~31, ti = me.y;                                  // entries older than i: word < iw
     const int c = (int)skey[p];
     const int rem = c % (W * H);
     const int y = rem / W, x = rem - y * W;
     const int xl = max(x - R, 0) - x, xh = min(x + R, W - 1) - x;          // clipped dx range
     const int KM = K - 1;
+    const int xr = R - x;                                                  // (column + xr) & 31 = dx + R
     const int4* rec2 = reinterpret_cast<const int4*>(rec);                 // entries (2k, 2k + 1)
-    int ra[ROWS];                                                          // even start of the row's mask
+    int ra[ROWS], rb[ROWS];                                                // span of row j (empty outside the image)
     uint32_t mask[ROWS];
-    bool tails = false;
-    // ---- pass 1
 #pragma unroll
     for (int j = 0; j < ROWS; j++) {
-        const int dy = j - R;
-        ra[j] = 0;
-        mask[j] = 0u;
-        if ((unsigned)(y + dy) >= (unsigned)H) continue;
-        const int rowc = c + dy * W;
+        const bool in = (unsigned)(y + j - R) < (unsigned)H;
+        const int rowc = in ? c + (j - R) * W : c;
         const int a = cell_start[rowc + xl], b = cell_start[rowc + xh + 1];
+        ra[j] = a;
+        rb[j] = in ? b : a;
+    }
+    // ---- pass 1
+    bool tails = false;
+#pragma unroll
+    for (int j = 0; j < ROWS; j++) {
+        const int a = ra[j], b = rb[j];
         const int a2 = a & ~1, len = min(b - a2, 32);
         ra[j] = a2;
         tails |= b - a2 > 32;
@@ -202,35 +204,43 @@ __global__ void __launch_bounds__(G_THREADS) g_search_rows_kernel(const uint32_t
 #pragma unroll 2
         for (int q2 = a2 >> 1; done < len; q2++, done += 2) {              // the entry past an odd end is masked off below
             const int4 v = rec2[q2];
-            m = __funnelshift_r(m, (v.x < i && ti - v.y <= delta_t) ? 1u : 0u, 1);
-            m = __funnelshift_r(m, (v.z < i && ti - v.w <= delta_t) ? 1u : 0u, 1);
+            m = __funnelshift_r(m, (v.x < iw && ti - v.y <= delta_t) ? 1u : 0u, 1);
+            m = __funnelshift_r(m, (v.z < iw && ti - v.w <= delta_t) ? 1u : 0u, 1);
         }
         m = done ? m >> (32 - done) : 0u;                                  // bit k <-> entry a2 + k
         if (a & 1) m &= ~1u;
         if (len < 32) m &= (1u << max(len, 0)) - 1u;
         mask[j] = m;
     }
-    auto admissible = [&](int q) { const int2 r = rec[q]; return r.x < i && ti - r.y <= delta_t; };   // ev_graph.cu:63, 69
+    // spiral position of an entry of row j from its packed word, and the address of this thread's counter for it
+    auto position = [&](int j, int word) -> uint32_t {
+        const int k = (word + xr) & 31;                                    // dx + R
+        const unsigned long long t = (ROWS > 8 && k >= 8) ? T.hi[j] : T.lo[j];
+        return (uint32_t)(t >> ((k & 7) * 8)) & 255u;
+    };
+    auto counter = [&](uint32_t s) -> uint32_t { return slot_a + ((s & 0xfcu) << 7) + (s & 3u); };
+    auto admissible = [&](int2 r) { return r.x < iw && ti - r.y <= delta_t; };   // ev_graph.cu:63, 69
     // ---- count
     if (tails) {
         for (int j = 0; j < ROWS; j++) {
             if ((unsigned)(y + j - R) >= (unsigned)H) continue;
             const int rowc = c + (j - R) * W;
-            const int prow = j * ROWS + R - rowc;
             const int b = cell_start[rowc + xh + 1];
-            for (int q = (cell_start[rowc + xl] & ~1) + 32; q < b; q++)
-                if (admissible(q)) {
-                    const uint32_t h = slot_a + gsr_lds16(off_a + 2 * (prow + (int)skey[q]));
+            for (int q = (cell_start[rowc + xl] & ~1) + 32; q < b; q++) {
+                const int2 r = rec[q];
+                if (admissible(r)) {
+                    const int k = (r.x + xr) & 31;
+                    const uint32_t h = counter((uint32_t)((k >= 8 ? T.hi[j] : T.lo[j]) >> ((k & 7) * 8)) & 255u);
                     gsr_sts8(h, gsr_lds8(h) + 1);                          // <= Q <= 255
                 }
+            }
         }
     }
 #pragma unroll
     for (int j = 0; j < ROWS; j++) {
-        const int prow = j * ROWS + R - (c + (j - R) * W);
 #pragma unroll 1
         for (uint32_t m = mask[j]; m; m &= m - 1) {
-            const uint32_t h = slot_a + gsr_lds16(off_a + 2 * (prow + (int)skey[ra[j] + __ffs((int)m) - 1]));
+            const uint32_t h = counter(position(j, rec[ra[j] + __ffs((int)m) - 1].x));
             gsr_sts8(h, gsr_lds8(h) + 1);
         }
     }
@@ -243,6 +253,7 @@ __global__ void __launch_bounds__(G_THREADS) g_search_rows_kernel(const uint32_t
         gsr_sts32(slot_a + w * (4 * G_THREADS), (incl << 8) + run * 0x01010101u);   // bytes <= 124 + 31
         run = min(run + (incl >> 24), 31u);
     }
+    const int i = me.x >> 5;
     const int m_out = min((int)run, KM);
     int32_t* out = nbr + (int64_t)i * K;
     uint8_t* ocls = nbr_cls ? nbr_cls + (int64_t)i * K : nullptr;
@@ -250,45 +261,49 @@ __global__ void __launch_bounds__(G_THREADS) g_search_rows_kernel(const uint32_t
     if (ocls) ocls[0] = (uint8_t)(R * ROWS + R);
     count[i] = (uint32_t)(m_out + 1);
     // ---- place, newest first inside every pixel
-    auto place = [&](int q, int j, int prow) {
-        const int cell = prow + (int)skey[q];                              // j * ROWS + dx + R
-        const uint32_t h = slot_a + gsr_lds16(off_a + 2 * cell);
+    auto place = [&](int word, int j, uint32_t s) {
+        const uint32_t h = counter(s);
         const int slot = (int)gsr_lds8(h);
         if (slot < KM) {
             gsr_sts8(h, (uint32_t)slot + 1);
-            out[1 + slot] = rec[q].x;
-            if (ocls) ocls[1 + slot] = (uint8_t)((cell - j * ROWS) * ROWS + j);   // (dx + R) * (2R + 1) + dy + R
+            out[1 + slot] = word >> 5;
+            if (ocls) ocls[1 + slot] = (uint8_t)(((word + xr) & 31) * ROWS + j);   // (dx + R) * (2R + 1) + dy + R
         }
     };
     if (tails) {
         for (int j = 0; j < ROWS; j++) {
             if ((unsigned)(y + j - R) >= (unsigned)H) continue;
             const int rowc = c + (j - R) * W;
-            const int prow = j * ROWS + R - rowc;
             const int lo = (cell_start[rowc + xl] & ~1) + 32;
-            for (int q = cell_start[rowc + xh + 1] - 1; q >= lo; q--)
-                if (admissible(q)) place(q, j, prow);
+            for (int q = cell_start[rowc + xh + 1] - 1; q >= lo; q--) {
+                const int2 r = rec[q];
+                if (admissible(r)) {
+                    const int k = (r.x + xr) & 31;
+                    place(r.x, j, (uint32_t)((k >= 8 ? T.hi[j] : T.lo[j]) >> ((k & 7) * 8)) & 255u);
+                }
+            }
         }
     }
 #pragma unroll
     for (int j = 0; j < ROWS; j++) {
-        const int prow = j * ROWS + R - (c + (j - R) * W);
 #pragma unroll 1
         for (uint32_t m = mask[j]; m; ) {
             const int bit = 31 - __clz((int)m);
             m &= ~(1u << bit);
-            place(ra[j] + bit, j, prow);
+            const int word = rec[ra[j] + bit].x;
+            place(word, j, position(j, word));
         }
     }
 }
 
-// off_of table of the spiral walk of spiral.h:1-15 (layer starts at 1, leg 0) for one radius
+// spiral positions of the walk of spiral.h:1-15 (layer starts at 1, leg 0) for one radius, packed per row
 static GsrTable gsr_table(int R) {
     GsrTable T;
-    const int side = 2 * R + 1;
+    memset(&T, 0, sizeof(T));
     int sx = 0, sy = 0, layer = 1, leg = 0;
-    for (int s = 0; s < side * side; s++) {
-        T.off_of[(sy + R) * side + sx + R] = (uint16_t)((s >> 2) * 4 * G_THREADS + (s & 3));
+    for (int s = 0; s < (2 * R + 1) * (2 * R + 1); s++) {
+        const int j = sy + R, k = sx + R;
+        (k >= 8 ? T.hi[j] : T.lo[j]) |= (unsigned long long)s << ((k & 7) * 8);
         switch (leg) {
         case 0: ++sx; if (sx == layer) ++leg; break;
         case 1: ++sy; if (sy == layer) ++leg; break;
@@ -373,7 +388,8 @@ static int graph_rows(const int32_t* batch, const int32_t* pos, int64_t n, int B
     static const bool rowspan_on = [] { const char* e = getenv("EVAD_GRAPH_ROWSPAN"); return !(e && e[0] == '0'); }();
     const int nsp = (2 * radius + 1) * (2 * radius + 1);
     const bool rowspan = rowspan_on && radius >= 1 && radius <= 7 && K >= 2 && Q <= 255 && delta_t_us > -(1 << 24) &&
-                         delta_t_us < (1 << 24);
+                         delta_t_us < (1 << 24) && n < (1ll << 26);
+    const int xs = rowspan ? 5 : 0;
     uint32_t* long_bucket = rowspan ? w.long_bucket : nullptr;
     g_keys_kernel<<<evad_cdiv(n, 256), 256, 0, st>>>(batch, pos, n, B, H, W, w.k0, status, long_bucket);
     EVAD_CHECK_LAUNCH();
@@ -382,7 +398,7 @@ static int graph_rows(const int32_t* batch, const int32_t* pos, int64_t n, int B
     uint32_t *skey, *sidx;
     EVAD_TRY(evad_sort_pairs_u32(w.k0, w.v0, w.k1, w.v1, 1, n, key_bits, w.sort_tmp, &skey, &sidx, st));
     const int64_t m = (ncells + 1 > n) ? ncells + 1 : n;
-    g_cells_kernel<<<evad_cdiv(m, 256), 256, 0, st>>>(skey, sidx, pos, n, ncells, cell_start, w.rec, cell_perm, Q, long_bucket);
+    g_cells_kernel<<<evad_cdiv(m, 256), 256, 0, st>>>(skey, sidx, pos, n, ncells, cell_start, w.rec, cell_perm, Q, long_bucket, W, xs);
     EVAD_CHECK_LAUNCH();
     if (rowspan) {
         switch (radius) {
@@ -393,7 +409,7 @@ static int graph_rows(const int32_t* batch, const int32_t* pos, int64_t n, int B
         EVAD_CHECK_LAUNCH();
     }
     g_search_kernel<<<evad_cdiv(n, G_THREADS), G_THREADS, 2 * nsp, st>>>(skey, w.rec, cell_start, n, H, W, radius,
-                                                                    (float)delta_t_us, Q, K, nbr, nbr_cls, count, long_bucket, 1);
+                                                                    (float)delta_t_us, Q, K, nbr, nbr_cls, count, long_bucket, 1, xs);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }
