@@ -148,7 +148,7 @@ def _declare(L):
     _sig(L, "evad_asy_masked_isdiff", c_i, [c_p, c_i64, c_p, c_p, c_i, c_f, c_f, c_p])
     _sig(L, "evad_bbox_pool", c_i, [c_p, c_i, c_i, c_p, c_i, c_p, c_i64, c_p, c_p, c_i, c_p, c_i, c_i, c_p, c_p, c_i, c_i, c_p, c_p])
     _sig(L, "evad_sample_concat_h2", c_i, [c_p, c_i, c_i, c_p, c_i, c_p, c_i64, c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_f,
-                                           c_i, c_p, c_i, c_p, c_p])
+                                           c_i, c_p, c_i, c_p, c_p, c_p])
     _sig(L, "evad_sample_concat", c_i, [c_p, c_i, c_i, c_p, c_i, c_p, c_i64, c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_f,
                                         c_i, c_p, c_i, c_p])
 

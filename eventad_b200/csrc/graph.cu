@@ -34,20 +34,29 @@ __global__ void __launch_bounds__(256) g_keys_kernel(const int32_t* __restrict__
     if (i == 0 && long_bucket) *long_bucket = 0u;             // raised by g_cells_kernel, read by the search kernels
 }
 
-// cell_start[c] = first sorted position whose key >= c  (c = 0..ncells), plus sorted-order timestamps.
+// cell_start[c] = first sorted position whose key >= c  (c = 0..ncells), plus sorted-order (index, timestamp) records.
 __global__ void __launch_bounds__(256) g_cells_kernel(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ sidx,
                                                       const int32_t* __restrict__ pos, int64_t n, int64_t ncells,
                                                       int32_t* __restrict__ cell_start, int2* __restrict__ rec,
                                                       int32_t* __restrict__ cell_perm, int Q,
                                                       uint32_t* __restrict__ long_bucket, int W, int xs) {
     int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t <= ncells) {
-        int64_t lo = 0, hi = n;                               // lower_bound(skey, t)
-        while (lo < hi) {
-            int64_t mid = (lo + hi) >> 1;
-            if ((int64_t)skey[mid] < t) lo = mid + 1; else hi = mid;
+    {
+        // position t (0..n) is the start of every cell in (skey[t-1], skey[t]] (keys -1 before the first and ncells behind
+        // the last event): short runs are written by the thread, long ones (empty image regions) by its whole warp
+        const bool has = t <= n;
+        const int64_t prev = (has && t > 0) ? (int64_t)skey[t - 1] : -1;
+        const int64_t cur = !has ? prev : t < n ? (int64_t)skey[t] : ncells;
+        const int64_t first = prev + 1, cnt = cur - prev;
+        if (cnt <= 4)
+            for (int64_t k = 0; k < cnt; k++) cell_start[first + k] = (int32_t)t;
+        const int lane = threadIdx.x & 31;
+        for (uint32_t big = __ballot_sync(0xffffffffu, cnt > 4); big; big &= big - 1) {
+            const int l = __ffs((int)big) - 1;
+            const int64_t f = __shfl_sync(0xffffffffu, first, l), c = __shfl_sync(0xffffffffu, cnt, l);
+            const int32_t v = (int32_t)__shfl_sync(0xffffffffu, t, l);
+            for (int64_t k = lane; k < c; k += 32) cell_start[f + k] = v;
         }
-        cell_start[t] = (int32_t)lo;
     }
     if (t < n) {
         uint32_t i = sidx[t];
@@ -397,8 +406,7 @@ static int graph_rows(const int32_t* batch, const int32_t* pos, int64_t n, int B
     while ((1ll << key_bits) < ncells) key_bits++;
     uint32_t *skey, *sidx;
     EVAD_TRY(evad_sort_pairs_u32(w.k0, w.v0, w.k1, w.v1, 1, n, key_bits, w.sort_tmp, &skey, &sidx, st));
-    const int64_t m = (ncells + 1 > n) ? ncells + 1 : n;
-    g_cells_kernel<<<evad_cdiv(m, 256), 256, 0, st>>>(skey, sidx, pos, n, ncells, cell_start, w.rec, cell_perm, Q, long_bucket, W, xs);
+    g_cells_kernel<<<evad_cdiv(n + 1, 256), 256, 0, st>>>(skey, sidx, pos, n, ncells, cell_start, w.rec, cell_perm, Q, long_bucket, W, xs);
     EVAD_CHECK_LAUNCH();
     if (rowspan) {
         switch (radius) {

@@ -238,10 +238,12 @@ __global__ void __launch_bounds__(256) sample_concat_row_kernel(const float* __r
                                                                 const int32_t* __restrict__ batch, int64_t n_cap,
                                                                 const int32_t* __restrict__ n_dev, PoolSample S,
                                                                 int append_pos, float* __restrict__ out,
-                                                                uint32_t* __restrict__ status) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+                                                                uint32_t* __restrict__ status,
+                                                                const int32_t* __restrict__ visit) {
+    const int64_t tix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t n = n_dev ? min((int64_t)*n_dev, n_cap) : n_cap;
-    if (i >= n) return;
+    if (tix >= n) return;
+    const int64_t i = visit ? visit[tix] : tix;               // visiting order only: row i is written either way
     const float px = pos[i * ld_pos], py = pos[i * ld_pos + 1];
     int tap[8];
     float wgt[8];
@@ -293,7 +295,7 @@ extern "C" int evad_sample_concat(const float* x, int ldx, int cx, const float* 
     PoolSample S{feat, feat_b, feat_h, feat_w, feat_c, width, height};
     if (feat && cx == 1 && feat_c == 16 && ldo == 20 && (((uintptr_t)feat | (uintptr_t)out) & 15) == 0) {
         sample_concat_row_kernel<1, 16, 20, false><<<evad_cdiv(n_cap, 256), 256, 0, (cudaStream_t)stream>>>(
-            x, ldx, pos, ld_pos, batch, n_cap, n_dev, S, append_pos, out, nullptr);
+            x, ldx, pos, ld_pos, batch, n_cap, n_dev, S, append_pos, out, nullptr, nullptr);
         EVAD_CHECK_LAUNCH();
         return EVAD_OK;
     }
@@ -313,18 +315,19 @@ extern "C" int evad_sample_concat(const float* x, int ldx, int cx, const float* 
 
 // the layer-1 row shape of evad_sample_concat (one polarity channel + 16 sampled channels + position, rows of 20) with the
 // row written as h2 words for evad_spline_conv_l1_h16; EVAD_ERR_UNSUPPORTED for any other shape (caller: evad_sample_concat
-// + evad_split_h2)
+// + evad_split_h2).  visit (optional, a permutation of 0..n-1): the order in which threads take the nodes, e.g. the graph
+// build's cell_perm so that neighbouring threads sample neighbouring map cells; the output is the same either way
 extern "C" int evad_sample_concat_h2(const float* x, int ldx, int cx, const float* pos, int ld_pos, const int32_t* batch,
                                      int64_t n_cap, const int32_t* n_dev, const float* feat, int feat_b, int feat_h,
                                      int feat_w, int feat_c, float width, float height, int append_pos, uint32_t* out,
-                                     int ldo, uint32_t* status, void* stream) {
+                                     int ldo, const int32_t* visit, uint32_t* status, void* stream) {
     if (!pos || !out || n_cap < 0 || cx < 0 || (cx > 0 && !x) || (feat && !batch)) return EVAD_ERR_ARG;
     if (!(feat && cx == 1 && feat_c == 16 && ldo == 20 && (((uintptr_t)feat | (uintptr_t)out) & 15) == 0))
         return EVAD_ERR_UNSUPPORTED;
     if (n_cap == 0) return EVAD_OK;
     PoolSample S{feat, feat_b, feat_h, feat_w, feat_c, width, height};
     sample_concat_row_kernel<1, 16, 20, true><<<evad_cdiv(n_cap, 256), 256, 0, (cudaStream_t)stream>>>(
-        x, ldx, pos, ld_pos, batch, n_cap, n_dev, S, append_pos, reinterpret_cast<float*>(out), status);
+        x, ldx, pos, ld_pos, batch, n_cap, n_dev, S, append_pos, reinterpret_cast<float*>(out), status, visit);
     EVAD_CHECK_LAUNCH();
     return EVAD_OK;
 }

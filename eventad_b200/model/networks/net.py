@@ -8,6 +8,8 @@
     outputs are read: graph CSR -> x0 assembly -> layer 1 (2 launches) -> pool (sampling fused) -> layer ... ;
     it is CUDA-graph capturable.
 """
+import os
+
 import torch
 
 from ... import _lib, ops
@@ -18,6 +20,9 @@ from ..layers.ev_tgn import EV_TGN, denormalize_pos
 from ..layers.pooling import Pooling
 from ..utils import shallow_copy
 from .net_img import HookModule
+
+# EVAD_SAMPLE_VISIT=0: the layer-1 input rows are produced in event order instead of pixel order (same rows either way)
+SAMPLE_VISIT = os.environ.get("EVAD_SAMPLE_VISIT", "1") != "0"
 
 
 def sampling_skip(data, image_feat):
@@ -257,7 +262,9 @@ class Net(torch.nn.Module):
         x0 = None
         if cls1 is not None and cin1 == 19 and self.conv_block1.h16_chain_ok(src, cls1, ell):
             # fp16-pair layer-1 kernel: x0 is produced as h2 words (ops.split_h2) by the sampling kernel itself
-            x0 = ops.sample_concat_h2(x, pos, batch_i32, f[0], width, height, status)
+            # threads take the nodes in pixel order: neighbouring threads sample the same map cells
+            x0 = ops.sample_concat_h2(x, pos, batch_i32, f[0], width, height, status,
+                                      visit=graph["cell_perm"] if SAMPLE_VISIT else None)
         x0_h2 = x0 is not None
         if x0 is None:
             x0 = ops.sample_concat(x, pos, batch_i32, f[0], width, height, append_pos=True, ldo=(cin1 + 3) // 4 * 4)

@@ -167,7 +167,7 @@ def sample_concat(x, pos, batch_i32, feat_nhwc, width, height, append_pos=False,
     return out
 
 
-def sample_concat_h2(x, pos, batch_i32, feat_nhwc, width, height, status):
+def sample_concat_h2(x, pos, batch_i32, feat_nhwc, width, height, status, visit=None):
     """sample_concat for the layer-1 row shape ([polarity | 16 sampled channels | pos_xy | 0], rows of 20) written as h2
     words (split_h2 fused into the producer); None when the shape is another one."""
     if (x is None or feat_nhwc is None or x.shape[1] != 1 or feat_nhwc.shape[3] != 16 or pos.shape[0] == 0 or
@@ -180,7 +180,7 @@ def sample_concat_h2(x, pos, batch_i32, feat_nhwc, width, height, status):
     with _timed('sample_concat'):
         check(_lib.lib().evad_sample_concat_h2(ptr(x), x.stride(0), 1, ptr(pos), pos.stride(0), ptr(batch_i32), n, None,
                                                ptr(feat_nhwc), fb, fh, fw, fc, float(width), float(height), 1, ptr(out), 20,
-                                               ptr(status), stream()), "evad_sample_concat_h2")
+                                               ptr(visit), ptr(status), stream()), "evad_sample_concat_h2")
     return out
 
 

@@ -406,6 +406,7 @@ int evad_sample_concat(const float* x, int ldx, int cx, const float* pos, int ld
 int evad_sample_concat_h2(const float* x, int ldx, int cx, const float* pos, int ld_pos, const int32_t* batch,
                           int64_t n_cap, const int32_t* n_dev, const float* feat, int feat_b, int feat_h, int feat_w,
                           int feat_c, float width, float height, int append_pos, uint32_t* out, int ldo,
+                          const int32_t* visit /* optional permutation: thread order over the nodes, output unchanged */,
                           uint32_t* status, void* stream);
 
 /* ---- Event ingest on the device (csrc/ingest.cu) ----
