@@ -13,6 +13,7 @@
 // yields them de-duplicated and sorted with no global sort and no atomics on global memory.
 #include "common.cuh"
 #include "sample.cuh"
+#include <stdlib.h>
 
 #define PL_THREADS 128
 #define PL_BITS 4096                                        // bitmap chunk: one 32-bit word per thread
@@ -676,6 +677,122 @@ __global__ void __launch_bounds__(PL_THREADS) pool_edges_kernel(
     if (!FILL && threadIdx.x == 0) deg[c] = total;
 }
 
+// The counting launch (pool_edges_kernel<false>) with one WARP per destination cluster: a cluster has a few dozen members, so
+// a 128-thread CTA leaves most threads idle in the member loop and spends the rest of its time in block barriers; here
+// lanes take the members, the 4096-bit window is private to the warp (four words per lane, scanned with shuffles) and
+// nothing waits on another warp.  Writes deg / parked / tmp exactly like the CTA version.
+#define PEW_WARPS 4
+__global__ void __launch_bounds__(PEW_WARPS * 32) pool_edges_count_warp_kernel(
+    const uint32_t* __restrict__ sidx, const int32_t* __restrict__ seg_start, const int32_t* __restrict__ n_out,
+    const int32_t* __restrict__ rowptr_in, int in_stride, int keep_self, const int32_t* __restrict__ src_in,
+    const int32_t* __restrict__ cluster, uint32_t* __restrict__ deg, int32_t* __restrict__ tmp, uint8_t* __restrict__ parked) {
+    __shared__ uint32_t s_bits[PEW_WARPS][PL_BITS / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c = blockIdx.x * PEW_WARPS + warp;
+    const int nc = *n_out;
+    if (c > nc) return;
+    if (c == nc) {
+        if (lane == 0) deg[c] = 0;
+        return;
+    }
+    uint32_t* bits = s_bits[warp];
+    const int s0 = seg_start[c], s1 = seg_start[c + 1];
+#pragma unroll
+    for (int k = 0; k < PL_BITS / 1024; k++) bits[lane + 32 * k] = 0u;
+    __syncwarp();
+    const int w0 = max(0, c - PL_BITS / 2);
+    bool oow = false;
+    for (int p = s0 + lane; p < s1; p += 32) {
+        const int i = (int)sidx[p];
+        if (in_stride == 16) {
+            // fixed-stride rows of 16 slots: four source ids per 128-bit load, their four cluster gathers in flight
+            const int dg = rowptr_in[i];
+            const int4* row = reinterpret_cast<const int4*>(src_in) + (int64_t)i * 4;
+            for (int g = 0; 4 * g < dg; g++) {
+                const int4 s4 = __ldg(row + g);
+                const int sj[4] = {s4.x, s4.y, s4.z, s4.w};
+                int scs[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) scs[k] = 4 * g + k < dg ? cluster[sj[k]] : c;
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    if (4 * g + k >= dg) break;
+                    const int sc = scs[k], r = sc - w0;
+                    if (sc == c && !keep_self) continue;
+                    if (r >= 0 && r < PL_BITS) atomicOr(&bits[r >> 5], 1u << (r & 31));
+                    else oow = true;
+                }
+            }
+            continue;
+        }
+        for (int e = pl_row_begin(rowptr_in, in_stride, i), e1 = pl_row_end(rowptr_in, in_stride, i); e < e1; e++) {
+            const int sc = cluster[src_in[e]];
+            const int r = sc - w0;
+            if (sc == c && !keep_self) continue;             // Pooling(self_loop=False) drops them (pooling.py:60-63)
+            if (r >= 0 && r < PL_BITS) atomicOr(&bits[r >> 5], 1u << (r & 31));
+            else oow = true;
+        }
+    }
+    __syncwarp();
+    if (!__any_sync(0xffffffffu, oow)) {
+        constexpr int WPL = PL_BITS / 1024;                  // words per lane: lane l owns ids w0 + 32 WPL l ..
+        uint32_t word[WPL];
+        uint32_t pc = 0;
+#pragma unroll
+        for (int k = 0; k < WPL; k++) { word[k] = bits[lane * WPL + k]; pc += __popc(word[k]); }
+        uint32_t inc = pc;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += t;
+        }
+        const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+        const bool park = total <= PL_ROWCAP;
+        if (park) {
+            uint32_t off = inc - pc;
+#pragma unroll
+            for (int k = 0; k < WPL; k++)
+                for (uint32_t wd = word[k]; wd; wd &= wd - 1)
+                    tmp[(int64_t)c * PL_ROWCAP + off++] = w0 + (lane * WPL + k) * 32 + __ffs((int)wd) - 1;
+        }
+        if (lane == 0) { deg[c] = total; parked[c] = park ? 1 : 0; }
+        return;
+    }
+    if (lane == 0) parked[c] = 0;
+    // ---- general path: id range of the sources, then 4096-id chunks (count only; the FILL launch repeats the walk)
+    int lo = 0x7fffffff, hi = -1;
+    for (int p = s0 + lane; p < s1; p += 32) {
+        const int i = (int)sidx[p];
+        for (int e = pl_row_begin(rowptr_in, in_stride, i), e1 = pl_row_end(rowptr_in, in_stride, i); e < e1; e++) {
+            const int sc = cluster[src_in[e]];
+            if (sc != c || keep_self) { lo = min(lo, sc); hi = max(hi, sc); }
+        }
+    }
+    lo = __reduce_min_sync(0xffffffffu, lo);
+    hi = __reduce_max_sync(0xffffffffu, hi);
+    uint32_t total = 0;
+    for (int64_t wb = lo; wb <= hi; wb += PL_BITS) {
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < PL_BITS / 1024; k++) bits[lane + 32 * k] = 0u;
+        __syncwarp();
+        for (int p = s0 + lane; p < s1; p += 32) {
+            const int i = (int)sidx[p];
+            for (int e = pl_row_begin(rowptr_in, in_stride, i), e1 = pl_row_end(rowptr_in, in_stride, i); e < e1; e++) {
+                const int sc = cluster[src_in[e]];
+                const int64_t r = (int64_t)sc - wb;
+                if ((sc != c || keep_self) && r >= 0 && r < PL_BITS) atomicOr(&bits[r >> 5], 1u << (r & 31));
+            }
+        }
+        __syncwarp();
+        uint32_t pc = 0;
+#pragma unroll
+        for (int k = 0; k < PL_BITS / 1024; k++) pc += __popc(bits[lane + 32 * k]);
+        total += __reduce_add_sync(0xffffffffu, pc);
+    }
+    if (lane == 0) deg[c] = total;
+}
+
 // ------------------------------------------------------------------------------------------------ host side
 struct PoolWs {
     uint32_t *k0, *v0, *k1, *v1, *flag, *excl, *deg, *rowptr_u, *sort_tmp, *scan_tmp;
@@ -784,7 +901,12 @@ extern "C" int evad_voxel_pool(const evad_pool_params_t* p, int64_t n_cap, const
     }
     EVAD_CHECK_LAUNCH();
     if (want_edges) {
-        pool_edges_kernel<false><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, p->ell_stride, p->self_loop, src_in,
+        static const bool count_by_warp = [] { const char* e = getenv("EVAD_POOL_EDGES_WARP"); return !(e && e[0] == '0'); }();
+        if (count_by_warp)
+            pool_edges_count_warp_kernel<<<(unsigned)evad_cdiv(c_cap + 1, PEW_WARPS), PEW_WARPS * 32, 0, st>>>(
+                sidx, w.seg_start, n_out, rowptr_in, p->ell_stride, p->self_loop, src_in, cluster, w.deg, w.row_tmp, w.parked);
+        else
+            pool_edges_kernel<false><<<(unsigned)(c_cap + 1), PL_THREADS, 0, st>>>(sidx, w.seg_start, n_out, rowptr_in, p->ell_stride, p->self_loop, src_in,
                                                                              cluster, w.deg, nullptr, nullptr, e_cap,
                                                                              w.row_tmp, w.parked, status, nullptr, nullptr);
         EVAD_CHECK_LAUNCH();
