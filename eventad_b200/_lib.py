@@ -81,6 +81,7 @@ def _declare(L):
                                       c_p, c_p, c_p, c_p, c_i64, c_p, c_p, c_p, c_p, c_p, c_sz, c_p])
     _sig(L, "evad_graph_build_rows", c_i, [c_p, c_p, c_i64, c_i, c_i, c_i, c_i, c_i, c_i, c_i,
                                            c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_p])
+    _sig(L, "evad_graph_set_span_limit", c_i, [c_i])
     _sig(L, "evad_stream_state_bytes", c_sz, [c_i, c_i, c_i, c_i])
     _sig(L, "evad_stream_reset", c_i, [c_p, c_i, c_i, c_i, c_i, c_p])
     _sig(L, "evad_stream_ws_bytes", c_sz, [c_i64, c_i])

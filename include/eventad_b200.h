@@ -105,6 +105,12 @@ int evad_graph_build_rows(const int32_t* batch, const int32_t* pos, int64_t n_ev
                           int32_t* count, uint8_t* nbr_cls, int32_t* cell_perm, int32_t* cell_start, uint32_t* status,
                           void* ws, size_t ws_bytes, void* stream);
 
+/* Tuning knob of the graph build (no reference counterpart).  The spiral search of an event runs over the 2r+1 row spans
+ * of the pixel-sorted events when each of them holds at most min(limit, max_queue_size, 32) records, and as the per-cell
+ * walk (early exit at K neighbours, FIFO cap) otherwise -- decided per event on the device; both give the same edges.
+ * Default 32; 0 = always walk.  Returns the previous value; a negative argument only reads it. */
+int evad_graph_set_span_limit(int limit);
+
 /* ------------------------------------------------------------------------------------------------------------
  * Event-graph construction, streaming ("append") mode: EV_TGN.forward(reset=False)
  * (src/dagr/model/layers/ev_tgn.py:45-56), AsyncGraph.forward growth path (src/dagr/graph/ev_graph.py:75-103),

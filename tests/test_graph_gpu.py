@@ -113,14 +113,24 @@ def test_fixed_stride_rows_equal_the_compacted_graph(n, B, dist):
                                              (16, 16, 6000, 9, 48, 2, 1500), (30, 20, 5000, 16, 128, 7, 3000),
                                              (30, 20, 5000, 12, 128, 6, 3000), (9, 9, 700, 16, 200, 1, 10_000),
                                              (40, 30, 3000, 16, 128, 4, 0)])
-def test_row_span_search_saturated_lists(W, H, n, K, Q, r, dt):
-    """Tens of events per pixel but never more than Q (g_search_rows_kernel takes the call): the K-1 list overflows on most
-    events, so what is kept and in which order is the spiral-position / newest-first rule; offset classes are recomputed
-    from the coordinates of both ends."""
+@pytest.mark.parametrize("span_limit", [32, 8, 0])
+def test_row_span_search_saturated_lists(W, H, n, K, Q, r, dt, span_limit):
+    """Tens of events per pixel: the K-1 list overflows on most events, so what is kept and in which order is the
+    spiral-position / newest-first rule; offset classes are recomputed from the coordinates of both ends.  The search
+    kernel picks, per event, the row-span search (all spans <= min(span_limit, Q, 32) records) or the per-cell walk:
+    32 = default mix, 8 = more events walk, 0 = all walk."""
+    from eventad_b200 import _lib
+    old = _lib.lib().evad_graph_set_span_limit(span_limit)
+    try:
+        _row_span_case(W, H, n, K, Q, r, dt)
+    finally:
+        _lib.lib().evad_graph_set_span_limit(old)
+
+
+def _row_span_case(W, H, n, K, Q, r, dt):
     from eventad_b200.graph.ev_graph import SlidingWindowGraph
     rng = np.random.default_rng(W * H + K)
     x, y = rng.integers(0, W, n), rng.integers(0, H, n)
-    assert np.bincount(y * W + x).max() <= Q
     t = np.sort(rng.integers(0, 20_000, n)) // 3 * 3
     pos = np.stack([x, y, t], 1).astype(np.int32)
     batch = np.zeros(n, np.int32)
@@ -136,3 +146,20 @@ def test_row_span_search_saturated_lists(W, H, n, K, Q, r, dt):
     dst = np.repeat(np.arange(n), cnt)
     want = (x[eo[0]] - x[dst] + r) * (2 * r + 1) + (y[eo[0]] - y[dst] + r)
     assert np.array_equal(rows["nbr_cls"].cpu().numpy()[:n].reshape(n, K)[mask].astype(np.int64), want)
+
+
+@pytest.mark.parametrize("Q", [128, 16])
+def test_sparse_scene_with_hot_pixels(Q):
+    """A sparse scene (row-span search) with one pixel far beyond the FIFO capacity and one whose row span exceeds the
+    32-record masks: the events around them go through the walk list, everything else through the row spans."""
+    rng = np.random.default_rng(17)
+    W, H, n = 64, 48, 4000
+    x, y = rng.integers(0, W, n), rng.integers(0, H, n)
+    x[:300] = 20; y[:300] = 11                          # 300 events on one pixel
+    x[300:345] = 40; y[300:345] = 30                    # 45 on another
+    t = np.sort(rng.integers(0, 30_000, n)) // 5 * 5
+    perm = rng.permutation(n)
+    pos = np.stack([x[perm], y[perm], t], 1).astype(np.int32)
+    batch = np.zeros(n, np.int32)
+    e, eo, _ = _run_both(batch, pos, W, H, 1, K=16, Q=Q, r=4, dt=10_000)
+    assert np.array_equal(e.cpu().numpy(), eo)
