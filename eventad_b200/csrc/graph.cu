@@ -10,8 +10,12 @@
 //
 // B200 design: no [B,Q,H,W] FIFO tensor (39 MB per sample to clear and walk with stride H*W).  Events are bucketed
 // per pixel with a stable radix sort (primitives.cu); the bucket of a pixel, read from its tail, IS the FIFO.
-// The search runs one thread per event in pixel-sorted order, so the 81 cell lookups of neighbouring threads hit
-// the same L1 lines; candidate lists (index, timestamp) are contiguous per pixel row.
+// The search runs one thread per event in pixel-sorted order, so neighbouring threads read the same records; the
+// records (index, timestamp) of the 2r+1 pixels of an image row are one contiguous span, which is what the default search
+// (g_search_rows_kernel) reads instead of (2r+1)^2 buckets; the reference's per-cell walk (g_walk_event) remains for
+// crowded neighbourhoods, overflowed FIFOs and dense scenes.  Kernel order of one build:
+//   g_keys -> 3 x (rs_hist, scan, rs_scatter) -> g_cells (+ g_cells_big) -> g_search_rows -> g_search_list -> g_search
+// of which the last three each decide on the device whether they have work (flags[], g_dense_scene).
 #include "common.cuh"
 #include <stdlib.h>
 #include <string.h>
