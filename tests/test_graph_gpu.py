@@ -163,3 +163,31 @@ def test_sparse_scene_with_hot_pixels(Q):
     batch = np.zeros(n, np.int32)
     e, eo, _ = _run_both(batch, pos, W, H, 1, K=16, Q=Q, r=4, dt=10_000)
     assert np.array_equal(e.cpu().numpy(), eo)
+
+
+def test_graph_search_random_configs():
+    """40 seeded random configurations (sensor size, density, K, Q, radius, time gate, batch size, ties, unsorted time):
+    whatever mix of row-span search and per-cell walk the build picks, edge_index equals the C oracle's."""
+    rng = np.random.default_rng(2024)
+    for case in range(40):
+        W, H = int(rng.integers(3, 90)), int(rng.integers(3, 70))
+        B = int(rng.integers(1, 4))
+        dens = float(rng.choice([0.2, 0.8, 1.5, 3.0, 8.0]))
+        n = max(1, min(int(W * H * B * dens), 30_000))
+        K = int(rng.integers(2, 33))
+        Q = int(rng.choice([1, 3, 8, 31, 32, 33, 128, 300]))
+        r = int(rng.integers(1, 9))                       # 8: beyond the row-span kernel, walk only
+        dt = int(rng.choice([0, 50, 700, 5000, 10_000, 40_000]))
+        x, y = rng.integers(0, W, n), rng.integers(0, H, n)
+        if case % 3 == 0:                                 # a few hot pixels
+            hot = rng.integers(0, n, max(1, n // 10))
+            x[hot], y[hot] = x[hot[0]], y[hot[0]]
+        t = rng.integers(0, 30_000, n)
+        if case % 4:
+            t = np.sort(t)
+        if case % 5 == 0:
+            t = t // 16 * 16
+        batch = np.sort(rng.integers(0, B, n)).astype(np.int32)
+        pos = np.stack([x, y, t], 1).astype(np.int32)
+        e, eo, _ = _run_both(batch, pos, W, H, B, K=K, Q=Q, r=r, dt=dt)
+        assert np.array_equal(e.cpu().numpy(), eo), (case, W, H, B, n, K, Q, r, dt)
