@@ -160,6 +160,36 @@ def test_pooling(B, n, level, aggr):
     assert torch.equal(out.edge_attr.cpu(), ref.edge_attr)
 
 
+@pytest.mark.parametrize("B,n,deg", [(3, 16_000, 16), (1, 30_000, 3)])
+def test_pooling_long_range_edges(B, n, deg):
+    """Coarse edges from a fine graph whose edges are random node pairs: the sources of a cluster lie all over the id
+    range (outside the 4096-id window of the one-pass bitmap) and rows hold more than 64 distinct sources, i.e. the
+    general path of the edge kernels (counting by warp, filling by CTA) instead of the parked-row fast path."""
+    from eventad_b200.data import Batch
+    from oracle import dagr_layers
+    from oracle.dagr_net import compute_pooling_at_each_layer
+    model, args = make_backbone(use_image=False)
+    d = make_data(n, B, seed=9, dist="U")
+    N = d.pos.shape[0]
+    g = torch.Generator().manual_seed(4)
+    dst = torch.arange(N).repeat_interleave(deg)
+    src = torch.randint(0, N, (N * deg,), generator=g)
+    same = d.batch[src] == d.batch[dst]                  # edges stay inside a sample, like the reference's graph
+    ei = torch.stack([src[same], dst[same]]).long()
+    pool = model.backbone.pool1
+    x = torch.randn(N, 8, generator=g)
+    voxel3 = compute_pooling_at_each_layer(args.pooling_dim_at_output, 4)[0]
+    ref = dagr_layers.pooling(x, d.pos, d.batch, ei, voxel3, 320, 240, args.batch_size, pool.transform.max, "max")
+    data = Batch(x=x.cuda(), pos=d.pos.cuda(), batch=d.batch.cuda(), edge_index=ei.cuda())
+    data.width, data.height = d.width, d.height
+    out = pool.cuda()(data)
+    assert torch.equal(out.cluster.cpu(), ref.cluster)
+    assert torch.equal(out.edge_index.cpu(), ref.edge_index)
+    deg_c = torch.bincount(ref.edge_index[1])
+    assert int(deg_c.max()) > 64 or deg < 8              # rows beyond the parked-row capacity were exercised
+    assert torch.equal(out.x.cpu(), ref.x) and torch.equal(out.pos.cpu(), ref.pos)
+
+
 @pytest.mark.parametrize("level,self_loop,keep_t", [(0, True, False), (0, False, True), (1, True, True), (2, True, False)])
 def test_pooling_options(level, self_loop, keep_t):
     """Pooling(self_loop=..., keep_temporal_ordering=...) (pooling.py:59-63,69-72) vs the oracle, bit-exact edges.  The
