@@ -484,6 +484,31 @@ def leg_full_model(dev, world, rank, windows=100, B=6, events=100_000):
            "what": "EventADModel.forward(data, labels, testing=True): ResNet-50 (cuDNN, channels_last, random weights) + fused "
                    "event branch + evad_bbox_pool + batched GRU head; 'FPS' as utils/fps.py:58-59 counts it = boxes of frame t "
                    "and t-1 per second"}
+    # ---- the same clip through engine.GraphedEventAD: CNN branch, event branch and pooling + head as three graph replays
+    try:
+        from eventad_b200.engine import GraphedEventAD
+        runner = GraphedEventAD(ead, B, int(sets[0].pos.shape[0]), device=dev)
+
+        def run_g(n_batches):
+            for i in range(n_batches):
+                d = sets[i % 3]
+                runner(d, d.bbox[:, 4])
+        with torch.no_grad():
+            run_g(3)
+            torch.cuda.synchronize()
+            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            g0.record()
+            run_g(nb)
+            g1.record()
+            torch.cuda.synchronize()
+        gms = g0.elapsed_time(g1)
+        res["cuda_graphs"] = {"ms_per_batch": gms / nb, "windows_per_s": nb * B / (gms * 1e-3),
+                              "fps_reference_definition": boxes / (gms * 1e-3),
+                              "what": "engine.GraphedEventAD on the same clip: the CNN branch, the fused event branch (CNN maps "
+                                      "consumed in place) and box pooling + GRU head as three CUDA-graph replays per batch; "
+                                      "same kernels and results as the eager forward above (tests/test_eventad_gpu.py)"}
+    except Exception as ex:                                   # noqa: BLE001 - extra key only
+        res["cuda_graphs"] = {"error": repr(ex)[:200]}
     # ---- the CNN branch (HookModule.forward) eager vs captured in a CUDA graph (fp32 / bf16 autocast)
     try:
         from eventad_b200.engine import GraphedImageBranch

@@ -175,10 +175,11 @@ class EventADModel(nn.Module):
         ok = (tid_f == tid.to(tid_f.dtype)) & (tid >= 1)
         m = bb.shape[0]
         order = torch.arange(m, device=device)
-        key = bbb * (T + 1) + tid
-        first = torch.full((batch_size * (T + 1),), m, dtype=torch.long, device=device)
-        first.scatter_reduce_(0, key[ok], order[ok], reduce="amin", include_self=True)
-        first = first.view(batch_size, T + 1)
+        # rows that do not count go to a spare slot behind the table: fixed shapes, no host sync (CUDA-graph capturable)
+        key = torch.where(ok, bbb * (T + 1) + tid, torch.full_like(bbb, batch_size * (T + 1)))
+        first = torch.full((batch_size * (T + 1) + 1,), m, dtype=torch.long, device=device)
+        first.scatter_reduce_(0, key, order, reduce="amin", include_self=True)
+        first = first[:-1].view(batch_size, T + 1)
         has = first < m
         idx = first.clamp(max=m - 1)
         width = torch.as_tensor(data.width, device=device).double().view(-1, 1)
@@ -223,6 +224,11 @@ class EventADModel(nn.Module):
         over the samples that produced at least one prediction, each a list of [1, 2] logits in track-id order."""
         batch_features = self.extract_features(data)
         logits, valid, target, loss = self.head(batch_features, data, labels)
+        return self.collect(logits, valid, target, loss)
+
+    @staticmethod
+    def collect(logits, valid, target, loss):
+        """The reference's return structure from the batched head's tensors (one host read)."""
         losses = {"cross_entropy": loss}
         v = valid.cpu()                                                         # the one host read of the head
         all_outputs, all_labels = [], []

@@ -94,3 +94,39 @@ def test_bbox_pool_edge_cases():
     assert float(bf[:, :, 31:].abs().sum()) == 0 and float(bf[1].abs().sum()) == 0
     assert_close(bf[2, 1, 4], feat[6:9].mean(0), what="fewer than 5 nodes")
     assert float(bf[:, 0].abs().sum()) == 0                                  # no bbox0 given
+
+
+@pytest.mark.parametrize("B,events,drop", [(2, 20_000, 0.0), (3, 8_000, 0.4)])
+def test_graphed_full_model_equals_eager_forward(B, events, drop):
+    """engine.GraphedEventAD (CNN branch, event branch and box pooling + GRU head as three CUDA-graph replays) returns
+    what EventADModel.forward returns on the same batches -- same samples with predictions, same track order, logits
+    within the score tolerance (the CNN maps come from cuDNN twice: eager NCHW hooks vs captured channels-last) -- and
+    keeps doing so on the next batch of the same shape (static buffers re-loaded, padding rows re-zeroed)."""
+    from eventad_b200 import synthetic
+    from eventad_b200.engine import GraphedEventAD
+    from eventad_b200.models.EventAD import EventADModel
+    model, args = synthetic.make_backbone(seed=0, use_image=True)
+    model.cache_luts(320, 240, args.radius)
+    torch.manual_seed(1)
+    ead = EventADModel(model).cuda().eval()
+    ead.emulate_feature_cache = False
+    runner = None
+    for s in range(3):
+        d = synthetic.make_data(events, B, seed=40 + s, dist="U", device="cuda")
+        for k, v in synthetic.make_boxes(B, seed=60 + s, drop=drop if s else 0.0).items():
+            setattr(d, k, v.cuda())
+        d.image = torch.rand((B, 3, 240, 320), generator=torch.Generator().manual_seed(s)).cuda()
+        labels = d.bbox[:, 4]
+        # fp32 convolutions on both sides: with cuDNN's default TF32 the eager and the captured ResNet pick different
+        # algorithms and their maps differ by 1e-3 relative, which is the CNN's noise, not the runner's
+        with torch.no_grad(), torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+            l0, o0, t0 = ead(d, labels, testing=True)
+            if runner is None:
+                runner = GraphedEventAD(ead, B, d.pos.shape[0])
+            l1, o1, t1 = runner(d, labels)
+        assert [len(a) for a in o0] == [len(a) for a in o1] and len(o0) > 0
+        for a, b in zip(o0, o1):
+            for x, y in zip(a, b):
+                assert_close(y, x, what="graphed logits")
+        assert [[int(v) for v in a] for a in t0] == [[int(v) for v in a] for a in t1]
+        assert abs(float(l0["cross_entropy"]) - float(l1["cross_entropy"])) <= 1e-4 * abs(float(l0["cross_entropy"])) + 1e-4
