@@ -560,6 +560,21 @@ def leg_full_model(dev, world, rank, windows=100, B=6, events=100_000):
                          "trainable_params": n_par, "bucket_bytes": 4 * n_par, "batch": B,
                          "what": "forward (frozen DAGR under no_grad + head) + backward + one flat fp32 gradient all-reduce "
                                  "(NCCL when world > 1; a flatten / unflatten copy at world 1) + clip_grad_norm + AdamW"}
+    # the same step with the frozen part (CNN branch, event branch, box pooling) as CUDA-graph replays; single rank only:
+    # a rank whose capture failed would otherwise leave the others waiting in the all-reduce
+    if world == 1 and isinstance(res.get("cuda_graphs"), dict) and "error" not in res["cuda_graphs"]:
+        try:
+            for i in range(3):
+                train.train_step(ead, sets[i % 3], sets[i % 3].bbox[:, 4], opt, feature_fn=runner.features)
+            torch.cuda.synchronize()
+            e0.record()
+            for i in range(steps):
+                train.train_step(ead, sets[i % 3], sets[i % 3].bbox[:, 4], opt, feature_fn=runner.features)
+            e1.record()
+            torch.cuda.synchronize()
+            res["train_step"]["ms_per_step_graphed_features"] = e0.elapsed_time(e1) / steps
+        except Exception as ex:                                   # noqa: BLE001 - extra key only
+            res["train_step"]["graphed_features_error"] = repr(ex)[:200]
     return res
 
 # ------------------------------------------------------------------------------------------------ our arm

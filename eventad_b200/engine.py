@@ -242,7 +242,8 @@ class GraphedEventAD:
         if labels is not None and labels.shape[0]:
             self.box["labels"][:labels.shape[0]].copy_(labels.long(), non_blocking=True)
 
-    def _head(self):
+    def _pool(self):
+        """evad_bbox_pool of both frame lists on the out4 graph of the last event-branch replay -> [B, 2, T + 1, C]."""
         from . import _lib
         ead, box = self.ead, self.box
         o4 = self.ev.res["outs"][1]
@@ -258,30 +259,52 @@ class GraphedEventAD:
                                         feat.shape[0], _lib.ptr(n4), _lib.ptr(bb), bb.stride(0), _lib.ptr(bbb), bb.shape[0],
                                         frame, _lib.ptr(box["width"]), _lib.ptr(box["height"]), 2, ead.max_boxes,
                                         _lib.ptr(out), _lib.stream()), "evad_bbox_pool")
+        return out
+
+    def _head(self):
+        box = self.box
         view = Batch(bbox=box["bbox"], bbox_batch=box["bbox_batch"], width=box["width"], height=box["height"])
-        return ead.head(out, view, box["labels"])
+        return self.ead.head(self._pool(), view, box["labels"])
+
+    def _capture(self, fn, warm=3):
+        side = torch.cuda.Stream(device=self.dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warm):                        # cuDNN RNN plans, workspaces
+                fn()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            out = fn()
+        return g, out
+
+    def _branches(self, data, labels):
+        self.img(data.image)
+        self._load_boxes(data, labels)
+        if self.ev.graph is None:
+            self.ev.capture(data, None)
+        self.ev(data, None, finalize=False)
+
+    @torch.no_grad()
+    def features(self, data):
+        """`EventADModel.extract_features(data)` (EventAD.py:335-404) from three graph replays: [B, 2, max_boxes + 1, C],
+        a static buffer that the next call overwrites.  For the training step (DAGR frozen, :149-150): the head runs in
+        autograd on top of it (train.train_step(feature_fn=...))."""
+        self._branches(data, None)
+        if getattr(self, "pool_graph", None) is None:
+            self.pool_graph, self.pool_out = self._capture(self._pool, warm=1)
+        self.pool_graph.replay()
+        return self.pool_out
 
     @torch.no_grad()
     def __call__(self, data, labels=None):
         """data: Batch with image, x, pos, batch (already `format_data`-ed, on the device), bbox / bbox0 (+ _batch).
         Returns what EventADModel.forward(data, labels, testing=True) returns."""
         from . import _lib
-        self.img(data.image)
-        self._load_boxes(data, labels)
-        if self.ev.graph is None:
-            self.ev.capture(data, None)
-        self.ev(data, None, finalize=False)
+        self._branches(data, labels)
         if self.graph is None:
-            side = torch.cuda.Stream(device=self.dev)
-            side.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.stream(side):
-                for _ in range(3):                       # cuDNN RNN plans, workspaces
-                    self._head()
-            torch.cuda.current_stream().wait_stream(side)
-            torch.cuda.synchronize()
-            self.graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(self.graph):
-                self.out = self._head()
+            self.graph, self.out = self._capture(self._head)
         self.graph.replay()
         res = self.ead.collect(*self.out)
         if int(self.ev.res["readback"][12].item()):

@@ -18,11 +18,12 @@ def make_optimizer(model, lr=1e-3, weight_decay=1e-5):
     return torch.optim.AdamW(head_parameters(model), lr=lr, weight_decay=weight_decay)
 
 
-def train_step(model, data, labels, optimizer, grad_clip=1.0, timers=None):
+def train_step(model, data, labels, optimizer, grad_clip=1.0, timers=None, feature_fn=None):
     """zero_grad -> forward -> backward -> all-reduce of the flat head gradient -> clip -> step.  Returns the loss tensor
-    (no host sync).  timers: optional dict filled with CUDA events around the all-reduce."""
+    (no host sync).  timers: optional dict filled with CUDA events around the all-reduce.  feature_fn: replaces
+    model.extract_features (e.g. engine.GraphedEventAD(model, ...).features: the frozen part as CUDA-graph replays)."""
     optimizer.zero_grad(set_to_none=False)
-    feats = model.extract_features(data)                      # frozen DAGR + box pooling (no autograd graph)
+    feats = (feature_fn or model.extract_features)(data)      # frozen DAGR + box pooling (no autograd graph)
     with torch.enable_grad():
         logits, valid, target, loss = model.head(feats, data, labels)
         loss.backward()

@@ -130,3 +130,36 @@ def test_graphed_full_model_equals_eager_forward(B, events, drop):
                 assert_close(y, x, what="graphed logits")
         assert [[int(v) for v in a] for a in t0] == [[int(v) for v in a] for a in t1]
         assert abs(float(l0["cross_entropy"]) - float(l1["cross_entropy"])) <= 1e-4 * abs(float(l0["cross_entropy"])) + 1e-4
+
+
+def test_graphed_features_feed_the_training_step():
+    """GraphedEventAD.features == EventADModel.extract_features, and train_step(feature_fn=...) takes the same step as the
+    eager one: equal loss and equal head gradients from the same start."""
+    import copy
+    from eventad_b200 import synthetic, train
+    from eventad_b200.engine import GraphedEventAD
+    from eventad_b200.models.EventAD import EventADModel
+    B, events = 2, 10_000
+    model, args = synthetic.make_backbone(seed=0, use_image=True)
+    model.cache_luts(320, 240, args.radius)
+    torch.manual_seed(1)
+    ead = EventADModel(model).cuda()
+    ead.emulate_feature_cache = False
+    d = synthetic.make_data(events, B, seed=44, dist="U", device="cuda")
+    for k, v in synthetic.make_boxes(B, seed=66).items():
+        setattr(d, k, v.cuda())
+    d.image = torch.rand((B, 3, 240, 320), generator=torch.Generator().manual_seed(3)).cuda()
+    labels = d.bbox[:, 4]
+    with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+        runner = GraphedEventAD(ead, B, d.pos.shape[0])
+        assert_close(runner.features(d), ead.extract_features(d), what="graphed box features")
+        ead.train()                                      # cuDNN's RNN backward needs training mode ...
+        ead.gru_net_event.gru.dropout = 0.0              # ... without its dropouts (GRU layers, fusion MLP) the steps compare
+        ead.fusion_module.fusion[2].p = 0.0
+        ead2 = copy.deepcopy(ead)
+        o1, o2 = train.make_optimizer(ead), train.make_optimizer(ead2)
+        l1 = train.train_step(ead, d, labels, o1)
+        l2 = train.train_step(ead2, d, labels, o2, feature_fn=runner.features)
+        assert abs(float(l1) - float(l2)) <= 1e-4 * abs(float(l1)) + 1e-5
+        for p, q in zip(train.head_parameters(ead), train.head_parameters(ead2)):
+            assert_close(q, p, rtol=1e-3, atol=1e-5, what="head parameter after one step")
