@@ -507,8 +507,27 @@ def leg_full_model(dev, world, rank, windows=100, B=6, events=100_000):
                               "what": "engine.GraphedEventAD on the same clip: the CNN branch, the fused event branch (CNN maps "
                                       "consumed in place) and box pooling + GRU head as three CUDA-graph replays per batch; "
                                       "same kernels and results as the eager forward above (tests/test_eventad_gpu.py)"}
+        from eventad_b200.engine import PipelinedEventAD
+        pipe = PipelinedEventAD(ead, B, int(sets[0].pos.shape[0]), device=dev)
+
+        def run_p(n_batches):
+            for i in range(n_batches):
+                d = sets[i % 3]
+                pipe.submit(d, d.bbox[:, 4])
+            pipe.drain()
+        with torch.no_grad():
+            run_p(4)
+            torch.cuda.synchronize()
+            g0.record()
+            run_p(nb)
+            g1.record()
+            torch.cuda.synchronize()
+        pms = g0.elapsed_time(g1)
+        res["cuda_graphs"]["pipelined"] = {"ms_per_batch": pms / nb, "windows_per_s": nb * B / (pms * 1e-3),
+                                           "what": "engine.PipelinedEventAD: two such runners on two streams, batches "
+                                                   "alternating, the host read of a batch behind the launch of the next"}
     except Exception as ex:                                   # noqa: BLE001 - extra key only
-        res["cuda_graphs"] = {"error": repr(ex)[:200]}
+        res["cuda_graphs"] = dict(res.get("cuda_graphs") or {}, error=repr(ex)[:200])
     # ---- the CNN branch (HookModule.forward) eager vs captured in a CUDA graph (fp32 / bf16 autocast)
     try:
         from eventad_b200.engine import GraphedImageBranch

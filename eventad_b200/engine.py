@@ -301,15 +301,57 @@ class GraphedEventAD:
     def __call__(self, data, labels=None):
         """data: Batch with image, x, pos, batch (already `format_data`-ed, on the device), bbox / bbox0 (+ _batch).
         Returns what EventADModel.forward(data, labels, testing=True) returns."""
-        from . import _lib
+        self.launch(data, labels)
+        return self.finish()
+
+    @torch.no_grad()
+    def launch(self, data, labels=None):
+        """Everything of a call that is enqueued on the current stream (input copies, three replays); no host read."""
         self._branches(data, labels)
         if self.graph is None:
             self.graph, self.out = self._capture(self._head)
         self.graph.replay()
-        res = self.ead.collect(*self.out)
+
+    @torch.no_grad()
+    def finish(self):
+        """The host side of the call launched last: one read of the head's tensors, the reference's return structure."""
+        from . import _lib
+        logits, valid, target, loss = self.out           # static buffers of the head graph: hand out copies
+        res = self.ead.collect(logits.clone(), valid, target.clone(), loss.clone())
         if int(self.ev.res["readback"][12].item()):
             _lib.check_status(self.ev.res["status"], "fused DAGR forward")
         return res
+
+
+class PipelinedEventAD:
+    """Two GraphedEventAD runners on two streams, batches alternating between them: while the host reads batch k's
+    scores, and while batch k's event branch and head (small launch-bound kernels) run, the CNN branch of batch k + 1 is
+    already on the GPU.  `submit(data, labels)` launches a batch and returns the result of the batch submitted before it
+    (None for the first); `drain()` returns the last one.  Same graphs, same results as GraphedEventAD."""
+
+    def __init__(self, ead, batch, n_events_total, depth=2, **kw):
+        self.runners = [GraphedEventAD(ead, batch, n_events_total, **kw) for _ in range(int(depth))]
+        dev = self.runners[0].dev
+        self.streams = [torch.cuda.Stream(device=dev) for _ in self.runners]
+        self.k, self.pending = 0, None
+
+    def _finish(self, i):
+        with torch.cuda.stream(self.streams[i]):
+            return self.runners[i].finish()
+
+    def submit(self, data, labels=None):
+        i = self.k % len(self.runners)
+        self.k += 1
+        s = self.streams[i]
+        s.wait_stream(torch.cuda.current_stream())       # the caller's tensors are ready on its stream
+        with torch.cuda.stream(s):
+            self.runners[i].launch(data, labels)
+        prev, self.pending = self.pending, i
+        return self._finish(prev) if prev is not None else None
+
+    def drain(self):
+        prev, self.pending = self.pending, None
+        return self._finish(prev) if prev is not None else None
 
 
 class StreamedRunner:

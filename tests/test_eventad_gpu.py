@@ -163,3 +163,37 @@ def test_graphed_features_feed_the_training_step():
         assert abs(float(l1) - float(l2)) <= 1e-4 * abs(float(l1)) + 1e-5
         for p, q in zip(train.head_parameters(ead), train.head_parameters(ead2)):
             assert_close(q, p, rtol=1e-3, atol=1e-5, what="head parameter after one step")
+
+
+def test_pipelined_full_model_equals_eager_forward():
+    """engine.PipelinedEventAD (two graphed runners on two streams, results one batch behind): five batches, each equal to
+    the eager forward of that batch."""
+    from eventad_b200 import synthetic
+    from eventad_b200.engine import PipelinedEventAD
+    from eventad_b200.models.EventAD import EventADModel
+    B, events = 2, 12_000
+    model, args = synthetic.make_backbone(seed=0, use_image=True)
+    model.cache_luts(320, 240, args.radius)
+    torch.manual_seed(1)
+    ead = EventADModel(model).cuda().eval()
+    ead.emulate_feature_cache = False
+    batches = []
+    for s in range(5):
+        d = synthetic.make_data(events, B, seed=70 + s, dist="U", device="cuda")
+        for k, v in synthetic.make_boxes(B, seed=80 + s, drop=0.3 if s % 2 else 0.0).items():
+            setattr(d, k, v.cuda())
+        d.image = torch.rand((B, 3, 240, 320), generator=torch.Generator().manual_seed(10 + s)).cuda()
+        batches.append(d)
+    with torch.no_grad(), torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+        want = [ead(d, d.bbox[:, 4], testing=True) for d in batches]
+        pipe = PipelinedEventAD(ead, B, batches[0].pos.shape[0])
+        got = [pipe.submit(d, d.bbox[:, 4]) for d in batches]
+        assert got[0] is None
+        got = got[1:] + [pipe.drain()]
+    assert pipe.drain() is None
+    for (l0, o0, t0), (l1, o1, t1) in zip(want, got):
+        assert [len(a) for a in o0] == [len(a) for a in o1] and len(o0) > 0
+        for a, b in zip(o0, o1):
+            for x, y in zip(a, b):
+                assert_close(y, x, what="pipelined logits")
+        assert [[int(v) for v in a] for a in t0] == [[int(v) for v in a] for a in t1]
