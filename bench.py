@@ -508,7 +508,7 @@ def leg_full_model(dev, world, rank, windows=100, B=6, events=100_000):
                                       "consumed in place) and box pooling + GRU head as three CUDA-graph replays per batch; "
                                       "same kernels and results as the eager forward above (tests/test_eventad_gpu.py)"}
         from eventad_b200.engine import PipelinedEventAD
-        pipe = PipelinedEventAD(ead, B, int(sets[0].pos.shape[0]), device=dev)
+        pipe = PipelinedEventAD(ead, B, int(sets[0].pos.shape[0]), device=dev, overlap=True)
 
         def run_p(n_batches):
             for i in range(n_batches):
@@ -524,8 +524,10 @@ def leg_full_model(dev, world, rank, windows=100, B=6, events=100_000):
             torch.cuda.synchronize()
         pms = g0.elapsed_time(g1)
         res["cuda_graphs"]["pipelined"] = {"ms_per_batch": pms / nb, "windows_per_s": nb * B / (pms * 1e-3),
-                                           "what": "engine.PipelinedEventAD: two such runners on two streams, batches "
-                                                   "alternating, the host read of a batch behind the launch of the next"}
+                                           "what": "engine.PipelinedEventAD(overlap=True): two runners on two streams, "
+                                                   "batches alternating, the host read of a batch behind the launch of the next; "
+                                                   "inside a runner the CNN branch and the event branch are the two arms of one "
+                                                   "graph (engine.OverlappedBranches)"}
     except Exception as ex:                                   # noqa: BLE001 - extra key only
         res["cuda_graphs"] = dict(res.get("cuda_graphs") or {}, error=repr(ex)[:200])
     # ---- the CNN branch (HookModule.forward) eager vs captured in a CUDA graph (fp32 / bf16 autocast)

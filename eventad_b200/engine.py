@@ -194,6 +194,87 @@ class GraphedImageBranch:
         return self.features, self.outputs
 
 
+class OverlappedBranches:
+    """The CNN branch and the event branch of one batch as ONE CUDA graph with two parallel arms: the hooked ResNet runs
+    on a side stream and records an event as each of its five feature maps (1x1 `feature_dconv` applied in the hook) is
+    done; the event branch waits for map k only right before its first kernel that samples it (`Net.enqueue_fused(
+    maps_ready=...)`): the pixel sort and neighbour search need no map, layer 1 needs the stem's, pooling k the k-th
+    stage's.  At small batches both arms are chains of small kernels that leave most of the GPU idle, so the event branch
+    disappears behind the ResNet.  Same kernels as GraphedImageBranch + GraphedForward, same results."""
+
+    def __init__(self, net, batch, n_events_total, height, width, time_window, device):
+        from . import _lib, ops
+        self.net, self.hook, self.dev = net, net.net.to(device).eval().to(memory_format=torch.channels_last), torch.device(device)
+        self.meta = (int(width), int(height), int(time_window), int(batch))
+        n = int(n_events_total)
+        self.image = torch.zeros((int(batch), 3, int(height), int(width)), device=device).contiguous(
+            memory_format=torch.channels_last)
+        self.x = torch.zeros((n, 1), dtype=torch.float32, device=device)
+        self.pos = torch.zeros((n, 3), dtype=torch.float32, device=device)
+        self.batch = torch.zeros(n, dtype=torch.int32, device=device)
+        self.scratch, self._ops = _lib.Scratch(), ops
+        self.side = torch.cuda.Stream(device=self.dev)
+        self.graph, self.res, self.features = None, None, None
+
+    def _enqueue(self):
+        h, ops = self.hook, self._ops
+        main = torch.cuda.current_stream()
+        maps, ready = [], []
+
+        def on_feature(k):
+            def hook(_m, _i, o):
+                m = h.feature_dconv[k](o) if len(h.feature_dconv) > 0 else o
+                maps.append(m.float().contiguous(memory_format=torch.channels_last))
+                ev = torch.cuda.Event()
+                ev.record(torch.cuda.current_stream())
+                ready.append(ev)
+            return hook
+        extra = [h.extract_layer(h.module, name.split(".")).register_forward_hook(on_feature(k))
+                 for k, name in enumerate(h.feature_layers)]
+        try:
+            self.side.wait_stream(main)
+            with torch.cuda.stream(self.side):
+                h.features, h.outputs = [], []
+                h.module(self.image)
+        finally:
+            for e in extra:
+                e.remove()
+        w, hh, tw, b = self.meta
+        res = self.net.enqueue_fused(self.x, self.pos, self.batch, b, [ops.to_channel_last(m) for m in maps], w, hh, tw,
+                                     scratch=self.scratch, maps_ready=lambda k: main.wait_event(ready[k]))
+        main.wait_stream(self.side)
+        return res, maps
+
+    def load(self, data):
+        self.image.copy_(data.image, non_blocking=True)
+        self.x.copy_(data.x.view(-1, 1), non_blocking=True)
+        self.pos.copy_(data.pos, non_blocking=True)
+        self.batch.copy_(data.batch, non_blocking=True)
+
+    @torch.no_grad()
+    def capture(self, data):
+        self.load(data)
+        warm = torch.cuda.Stream(device=self.dev)
+        warm.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(warm):
+            for _ in range(3):                           # cuDNN algorithm selection, workspaces, cached LUTs
+                self._enqueue()
+        torch.cuda.current_stream().wait_stream(warm)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.res, self.features = self._enqueue()
+        return self
+
+    @torch.no_grad()
+    def __call__(self, data):
+        if self.graph is None:
+            self.capture(data)
+        self.load(data)
+        self.graph.replay()
+        return self.res
+
+
 class GraphedEventAD:
     """BASELINE configs[1] -- full EventAD inference of one batch of windows (models/EventAD.py:178-333 with
     `extract_features` :335-404) -- as three CUDA-graph replays: the CNN branch (GraphedImageBranch), the fused event
@@ -207,14 +288,22 @@ class GraphedEventAD:
     the head skip).  The reference's feature cache (`hash(str(x.sum()))`, :349-354) is not consulted: features are
     recomputed for every call, which is what the cache yields whenever the input changes."""
 
-    def __init__(self, ead, batch, n_events_total, height=240, width=320, time_window=1_000_000, device="cuda", max_rows=None):
+    def __init__(self, ead, batch, n_events_total, height=240, width=320, time_window=1_000_000, device="cuda", max_rows=None,
+                 overlap=False):
+        """overlap: the CNN branch and the event branch as the two arms of one graph (OverlappedBranches) instead of two
+        graphs one after the other -- the latency setting for small batches."""
         self.ead = ead.to(device).eval()
         self.net = ead.dagr_model.backbone
         self.B, self.dev = int(batch), torch.device(device)
         self.meta = (int(width), int(height), int(time_window))
-        self.img = GraphedImageBranch(self.net.net, batch, height, width, device=device).capture()
-        self.ev = GraphedForward(self.net, n_events_total, batch, self.img.features, width, height, time_window, device,
-                                 static_feats=True)
+        self.front = None
+        if overlap:
+            self.front = OverlappedBranches(self.net, batch, n_events_total, height, width, time_window, device)
+            self.img = self.ev = None
+        else:
+            self.img = GraphedImageBranch(self.net.net, batch, height, width, device=device).capture()
+            self.ev = GraphedForward(self.net, n_events_total, batch, self.img.features, width, height, time_window, device,
+                                     static_feats=True)
         self.rows = int(max_rows or batch * ead.max_boxes)
         self.box, self.graph, self.out = None, None, None
 
@@ -246,9 +335,10 @@ class GraphedEventAD:
         """evad_bbox_pool of both frame lists on the out4 graph of the last event-branch replay -> [B, 2, T + 1, C]."""
         from . import _lib
         ead, box = self.ead, self.box
-        o4 = self.ev.res["outs"][1]
+        res = self._res()
+        o4 = res["outs"][1]
         k = o4["k"]
-        n4 = self.ev.res["readback"][2 * k:2 * k + 1]    # device cell: nodes of the out4 graph
+        n4 = res["readback"][2 * k:2 * k + 1]            # device cell: nodes of the out4 graph
         feat, pos, nb = o4["x"], o4["pos"], o4["batch"]
         C = feat.shape[1]
         out = torch.zeros((self.B, 2, ead.max_boxes + 1, C), dtype=torch.float32, device=self.dev)
@@ -279,9 +369,15 @@ class GraphedEventAD:
             out = fn()
         return g, out
 
+    def _res(self):
+        return self.front.res if self.front is not None else self.ev.res
+
     def _branches(self, data, labels):
-        self.img(data.image)
         self._load_boxes(data, labels)
+        if self.front is not None:
+            self.front(data)
+            return
+        self.img(data.image)
         if self.ev.graph is None:
             self.ev.capture(data, None)
         self.ev(data, None, finalize=False)
@@ -318,8 +414,8 @@ class GraphedEventAD:
         from . import _lib
         logits, valid, target, loss = self.out           # static buffers of the head graph: hand out copies
         res = self.ead.collect(logits.clone(), valid, target.clone(), loss.clone())
-        if int(self.ev.res["readback"][12].item()):
-            _lib.check_status(self.ev.res["status"], "fused DAGR forward")
+        if int(self._res()["readback"][12].item()):
+            _lib.check_status(self._res()["status"], "fused DAGR forward")
         return res
 
 

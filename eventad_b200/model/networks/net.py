@@ -207,10 +207,20 @@ class Net(torch.nn.Module):
         return [out3, out4]
 
     # ------------------------------------------------------------------------------------------------ fused
-    def enqueue_fused(self, x, pos, batch_i32, num_graphs, feats_nhwc, width, height, time_window, scratch=None):
+    def enqueue_fused(self, x, pos, batch_i32, num_graphs, feats_nhwc, width, height, time_window, scratch=None,
+                      maps_ready=None):
         """Enqueues the whole event branch; returns device tensors sized by host-known upper bounds plus `counts`
         (int32[12]: n1,E1,n2,E2,n3,E3,n4,E4) and `status`.  No host synchronisation; capturable in a CUDA graph.
-        `scratch` (a _lib.Scratch): private workspaces and status word of the caller (one per captured graph)."""
+        `scratch` (a _lib.Scratch): private workspaces and status word of the caller (one per captured graph).
+        `maps_ready` (callable(level)): called right before the first kernel that reads CNN map `level` is enqueued, for a
+        caller that produces the maps on another stream (engine.GraphedEventAD(overlap=True) waits on an event there)."""
+        self._maps_ready = maps_ready
+        try:
+            return self._enqueue_fused_scratch(x, pos, batch_i32, num_graphs, feats_nhwc, width, height, time_window, scratch)
+        finally:
+            self._maps_ready = None
+
+    def _enqueue_fused_scratch(self, x, pos, batch_i32, num_graphs, feats_nhwc, width, height, time_window, scratch):
         g = self.events_to_graph
         if g.graph_creators is None:
             g.init_graph_creator(Data(pos=pos, width=[width], height=[height], time_window=[time_window],
@@ -260,6 +270,9 @@ class Net(torch.nn.Module):
         gc.max_index, gc.all_timestamps, gc._history = n, pos_int[:, 2], [(batch_i32, pos_int, 0)]   # AsyncGraph bookkeeping
         status = gc._status
         x0 = None
+        mr = getattr(self, "_maps_ready", None)
+        if mr is not None:
+            mr(0)                                            # the first CNN map is read from here on
         if cls1 is not None and cin1 == 19 and self.conv_block1.h16_chain_ok(src, cls1, ell):
             # fp16-pair layer-1 kernel: x0 is produced as h2 words (ops.split_h2) by the sampling kernel itself
             # threads take the nodes in pixel order: neighbouring threads sample the same map cells
@@ -291,6 +304,9 @@ class Net(torch.nn.Module):
             c_cap = max(1, min(cur["n_cap"], key_bound))
             e_cap = max(1, min(cur["e_cap"], c_cap * 64))
             cin_next = layers[k].in_channel
+            mr = getattr(self, "_maps_ready", None)
+            if mr is not None:
+                mr(k + 1)
             if k == 0 and pool1 is not None:
                 r = pool1(c_cap, e_cap, (cin_next + 3) // 4 * 4, counts[0:1], counts[1:2], status)
             else:

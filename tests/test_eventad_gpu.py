@@ -96,8 +96,9 @@ def test_bbox_pool_edge_cases():
     assert float(bf[:, 0].abs().sum()) == 0                                  # no bbox0 given
 
 
-@pytest.mark.parametrize("B,events,drop", [(2, 20_000, 0.0), (3, 8_000, 0.4)])
-def test_graphed_full_model_equals_eager_forward(B, events, drop):
+@pytest.mark.parametrize("B,events,drop,overlap", [(2, 20_000, 0.0, False), (3, 8_000, 0.4, False), (1, 30_000, 0.0, True),
+                                                   (3, 8_000, 0.4, True)])
+def test_graphed_full_model_equals_eager_forward(B, events, drop, overlap):
     """engine.GraphedEventAD (CNN branch, event branch and box pooling + GRU head as three CUDA-graph replays) returns
     what EventADModel.forward returns on the same batches -- same samples with predictions, same track order, logits
     within the score tolerance (the CNN maps come from cuDNN twice: eager NCHW hooks vs captured channels-last) -- and
@@ -122,7 +123,7 @@ def test_graphed_full_model_equals_eager_forward(B, events, drop):
         with torch.no_grad(), torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
             l0, o0, t0 = ead(d, labels, testing=True)
             if runner is None:
-                runner = GraphedEventAD(ead, B, d.pos.shape[0])
+                runner = GraphedEventAD(ead, B, d.pos.shape[0], overlap=overlap)   # overlap: both branches as one graph
             l1, o1, t1 = runner(d, labels)
         assert [len(a) for a in o0] == [len(a) for a in o1] and len(o0) > 0
         for a, b in zip(o0, o1):
